@@ -1,0 +1,89 @@
+"""The oracle against the golden vectors made from the real third-party code
+(tests/golden/make_golden.py): vLLM awq_pack, vLLM top-p, transformers Qwen2."""
+import os
+
+import numpy as np
+
+from oracle.awq import unpack_awq, pack_awq, dequantize_awq, AWQ_ORDER
+from oracle.qwen2 import OracleQwen2, Qwen2Dims
+from oracle.sampler import top_p_keep_mask, sample, hash_uniform
+from vgate_b200.weights import ModelDims, synthetic_checkpoint
+
+
+def test_awq_unpack_inverts_vllm_pack(golden_dir):
+    g = np.load(os.path.join(golden_dir, "awq_pack.npz"))
+    assert np.array_equal(unpack_awq(g["packed"]), g["q"])
+    assert np.array_equal(pack_awq(g["q"]), g["packed"])
+
+
+def test_awq_order_constant():
+    # awq_triton.py:53-57
+    assert AWQ_ORDER.tolist() == [0, 4, 1, 5, 2, 6, 3, 7]
+    w = np.array([[0x76543210]], dtype=np.uint32).view(np.int32)
+    assert unpack_awq(w).tolist() == [[0, 4, 1, 5, 2, 6, 3, 7]]
+
+
+def test_awq_dequant_formula():
+    rng = np.random.default_rng(0)
+    K, N, G = 256, 16, 128
+    q = rng.integers(0, 16, (K, N)).astype(np.uint8)
+    z = rng.integers(0, 16, (K // G, N)).astype(np.uint8)
+    s = (rng.random((K // G, N)) * 0.01).astype(np.float16)
+    w = dequantize_awq(pack_awq(q), pack_awq(z), s, G)
+    ref = ((q.astype(np.float32) - np.repeat(z, G, 0).astype(np.float32)).astype(np.float16)
+           * np.repeat(s, G, 0)).astype(np.float16)
+    assert w.dtype == np.float16 and np.array_equal(w, ref)
+
+
+def test_top_p_mask_matches_vllm(golden_dir):
+    g = np.load(os.path.join(golden_dir, "top_p.npz"))
+    for row in range(g["logits"].shape[0]):
+        keep = top_p_keep_mask(g["logits"][row], float(g["p"][row]))
+        assert np.array_equal(keep, g["keep"][row]), row
+
+
+def test_sampler_greedy_and_determinism():
+    rng = np.random.default_rng(1)
+    l = rng.standard_normal(5000).astype(np.float32)
+    assert sample(l, 0.0, 0.9, 1, 0) == int(np.argmax(l))
+    a = sample(l, 0.7, 0.9, 123, 4)
+    assert a == sample(l, 0.7, 0.9, 123, 4)
+    keep = top_p_keep_mask(l / np.float32(0.7), 0.9)
+    assert keep[a]
+    u = hash_uniform(5, 9, 1000)
+    assert u.dtype == np.float32 and (u > 0).all() and (u < 1).all()
+    assert abs(u.mean() - 0.5) < 0.05
+
+
+def _small():
+    d = ModelDims(hidden=128, intermediate=256, n_layers=2, n_heads=2, n_kv_heads=1, head_dim=64, vocab=256)
+    return d, synthetic_checkpoint(d, seed=3)
+
+
+def test_qwen2_logits_match_transformers(golden_dir):
+    g = np.load(os.path.join(golden_dir, "hf_qwen2.npz"))
+    d, ck = _small()
+    m = OracleQwen2(Qwen2Dims(**d.to_dict()), ck, mode="fp32")
+    logits = m.forward(g["ids"]).numpy()
+    assert np.abs(logits - g["logits"]).max() < 2e-4
+    # incremental decode through the KV cache equals the one-shot prefill
+    m.reset()
+    l0 = m.forward(g["ids"][:, :7]).numpy()
+    l1 = np.concatenate([m.forward(g["ids"][:, t:t + 1]).numpy() for t in range(7, 12)], axis=1)
+    assert np.abs(np.concatenate([l0, l1], 1) - g["logits"]).max() < 2e-4
+
+
+def test_qwen2_greedy_matches_transformers(golden_dir):
+    g = np.load(os.path.join(golden_dir, "hf_qwen2.npz"))
+    d, ck = _small()
+    m = OracleQwen2(Qwen2Dims(**d.to_dict()), ck, mode="fp32")
+    toks = m.generate_greedy(g["ids"], g["greedy"].shape[1])
+    assert np.array_equal(toks, g["greedy"])
+
+
+def test_fp16_mode_close_to_fp32():
+    d, ck = _small()
+    a = OracleQwen2(Qwen2Dims(**d.to_dict()), ck, mode="fp32")
+    b = OracleQwen2(Qwen2Dims(**d.to_dict()), ck, mode="fp16")
+    ids = np.random.default_rng(2).integers(0, d.vocab, (2, 9))
+    assert np.abs(a.forward(ids).numpy() - b.forward(ids).numpy()).max() < 2e-2

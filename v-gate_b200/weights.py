@@ -1,0 +1,111 @@
+"""Checkpoints for the b200 worker: model dimensions, a seeded synthetic
+AWQ-shaped checkpoint (there are no weights offline) and a safetensors loader
+for a mounted HF model directory.
+
+Tensor names and shapes are the HF / AutoAWQ ones that vLLM's loader consumes
+(vLLM ``model_executor/layers/quantization/awq.py:214-253``):
+``qweight int32 [K, N/8]``, ``qzeros int32 [K/G, N/8]``, ``scales fp16 [K/G, N]``.
+"""
+from dataclasses import dataclass, asdict
+import json
+import os
+import numpy as np
+
+
+@dataclass
+class ModelDims:
+    hidden: int = 1536
+    intermediate: int = 8960
+    n_layers: int = 28
+    n_heads: int = 12
+    n_kv_heads: int = 2
+    head_dim: int = 128
+    vocab: int = 151936
+    rms_eps: float = 1e-6
+    rope_theta: float = 1e6
+    group_size: int = 128
+    tie_embeddings: bool = True
+
+    def to_dict(self):
+        return asdict(self)
+
+
+# Public HF config.json values.
+QWEN25_1P5B = ModelDims()
+PRESETS = {
+    "qwen2.5-1.5b-awq": QWEN25_1P5B,
+    # reduced-depth / reduced-vocab shapes used by parity tests (same per-layer kernels)
+    "qwen2.5-1.5b-awq-l4": ModelDims(n_layers=4),
+    "qwen2.5-1.5b-awq-l2-v8k": ModelDims(n_layers=2, vocab=8192),
+    "tiny-awq": ModelDims(hidden=256, intermediate=512, n_layers=2, n_heads=2, n_kv_heads=1,
+                          head_dim=128, vocab=1024),
+}
+
+
+def linear_shapes(d: ModelDims):
+    """(name, K, N, has_bias) for the seven AWQ linears of one decoder layer."""
+    H, I, hd = d.hidden, d.intermediate, d.head_dim
+    return [
+        ("self_attn.q_proj", H, d.n_heads * hd, True),
+        ("self_attn.k_proj", H, d.n_kv_heads * hd, True),
+        ("self_attn.v_proj", H, d.n_kv_heads * hd, True),
+        ("self_attn.o_proj", d.n_heads * hd, H, False),
+        ("mlp.gate_proj", H, I, False),
+        ("mlp.up_proj", H, I, False),
+        ("mlp.down_proj", I, H, False),
+    ]
+
+
+def synthetic_checkpoint(d: ModelDims, seed: int = 0, w_std: float = 0.02) -> dict:
+    """Seeded random-init AWQ checkpoint (numpy arrays, HF tensor names).
+
+    int4 nibbles and zero points are uniform (a uniform random int32 word is
+    eight uniform nibbles in any packing order); scales are chosen so that the
+    dequantised weights have standard deviation ~``w_std``: (q - z) for uniform
+    q, z in [0, 15] has std sqrt(2 * 255 / 12) = 6.52.
+    """
+    rng = np.random.default_rng(seed)
+    G = d.group_size
+    ck = {}
+
+    def f16(a):
+        return np.asarray(a, dtype=np.float16)
+
+    ck["model.embed_tokens.weight"] = f16(rng.standard_normal((d.vocab, d.hidden), dtype=np.float32) * w_std)
+    if not d.tie_embeddings:
+        ck["lm_head.weight"] = f16(rng.standard_normal((d.vocab, d.hidden), dtype=np.float32) * w_std)
+    ck["model.norm.weight"] = f16(1.0 + 0.1 * rng.standard_normal(d.hidden, dtype=np.float32))
+    for i in range(d.n_layers):
+        p = f"model.layers.{i}."
+        ck[p + "input_layernorm.weight"] = f16(1.0 + 0.1 * rng.standard_normal(d.hidden, dtype=np.float32))
+        ck[p + "post_attention_layernorm.weight"] = f16(1.0 + 0.1 * rng.standard_normal(d.hidden, dtype=np.float32))
+        for name, K, N, has_bias in linear_shapes(d):
+            assert K % G == 0 and N % 8 == 0, (name, K, N)
+            ck[p + name + ".qweight"] = rng.integers(0, 2**32, size=(K, N // 8), dtype=np.uint32).view(np.int32)
+            ck[p + name + ".qzeros"] = rng.integers(0, 2**32, size=(K // G, N // 8), dtype=np.uint32).view(np.int32)
+            s = (w_std / 6.52) * (0.5 + rng.random((K // G, N), dtype=np.float32))
+            ck[p + name + ".scales"] = f16(s)
+            if has_bias:
+                ck[p + name + ".bias"] = f16(rng.standard_normal(N, dtype=np.float32) * w_std)
+    return ck
+
+
+def load_hf_checkpoint(model_dir: str):
+    """(dims, checkpoint dict) from a mounted HF AWQ model directory."""
+    from safetensors.numpy import load_file
+    with open(os.path.join(model_dir, "config.json")) as f:
+        c = json.load(f)
+    q = c.get("quantization_config", {})
+    if q.get("quant_method", "awq") != "awq" or q.get("bits", 4) != 4:
+        raise ValueError(f"unsupported quantization_config {q}")
+    d = ModelDims(
+        hidden=c["hidden_size"], intermediate=c["intermediate_size"], n_layers=c["num_hidden_layers"],
+        n_heads=c["num_attention_heads"], n_kv_heads=c["num_key_value_heads"],
+        head_dim=c.get("head_dim") or c["hidden_size"] // c["num_attention_heads"],
+        vocab=c["vocab_size"], rms_eps=c.get("rms_norm_eps", 1e-6), rope_theta=c.get("rope_theta", 1e6),
+        group_size=q.get("group_size", 128), tie_embeddings=c.get("tie_word_embeddings", False))
+    ck = {}
+    for fn in sorted(os.listdir(model_dir)):
+        if fn.endswith(".safetensors"):
+            ck.update(load_file(os.path.join(model_dir, fn)))
+    return d, ck
