@@ -1,0 +1,178 @@
+/* libb200gate -- C ABI of the B200-native worker engine behind V-Gate's
+ * `model.engine_type: b200` backend.
+ *
+ * This is the boundary a replacement engine must export.  It stands where the
+ * reference's vLLM adapter reaches into its engine:
+ *
+ *   b200_engine_create / _load_tensor / _finalize   <- VLLMBackend.load_model
+ *                                                      (vgate/backends/vllm_backend.py:61-86)
+ *   b200_submit + b200_wait                         <- VLLMBackend.generate / _agenerate_one
+ *                                                      (vllm_backend.py:97-132)
+ *   b200_submit + b200_poll (+ b200_abort)          <- VLLMBackend.stream_generate
+ *                                                      (vllm_backend.py:134-146; generator close main.py:372-376)
+ *   ttft_s / gen_time_s out-params                  <- _extract_metrics (vllm_backend.py:22-32)
+ *   b200_engine_destroy                             <- VLLMBackend.shutdown (vllm_backend.py:148-149)
+ *   temperature / top_p / max_tokens arguments      <- create_sampling_params (vllm_backend.py:88-95),
+ *                                                      wire form vgate/worker_api.py:70-73
+ *
+ * Conventions: every call returns 0 (B200_OK) or a negative B200_ERR_* code; no
+ * exception crosses the boundary; b200_last_error() gives the text of the last
+ * failure on the calling thread.  Plain pointers and sizes only.  The engine owns
+ * all of its device memory, one scheduler thread and its CUDA stream.  submit /
+ * wait / poll / abort / stats are thread-safe and may be called concurrently from
+ * any number of threads (V-Gate calls generate() from executor threads,
+ * vgate/worker_api.py:112, vgate/batcher.py:374).
+ *
+ * The b200_op_* entry points expose each kernel of the path on raw device
+ * pointers for parity tests and profilers; they launch on `stream` (a
+ * cudaStream_t passed as void*, NULL = legacy default stream) and do not
+ * synchronise.
+ */
+#ifndef B200GATE_H
+#define B200GATE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_ERR_INVALID (-1)   /* bad argument / unsupported shape */
+#define B200_ERR_CUDA (-2)      /* a CUDA call failed; engine is poisoned */
+#define B200_ERR_CAPACITY (-3)  /* request can never fit (prompt + max_tokens > max_model_len, KV pool) */
+#define B200_ERR_STATE (-4)     /* call made in the wrong engine state */
+#define B200_ERR_NOT_FOUND (-5) /* unknown request id */
+#define B200_ERR_ABORTED (-6)   /* request was aborted or engine shut down */
+
+#define B200_DTYPE_F16 0
+#define B200_DTYPE_I32 1
+#define B200_DTYPE_F32 2
+
+#define B200_ABI_VERSION 1
+
+typedef struct b200_engine b200_engine;
+
+/* Model + runtime shape.  Zero-initialise, set struct_size = sizeof(b200_config). */
+typedef struct b200_config {
+  int32_t struct_size;
+  int32_t device;          /* CUDA ordinal inside this process (CUDA_VISIBLE_DEVICES picks the GPU) */
+  int32_t hidden;          /* 1536 */
+  int32_t intermediate;    /* 8960 */
+  int32_t n_layers;        /* 28 */
+  int32_t n_heads;         /* 12 */
+  int32_t n_kv_heads;      /* 2 */
+  int32_t head_dim;        /* 128 (only value supported) */
+  int32_t vocab;           /* 151936 */
+  int32_t group_size;      /* AWQ group, 128 */
+  int32_t tie_embeddings;  /* 1: lm_head = embed_tokens */
+  float rms_eps;           /* 1e-6 */
+  float rope_theta;        /* 1e6 */
+  int32_t max_seqs;        /* concurrent sequences (decode batch ceiling), e.g. 256 */
+  int32_t max_model_len;   /* prompt + generated tokens per sequence, e.g. 2048 */
+  int32_t max_batch_tokens;/* prefill token budget per step, e.g. 8192 */
+  int64_t kv_bytes;        /* KV pool size; 0 = max_seqs * max_model_len tokens */
+  int32_t eos_token_id;    /* -1 disables EOS (synthetic checkpoints) */
+  int32_t use_cuda_graphs; /* 1: capture the decode step per batch bucket */
+  int32_t gemm_path;       /* 0 auto, 1 force CUDA-core GEMV, 2 force tcgen05 GEMM */
+  int32_t reserved[8];
+} b200_config;
+
+typedef struct b200_stats {
+  int64_t steps_prefill, steps_decode;
+  int64_t tokens_prefill, tokens_generated;
+  double gpu_seconds_prefill, gpu_seconds_decode; /* CUDA-event time of the forward passes */
+  int64_t decode_batch_sum;        /* sum over decode steps of the batch size */
+  double hbm_bytes_decode;         /* algorithmic bytes (weights + KV read + KV write) over decode steps */
+  int64_t kernel_launches;         /* kernels this library launched (graph nodes counted per replay) */
+  int64_t requests_finished, requests_aborted;
+  int32_t running, waiting;
+  int32_t kv_blocks_total, kv_blocks_free;
+} b200_stats;
+
+int32_t b200_abi_version(void);
+const char* b200_last_error(void);
+
+/* ---- engine lifecycle -------------------------------------------------------------- */
+int32_t b200_engine_create(const b200_config* cfg, b200_engine** out);
+/* HF tensor names ("model.layers.3.self_attn.q_proj.qweight", ...).  `data` is a host
+ * pointer; the engine copies and repacks, the caller keeps ownership. */
+int32_t b200_engine_load_tensor(b200_engine* e, const char* name, const void* data, int32_t dtype,
+                                int32_t ndim, const int64_t* shape);
+/* All tensors loaded: build kernel-side layouts, allocate KV pool, warm up, capture graphs,
+ * start the scheduler thread. */
+int32_t b200_engine_finalize(b200_engine* e);
+void b200_engine_destroy(b200_engine* e);
+
+/* ---- requests ---------------------------------------------------------------------- */
+/* Returns a request id >= 0, or a negative error code.  Greedy iff temperature < 1e-5. */
+int64_t b200_submit(b200_engine* e, const int32_t* prompt_ids, int32_t n_prompt, float temperature,
+                    float top_p, int32_t max_tokens, uint64_t seed);
+/* Blocks until the request finishes; copies up to `cap` generated ids; releases the request. */
+int32_t b200_wait(b200_engine* e, int64_t rid, int32_t* out_ids, int32_t cap, int32_t* n_out,
+                  double* ttft_s, double* gen_time_s);
+/* Non-blocking (timeout_ms = 0) or bounded wait for tokens not yet returned by poll.
+ * When *finished becomes 1 the request is released. */
+int32_t b200_poll(b200_engine* e, int64_t rid, int32_t* out_ids, int32_t cap, int32_t* n_new,
+                  int32_t* finished, int32_t timeout_ms);
+int32_t b200_abort(b200_engine* e, int64_t rid);
+int32_t b200_stats_get(b200_engine* e, b200_stats* out);
+
+/* Synchronous batch generate on the engine's stream for benchmarks and parity tests:
+ * all prompts have the same length, greedy, exactly max_tokens each, device-resident
+ * loop without per-request bookkeeping.  `prompt_ids` is a HOST pointer [n_seqs, n_prompt];
+ * `out_ids` a HOST pointer [n_seqs, max_tokens].  If `logits_out` (HOST, fp32
+ * [n_seqs, n_logit_steps, vocab]) is non-NULL the logits of the first n_logit_steps
+ * generated positions are returned as well.  gpu_seconds gets the CUDA-event time
+ * [0] prefill, [1] decode.  Must not overlap with submit()ed requests. */
+int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n_seqs, int32_t n_prompt,
+                            int32_t max_tokens, int32_t* out_ids, float* logits_out,
+                            int32_t n_logit_steps, double* gpu_seconds);
+
+/* ---- kernels on raw device pointers (tests, ncu) -------------------------------------- */
+/* AWQ checkpoint tensors -> kernel layout.  qweight int32 [K, N/8], qzeros int32 [K/G, N/8],
+ * scales fp16 [K/G, N]  ->  wq uint32 [N, K/8] (k-packed, AWQ nibble order along K),
+ * sc fp16 [N, K/G], zp fp16 [N, K/G] holding 1024 + zero. */
+int32_t b200_op_awq_repack(const int32_t* qweight, const int32_t* qzeros, const void* scales, int32_t K,
+                           int32_t N, int32_t G, uint32_t* wq, void* sc, void* zp, void* stream);
+/* kernel layout -> dense fp16 W[N, K] = fp16((q - z) * s): the bit-exact unpack check. */
+int32_t b200_op_awq_dequant(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N,
+                            int32_t G, void* w_out, void* stream);
+/* y[b, n] (fp32, row stride ldy) = (accumulate ? y : 0) + sum_k x[b, k] * W[n, k] + bias[n].
+ * x fp16 [B, K] row stride ldx.  CUDA-core W4A16 GEMV (128-bit loads, warp-shuffle reduce). */
+int32_t b200_op_w4_gemv(const uint32_t* wq, const void* sc, const void* zp, const void* x, int32_t ldx,
+                        float* y, int32_t ldy, const void* bias, int32_t B, int32_t K, int32_t N, int32_t G,
+                        int32_t accumulate, void* stream);
+/* Same contract with dense fp16 weights W[N, K] (lm_head). */
+int32_t b200_op_f16_gemv(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t B,
+                         int32_t K, int32_t N, int32_t accumulate, void* stream);
+/* h[t] (+= sum of n_parts partial tensors parts[p, t, :]) ; xn[r] = fp16(rmsnorm(h[rows ? rows[r] : r]) * g).
+ * h fp32 [T, H] is updated in place when n_parts > 0. */
+int32_t b200_op_rmsnorm(float* h, const float* parts, int32_t n_parts, int64_t part_stride,
+                        const void* gamma, float eps, const int32_t* rows, int32_t n_rows, int32_t H,
+                        void* xn, void* stream);
+/* qkv fp32 [T, (nh + 2 nkv) * 128] -> q fp16 [T, nh * 128] (rotated), K/V written (K rotated) into the
+ * paged cache at slot[t] (= block * 16 + offset, -1 = skip).  cos/sin fp32 [max_pos, 64]. */
+int32_t b200_op_rope_kv(const float* qkv, const int32_t* pos, const int32_t* slot, const float* cos_t,
+                        const float* sin_t, int32_t T, int32_t n_heads, int32_t n_kv, void* q_out,
+                        void* k_cache, void* v_cache, void* stream);
+/* Paged GQA attention, one query row per t: out fp16 [T, nh * 128].  Row t attends to the first
+ * ctx_len[t] tokens of block table row bt_row[t].  K/V cache fp16 [n_blocks, n_kv, 16, 128]. */
+int32_t b200_op_paged_attn(const void* q, const void* k_cache, const void* v_cache,
+                           const int32_t* block_tables, int32_t bt_stride, const int32_t* bt_row,
+                           const int32_t* ctx_len, int32_t T, int32_t n_heads, int32_t n_kv, void* out,
+                           void* stream);
+/* gu fp32 [T, 2 I] (gate | up) -> act fp16 [T, I] = silu(gate) * up. */
+int32_t b200_op_swiglu(const float* gu, int32_t T, int32_t I, void* act, void* stream);
+/* h fp32 [T, H] = embed fp16 [V, H] rows ids[t]. */
+int32_t b200_op_embed(const void* table, const int32_t* ids, int32_t T, int32_t H, float* h, void* stream);
+/* Per row: greedy argmax when temperature[r] < 1e-5, else temperature + top-p + exponential-race
+ * draw with the counter hash (seed[r], step[r]).  logits fp32 [B, V] -> out int32 [B]. */
+int32_t b200_op_sample(const float* logits, int32_t B, int32_t V, const float* temperature,
+                       const float* top_p, const uint32_t* seed, const int32_t* step, int32_t* out,
+                       void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GATE_H */

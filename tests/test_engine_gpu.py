@@ -1,0 +1,170 @@
+"""End-to-end parity of the engine (C ABI) against the CPU oracle on seeded random-init
+checkpoints: logits within 2e-2 max-abs of the fp32 oracle, greedy tokens identical to the oracle
+in the reference's arithmetic class (fp16 activations, fp32 accumulation)."""
+import threading
+
+import numpy as np
+import pytest
+
+from oracle.qwen2 import OracleQwen2, Qwen2Dims
+from vgate_b200.weights import PRESETS, synthetic_checkpoint
+
+pytestmark = pytest.mark.gpu
+
+LOGIT_TOL = 2e-2          # north_star: logits within 2e-2 max-abs of the reference
+
+
+@pytest.fixture(scope="module")
+def small():
+    from vgate_b200.engine import Engine
+    dims = PRESETS["qwen2.5-1.5b-awq-l2-v8k"]
+    ckpt = synthetic_checkpoint(dims, seed=0)
+    eng = Engine(dims, max_seqs=16, max_model_len=512, max_batch_tokens=256).load_checkpoint(ckpt)
+    yield dims, ckpt, eng
+    eng.close()
+
+
+def _oracle(dims, ckpt, mode):
+    return OracleQwen2(Qwen2Dims(**dims.to_dict()), ckpt, mode=mode)
+
+
+def test_logits_and_greedy_tokens_match_oracle(small):
+    dims, ckpt, eng = small
+    rng = np.random.default_rng(1)
+    prompts = rng.integers(0, dims.vocab, size=(6, 40), dtype=np.int32)
+    n_new = 12
+    toks, logits, _ = eng.generate_batch(prompts, n_new, n_logit_steps=n_new)
+    ref32_toks, ref32_logits = _oracle(dims, ckpt, "fp32").generate_greedy(prompts, n_new, return_logits=True)
+    ref16_toks = _oracle(dims, ckpt, "fp16").generate_greedy(prompts, n_new)
+    # logits: compare while the prefixes agree (after a divergence the inputs differ)
+    for b in range(prompts.shape[0]):
+        n_same = 0
+        while n_same < n_new and toks[b, n_same] == ref32_toks[b, n_same]:
+            n_same += 1
+        upto = min(n_new, n_same + 1)
+        assert np.abs(logits[b, :upto] - ref32_logits[b, :upto]).max() < LOGIT_TOL, b
+    assert np.array_equal(toks, ref16_toks)
+
+
+def test_submit_wait_equals_generate_batch(small):
+    dims, ckpt, eng = small
+    rng = np.random.default_rng(2)
+    prompts = rng.integers(0, dims.vocab, size=(5, 33), dtype=np.int32)
+    toks, _, _ = eng.generate_batch(prompts, 10)
+    rids = [eng.submit(p, temperature=0.0, top_p=1.0, max_tokens=10) for p in prompts]
+    for b, rid in enumerate(rids):
+        out, ttft, gen = eng.wait(rid, 10)
+        assert np.array_equal(out, toks[b])
+        assert ttft > 0 and gen >= 0
+
+
+def test_continuous_batching_ragged_and_staggered(small):
+    """Requests of different lengths, submitted from several threads while others decode, produce
+    exactly what each produces alone (batch composition never changes a sequence's tokens)."""
+    dims, ckpt, eng = small
+    rng = np.random.default_rng(3)
+    lens = [1, 5, 16, 17, 31, 64, 100, 7, 48, 3, 90, 22]
+    news = [9, 3, 12, 1, 7, 16, 5, 11, 2, 14, 6, 8]
+    prompts = [rng.integers(0, dims.vocab, size=n, dtype=np.int32) for n in lens]
+    solo = []
+    for p, n in zip(prompts, news):
+        solo.append(eng.wait(eng.submit(p, 0.0, 1.0, n), n)[0])
+    results = [None] * len(prompts)
+
+    def worker(i):
+        results[i] = eng.wait(eng.submit(prompts[i], 0.0, 1.0, news[i]), news[i])[0]
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(len(prompts))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for i in range(len(prompts)):
+        assert len(results[i]) == news[i]
+        assert np.array_equal(results[i], solo[i]), i
+    st = eng.stats()
+    assert st["running"] == 0 and st["waiting"] == 0
+    assert st["kv_blocks_free"] == st["kv_blocks_total"]      # every block returned to the allocator
+
+
+def test_poll_streams_tokens_and_abort(small):
+    dims, ckpt, eng = small
+    rng = np.random.default_rng(4)
+    p = rng.integers(0, dims.vocab, size=20, dtype=np.int32)
+    full = eng.wait(eng.submit(p, 0.0, 1.0, 15), 15)[0]
+    rid = eng.submit(p, 0.0, 1.0, 15)
+    got, finished = [], False
+    while not finished:
+        ids, finished = eng.poll(rid, cap=4, timeout_ms=200)
+        assert len(ids) <= 4
+        got.extend(ids.tolist())
+    assert got == full.tolist()
+    # abort: the request ends early and its blocks are returned
+    rid = eng.submit(p, 0.0, 1.0, 400)
+    ids, _ = eng.poll(rid, cap=8, timeout_ms=2000)
+    eng.abort(rid)
+    from vgate_b200.engine import B200Error
+    with pytest.raises(B200Error):
+        while True:
+            _, fin = eng.poll(rid, cap=64, timeout_ms=200)
+            if fin:
+                break
+    st = eng.stats()
+    assert st["kv_blocks_free"] == st["kv_blocks_total"]
+
+
+def test_sampling_requests_are_seeded(small):
+    dims, ckpt, eng = small
+    rng = np.random.default_rng(5)
+    p = rng.integers(0, dims.vocab, size=12, dtype=np.int32)
+    a = eng.wait(eng.submit(p, 0.8, 0.9, 12, seed=7), 12)[0]
+    b = eng.wait(eng.submit(p, 0.8, 0.9, 12, seed=7), 12)[0]
+    c = eng.wait(eng.submit(p, 0.8, 0.9, 12, seed=8), 12)[0]
+    assert np.array_equal(a, b)
+    assert not np.array_equal(a, c)
+
+
+def test_capacity_and_argument_errors(small):
+    dims, ckpt, eng = small
+    from vgate_b200.engine import B200Error
+    with pytest.raises(B200Error):
+        eng.submit(np.zeros(500, np.int32), 0.0, 1.0, 100)          # prompt + max_tokens > max_model_len
+    with pytest.raises(B200Error):
+        eng.submit(np.array([dims.vocab], np.int32), 0.0, 1.0, 4)   # token id out of range
+    with pytest.raises(B200Error):
+        eng.submit(np.array([1], np.int32), 0.0, 0.0, 4)            # top_p == 0
+    with pytest.raises(B200Error):
+        eng.wait(123456, 4)
+
+
+def test_backend_contract_on_gpu(monkeypatch):
+    """B200Backend end to end with the reference's contract assertions (tests/test_backends.py:45-94)."""
+    import asyncio
+    from types import SimpleNamespace
+    from vgate_b200 import B200Backend
+    from vgate_b200.tokenizer import ByteTokenizer
+
+    monkeypatch.setenv("VGATE_B200_SYNTHETIC", "qwen2.5-1.5b-awq-l2-v8k")
+    monkeypatch.setenv("VGATE_B200_MAX_SEQS", "8")
+    monkeypatch.setenv("VGATE_B200_MAX_BATCH_TOKENS", "256")
+    be = B200Backend()
+    be.load_model(SimpleNamespace(model_id="Qwen/Qwen2.5-1.5B-Instruct-AWQ", max_model_len=256))
+    try:
+        sp = be.create_sampling_params(0.0, 1.0, 6)
+        res = be.generate(["User: hello\nAssistant:", "User: bye\nAssistant:"], sp)
+        assert len(res) == 2
+        for r in res:
+            assert set(r) >= {"text", "token_ids", "num_tokens", "metrics"}
+            assert r["num_tokens"] == len(r["token_ids"]) == 6
+            assert ByteTokenizer.parse(r["text"]) == r["token_ids"]
+            assert r["metrics"]["ttft"] > 0 and r["metrics"]["gen_time"] >= 0
+
+        async def collect():
+            return [c async for c in be.stream_generate("User: hello\nAssistant:", sp)]
+
+        chunks = asyncio.run(collect())
+        assert "".join(c["delta"] for c in chunks) == res[0]["text"]
+        counts = [c["num_tokens"] for c in chunks]
+        assert counts == sorted(counts) and counts[-1] == 6
+    finally:
+        be.shutdown()

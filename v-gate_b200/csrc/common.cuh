@@ -1,0 +1,123 @@
+// Shared device helpers for libb200gate (sm_100a only).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#if defined(__CUDA_ARCH__) && !defined(__CUDA_ARCH_FEAT_SM100_ALL) && !defined(__CUDA_ARCH_FEAT_SM103_ALL)
+#error "libb200gate kernels are written for sm_100a (compile with -gencode arch=compute_100a,code=sm_100a)"
+#endif
+
+namespace b200 {
+
+constexpr int kWarp = 32;
+
+// ---- warp / block reductions -------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---- 128-bit streaming loads -------------------------------------------------
+// Weights are read exactly once per step: keep them out of L1.
+__device__ __forceinline__ uint4 ldg_stream(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+// Activations are re-read by every warp of the CTA: let L1 keep them.
+__device__ __forceinline__ uint4 ldg_cached(const void* p) {
+  return __ldg(reinterpret_cast<const uint4*>(p));
+}
+
+// ---- Blackwell mixed-precision FMA: d = fp32(a) * fp32(b) + c, one rounding (SASS FHFMA) ----
+__device__ __forceinline__ float fhfma_lo(uint32_t a2, uint32_t b2, float c) {
+  asm("{.reg .b16 al, ah, bl, bh;\n\t"
+      "mov.b32 {al, ah}, %1;\n\t"
+      "mov.b32 {bl, bh}, %2;\n\t"
+      "fma.rn.f32.f16 %0, al, bl, %0;}" : "+f"(c) : "r"(a2), "r"(b2));
+  return c;
+}
+__device__ __forceinline__ float fhfma_hi(uint32_t a2, uint32_t b2, float c) {
+  asm("{.reg .b16 al, ah, bl, bh;\n\t"
+      "mov.b32 {al, ah}, %1;\n\t"
+      "mov.b32 {bl, bh}, %2;\n\t"
+      "fma.rn.f32.f16 %0, ah, bh, %0;}" : "+f"(c) : "r"(a2), "r"(b2));
+  return c;
+}
+// acc += a2.lo*b2.lo + a2.hi*b2.hi   (two exact-product FMAs in k order)
+__device__ __forceinline__ float fhfma2(uint32_t a2, uint32_t b2, float c) {
+  return fhfma_hi(a2, b2, fhfma_lo(a2, b2, c));
+}
+
+// ---- AWQ int4 -> fp16 dequant --------------------------------------------------
+// A packed word holds eight 4-bit weights of one output row for eight consecutive k;
+// logical k_i sits in nibble kAwqOrder[i] = {0,4,1,5,2,6,3,7} (the AWQ interleave, applied
+// along K at load time).  `(w >> 4j) & 0x000f000f | 0x64006400` is then the fp16 pair
+// (1024 + q[2j], 1024 + q[2j+1]).  Subtracting (1024 + z) is exact in fp16 and the one
+// multiply by the scale rounds exactly like the reference's fp16 `(q - z) * s`.
+__device__ __forceinline__ void dequant8(uint32_t w, uint32_t z1024_2, uint32_t s2, uint32_t out[4]) {
+  const __half2 z = *reinterpret_cast<const __half2*>(&z1024_2);
+  const __half2 s = *reinterpret_cast<const __half2*>(&s2);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t v = ((w >> (4 * j)) & 0x000f000fu) | 0x64006400u;
+    __half2 h = __hmul2(__hsub2(*reinterpret_cast<__half2*>(&v), z), s);
+    out[j] = *reinterpret_cast<uint32_t*>(&h);
+  }
+}
+
+__device__ __forceinline__ uint32_t pack_half2(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+
+// ---- shared-memory addresses, mbarrier, bulk async copies (TMA 1-D) ---------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
+// Bounded wait: a pipeline bug must fail loudly (trap -> sticky CUDA error), never hang the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  for (uint32_t spin = 0; spin < (1u << 24); ++spin)
+    if (mbar_try_wait(bar, parity)) return;
+  __trap();
+}
+// global -> shared bulk copy (SASS UBLKCP); bytes % 16 == 0, both addresses 16-byte aligned.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+}  // namespace b200

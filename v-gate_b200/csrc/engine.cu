@@ -1,0 +1,935 @@
+// The worker engine behind the C ABI: weight store, block-table KV allocator, continuous-batching
+// scheduler thread, forward pass.  Stands where the reference's vLLM AsyncLLMEngine stands
+// (vgate/backends/vllm_backend.py:61-132): independent requests are submitted from any thread,
+// batched per step by the scheduler, and each caller blocks until its own request is finished.
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------
+thread_local std::string g_last_error;
+thread_local int64_t g_launch_count = 0;
+
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+int cuda_fail(cudaError_t err, const char* what, const char* file, int line) {
+  g_last_error = std::string("CUDA error ") + cudaGetErrorName(err) + " (" + cudaGetErrorString(err) + ") at " +
+                 file + ":" + std::to_string(line) + " in " + what;
+  return B200_ERR_CUDA;
+}
+
+static double now_s() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Decode-step bookkeeping on the device: consume the token sampled by the previous forward pass.
+//   out_tokens[i, n_gen[i]] = next_ids[i]; ids[i] = next_ids[i]; pos[i] += 1; slot/ctx follow.
+__global__ void advance_decode_kernel(int B, const int32_t* __restrict__ next_ids, int32_t* __restrict__ ids,
+                                      int32_t* __restrict__ pos, int32_t* __restrict__ slot,
+                                      int32_t* __restrict__ ctx, int32_t* __restrict__ n_gen,
+                                      const int32_t* __restrict__ bt_row, const int32_t* __restrict__ block_tables,
+                                      int bt_stride, int32_t* __restrict__ out_tokens, int out_stride) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  const int tok = next_ids[i];
+  const int g = n_gen[i];
+  if (out_tokens && g < out_stride) out_tokens[(size_t)i * out_stride + g] = tok;
+  n_gen[i] = g + 1;
+  ids[i] = tok;
+  const int p = pos[i] + 1;
+  pos[i] = p;
+  const int blk = p / kBlockTokens;
+  slot[i] = blk < bt_stride ? block_tables[(size_t)bt_row[i] * bt_stride + blk] * kBlockTokens + p % kBlockTokens : -1;
+  ctx[i] = p + 1;
+}
+
+// ---------------------------------------------------------------------------------------------
+struct DevMem {
+  void* p = nullptr;
+  size_t bytes = 0;
+  int alloc(size_t n) {
+    bytes = n;
+    B200_CUDA(cudaMalloc(&p, n ? n : 16));
+    return B200_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; }
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct LayerWeights {
+  DevMem wq[4], sc[4], zp[4];      // 0 qkv, 1 o, 2 gate_up, 3 down
+  DevMem bias_qkv, ln1, ln2;
+  W4Linear lin[4];
+};
+
+struct PendingLinear {             // raw checkpoint tensors waiting for their siblings
+  DevMem qweight, qzeros, scales;
+  bool have_w = false, have_z = false, have_s = false;
+};
+
+enum class ReqState { WAITING, RUNNING, FINISHED, ABORTED, FAILED };
+
+struct Request {
+  int64_t id = 0;
+  std::vector<int32_t> prompt;
+  float temperature = 0.f, top_p = 1.f;
+  int max_tokens = 0;
+  uint32_t seed = 0;
+  ReqState state = ReqState::WAITING;
+  bool abort_requested = false;
+  int seq_slot = -1;
+  std::vector<int32_t> blocks;
+  std::vector<int32_t> out;
+  size_t n_polled = 0;
+  double t_submit = 0, t_first = 0, t_last = 0;
+};
+
+}  // namespace b200
+
+using namespace b200;
+
+struct b200_engine {
+  b200_config cfg{};
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool finalized = false;
+  std::string fatal;                           // non-empty: engine poisoned
+
+  // ---- model ----
+  int H = 0, I = 0, L = 0, NH = 0, NKV = 0, V = 0, G = 0, QKV = 0;
+  std::vector<LayerWeights> layers;
+  DevMem embed, lm_head_w, final_norm;
+  std::map<std::string, PendingLinear> pending;
+  int tensors_loaded = 0, tensors_expected = 0;
+  DevMem cos_t, sin_t;
+
+  // ---- KV pool + block-table allocator ----
+  DevMem k_cache, v_cache;                     // [L][n_blocks][NKV][16][128] fp16
+  size_t kv_layer_elems = 0;
+  int n_blocks = 0, max_blocks_per_seq = 0;
+  std::vector<int32_t> free_blocks;            // LIFO free list
+  std::vector<int32_t> free_slots;
+
+  // ---- activations / metadata ----
+  int Tmax = 0;
+  DevMem h, xn, qkv, qh, attn, gu, act, xn_last, logits;
+  DevMem d_ids, d_pos, d_slot, d_btrow, d_ctx, d_lastrows, d_bt, d_temp, d_topp, d_seed, d_step, d_next, d_ngen;
+  DevMem d_out_tokens;
+  int32_t* hp_i32 = nullptr;                   // pinned staging
+  float* hp_f32 = nullptr;
+  size_t hp_cap = 0;
+
+  // ---- decode CUDA graphs (generate_batch path) ----
+  std::map<int, cudaGraphExec_t> decode_graphs;
+  std::map<int, int64_t> graph_launches_per_step;
+
+  // ---- scheduler ----
+  std::mutex mu;
+  std::condition_variable cv_work, cv_done;
+  std::thread worker;
+  bool stop = false;
+  bool exclusive = false;                      // generate_batch owns the device
+  int64_t next_id = 1;
+  std::deque<std::shared_ptr<Request>> waiting;
+  std::vector<std::shared_ptr<Request>> running;
+  std::unordered_map<int64_t, std::shared_ptr<Request>> table;
+  b200_stats stats{};
+
+  // =========================================================================================
+  size_t layer_kv_offset(int l) const { return (size_t)l * kv_layer_elems; }
+
+  int linear(const W4Linear& w, const __half* x, int ldx, float* y, int ldy, int T, bool accumulate) {
+    return launch_w4_gemv(w, x, ldx, y, ldy, T, accumulate, stream);
+  }
+
+  // One forward pass over T token rows whose metadata already sits in the d_* buffers; samples one
+  // token for each of the n_rows "last" rows into d_next.  `rows` == nullptr: row r is token r.
+  int forward(int T, int n_rows, const int32_t* rows, bool want_sample = true) {
+    int rc;
+    if ((rc = launch_embed(embed.as<__half>(), d_ids.as<int32_t>(), T, H, h.as<float>(), stream))) return rc;
+    for (int l = 0; l < L; ++l) {
+      LayerWeights& w = layers[l];
+      __half* kc = k_cache.as<__half>() + layer_kv_offset(l);
+      __half* vc = v_cache.as<__half>() + layer_kv_offset(l);
+      if ((rc = launch_rmsnorm(h.as<float>(), nullptr, 0, 0, w.ln1.as<__half>(), cfg.rms_eps, nullptr, T, H,
+                               xn.as<__half>(), stream))) return rc;
+      if ((rc = linear(w.lin[0], xn.as<__half>(), H, qkv.as<float>(), QKV, T, false))) return rc;
+      if ((rc = launch_rope_kv(qkv.as<float>(), d_pos.as<int32_t>(), d_slot.as<int32_t>(), cos_t.as<float>(),
+                               sin_t.as<float>(), T, NH, NKV, qh.as<__half>(), kc, vc, stream))) return rc;
+      if ((rc = launch_paged_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
+                                  d_btrow.as<int32_t>(), d_ctx.as<int32_t>(), T, NH, NKV, attn.as<__half>(),
+                                  stream))) return rc;
+      if ((rc = linear(w.lin[1], attn.as<__half>(), NH * kHeadDim, h.as<float>(), H, T, true))) return rc;
+      if ((rc = launch_rmsnorm(h.as<float>(), nullptr, 0, 0, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H,
+                               xn.as<__half>(), stream))) return rc;
+      if ((rc = linear(w.lin[2], xn.as<__half>(), H, gu.as<float>(), 2 * I, T, false))) return rc;
+      if ((rc = launch_swiglu(gu.as<float>(), T, I, act.as<__half>(), stream))) return rc;
+      if ((rc = linear(w.lin[3], act.as<__half>(), I, h.as<float>(), H, T, true))) return rc;
+    }
+    if ((rc = launch_rmsnorm(h.as<float>(), nullptr, 0, 0, final_norm.as<__half>(), cfg.rms_eps, rows, n_rows, H,
+                             xn_last.as<__half>(), stream))) return rc;
+    const __half* head = cfg.tie_embeddings ? embed.as<__half>() : lm_head_w.as<__half>();
+    if ((rc = launch_f16_gemv(head, xn_last.as<__half>(), H, logits.as<float>(), V, n_rows, H, V, false, stream)))
+      return rc;
+    if (want_sample) {
+      if ((rc = launch_sample(logits.as<float>(), n_rows, V, d_temp.as<float>(), d_topp.as<float>(),
+                              d_seed.as<uint32_t>(), d_step.as<int32_t>(), d_next.as<int32_t>(), stream))) return rc;
+    }
+    return B200_OK;
+  }
+
+  double decode_step_bytes(int B, int64_t ctx_sum) const {
+    // algorithmic HBM bytes of one decode step: weights once + KV read + KV write
+    double w = 0;
+    for (int i = 0; i < 4; ++i) {
+      const W4Linear& lw = layers[0].lin[i];
+      w += (double)lw.N * lw.K / 2 + 2.0 * lw.N * (lw.K / lw.G) * 2;
+    }
+    w = w * L + (double)V * H * 2;
+    const double kv_tok = 2.0 * L * NKV * kHeadDim * 2;
+    return w + kv_tok * (double)ctx_sum + kv_tok * B;
+  }
+
+  // ---- block allocator ---------------------------------------------------------------------
+  bool alloc_blocks(int n, std::vector<int32_t>& out) {
+    if ((int)free_blocks.size() < n) return false;
+    for (int i = 0; i < n; ++i) { out.push_back(free_blocks.back()); free_blocks.pop_back(); }
+    return true;
+  }
+  void release_request_resources(Request& r) {
+    for (int32_t b : r.blocks) free_blocks.push_back(b);
+    r.blocks.clear();
+    if (r.seq_slot >= 0) free_slots.push_back(r.seq_slot);
+    r.seq_slot = -1;
+  }
+
+  int upload_i32(DevMem& dst, const std::vector<int32_t>& src) {
+    if (src.empty()) return B200_OK;
+    B200_CUDA(cudaMemcpyAsync(dst.p, src.data(), src.size() * 4, cudaMemcpyHostToDevice, stream));
+    return B200_OK;
+  }
+  int upload_f32(DevMem& dst, const std::vector<float>& src) {
+    if (src.empty()) return B200_OK;
+    B200_CUDA(cudaMemcpyAsync(dst.p, src.data(), src.size() * 4, cudaMemcpyHostToDevice, stream));
+    return B200_OK;
+  }
+
+  // ---- one scheduler step over `batch`; prefill rows for new requests, one row for running ones.
+  int run_step(const std::vector<std::shared_ptr<Request>>& batch, bool is_prefill) {
+    std::vector<int32_t> ids, pos, slot, btrow, ctx, lastrows, bt, step;
+    std::vector<float> temp, topp;
+    std::vector<int32_t> seed;
+    const int n = (int)batch.size();
+    bt.assign((size_t)cfg.max_seqs * max_blocks_per_seq, 0);
+    int64_t ctx_sum = 0;
+    for (int r = 0; r < n; ++r) {
+      Request& q = *batch[r];
+      const int n_ctx = (int)q.prompt.size() + (int)q.out.size();   // tokens known so far
+      const int first = is_prefill ? 0 : n_ctx - 1;
+      for (int p = first; p < n_ctx; ++p) {
+        ids.push_back(p < (int)q.prompt.size() ? q.prompt[p] : q.out[p - q.prompt.size()]);
+        pos.push_back(p);
+        slot.push_back(q.blocks[p / kBlockTokens] * kBlockTokens + p % kBlockTokens);
+        btrow.push_back(q.seq_slot);
+        ctx.push_back(p + 1);
+      }
+      ctx_sum += n_ctx;
+      lastrows.push_back((int)ids.size() - 1);
+      temp.push_back(q.temperature);
+      topp.push_back(q.top_p);
+      seed.push_back((int32_t)q.seed);
+      step.push_back((int32_t)q.out.size());
+    }
+    // block tables: only rows of sequences in this batch are read by the kernels
+    for (int r = 0; r < n; ++r) {
+      Request& q = *batch[r];
+      std::copy(q.blocks.begin(), q.blocks.end(), bt.begin() + (size_t)q.seq_slot * max_blocks_per_seq);
+    }
+    const int T = (int)ids.size();
+    int rc;
+    if ((rc = upload_i32(d_ids, ids)) || (rc = upload_i32(d_pos, pos)) || (rc = upload_i32(d_slot, slot)) ||
+        (rc = upload_i32(d_btrow, btrow)) || (rc = upload_i32(d_ctx, ctx)) || (rc = upload_i32(d_lastrows, lastrows)) ||
+        (rc = upload_i32(d_bt, bt)) || (rc = upload_f32(d_temp, temp)) || (rc = upload_f32(d_topp, topp)) ||
+        (rc = upload_i32(d_seed, seed)) || (rc = upload_i32(d_step, step)))
+      return rc;
+    const int64_t launches0 = g_launch_count;
+    B200_CUDA(cudaEventRecord(ev0, stream));
+    if ((rc = forward(T, n, d_lastrows.as<int32_t>()))) return rc;
+    B200_CUDA(cudaEventRecord(ev1, stream));
+    std::vector<int32_t> next(n);
+    B200_CUDA(cudaMemcpyAsync(next.data(), d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+    B200_CUDA(cudaStreamSynchronize(stream));
+    float ms = 0.f;
+    B200_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+    const double t = now_s();
+    std::lock_guard<std::mutex> lk(mu);
+    stats.kernel_launches += g_launch_count - launches0;
+    if (is_prefill) {
+      stats.steps_prefill++; stats.tokens_prefill += T; stats.gpu_seconds_prefill += ms * 1e-3;
+    } else {
+      stats.steps_decode++; stats.gpu_seconds_decode += ms * 1e-3; stats.decode_batch_sum += n;
+      stats.hbm_bytes_decode += decode_step_bytes(n, ctx_sum);
+    }
+    stats.tokens_generated += n;
+    for (int r = 0; r < n; ++r) {
+      Request& q = *batch[r];
+      q.out.push_back(next[r]);
+      if (q.out.size() == 1) q.t_first = t;
+      q.t_last = t;
+    }
+    return B200_OK;
+  }
+
+  void fail_all(const std::string& why) {       // mu held
+    fatal = why;
+    for (auto& kv : table) {
+      Request& r = *kv.second;
+      if (r.state == ReqState::WAITING || r.state == ReqState::RUNNING) r.state = ReqState::FAILED;
+    }
+    waiting.clear();
+    running.clear();
+    cv_done.notify_all();
+  }
+
+  void scheduler_loop() {
+    cudaSetDevice(cfg.device);
+    std::unique_lock<std::mutex> lk(mu);
+    while (true) {
+      cv_work.wait(lk, [&] { return stop || (!exclusive && (!waiting.empty() || !running.empty())); });
+      if (stop) break;
+      // retire aborted requests
+      for (auto it = running.begin(); it != running.end();) {
+        if ((*it)->abort_requested) {
+          (*it)->state = ReqState::ABORTED; release_request_resources(**it); stats.requests_aborted++;
+          it = running.erase(it);
+        } else ++it;
+      }
+      for (auto it = waiting.begin(); it != waiting.end();) {
+        if ((*it)->abort_requested) { (*it)->state = ReqState::ABORTED; stats.requests_aborted++; it = waiting.erase(it); }
+        else ++it;
+      }
+      cv_done.notify_all();
+      // admit: FIFO, whole prompts, within the token budget, with blocks reserved for the full
+      // generation so a running sequence never has to be preempted.
+      std::vector<std::shared_ptr<Request>> admitted;
+      int budget = cfg.max_batch_tokens;
+      while (!waiting.empty() && !free_slots.empty()) {
+        auto& r = waiting.front();
+        const int need_tokens = (int)r->prompt.size() + r->max_tokens;
+        const int need_blocks = (need_tokens + kBlockTokens - 1) / kBlockTokens;
+        if ((int)r->prompt.size() > budget && !admitted.empty()) break;
+        if ((int)free_blocks.size() < need_blocks) break;
+        alloc_blocks(need_blocks, r->blocks);
+        r->seq_slot = free_slots.back(); free_slots.pop_back();
+        r->state = ReqState::RUNNING;
+        budget -= (int)r->prompt.size();
+        admitted.push_back(r);
+        waiting.pop_front();
+        if (budget <= 0) break;
+      }
+      std::vector<std::shared_ptr<Request>> batch = admitted.empty() ? running : admitted;
+      const bool is_prefill = !admitted.empty();
+      if (batch.empty()) continue;
+      lk.unlock();
+      const int rc = run_step(batch, is_prefill);
+      lk.lock();
+      if (rc != B200_OK) { fail_all(g_last_error); continue; }
+      if (is_prefill) for (auto& r : admitted) running.push_back(r);
+      // retire finished sequences
+      for (auto it = running.begin(); it != running.end();) {
+        Request& r = **it;
+        const bool eos = cfg.eos_token_id >= 0 && !r.out.empty() && r.out.back() == cfg.eos_token_id;
+        if ((int)r.out.size() >= r.max_tokens || eos) {
+          r.state = ReqState::FINISHED; release_request_resources(r); stats.requests_finished++;
+          it = running.erase(it);
+        } else ++it;
+      }
+      cv_done.notify_all();
+    }
+  }
+};
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+int32_t b200_abi_version(void) { return B200_ABI_VERSION; }
+const char* b200_last_error(void) { return g_last_error.c_str(); }
+
+int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
+  B200_REQUIRE(cfg && out, "null argument");
+  B200_REQUIRE(cfg->struct_size == (int32_t)sizeof(b200_config), "b200_config.struct_size mismatch");
+  B200_REQUIRE(cfg->head_dim == kHeadDim, "head_dim must be 128");
+  B200_REQUIRE(cfg->hidden > 0 && cfg->hidden % 128 == 0 && cfg->intermediate % 128 == 0, "hidden/intermediate % 128");
+  B200_REQUIRE(cfg->group_size == 128 || cfg->group_size == 64 || cfg->group_size == 32, "group_size in {32,64,128}");
+  B200_REQUIRE(cfg->n_heads % cfg->n_kv_heads == 0 && cfg->n_heads / cfg->n_kv_heads <= 8, "GQA group <= 8");
+  B200_REQUIRE(cfg->max_seqs > 0 && cfg->max_model_len > 0 && cfg->max_batch_tokens > 0, "max_seqs/max_model_len/max_batch_tokens");
+  int ndev = 0;
+  B200_CUDA(cudaGetDeviceCount(&ndev));
+  B200_REQUIRE(cfg->device >= 0 && cfg->device < ndev, "device ordinal out of range");
+  B200_CUDA(cudaSetDevice(cfg->device));
+  cudaDeviceProp prop;
+  B200_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+  if (prop.major != 10) {
+    set_last_error(std::string("libb200gate needs an sm_100 GPU (B200); found ") + prop.name + " sm_" +
+                   std::to_string(prop.major) + std::to_string(prop.minor));
+    return B200_ERR_INVALID;
+  }
+  auto* e = new b200_engine();
+  e->cfg = *cfg;
+  e->H = cfg->hidden; e->I = cfg->intermediate; e->L = cfg->n_layers; e->NH = cfg->n_heads; e->NKV = cfg->n_kv_heads;
+  e->V = cfg->vocab; e->G = cfg->group_size; e->QKV = (cfg->n_heads + 2 * cfg->n_kv_heads) * kHeadDim;
+  int rc = B200_OK;
+  auto fail = [&](int code) { b200_engine_destroy(e); return code; };
+  if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess) {
+    set_last_error("cudaStreamCreate/cudaEventCreate failed");
+    return fail(B200_ERR_CUDA);
+  }
+  e->layers.resize(e->L);
+  const int Ks[4] = {e->H, e->NH * kHeadDim, e->H, e->I};
+  const int Ns[4] = {e->QKV, e->H, 2 * e->I, e->H};
+  for (int l = 0; l < e->L && rc == B200_OK; ++l) {
+    LayerWeights& w = e->layers[l];
+    for (int i = 0; i < 4 && rc == B200_OK; ++i) {
+      const size_t K = Ks[i], N = Ns[i];
+      if ((rc = w.wq[i].alloc(N * (K / 8) * 4)) || (rc = w.sc[i].alloc(N * (K / e->G) * 2)) ||
+          (rc = w.zp[i].alloc(N * (K / e->G) * 2))) break;
+      w.lin[i].wq = w.wq[i].as<uint32_t>(); w.lin[i].sc = w.sc[i].as<__half>(); w.lin[i].zp = w.zp[i].as<__half>();
+      w.lin[i].K = (int)K; w.lin[i].N = (int)N; w.lin[i].G = e->G;
+    }
+    if (rc == B200_OK && !((rc = w.bias_qkv.alloc((size_t)e->QKV * 2)) || (rc = w.ln1.alloc((size_t)e->H * 2)) ||
+                           (rc = w.ln2.alloc((size_t)e->H * 2))))
+      w.lin[0].bias = w.bias_qkv.as<__half>();
+  }
+  if (rc == B200_OK) rc = e->embed.alloc((size_t)e->V * e->H * 2);
+  if (rc == B200_OK && !cfg->tie_embeddings) rc = e->lm_head_w.alloc((size_t)e->V * e->H * 2);
+  if (rc == B200_OK) rc = e->final_norm.alloc((size_t)e->H * 2);
+  if (rc != B200_OK) return fail(rc);
+  // per layer: 7 linears x 3 tensors + 3 biases + 2 norms; + embed + final norm (+ lm_head)
+  e->tensors_expected = e->L * (7 * 3 + 3 + 2) + 2 + (cfg->tie_embeddings ? 0 : 1);
+  *out = e;
+  return B200_OK;
+}
+
+static int copy_to(DevMem& dst, size_t dst_off, const void* src, size_t bytes, cudaStream_t s) {
+  if (dst_off + bytes > dst.bytes) { set_last_error("tensor larger than its destination"); return B200_ERR_INVALID; }
+  B200_CUDA(cudaMemcpyAsync((char*)dst.p + dst_off, src, bytes, cudaMemcpyHostToDevice, s));
+  B200_CUDA(cudaStreamSynchronize(s));   // caller may free `src` right after we return
+  return B200_OK;
+}
+
+int32_t b200_engine_load_tensor(b200_engine* e, const char* name_c, const void* data, int32_t dtype, int32_t ndim,
+                                const int64_t* shape) {
+  B200_REQUIRE(e && name_c && data && shape && ndim >= 1 && ndim <= 2, "load_tensor: null / ndim");
+  if (e->finalized) { set_last_error("load_tensor after finalize"); return B200_ERR_STATE; }
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  const std::string name(name_c);
+  size_t count = 1;
+  for (int i = 0; i < ndim; ++i) count *= (size_t)shape[i];
+  const size_t esz = dtype == B200_DTYPE_F16 ? 2 : 4;
+  auto expect = [&](bool ok, const char* what) {
+    if (!ok) set_last_error("load_tensor " + name + ": unexpected " + what);
+    return ok;
+  };
+  int rc;
+  if (name == "model.embed_tokens.weight" || name == "lm_head.weight" || name == "model.norm.weight") {
+    if (!expect(dtype == B200_DTYPE_F16, "dtype")) return B200_ERR_INVALID;
+    DevMem& dst = name == "model.norm.weight" ? e->final_norm : name == "lm_head.weight" ? e->lm_head_w : e->embed;
+    if (name == "lm_head.weight" && e->cfg.tie_embeddings) return B200_OK;   // tied: ignore the duplicate
+    if (!expect(count * esz == dst.bytes, "shape")) return B200_ERR_INVALID;
+    if ((rc = copy_to(dst, 0, data, count * esz, e->stream))) return rc;
+    e->tensors_loaded++;
+    return B200_OK;
+  }
+  if (name == "b200.rope_cos" || name == "b200.rope_sin") {
+    // Optional: host-computed RoPE table fp32 [>= max_model_len + 1, 64] (bit-identical to the
+    // HF/vLLM fp32 cos/sin cache).  Without it finalize() computes the table itself.
+    if (!expect(dtype == B200_DTYPE_F32 && ndim == 2 && shape[1] == 64 && shape[0] >= e->cfg.max_model_len + 1, "rope table"))
+      return B200_ERR_INVALID;
+    DevMem& dst = name == "b200.rope_cos" ? e->cos_t : e->sin_t;
+    dst.release();
+    if ((rc = dst.alloc(count * 4)) || (rc = copy_to(dst, 0, data, count * 4, e->stream))) return rc;
+    return B200_OK;
+  }
+  int layer = -1;
+  char rest[128] = {0};
+  if (sscanf(name_c, "model.layers.%d.%127s", &layer, rest) != 2 || layer < 0 || layer >= e->L) {
+    set_last_error("load_tensor: unknown tensor name " + name);
+    return B200_ERR_INVALID;
+  }
+  LayerWeights& w = e->layers[layer];
+  const std::string r(rest);
+  if (r == "input_layernorm.weight" || r == "post_attention_layernorm.weight") {
+    if (!expect(dtype == B200_DTYPE_F16 && (int)count == e->H, "dtype/shape")) return B200_ERR_INVALID;
+    if ((rc = copy_to(r[0] == 'i' ? w.ln1 : w.ln2, 0, data, count * 2, e->stream))) return rc;
+    e->tensors_loaded++;
+    return B200_OK;
+  }
+  struct Proj { const char* key; int lin; int row_off; int K; int N; };
+  const int hd = kHeadDim;
+  const Proj projs[7] = {
+      {"self_attn.q_proj", 0, 0, e->H, e->NH * hd},
+      {"self_attn.k_proj", 0, e->NH * hd, e->H, e->NKV * hd},
+      {"self_attn.v_proj", 0, (e->NH + e->NKV) * hd, e->H, e->NKV * hd},
+      {"self_attn.o_proj", 1, 0, e->NH * hd, e->H},
+      {"mlp.gate_proj", 2, 0, e->H, e->I},
+      {"mlp.up_proj", 2, e->I, e->H, e->I},
+      {"mlp.down_proj", 3, 0, e->I, e->H},
+  };
+  for (const Proj& pj : projs) {
+    const std::string key(pj.key);
+    if (r.compare(0, key.size() + 1, key + ".") != 0) continue;
+    const std::string kind = r.substr(key.size() + 1);
+    if (kind == "bias") {
+      if (!expect(pj.lin == 0 && dtype == B200_DTYPE_F16 && (int)count == pj.N, "bias")) return B200_ERR_INVALID;
+      if ((rc = copy_to(w.bias_qkv, (size_t)pj.row_off * 2, data, count * 2, e->stream))) return rc;
+      e->tensors_loaded++;
+      return B200_OK;
+    }
+    PendingLinear& pl = e->pending[std::to_string(layer) + "." + key];
+    const int K = pj.K, N = pj.N, Gs = e->G;
+    if (kind == "qweight") {
+      if (!expect(dtype == B200_DTYPE_I32 && ndim == 2 && shape[0] == K && shape[1] == N / 8, "qweight")) return B200_ERR_INVALID;
+      if ((rc = pl.qweight.alloc(count * 4)) || (rc = copy_to(pl.qweight, 0, data, count * 4, e->stream))) return rc;
+      pl.have_w = true;
+    } else if (kind == "qzeros") {
+      if (!expect(dtype == B200_DTYPE_I32 && ndim == 2 && shape[0] == K / Gs && shape[1] == N / 8, "qzeros")) return B200_ERR_INVALID;
+      if ((rc = pl.qzeros.alloc(count * 4)) || (rc = copy_to(pl.qzeros, 0, data, count * 4, e->stream))) return rc;
+      pl.have_z = true;
+    } else if (kind == "scales") {
+      if (!expect(dtype == B200_DTYPE_F16 && ndim == 2 && shape[0] == K / Gs && shape[1] == N, "scales")) return B200_ERR_INVALID;
+      if ((rc = pl.scales.alloc(count * 2)) || (rc = copy_to(pl.scales, 0, data, count * 2, e->stream))) return rc;
+      pl.have_s = true;
+    } else {
+      set_last_error("load_tensor: unknown tensor kind " + name);
+      return B200_ERR_INVALID;
+    }
+    e->tensors_loaded++;
+    if (pl.have_w && pl.have_z && pl.have_s) {
+      // The fused destination has N_total rows; this projection fills rows [row_off, row_off + N).
+      rc = launch_awq_repack(pl.qweight.as<int32_t>(), pl.qzeros.as<int32_t>(), pl.scales.as<__half>(), K, N, Gs,
+                             w.wq[pj.lin].as<uint32_t>(), w.sc[pj.lin].as<__half>(), w.zp[pj.lin].as<__half>(),
+                             pj.row_off, e->stream);
+      if (rc == B200_OK && cudaStreamSynchronize(e->stream) != cudaSuccess) rc = B200_ERR_CUDA;
+      pl.qweight.release(); pl.qzeros.release(); pl.scales.release();
+      e->pending.erase(std::to_string(layer) + "." + key);
+      return rc;
+    }
+    return B200_OK;
+  }
+  set_last_error("load_tensor: unknown tensor name " + name);
+  return B200_ERR_INVALID;
+}
+
+int32_t b200_engine_finalize(b200_engine* e) {
+  B200_REQUIRE(e, "null engine");
+  if (e->finalized) { set_last_error("finalize called twice"); return B200_ERR_STATE; }
+  if (e->tensors_loaded != e->tensors_expected || !e->pending.empty()) {
+    set_last_error("finalize: " + std::to_string(e->tensors_loaded) + " of " + std::to_string(e->tensors_expected) +
+                   " checkpoint tensors loaded");
+    return B200_ERR_STATE;
+  }
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  const b200_config& c = e->cfg;
+  int rc;
+  // RoPE table: inv_freq = theta^(-2i/d), angle = pos * inv_freq, all fp32 like the HF/vLLM cache
+  if (!e->cos_t.p || !e->sin_t.p) {
+    const int P = c.max_model_len + 1;
+    std::vector<float> cs((size_t)P * 64), sn((size_t)P * 64);
+    for (int i = 0; i < 64; ++i) {
+      const float inv = 1.0f / powf(c.rope_theta, (float)(2 * i) / (float)kHeadDim);
+      for (int p = 0; p < P; ++p) {
+        const float a = (float)p * inv;
+        cs[(size_t)p * 64 + i] = cosf(a);
+        sn[(size_t)p * 64 + i] = sinf(a);
+      }
+    }
+    e->cos_t.release(); e->sin_t.release();
+    if ((rc = e->cos_t.alloc(cs.size() * 4)) || (rc = e->sin_t.alloc(sn.size() * 4))) return rc;
+    B200_CUDA(cudaMemcpy(e->cos_t.p, cs.data(), cs.size() * 4, cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(e->sin_t.p, sn.data(), sn.size() * 4, cudaMemcpyHostToDevice));
+  }
+  // KV pool
+  e->max_blocks_per_seq = (c.max_model_len + 1 + kBlockTokens - 1) / kBlockTokens + 1;
+  const size_t block_bytes_all_layers = (size_t)2 * e->L * e->NKV * kBlockTokens * kHeadDim * 2;
+  size_t kv_bytes = c.kv_bytes > 0 ? (size_t)c.kv_bytes : (size_t)c.max_seqs * e->max_blocks_per_seq * block_bytes_all_layers;
+  e->n_blocks = (int)(kv_bytes / block_bytes_all_layers);
+  B200_REQUIRE(e->n_blocks >= e->max_blocks_per_seq, "kv_bytes too small for one max_model_len sequence");
+  e->kv_layer_elems = (size_t)e->n_blocks * e->NKV * kBlockTokens * kHeadDim;
+  if ((rc = e->k_cache.alloc(e->kv_layer_elems * e->L * 2)) || (rc = e->v_cache.alloc(e->kv_layer_elems * e->L * 2))) return rc;
+  B200_CUDA(cudaMemset(e->k_cache.p, 0, e->k_cache.bytes));
+  B200_CUDA(cudaMemset(e->v_cache.p, 0, e->v_cache.bytes));
+  for (int b = e->n_blocks - 1; b >= 0; --b) e->free_blocks.push_back(b);
+  for (int s = c.max_seqs - 1; s >= 0; --s) e->free_slots.push_back(s);
+  // activations
+  e->Tmax = std::max(std::max(c.max_batch_tokens, c.max_model_len), c.max_seqs);
+  const size_t T = e->Tmax, S = c.max_seqs;
+  if ((rc = e->h.alloc(T * e->H * 4)) || (rc = e->xn.alloc(T * e->H * 2)) || (rc = e->qkv.alloc(T * e->QKV * 4)) ||
+      (rc = e->qh.alloc(T * e->NH * kHeadDim * 2)) || (rc = e->attn.alloc(T * e->NH * kHeadDim * 2)) ||
+      (rc = e->gu.alloc(T * 2 * e->I * 4)) || (rc = e->act.alloc(T * e->I * 2)) || (rc = e->xn_last.alloc(S * e->H * 2)) ||
+      (rc = e->logits.alloc(S * e->V * 4)) || (rc = e->d_ids.alloc(T * 4)) || (rc = e->d_pos.alloc(T * 4)) ||
+      (rc = e->d_slot.alloc(T * 4)) || (rc = e->d_btrow.alloc(T * 4)) || (rc = e->d_ctx.alloc(T * 4)) ||
+      (rc = e->d_lastrows.alloc(S * 4)) || (rc = e->d_bt.alloc(S * e->max_blocks_per_seq * 4)) ||
+      (rc = e->d_temp.alloc(S * 4)) || (rc = e->d_topp.alloc(S * 4)) || (rc = e->d_seed.alloc(S * 4)) ||
+      (rc = e->d_step.alloc(S * 4)) || (rc = e->d_next.alloc(S * 4)) || (rc = e->d_ngen.alloc(S * 4)))
+    return rc;
+  B200_CUDA(cudaDeviceSynchronize());
+  e->finalized = true;
+  e->worker = std::thread([e] { e->scheduler_loop(); });
+  return B200_OK;
+}
+
+void b200_engine_destroy(b200_engine* e) {
+  if (!e) return;
+  {
+    std::lock_guard<std::mutex> lk(e->mu);
+    e->stop = true;
+    for (auto& kv : e->table) {
+      Request& r = *kv.second;
+      if (r.state == ReqState::WAITING || r.state == ReqState::RUNNING) r.state = ReqState::ABORTED;
+    }
+    e->cv_work.notify_all();
+    e->cv_done.notify_all();
+  }
+  if (e->worker.joinable()) e->worker.join();
+  cudaSetDevice(e->cfg.device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (auto& g : e->decode_graphs) cudaGraphExecDestroy(g.second);
+  for (auto& w : e->layers) {
+    for (int i = 0; i < 4; ++i) { w.wq[i].release(); w.sc[i].release(); w.zp[i].release(); }
+    w.bias_qkv.release(); w.ln1.release(); w.ln2.release();
+  }
+  for (auto& kv : e->pending) { kv.second.qweight.release(); kv.second.qzeros.release(); kv.second.scales.release(); }
+  DevMem* all[] = {&e->embed, &e->lm_head_w, &e->final_norm, &e->cos_t, &e->sin_t, &e->k_cache, &e->v_cache, &e->h,
+                   &e->xn, &e->qkv, &e->qh, &e->attn, &e->gu, &e->act, &e->xn_last, &e->logits, &e->d_ids, &e->d_pos,
+                   &e->d_slot, &e->d_btrow, &e->d_ctx, &e->d_lastrows, &e->d_bt, &e->d_temp, &e->d_topp, &e->d_seed,
+                   &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens};
+  for (DevMem* m : all) m->release();
+  if (e->ev0) cudaEventDestroy(e->ev0);
+  if (e->ev1) cudaEventDestroy(e->ev1);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int64_t b200_submit(b200_engine* e, const int32_t* prompt_ids, int32_t n_prompt, float temperature, float top_p,
+                    int32_t max_tokens, uint64_t seed) {
+  B200_REQUIRE(e && prompt_ids, "null argument");
+  B200_REQUIRE(n_prompt > 0 && max_tokens > 0, "n_prompt > 0 && max_tokens > 0");
+  B200_REQUIRE(top_p > 0.f && top_p <= 1.f && temperature >= 0.f, "0 < top_p <= 1, temperature >= 0");
+  if (!e->finalized) { set_last_error("submit before finalize"); return B200_ERR_STATE; }
+  if (n_prompt + max_tokens > e->cfg.max_model_len) {
+    set_last_error("prompt (" + std::to_string(n_prompt) + ") + max_tokens (" + std::to_string(max_tokens) +
+                   ") exceeds max_model_len " + std::to_string(e->cfg.max_model_len));
+    return B200_ERR_CAPACITY;
+  }
+  for (int i = 0; i < n_prompt; ++i)
+    if (prompt_ids[i] < 0 || prompt_ids[i] >= e->V) { set_last_error("prompt token id out of range"); return B200_ERR_INVALID; }
+  auto r = std::make_shared<Request>();
+  r->prompt.assign(prompt_ids, prompt_ids + n_prompt);
+  r->temperature = temperature; r->top_p = top_p; r->max_tokens = max_tokens; r->seed = (uint32_t)(seed ^ (seed >> 32));
+  r->t_submit = now_s();
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (!e->fatal.empty()) { set_last_error("engine failed earlier: " + e->fatal); return B200_ERR_CUDA; }
+  if (e->stop) { set_last_error("engine is shutting down"); return B200_ERR_ABORTED; }
+  r->id = e->next_id++;
+  e->table[r->id] = r;
+  e->waiting.push_back(r);
+  e->cv_work.notify_all();
+  return r->id;
+}
+
+static int finish_code(b200_engine* e, const Request& r) {
+  switch (r.state) {
+    case ReqState::FINISHED: return B200_OK;
+    case ReqState::ABORTED: set_last_error("request aborted"); return B200_ERR_ABORTED;
+    case ReqState::FAILED: set_last_error("engine failure: " + e->fatal); return B200_ERR_CUDA;
+    default: return B200_OK;
+  }
+}
+
+int32_t b200_wait(b200_engine* e, int64_t rid, int32_t* out_ids, int32_t cap, int32_t* n_out, double* ttft_s,
+                  double* gen_time_s) {
+  B200_REQUIRE(e, "null engine");
+  std::unique_lock<std::mutex> lk(e->mu);
+  auto it = e->table.find(rid);
+  if (it == e->table.end()) { set_last_error("unknown request id"); return B200_ERR_NOT_FOUND; }
+  std::shared_ptr<Request> r = it->second;
+  e->cv_done.wait(lk, [&] { return r->state != ReqState::WAITING && r->state != ReqState::RUNNING; });
+  const int n = std::min<int>(cap, (int)r->out.size());
+  if (out_ids && n > 0) std::memcpy(out_ids, r->out.data(), (size_t)n * 4);
+  if (n_out) *n_out = (int)r->out.size();
+  // vLLM semantics (vllm_backend.py:26-31): ttft = first token latency, gen_time = last - first token
+  if (ttft_s) *ttft_s = r->out.empty() ? 0.0 : r->t_first - r->t_submit;
+  if (gen_time_s) *gen_time_s = r->out.empty() ? 0.0 : r->t_last - r->t_first;
+  const int code = finish_code(e, *r);
+  e->table.erase(rid);
+  return code;
+}
+
+int32_t b200_poll(b200_engine* e, int64_t rid, int32_t* out_ids, int32_t cap, int32_t* n_new, int32_t* finished,
+                  int32_t timeout_ms) {
+  B200_REQUIRE(e && n_new && finished, "null argument");
+  std::unique_lock<std::mutex> lk(e->mu);
+  auto it = e->table.find(rid);
+  if (it == e->table.end()) { set_last_error("unknown request id"); return B200_ERR_NOT_FOUND; }
+  std::shared_ptr<Request> r = it->second;
+  auto ready = [&] { return r->out.size() > r->n_polled || (r->state != ReqState::WAITING && r->state != ReqState::RUNNING); };
+  if (timeout_ms > 0) e->cv_done.wait_for(lk, std::chrono::milliseconds(timeout_ms), ready);
+  const int avail = (int)(r->out.size() - r->n_polled);
+  const int n = std::min(avail, std::max(cap, 0));
+  if (out_ids && n > 0) std::memcpy(out_ids, r->out.data() + r->n_polled, (size_t)n * 4);
+  r->n_polled += n;
+  *n_new = n;
+  const bool done = r->state != ReqState::WAITING && r->state != ReqState::RUNNING;
+  *finished = (done && r->n_polled == r->out.size()) ? 1 : 0;
+  int code = B200_OK;
+  if (*finished) { code = finish_code(e, *r); e->table.erase(rid); }
+  return code;
+}
+
+int32_t b200_abort(b200_engine* e, int64_t rid) {
+  B200_REQUIRE(e, "null engine");
+  std::lock_guard<std::mutex> lk(e->mu);
+  auto it = e->table.find(rid);
+  if (it == e->table.end()) { set_last_error("unknown request id"); return B200_ERR_NOT_FOUND; }
+  Request& r = *it->second;
+  if (r.state == ReqState::WAITING || r.state == ReqState::RUNNING) {
+    r.abort_requested = true;
+    e->cv_work.notify_all();
+  }
+  return B200_OK;
+}
+
+int32_t b200_stats_get(b200_engine* e, b200_stats* out) {
+  B200_REQUIRE(e && out, "null argument");
+  std::lock_guard<std::mutex> lk(e->mu);
+  *out = e->stats;
+  out->running = (int)e->running.size();
+  out->waiting = (int)e->waiting.size();
+  out->kv_blocks_total = e->n_blocks;
+  out->kv_blocks_free = (int)e->free_blocks.size();
+  return B200_OK;
+}
+
+int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n_seqs, int32_t n_prompt,
+                            int32_t max_tokens, int32_t* out_ids, float* logits_out, int32_t n_logit_steps,
+                            double* gpu_seconds) {
+  B200_REQUIRE(e && prompt_ids && out_ids, "null argument");
+  B200_REQUIRE(n_seqs > 0 && n_seqs <= e->cfg.max_seqs, "0 < n_seqs <= max_seqs");
+  B200_REQUIRE(n_prompt > 0 && max_tokens > 0 && n_prompt + max_tokens <= e->cfg.max_model_len, "prompt + max_tokens <= max_model_len");
+  B200_REQUIRE(n_logit_steps >= 0 && n_logit_steps <= max_tokens, "n_logit_steps <= max_tokens");
+  if (!e->finalized) { set_last_error("generate_batch before finalize"); return B200_ERR_STATE; }
+  for (int64_t i = 0; i < (int64_t)n_seqs * n_prompt; ++i)
+    if (prompt_ids[i] < 0 || prompt_ids[i] >= e->V) { set_last_error("prompt token id out of range"); return B200_ERR_INVALID; }
+  {
+    std::unique_lock<std::mutex> lk(e->mu);
+    if (!e->fatal.empty()) { set_last_error("engine failed earlier: " + e->fatal); return B200_ERR_CUDA; }
+    if (e->exclusive || !e->running.empty() || !e->waiting.empty()) {
+      set_last_error("generate_batch needs an idle engine");
+      return B200_ERR_STATE;
+    }
+    e->exclusive = true;
+  }
+  struct Release { b200_engine* e; ~Release() { std::lock_guard<std::mutex> lk(e->mu); e->exclusive = false; e->cv_work.notify_all(); } } release{e};
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  cudaStream_t s = e->stream;
+  const int bps = (n_prompt + max_tokens + 1 + kBlockTokens - 1) / kBlockTokens;   // blocks per sequence
+  B200_REQUIRE(bps <= e->max_blocks_per_seq, "sequence needs more blocks than max_blocks_per_seq");
+  if ((int64_t)bps * n_seqs > e->n_blocks) { set_last_error("KV pool too small for this batch"); return B200_ERR_CAPACITY; }
+  int rc;
+  // block tables: sequence i owns blocks [i*bps, (i+1)*bps) (pool is idle, so any assignment is free)
+  std::vector<int32_t> bt((size_t)e->cfg.max_seqs * e->max_blocks_per_seq, 0);
+  for (int i = 0; i < n_seqs; ++i)
+    for (int b = 0; b < bps; ++b) bt[(size_t)i * e->max_blocks_per_seq + b] = i * bps + b;
+  if ((rc = e->upload_i32(e->d_bt, bt))) return rc;
+  std::vector<float> temp(n_seqs, 0.f), topp(n_seqs, 1.f);
+  std::vector<int32_t> zeros(n_seqs, 0);
+  if ((rc = e->upload_f32(e->d_temp, temp)) || (rc = e->upload_f32(e->d_topp, topp)) || (rc = e->upload_i32(e->d_seed, zeros)) ||
+      (rc = e->upload_i32(e->d_step, zeros)) || (rc = e->upload_i32(e->d_ngen, zeros)))
+    return rc;
+  if (e->d_out_tokens.bytes < (size_t)n_seqs * max_tokens * 4) {
+    e->d_out_tokens.release();
+    if ((rc = e->d_out_tokens.alloc((size_t)n_seqs * max_tokens * 4))) return rc;
+  }
+  const int64_t launches0 = g_launch_count;
+  // ---- prefill in chunks of whole sequences ----
+  const int seqs_per_chunk = std::max(1, std::min(n_seqs, e->Tmax / n_prompt));
+  B200_REQUIRE(n_prompt <= e->Tmax, "prompt longer than the token buffers");
+  std::vector<int32_t> first_tokens(n_seqs);
+  B200_CUDA(cudaEventRecord(e->ev0, s));
+  for (int s0 = 0; s0 < n_seqs; s0 += seqs_per_chunk) {
+    const int ns = std::min(seqs_per_chunk, n_seqs - s0);
+    std::vector<int32_t> ids, pos, slot, btrow, ctx, lastrows;
+    for (int i = 0; i < ns; ++i) {
+      for (int p = 0; p < n_prompt; ++p) {
+        ids.push_back(prompt_ids[(size_t)(s0 + i) * n_prompt + p]);
+        pos.push_back(p);
+        slot.push_back(((s0 + i) * bps + p / kBlockTokens) * kBlockTokens + p % kBlockTokens);
+        btrow.push_back(s0 + i);
+        ctx.push_back(p + 1);
+      }
+      lastrows.push_back((i + 1) * n_prompt - 1);
+    }
+    if ((rc = e->upload_i32(e->d_ids, ids)) || (rc = e->upload_i32(e->d_pos, pos)) || (rc = e->upload_i32(e->d_slot, slot)) ||
+        (rc = e->upload_i32(e->d_btrow, btrow)) || (rc = e->upload_i32(e->d_ctx, ctx)) ||
+        (rc = e->upload_i32(e->d_lastrows, lastrows)))
+      return rc;
+    if ((rc = e->forward(ns * n_prompt, ns, e->d_lastrows.as<int32_t>()))) return rc;
+    B200_CUDA(cudaMemcpyAsync(first_tokens.data() + s0, e->d_next.p, (size_t)ns * 4, cudaMemcpyDeviceToHost, s));
+    if (logits_out && n_logit_steps > 0)
+      B200_CUDA(cudaMemcpy2DAsync(logits_out + (size_t)s0 * n_logit_steps * e->V, (size_t)n_logit_steps * e->V * 4,
+                                  e->logits.p, (size_t)e->V * 4, (size_t)e->V * 4, ns, cudaMemcpyDeviceToHost, s));
+    B200_CUDA(cudaStreamSynchronize(s));   // host vectors above go out of scope
+  }
+  B200_CUDA(cudaEventRecord(e->ev1, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  float ms_prefill = 0.f;
+  B200_CUDA(cudaEventElapsedTime(&ms_prefill, e->ev0, e->ev1));
+  // ---- decode: device-resident loop (advance -> forward), no host interaction per step ----
+  {
+    std::vector<int32_t> pos(n_seqs, n_prompt - 1), btrow(n_seqs);
+    for (int i = 0; i < n_seqs; ++i) btrow[i] = i;
+    if ((rc = e->upload_i32(e->d_pos, pos)) || (rc = e->upload_i32(e->d_btrow, btrow)) ||
+        (rc = e->upload_i32(e->d_next, first_tokens)))
+      return rc;
+    B200_CUDA(cudaStreamSynchronize(s));
+  }
+  auto advance = [&]() -> int {
+    advance_decode_kernel<<<(n_seqs + 127) / 128, 128, 0, s>>>(
+        n_seqs, e->d_next.as<int32_t>(), e->d_ids.as<int32_t>(), e->d_pos.as<int32_t>(), e->d_slot.as<int32_t>(),
+        e->d_ctx.as<int32_t>(), e->d_ngen.as<int32_t>(), e->d_btrow.as<int32_t>(), e->d_bt.as<int32_t>(),
+        e->max_blocks_per_seq, e->d_out_tokens.as<int32_t>(), max_tokens);
+    g_launch_count += 1;
+    B200_CUDA(cudaGetLastError());
+    return B200_OK;
+  };
+  auto step_once = [&]() -> int {
+    int r2;
+    if ((r2 = advance())) return r2;
+    return e->forward(n_seqs, n_seqs, nullptr);
+  };
+  B200_CUDA(cudaEventRecord(e->ev0, s));
+  // step 1 runs eagerly: it loads every kernel of the decode configuration before any capture
+  int t = 1;
+  if (t < max_tokens) {
+    if ((rc = step_once())) return rc;
+    if (logits_out && t < n_logit_steps)
+      B200_CUDA(cudaMemcpy2DAsync(logits_out + (size_t)t * e->V, (size_t)n_logit_steps * e->V * 4, e->logits.p,
+                                  (size_t)e->V * 4, (size_t)e->V * 4, n_seqs, cudaMemcpyDeviceToHost, s));
+    ++t;
+  }
+  cudaGraphExec_t graph = nullptr;
+  if (e->cfg.use_cuda_graphs && t < max_tokens) {
+    auto it = e->decode_graphs.find(n_seqs);
+    if (it != e->decode_graphs.end()) graph = it->second;
+    else {
+      cudaGraph_t g = nullptr;
+      B200_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      const int64_t before = g_launch_count;
+      rc = step_once();
+      const int64_t per_step = g_launch_count - before;
+      g_launch_count = before;
+      cudaError_t ce = cudaStreamEndCapture(s, &g);
+      if (rc != B200_OK) { if (g) cudaGraphDestroy(g); return rc; }
+      B200_CUDA(ce);
+      B200_CUDA(cudaGraphInstantiate(&graph, g, 0));
+      B200_CUDA(cudaGraphDestroy(g));
+      e->decode_graphs[n_seqs] = graph;
+      e->graph_launches_per_step[n_seqs] = per_step;
+    }
+  }
+  for (; t < max_tokens; ++t) {
+    if (graph) {
+      B200_CUDA(cudaGraphLaunch(graph, s));
+      g_launch_count += e->graph_launches_per_step[n_seqs];
+    } else if ((rc = step_once())) return rc;
+    if (logits_out && t < n_logit_steps)
+      B200_CUDA(cudaMemcpy2DAsync(logits_out + (size_t)t * e->V, (size_t)n_logit_steps * e->V * 4, e->logits.p,
+                                  (size_t)e->V * 4, (size_t)e->V * 4, n_seqs, cudaMemcpyDeviceToHost, s));
+  }
+  if ((rc = advance())) return rc;     // record the last sampled token
+  B200_CUDA(cudaEventRecord(e->ev1, s));
+  B200_CUDA(cudaMemcpyAsync(out_ids, e->d_out_tokens.p, (size_t)n_seqs * max_tokens * 4, cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  float ms_decode = 0.f;
+  B200_CUDA(cudaEventElapsedTime(&ms_decode, e->ev0, e->ev1));
+  if (gpu_seconds) { gpu_seconds[0] = ms_prefill * 1e-3; gpu_seconds[1] = ms_decode * 1e-3; }
+  std::lock_guard<std::mutex> lk(e->mu);
+  e->stats.kernel_launches += g_launch_count - launches0;
+  e->stats.steps_prefill += (n_seqs + seqs_per_chunk - 1) / seqs_per_chunk;
+  e->stats.tokens_prefill += (int64_t)n_seqs * n_prompt;
+  e->stats.gpu_seconds_prefill += ms_prefill * 1e-3;
+  e->stats.steps_decode += max_tokens - 1;
+  e->stats.gpu_seconds_decode += ms_decode * 1e-3;
+  e->stats.decode_batch_sum += (int64_t)n_seqs * (max_tokens - 1);
+  e->stats.tokens_generated += (int64_t)n_seqs * max_tokens;
+  for (int t = 1; t < max_tokens; ++t) e->stats.hbm_bytes_decode += e->decode_step_bytes(n_seqs, (int64_t)n_seqs * (n_prompt + t));
+  return B200_OK;
+}
+
+// ---- kernel entry points ----------------------------------------------------------------------
+int32_t b200_op_awq_repack(const int32_t* qweight, const int32_t* qzeros, const void* scales, int32_t K, int32_t N,
+                           int32_t G, uint32_t* wq, void* sc, void* zp, void* stream) {
+  return launch_awq_repack(qweight, qzeros, (const __half*)scales, K, N, G, wq, (__half*)sc, (__half*)zp, 0,
+                           (cudaStream_t)stream);
+}
+int32_t b200_op_awq_dequant(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N, int32_t G,
+                            void* w_out, void* stream) {
+  return launch_awq_dequant(wq, (const __half*)sc, (const __half*)zp, K, N, G, (__half*)w_out, (cudaStream_t)stream);
+}
+int32_t b200_op_w4_gemv(const uint32_t* wq, const void* sc, const void* zp, const void* x, int32_t ldx, float* y,
+                        int32_t ldy, const void* bias, int32_t B, int32_t K, int32_t N, int32_t G, int32_t accumulate,
+                        void* stream) {
+  W4Linear w;
+  w.wq = wq; w.sc = (const __half*)sc; w.zp = (const __half*)zp; w.bias = (const __half*)bias; w.K = K; w.N = N; w.G = G;
+  return launch_w4_gemv(w, (const __half*)x, ldx, y, ldy, B, accumulate != 0, (cudaStream_t)stream);
+}
+int32_t b200_op_f16_gemv(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t B, int32_t K,
+                         int32_t N, int32_t accumulate, void* stream) {
+  return launch_f16_gemv((const __half*)w, (const __half*)x, ldx, y, ldy, B, K, N, accumulate != 0, (cudaStream_t)stream);
+}
+int32_t b200_op_rmsnorm(float* h, const float* parts, int32_t n_parts, int64_t part_stride, const void* gamma, float eps,
+                        const int32_t* rows, int32_t n_rows, int32_t H, void* xn, void* stream) {
+  return launch_rmsnorm(h, parts, n_parts, part_stride, (const __half*)gamma, eps, rows, n_rows, H, (__half*)xn,
+                        (cudaStream_t)stream);
+}
+int32_t b200_op_rope_kv(const float* qkv, const int32_t* pos, const int32_t* slot, const float* cos_t, const float* sin_t,
+                        int32_t T, int32_t n_heads, int32_t n_kv, void* q_out, void* k_cache, void* v_cache, void* stream) {
+  return launch_rope_kv(qkv, pos, slot, cos_t, sin_t, T, n_heads, n_kv, (__half*)q_out, (__half*)k_cache, (__half*)v_cache,
+                        (cudaStream_t)stream);
+}
+int32_t b200_op_paged_attn(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_tables,
+                           int32_t bt_stride, const int32_t* bt_row, const int32_t* ctx_len, int32_t T, int32_t n_heads,
+                           int32_t n_kv, void* out, void* stream) {
+  return launch_paged_attn((const __half*)q, (const __half*)k_cache, (const __half*)v_cache, block_tables, bt_stride,
+                           bt_row, ctx_len, T, n_heads, n_kv, (__half*)out, (cudaStream_t)stream);
+}
+int32_t b200_op_swiglu(const float* gu, int32_t T, int32_t I, void* act, void* stream) {
+  return launch_swiglu(gu, T, I, (__half*)act, (cudaStream_t)stream);
+}
+int32_t b200_op_embed(const void* table, const int32_t* ids, int32_t T, int32_t H, float* h, void* stream) {
+  return launch_embed((const __half*)table, ids, T, H, h, (cudaStream_t)stream);
+}
+int32_t b200_op_sample(const float* logits, int32_t B, int32_t V, const float* temperature, const float* top_p,
+                       const uint32_t* seed, const int32_t* step, int32_t* out, void* stream) {
+  return launch_sample(logits, B, V, temperature, top_p, seed, step, out, (cudaStream_t)stream);
+}
+
+}  // extern "C"

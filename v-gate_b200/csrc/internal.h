@@ -1,0 +1,62 @@
+// Internal C++ launcher interface shared by the op wrappers and the engine.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <string>
+
+#include "../../include/b200gate.h"
+
+namespace b200 {
+
+constexpr int kHeadDim = 128;
+constexpr int kBlockTokens = 16;   // KV block size in tokens (vLLM default block_size)
+
+void set_last_error(const std::string& msg);
+int cuda_fail(cudaError_t err, const char* what, const char* file, int line);
+
+#define B200_CUDA(call)                                                        \
+  do {                                                                         \
+    cudaError_t _e = (call);                                                   \
+    if (_e != cudaSuccess) return ::b200::cuda_fail(_e, #call, __FILE__, __LINE__); \
+  } while (0)
+
+#define B200_REQUIRE(cond, msg)                                                \
+  do {                                                                         \
+    if (!(cond)) { ::b200::set_last_error(std::string("invalid argument: ") + msg); return B200_ERR_INVALID; } \
+  } while (0)
+
+// Every launcher returns B200_OK or an error code and bumps the launch counter.
+extern thread_local int64_t g_launch_count;
+
+// AWQ linear in kernel layout (see b200_op_awq_repack).
+struct W4Linear {
+  const uint32_t* wq = nullptr;  // [N, K/8]
+  const __half* sc = nullptr;    // [N, K/G]
+  const __half* zp = nullptr;    // [N, K/G]  (1024 + zero)
+  const __half* bias = nullptr;  // [N] or null
+  int K = 0, N = 0, G = 128;
+};
+
+int launch_awq_repack(const int32_t* qweight, const int32_t* qzeros, const __half* scales, int K, int N, int G,
+                      uint32_t* wq, __half* sc, __half* zp, int row_offset, cudaStream_t s);
+int launch_awq_dequant(const uint32_t* wq, const __half* sc, const __half* zp, int K, int N, int G, __half* w,
+                       cudaStream_t s);
+int launch_w4_gemv(const W4Linear& w, const __half* x, int ldx, float* y, int ldy, int B, bool accumulate,
+                   cudaStream_t s);
+int launch_f16_gemv(const __half* w, const __half* x, int ldx, float* y, int ldy, int B, int K, int N,
+                    bool accumulate, cudaStream_t s);
+int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_stride, const __half* gamma, float eps,
+                   const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s);
+int launch_rope_kv(const float* qkv, const int32_t* pos, const int32_t* slot, const float* cos_t,
+                   const float* sin_t, int T, int n_heads, int n_kv, __half* q_out, __half* k_cache,
+                   __half* v_cache, cudaStream_t s);
+int launch_paged_attn(const __half* q, const __half* k_cache, const __half* v_cache, const int32_t* block_tables,
+                      int bt_stride, const int32_t* bt_row, const int32_t* ctx_len, int T, int n_heads, int n_kv,
+                      __half* out, cudaStream_t s);
+int launch_swiglu(const float* gu, int T, int I, __half* act, cudaStream_t s);
+int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s);
+int launch_sample(const float* logits, int B, int V, const float* temperature, const float* top_p,
+                  const uint32_t* seed, const int32_t* step, int32_t* out, cudaStream_t s);
+
+}  // namespace b200

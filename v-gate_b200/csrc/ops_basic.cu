@@ -1,0 +1,246 @@
+// Small memory-bound kernels of the decode/prefill path: AWQ repack + dequant, embedding gather,
+// fused residual-sum + RMSNorm, RoPE + paged KV write, SwiGLU.
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200 {
+
+__constant__ int kAwqOrder[8] = {0, 4, 1, 5, 2, 6, 3, 7};
+
+// ---------------------------------------------------------------------------------------------
+// AWQ checkpoint layout -> kernel layout (one-time, at load).
+//   in : qweight[k][n/8] nibble kAwqOrder[n%8]              (awq_triton.py:53-70)
+//   out: wq[n][k/8]      nibble kAwqOrder[k%8]
+__global__ void awq_repack_weight_kernel(const uint32_t* __restrict__ qweight, int K, int N,
+                                         uint32_t* __restrict__ wq, int row_offset) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;   // n fastest: coalesced reads of qweight rows
+  const int j = blockIdx.y;                              // output word along K
+  if (n >= N) return;
+  const int in_shift = 4 * kAwqOrder[n & 7];
+  uint32_t out = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const uint32_t word = qweight[(size_t)(8 * j + i) * (N / 8) + (n >> 3)];
+    out |= ((word >> in_shift) & 0xFu) << (4 * kAwqOrder[i]);
+  }
+  wq[(size_t)(n + row_offset) * (K / 8) + j] = out;
+}
+
+__global__ void awq_repack_scales_kernel(const uint32_t* __restrict__ qzeros, const __half* __restrict__ scales,
+                                         int NG, int N, __half* __restrict__ sc, __half* __restrict__ zp,
+                                         int row_offset) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const int g = blockIdx.y;
+  if (n >= N) return;
+  const uint32_t zw = qzeros[(size_t)g * (N / 8) + (n >> 3)];
+  const int z = (zw >> (4 * kAwqOrder[n & 7])) & 0xF;
+  sc[(size_t)(n + row_offset) * NG + g] = scales[(size_t)g * N + n];
+  zp[(size_t)(n + row_offset) * NG + g] = __int2half_rn(1024 + z);
+}
+
+int launch_awq_repack(const int32_t* qweight, const int32_t* qzeros, const __half* scales, int K, int N, int G,
+                      uint32_t* wq, __half* sc, __half* zp, int row_offset, cudaStream_t s) {
+  B200_REQUIRE(K % G == 0 && G % 32 == 0 && N % 8 == 0 && K % 32 == 0, "awq_repack: K % G, G % 32, N % 8");
+  dim3 block(128);
+  dim3 grid_w((N + 127) / 128, K / 8);
+  awq_repack_weight_kernel<<<grid_w, block, 0, s>>>(reinterpret_cast<const uint32_t*>(qweight), K, N, wq, row_offset);
+  dim3 grid_s((N + 127) / 128, K / G);
+  awq_repack_scales_kernel<<<grid_s, block, 0, s>>>(reinterpret_cast<const uint32_t*>(qzeros), scales, K / G, N, sc,
+                                                    zp, row_offset);
+  g_launch_count += 2;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+// kernel layout -> dense fp16 [N, K]; uses the same dequant8 as the GEMV/GEMM kernels.
+__global__ void awq_dequant_kernel(const uint32_t* __restrict__ wq, const __half* __restrict__ sc,
+                                   const __half* __restrict__ zp, int K, int N, int G, __half* __restrict__ w) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;  // word along K
+  const int n = blockIdx.y;
+  if (j >= K / 8) return;
+  const int g = (8 * j) / G;
+  const __half2 s2 = __half2half2(sc[(size_t)n * (K / G) + g]);
+  const __half2 z2 = __half2half2(zp[(size_t)n * (K / G) + g]);
+  uint32_t o[4];
+  dequant8(wq[(size_t)n * (K / 8) + j], *reinterpret_cast<const uint32_t*>(&z2),
+           *reinterpret_cast<const uint32_t*>(&s2), o);
+  *reinterpret_cast<uint4*>(w + (size_t)n * K + 8 * j) = make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+int launch_awq_dequant(const uint32_t* wq, const __half* sc, const __half* zp, int K, int N, int G, __half* w,
+                       cudaStream_t s) {
+  B200_REQUIRE(K % G == 0 && K % 8 == 0, "awq_dequant: K % G");
+  dim3 grid((K / 8 + 127) / 128, N);
+  awq_dequant_kernel<<<grid, 128, 0, s>>>(wq, sc, zp, K, N, G, w);
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Embedding gather into the fp32 residual stream.
+__global__ void embed_kernel(const __half* __restrict__ table, const int32_t* __restrict__ ids, int H,
+                             float* __restrict__ h) {
+  const int t = blockIdx.x;
+  const __half* row = table + (size_t)ids[t] * H;
+  for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
+    const uint4 v = ldg_cached(row + i);
+    const __half2* p = reinterpret_cast<const __half2*>(&v);
+    float4 a, b;
+    float2 f;
+    f = __half22float2(p[0]); a.x = f.x; a.y = f.y;
+    f = __half22float2(p[1]); a.z = f.x; a.w = f.y;
+    f = __half22float2(p[2]); b.x = f.x; b.y = f.y;
+    f = __half22float2(p[3]); b.z = f.x; b.w = f.y;
+    *reinterpret_cast<float4*>(h + (size_t)t * H + i) = a;
+    *reinterpret_cast<float4*>(h + (size_t)t * H + i + 4) = b;
+  }
+}
+
+int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s) {
+  B200_REQUIRE(H % 8 == 0, "embed: H % 8");
+  if (T == 0) return B200_OK;
+  embed_kernel<<<T, 192, 0, s>>>(table, ids, H, h);
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fused residual-sum + RMSNorm.  One CTA per output row.
+//   v = h[row] + sum_p parts[p][row]     (fixed p order: deterministic split-K reduction)
+//   h[row] = v (when n_parts > 0);  xn[r] = fp16(v * rsqrt(mean(v^2) + eps) * gamma)
+// Follows vLLM qwen2.py:287-312 (RMSNorm with fused residual add), arithmetic in fp32.
+constexpr int kNormThreads = 256;
+constexpr int kNormMaxPerThread = 8;   // H <= 256 * 4 * 8 = 8192
+
+__global__ void __launch_bounds__(kNormThreads)
+rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_parts, int64_t part_stride,
+               const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows, int H,
+               __half* __restrict__ xn) {
+  const int r = blockIdx.x;
+  const int row = rows ? rows[r] : r;
+  float4 v[kNormMaxPerThread];
+  float ss = 0.f;
+  const int nvec = H / 4;
+#pragma unroll
+  for (int it = 0; it < kNormMaxPerThread; ++it) {
+    const int i = threadIdx.x + it * kNormThreads;
+    if (i < nvec) {
+      float4 a = *reinterpret_cast<const float4*>(h + (size_t)row * H + 4 * i);
+      for (int p = 0; p < n_parts; ++p) {
+        const float4 b = *reinterpret_cast<const float4*>(parts + p * part_stride + (size_t)row * H + 4 * i);
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+      }
+      if (n_parts > 0) *reinterpret_cast<float4*>(h + (size_t)row * H + 4 * i) = a;
+      v[it] = a;
+      ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+    }
+  }
+  __shared__ float red[kNormThreads / 32];
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int w = 0; w < kNormThreads / 32; ++w) tot += red[w];
+  const float rs = rsqrtf(tot / (float)H + eps);
+#pragma unroll
+  for (int it = 0; it < kNormMaxPerThread; ++it) {
+    const int i = threadIdx.x + it * kNormThreads;
+    if (i < nvec) {
+      const uint2 gw = *reinterpret_cast<const uint2*>(gamma + 4 * i);
+      const float2 g0 = __half22float2(*reinterpret_cast<const __half2*>(&gw.x));
+      const float2 g1 = __half22float2(*reinterpret_cast<const __half2*>(&gw.y));
+      uint2 o;
+      o.x = pack_half2(v[it].x * rs * g0.x, v[it].y * rs * g0.y);
+      o.y = pack_half2(v[it].z * rs * g1.x, v[it].w * rs * g1.y);
+      *reinterpret_cast<uint2*>(xn + (size_t)r * H + 4 * i) = o;
+    }
+  }
+}
+
+int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_stride, const __half* gamma, float eps,
+                   const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s) {
+  B200_REQUIRE(H % 4 == 0 && H <= kNormThreads * 4 * kNormMaxPerThread, "rmsnorm: H % 4 == 0 && H <= 8192");
+  if (n_rows == 0) return B200_OK;
+  rmsnorm_kernel<<<n_rows, kNormThreads, 0, s>>>(h, parts, n_parts, part_stride, gamma, eps, rows, H, xn);
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// RoPE (neox: rotate halves, vLLM qwen2.py:181 get_rope) fused with the paged KV-cache write.
+// One CTA per token; one thread per (head, i < 64) pair.  fp32 in, one rounding to fp16 out.
+__global__ void rope_kv_kernel(const float* __restrict__ qkv, const int32_t* __restrict__ pos,
+                               const int32_t* __restrict__ slot, const float* __restrict__ cos_t,
+                               const float* __restrict__ sin_t, int n_heads, int n_kv, __half* __restrict__ q_out,
+                               __half* __restrict__ k_cache, __half* __restrict__ v_cache) {
+  const int t = blockIdx.x;
+  const int p = pos[t];
+  const int sl = slot[t];
+  const int total_heads = n_heads + 2 * n_kv;
+  const float* row = qkv + (size_t)t * total_heads * kHeadDim;
+  for (int idx = threadIdx.x; idx < total_heads * 64; idx += blockDim.x) {
+    const int head = idx >> 6, i = idx & 63;
+    const float x1 = row[head * kHeadDim + i], x2 = row[head * kHeadDim + i + 64];
+    if (head < n_heads) {
+      const float c = cos_t[(size_t)p * 64 + i], sn = sin_t[(size_t)p * 64 + i];
+      __half* o = q_out + ((size_t)t * n_heads + head) * kHeadDim;
+      o[i] = __float2half_rn(x1 * c - x2 * sn);
+      o[i + 64] = __float2half_rn(x2 * c + x1 * sn);
+    } else if (sl >= 0) {
+      const int blk = sl / kBlockTokens, off = sl % kBlockTokens;
+      if (head < n_heads + n_kv) {
+        const int j = head - n_heads;
+        const float c = cos_t[(size_t)p * 64 + i], sn = sin_t[(size_t)p * 64 + i];
+        __half* o = k_cache + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
+        o[i] = __float2half_rn(x1 * c - x2 * sn);
+        o[i + 64] = __float2half_rn(x2 * c + x1 * sn);
+      } else {
+        const int j = head - n_heads - n_kv;
+        __half* o = v_cache + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
+        o[i] = __float2half_rn(x1);
+        o[i + 64] = __float2half_rn(x2);
+      }
+    }
+  }
+}
+
+int launch_rope_kv(const float* qkv, const int32_t* pos, const int32_t* slot, const float* cos_t,
+                   const float* sin_t, int T, int n_heads, int n_kv, __half* q_out, __half* k_cache,
+                   __half* v_cache, cudaStream_t s) {
+  if (T == 0) return B200_OK;
+  rope_kv_kernel<<<T, 256, 0, s>>>(qkv, pos, slot, cos_t, sin_t, n_heads, n_kv, q_out, k_cache, v_cache);
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// SwiGLU: act = fp16(silu(gate) * up), gate|up fp32 (vLLM qwen2.py:106-111 SiluAndMul).
+__global__ void swiglu_kernel(const float* __restrict__ gu, int I, __half* __restrict__ act) {
+  const int t = blockIdx.y;
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= I) return;
+  const float4 g = *reinterpret_cast<const float4*>(gu + (size_t)t * 2 * I + i);
+  const float4 u = *reinterpret_cast<const float4*>(gu + (size_t)t * 2 * I + I + i);
+  auto f = [](float a, float b) { return a / (1.f + expf(-a)) * b; };
+  uint2 o;
+  o.x = pack_half2(f(g.x, u.x), f(g.y, u.y));
+  o.y = pack_half2(f(g.z, u.z), f(g.w, u.w));
+  *reinterpret_cast<uint2*>(act + (size_t)t * I + i) = o;
+}
+
+int launch_swiglu(const float* gu, int T, int I, __half* act, cudaStream_t s) {
+  B200_REQUIRE(I % 4 == 0, "swiglu: I % 4");
+  if (T == 0) return B200_OK;
+  dim3 grid((I / 4 + 255) / 256, T);
+  swiglu_kernel<<<grid, 256, 0, s>>>(gu, I, act);
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // namespace b200

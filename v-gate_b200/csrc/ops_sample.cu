@@ -1,0 +1,170 @@
+// Sampling kernel: greedy argmax, or temperature + top-p + exponential-race draw.
+// One CTA per row of logits [B, V] fp32.
+//
+// Semantics follow vLLM (sampler.py:223-236 temperature / greedy threshold 1e-5;
+// topk_topp_sampler.py:349-369 top-p; :395-416 argmax(probs / Exp(1))):
+//   keep token i  <=>  (probability mass of tokens strictly more likely than i) < top_p
+// which is what the reference's "ascending sort, cumsum, drop cumsum <= 1 - p" computes.
+// No sort: the threshold is found by a 5-pass select over fixed-point probability masses
+// (uint64 sums are associative, so the result is deterministic), then one pass draws
+// argmax((x_i - max) - log(-log u_i)) over the kept set with the counter hash u(seed, step, i).
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200 {
+
+constexpr int kSampleThreads = 1024;
+
+__device__ __forceinline__ uint32_t float_key(float f) {   // order-preserving float -> uint32
+  const uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+__device__ __forceinline__ float hash_uniform(uint32_t seed, uint32_t step, uint32_t i) {
+  uint32_t x = i * 0x9E3779B1u + step * 0x85EBCA77u + seed * 0xC2B2AE3Du;
+  x ^= x >> 16; x *= 0x7FEB352Du; x ^= x >> 15; x *= 0x846CA68Bu; x ^= x >> 16;
+  return ((float)(x >> 8) + 0.5f) * (1.0f / 16777216.0f);
+}
+
+struct ArgMax { float v; int i; };
+__device__ __forceinline__ ArgMax better(ArgMax a, ArgMax b) {
+  return (b.v > a.v || (b.v == a.v && b.i < a.i)) ? b : a;
+}
+__device__ ArgMax block_argmax(ArgMax a, ArgMax* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ArgMax b;
+    b.v = __shfl_xor_sync(0xffffffffu, a.v, o);
+    b.i = __shfl_xor_sync(0xffffffffu, a.i, o);
+    a = better(a, b);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __syncthreads();
+  if (lane == 0) red[warp] = a;
+  __syncthreads();
+  if (warp == 0) {
+    a = lane < kSampleThreads / 32 ? red[lane] : ArgMax{-INFINITY, 0x7fffffff};
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      ArgMax b;
+      b.v = __shfl_xor_sync(0xffffffffu, a.v, o);
+      b.i = __shfl_xor_sync(0xffffffffu, a.i, o);
+      a = better(a, b);
+    }
+    if (lane == 0) red[0] = a;
+  }
+  __syncthreads();
+  return red[0];
+}
+
+__global__ void __launch_bounds__(kSampleThreads)
+sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__ temperature,
+              const float* __restrict__ top_p, const uint32_t* __restrict__ seed, const int32_t* __restrict__ step,
+              int32_t* __restrict__ out) {
+  __shared__ ArgMax red[kSampleThreads / 32];
+  __shared__ unsigned long long hist[256];
+  __shared__ unsigned long long s_above, s_target;
+  __shared__ int s_bin;
+  const int r = blockIdx.x, tid = threadIdx.x;
+  const float* l = logits + (size_t)r * V;
+  const float temp = temperature ? temperature[r] : 0.f;
+
+  // pass 0: argmax (greedy result, and the max for the softmax)
+  ArgMax best{-INFINITY, 0x7fffffff};
+  for (int i = tid; i < V; i += kSampleThreads) best = better(best, ArgMax{l[i], i});
+  best = block_argmax(best, red);
+  if (temp < 1e-5f) {
+    if (tid == 0) out[r] = best.i;
+    return;
+  }
+  // x_i = l_i / T exactly as the reference divides (sampler.py:232)
+  const float m = best.v / temp;
+  const float p = top_p ? top_p[r] : 1.f;
+  uint32_t thr_key = 0;        // keep iff key(x_i) >= thr_key
+
+  if (p < 1.f) {
+    constexpr float kBinsPerUnit = 8.f;     // level 0: linear bins over d = m - x in [0, 32)
+    auto bin0 = [&](float x) { return min(255, (int)((m - x) * kBinsPerUnit)); };
+    auto mass = [&](float x) { return (unsigned long long)(expf(x - m) * 4294967296.f); };
+    // ---- level 0 ----
+    if (tid < 256) hist[tid] = 0ull;
+    __syncthreads();
+    for (int i = tid; i < V; i += kSampleThreads) {
+      const float x = l[i] / temp;
+      atomicAdd(&hist[bin0(x)], mass(x));
+    }
+    __syncthreads();
+    if (tid == 0) {
+      unsigned long long total = 0;
+      for (int b = 0; b < 256; ++b) total += hist[b];
+      const unsigned long long target = (unsigned long long)((double)p * (double)total);
+      unsigned long long cum = 0;
+      int sel = -1;
+      for (int b = 0; b < 256; ++b) {            // bin 0 holds the most likely tokens
+        if (hist[b] == 0) continue;
+        sel = b;
+        if (cum + hist[b] >= target) break;
+        cum += hist[b];
+      }
+      // total >= target, so the loop always breaks; sel/cum then bracket the threshold bin.
+      s_bin = sel; s_above = cum; s_target = target;
+    }
+    __syncthreads();
+    const int sel0 = s_bin;
+    // ---- levels 1..4: radix select on the float key inside bin sel0 ----
+    uint32_t prefix = 0, pmask = 0;
+    for (int level = 0; level < 4; ++level) {
+      const int shift = 24 - 8 * level;
+      __syncthreads();
+      if (tid < 256) hist[tid] = 0ull;
+      __syncthreads();
+      for (int i = tid; i < V; i += kSampleThreads) {
+        const float x = l[i] / temp;
+        if (bin0(x) != sel0) continue;
+        const uint32_t key = float_key(x);
+        if ((key & pmask) != prefix) continue;
+        atomicAdd(&hist[(key >> shift) & 255u], mass(x));
+      }
+      __syncthreads();
+      if (tid == 0) {
+        unsigned long long cum = s_above;
+        int sel = -1;
+        for (int b = 255; b >= 0; --b) {         // larger key = more likely
+          if (hist[b] == 0) continue;
+          sel = b;
+          if (cum + hist[b] >= s_target) break;
+          cum += hist[b];
+        }
+        s_bin = sel; s_above = cum;
+      }
+      __syncthreads();
+      prefix |= (uint32_t)s_bin << shift;
+      pmask |= 255u << shift;
+    }
+    thr_key = prefix;
+  }
+
+  // ---- draw: exponential race in log form over the kept set ----
+  const uint32_t sd = seed ? seed[r] : 0u, st = step ? (uint32_t)step[r] : 0u;
+  ArgMax draw{-INFINITY, 0x7fffffff};
+  for (int i = tid; i < V; i += kSampleThreads) {
+    const float x = l[i] / temp;
+    if (float_key(x) < thr_key) continue;
+    const float u = hash_uniform(sd, st, (uint32_t)i);
+    const float score = (x - m) - logf(-logf(u));
+    draw = better(draw, ArgMax{score, i});
+  }
+  draw = block_argmax(draw, red);
+  if (tid == 0) out[r] = draw.i;
+}
+
+int launch_sample(const float* logits, int B, int V, const float* temperature, const float* top_p,
+                  const uint32_t* seed, const int32_t* step, int32_t* out, cudaStream_t s) {
+  if (B == 0) return B200_OK;
+  sample_kernel<<<B, kSampleThreads, 0, s>>>(logits, V, temperature, top_p, seed, step, out);
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // namespace b200
