@@ -143,6 +143,20 @@ int32_t b200_op_awq_dequant(const uint32_t* wq, const void* sc, const void* zp, 
 int32_t b200_op_w4_gemv(const uint32_t* wq, const void* sc, const void* zp, const void* x, int32_t ldx,
                         float* y, int32_t ldy, const void* bias, int32_t B, int32_t K, int32_t N, int32_t G,
                         int32_t accumulate, void* stream);
+/* Kernel layout -> the tiled layout the tcgen05 GEMM streams: wt uint4 [N/128, K/64, 2, 128],
+ * sct / zpt fp16 [N/128, K/G, 128].  N % 128 == 0, K % 64 == 0. */
+int32_t b200_op_w4_tile(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N, int32_t G,
+                        void* wt, void* sct, void* zpt, void* stream);
+/* tcgen05/TMEM W4A16 GEMM, same result contract as b200_op_w4_gemv for any T (token tiles of up to
+ * 256).  n_splits > 1: split-K; y then receives n_splits partial tensors, partial s at
+ * y + s * part_stride (bias and accumulate must be 0 / NULL), to be summed by the consumer
+ * (b200_op_rmsnorm does). */
+int32_t b200_op_w4_gemm_umma(const void* wt, const void* sct, const void* zpt, const void* x, int32_t ldx,
+                             float* y, int32_t ldy, const void* bias, int32_t T, int32_t K, int32_t N, int32_t G,
+                             int32_t accumulate, int32_t n_splits, int64_t part_stride, void* stream);
+/* tcgen05/TMEM GEMM with dense fp16 weights W[N, K] fed by TMA (lm_head); N % 128 == 0, K % 64 == 0. */
+int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T,
+                              int32_t K, int32_t N, int32_t accumulate, void* stream);
 /* Same contract with dense fp16 weights W[N, K] (lm_head). */
 int32_t b200_op_f16_gemv(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t B,
                          int32_t K, int32_t N, int32_t accumulate, void* stream);

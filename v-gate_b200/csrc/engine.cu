@@ -901,6 +901,37 @@ int32_t b200_op_w4_gemv(const uint32_t* wq, const void* sc, const void* zp, cons
   w.wq = wq; w.sc = (const __half*)sc; w.zp = (const __half*)zp; w.bias = (const __half*)bias; w.K = K; w.N = N; w.G = G;
   return launch_w4_gemv(w, (const __half*)x, ldx, y, ldy, B, accumulate != 0, (cudaStream_t)stream);
 }
+int32_t b200_op_w4_tile(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N, int32_t G, void* wt,
+                        void* sct, void* zpt, void* stream) {
+  return launch_umma_tile_w4(wq, (const __half*)sc, (const __half*)zp, K, N, G, (uint4*)wt, (__half*)sct, (__half*)zpt,
+                             (cudaStream_t)stream);
+}
+int32_t b200_op_w4_gemm_umma(const void* wt, const void* sct, const void* zpt, const void* x, int32_t ldx, float* y,
+                             int32_t ldy, const void* bias, int32_t T, int32_t K, int32_t N, int32_t G,
+                             int32_t accumulate, int32_t n_splits, int64_t part_stride, void* stream) {
+  B200_REQUIRE(T >= 0 && n_splits >= 1, "w4_gemm_umma: T >= 0, n_splits >= 1");
+  B200_REQUIRE(n_splits == 1 || (!accumulate && !bias), "w4_gemm_umma: split-K output is raw partials");
+  if (T == 0) return B200_OK;
+  UmmaW4 w;
+  w.wt = (const uint4*)wt; w.sct = (const __half*)sct; w.zpt = (const __half*)zpt; w.bias = (const __half*)bias;
+  w.K = K; w.N = N; w.G = G;
+  const int nt = umma_pick_nt(T);
+  CUtensorMap mx;
+  int rc = make_tensor_map_f16(&mx, x, T, K, ldx, nt);
+  if (rc) return rc;
+  const int mode = n_splits > 1 ? kUmmaPartialF32 : accumulate ? kUmmaAccumF32 : kUmmaStoreF32;
+  return launch_umma_w4(w, mx, nt, T, y, ldy, mode, n_splits, part_stride, (cudaStream_t)stream);
+}
+int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T, int32_t K,
+                              int32_t N, int32_t accumulate, void* stream) {
+  if (T == 0) return B200_OK;
+  const int nt = umma_pick_nt(T);
+  CUtensorMap mx, mw;
+  int rc = make_tensor_map_f16(&mx, x, T, K, ldx, nt);
+  if (rc) return rc;
+  if ((rc = make_tensor_map_f16(&mw, w, N, K, K, 128))) return rc;
+  return launch_umma_f16(mw, K, N, mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, (cudaStream_t)stream);
+}
 int32_t b200_op_f16_gemv(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t B, int32_t K,
                          int32_t N, int32_t accumulate, void* stream) {
   return launch_f16_gemv((const __half*)w, (const __half*)x, ldx, y, ldy, B, K, N, accumulate != 0, (cudaStream_t)stream);

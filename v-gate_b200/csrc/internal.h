@@ -1,5 +1,6 @@
 // Internal C++ launcher interface shared by the op wrappers and the engine.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
 #include <stdint.h>
@@ -37,6 +38,25 @@ struct W4Linear {
   const __half* bias = nullptr;  // [N] or null
   int K = 0, N = 0, G = 128;
 };
+
+// AWQ linear pre-tiled for the tcgen05 GEMM producers (ops_umma.cu).
+struct UmmaW4 {
+  const uint4* wt = nullptr;     // [N/128][K/64][2][128] uint4
+  const __half* sct = nullptr;   // [N/128][K/G][128]
+  const __half* zpt = nullptr;   // [N/128][K/G][128]  (1024 + zero)
+  const __half* bias = nullptr;
+  int K = 0, N = 0, G = 128;
+};
+enum { kUmmaStoreF32 = 0, kUmmaAccumF32 = 1, kUmmaPartialF32 = 2 };
+
+int launch_umma_tile_w4(const uint32_t* wq, const __half* sc, const __half* zp, int K, int N, int G, uint4* wt,
+                        __half* sct, __half* zpt, cudaStream_t s);
+int make_tensor_map_f16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows);
+int umma_pick_nt(int T);
+int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T, float* y, int ldy, int mode,
+                   int n_splits, int64_t part_stride, cudaStream_t s);
+int launch_umma_f16(const CUtensorMap& map_w, int K, int N, const CUtensorMap& map_x, int nt_sel, int T, float* y,
+                    int ldy, int mode, cudaStream_t s);
 
 int launch_awq_repack(const int32_t* qweight, const int32_t* qzeros, const __half* scales, int K, int N, int G,
                       uint32_t* wq, __half* sc, __half* zp, int row_offset, cudaStream_t s);
