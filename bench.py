@@ -1,0 +1,343 @@
+#!/usr/bin/env python
+"""Headline benchmark: generated tokens/s of the b200 worker engine on Qwen2.5-1.5B W4A16
+(AWQ-shape, random-init), 64 concurrent sequences x 128-token prompts x 256 new tokens, greedy.
+
+One "step" = one full pass of the hot path over one batch: prefill of all prompts + the
+device-resident decode loop until every sequence has `new_tokens` tokens.
+
+  python bench.py [--gpus N --steps K --warmup W]            this repo's CUDA path
+  python bench.py --impl reference ...                        the reference arithmetic on host cores
+                                                              (oracle/: fp32 PyTorch eager of the same model)
+Under torchrun each rank drives one independent replica on its own GPU (weak scaling, no
+collective on the data path: the path shards by request).  Rank 0 prints one JSON line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "generated_tokens_per_second"
+UNIT = "tok/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--preset", default="qwen2.5-1.5b-awq")
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--prompt-len", type=int, default=128)
+    ap.add_argument("--new-tokens", type=int, default=256)
+    ap.add_argument("--gemm-path", type=int, default=0)
+    ap.add_argument("--no-graphs", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample", default="8x128+16", help="reference sample: <batch>x<prompt>+<new tokens>")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"{a.preset} W4A16 random-init, batch {a.batch} x {a.prompt_len}-token prompts, greedy "
+            f"{a.new_tokens} new tokens (prefill + decode)")
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.proc, self.lines, self.gpu = None, [], gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax = float(f[2])
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_prompts(rng, a, vocab):
+    return rng.integers(0, vocab, size=(a.batch, a.prompt_len), dtype=np.int32)
+
+
+# ---------------------------------------------------------------------------------------------------
+def cpu_reference_run(preset, sample, steps=1, warmup=0):
+    """The reference arithmetic (oracle/: fp32 PyTorch eager forward of the same architecture, the CPU
+    path north_star names) on the host cores.  Returns tok/s over `steps` runs of the bounded sample."""
+    import torch
+    from oracle.qwen2 import OracleQwen2, Qwen2Dims
+    from vgate_b200.weights import PRESETS, synthetic_checkpoint
+    b, rest = sample.split("x")
+    p, n = rest.split("+")
+    b, p, n = int(b), int(p), int(n)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    dims = PRESETS[preset]
+    ck = synthetic_checkpoint(dims, seed=0)
+    model = OracleQwen2(Qwen2Dims(**dims.to_dict()), ck, mode="fp32")
+    del ck
+    rng = np.random.default_rng(1)
+    times = []
+    for i in range(warmup + steps):
+        prompts = rng.integers(0, dims.vocab, size=(b, p), dtype=np.int64)
+        t0 = time.perf_counter()
+        model.generate_greedy(prompts, n)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    total = sum(times)
+    return {"value": b * n * len(times) / total, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{b} seqs x {p}-token prompts, {n} new tokens, fp32 PyTorch eager, {len(times)} run(s), "
+                      f"{total / len(times):.1f} s each"}, total / len(times) * 1e3
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb, ms = cpu_reference_run(a.preset, a.cpu_sample, steps=max(1, a.steps), warmup=min(a.warmup, 1))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a), "reference_sample": cb["sample"]},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+def dominant_kernel_roofline(a, dims, hbm_peak, peak_src):
+    """Time the dominant decode kernel (the tcgen05 W4A16 GEMM on the fused gate_up projection) alone with
+    CUDA events on its launch stream, L2 flushed between launches."""
+    import ctypes as C
+    import torch
+    from vgate_b200 import _lib
+    lib = _lib.load()
+    K, N, G, T = dims.hidden, 2 * dims.intermediate, dims.group_size, a.batch
+    rng = np.random.default_rng(0)
+    dev = lambda arr: torch.from_numpy(arr).cuda()
+    ptr = lambda t: C.c_void_p(t.data_ptr())
+    wq = dev(rng.integers(0, 2**31, size=(N, K // 8), dtype=np.int32))
+    sc = dev(np.full((N, K // G), 0.003, dtype=np.float16))
+    zp = dev(np.full((N, K // G), 1032.0, dtype=np.float16))
+    wt = torch.empty(N * K // 8, dtype=torch.int32, device="cuda")
+    sct = torch.empty(N * (K // G), dtype=torch.float16, device="cuda")
+    zpt = torch.empty_like(sct)
+    x = dev(rng.standard_normal((T, K)).astype(np.float16))
+    y = torch.empty((T, N), dtype=torch.float32, device="cuda")
+    st = torch.cuda.Stream()
+    sp = C.c_void_p(st.cuda_stream)
+    _lib.check(lib.b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, ptr(wt), ptr(sct), ptr(zpt), sp))
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+    use_umma = T > 4 and a.gemm_path != 1
+
+    def launch():
+        if use_umma:
+            _lib.check(lib.b200_op_w4_gemm_umma(ptr(wt), ptr(sct), ptr(zpt), ptr(x), K, ptr(y), N, None, T, K, N, G, 0,
+                                                1, 0, sp))
+        else:
+            _lib.check(lib.b200_op_w4_gemv(ptr(wq), ptr(sc), ptr(zp), ptr(x), K, ptr(y), N, None, T, K, N, G, 0, sp))
+
+    times = []
+    with torch.cuda.stream(st):
+        for i in range(13):
+            flush.fill_(i)                      # evict L2 (126 MB) so weights come from HBM
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            launch()
+            e1.record(st)
+            st.synchronize()
+            if i >= 3:
+                times.append(e0.elapsed_time(e1) * 1e-3)
+    t = float(np.mean(times))
+    # algorithmic bytes per launch: packed weights + scales + zeros + activations in + fp32 out
+    alg = N * K / 2 + 2 * N * (K // G) * 2 + T * K * 2 + T * N * 4
+    ach = alg / t / 1e9
+    return {"bound": "hbm", "kernel": ("umma_gemm_kernel<W4> gate_up" if use_umma else "w4_gemv_kernel gate_up")
+            + f" [{T}x{K}]x[{N}x{K}]", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+            "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
+            "avg_launch_us": t * 1e6, "l2": "flushed between launches (256 MiB write)"}
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from vgate_b200.engine import Engine
+    from vgate_b200.weights import PRESETS, synthetic_checkpoint
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    hbm_peak, peak_src = load_peaks()
+    dims = PRESETS[a.preset]
+    ckpt = synthetic_checkpoint(dims, seed=0)
+    max_len = a.prompt_len + a.new_tokens + 16
+    eng = Engine(dims, device=local, max_seqs=max(a.batch, 8), max_model_len=max_len,
+                 max_batch_tokens=max(8192, a.prompt_len), use_cuda_graphs=not a.no_graphs,
+                 gemm_path=a.gemm_path).load_checkpoint(ckpt)
+    del ckpt
+    rng = np.random.default_rng(1000 + rank)          # unique prompts per rank and per step
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(a.warmup):
+        eng.generate_batch(make_prompts(rng, a, dims.vocab), a.new_tokens)
+    st0 = eng.stats()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    barrier()
+    t0 = time.perf_counter()
+    gpu_prefill = gpu_decode = 0.0
+    for _ in range(a.steps):
+        _, _, (tp, td) = eng.generate_batch(make_prompts(rng, a, dims.vocab), a.new_tokens)
+        gpu_prefill += tp
+        gpu_decode += td
+    barrier()
+    wall = time.perf_counter() - t0
+    clk = clocks.stop() if rank == 0 else None
+    st1 = eng.stats()
+
+    # device-timed whole-step time (CUDA events on the engine's stream), max over ranks
+    dev_time = gpu_prefill + gpu_decode
+    tt = torch.tensor([dev_time, wall, gpu_decode, gpu_prefill], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dev_time, wall, gpu_decode_max, gpu_prefill_max = tt.tolist()
+    tokens_per_rank = a.batch * a.new_tokens * a.steps
+    value = world * tokens_per_rank / dev_time
+
+    # ---- e2e: the public API, called the way V-Gate calls it ----
+    # B200Backend.generate([one prompt], sampling_params) from one thread per in-flight request
+    # (vgate/worker_api.py:112, vgate/batcher.py:422): host strings in, host dicts out; tokenisation,
+    # H2D of prompt ids, continuous batching, D2H of every step's sampled ids are all inside the timing.
+    e2e = None
+    if not a.no_e2e:
+        from concurrent.futures import ThreadPoolExecutor
+        from vgate_b200.backend import B200Backend
+        from vgate_b200.tokenizer import ByteTokenizer
+        be = B200Backend()
+        be.engine, be.tokenizer = eng, ByteTokenizer()
+        sp = be.create_sampling_params(0.0, 1.0, a.new_tokens)
+        pool = ThreadPoolExecutor(a.batch)
+
+        def e2e_round():
+            codes = rng.integers(32, 127, size=(a.batch, a.prompt_len), dtype=np.uint8)
+            prompts = [bytes(row).decode("ascii") for row in codes]      # 1 byte = 1 token
+            t_a = time.perf_counter()
+            results = list(pool.map(lambda pr: be.generate([pr], sp)[0], prompts))
+            return time.perf_counter() - t_a, results
+
+        e2e_round()                                       # warm
+        barrier()
+        tot_t, tot_n, tpots = 0.0, 0, []
+        for _ in range(max(1, a.steps)):
+            dt, results = e2e_round()
+            tot_t += dt
+            tot_n += sum(r["num_tokens"] for r in results)
+            tpots += [r["metrics"]["gen_time"] / r["num_tokens"] for r in results]   # vgate/batcher.py:431
+        barrier()
+        pool.shutdown()
+        t_e = torch.tensor([tot_t], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * tot_n / t_e.item(), "unit": UNIT,
+               "h2d_bytes_per_step": int(a.batch * a.prompt_len * 4),       # prompt token ids
+               "d2h_bytes_per_step": int(a.batch * a.new_tokens * 4),       # sampled ids, read back every decode step
+               "tpot_ms_p50": float(np.median(tpots) * 1e3),
+               "path": f"B200Backend.generate([prompt], sp) x {a.batch} concurrent threads (one prompt per call, as "
+                       "vgate/worker_api.py:112 issues them); continuous batching inside the engine"}
+
+    if rank == 0:
+        d_steps = st1["steps_decode"] - st0["steps_decode"]
+        d_bytes = st1["hbm_bytes_decode"] - st0["hbm_bytes_decode"]
+        step_ach = d_bytes / gpu_decode_max / 1e9 if gpu_decode_max > 0 else 0.0
+        roof = dominant_kernel_roofline(a, dims, hbm_peak, peak_src)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": dev_time / a.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f16 (int4 weights, fp16 activations, fp32 accumulate)", "data": "synthetic",
+            "config": {"workload": workload_name(a), "replicas": world, "parallelism": f"dp{world} (one replica per GPU)",
+                       "l2": "per-step working set (weights 1.15 GB + KV) exceeds the 126 MB L2",
+                       "cuda_graphs": not a.no_graphs, "gemm_path": a.gemm_path},
+            "wall_ms_per_step": wall / a.steps * 1e3,
+            "decode": {"tpot_ms_mean": gpu_decode_max / d_steps * 1e3 if d_steps else None,
+                       "steps": d_steps, "tok_per_s": world * a.batch * d_steps / gpu_decode_max if gpu_decode_max else None,
+                       "hbm_gbs": step_ach, "hbm_roofline_frac": step_ach / hbm_peak},
+            "prefill": {"tok_per_s": world * a.batch * a.prompt_len * a.steps / gpu_prefill_max if gpu_prefill_max else None},
+            "roofline": roof,
+            "gpu_launches": int(st1["kernel_launches"] - st0["kernel_launches"]),
+            "clocks": clk,
+        }
+        if e2e is not None:
+            line["e2e"] = e2e
+        if not a.no_cpu_baseline:
+            try:
+                line["cpu_baseline"], _ = cpu_reference_run(a.preset, a.cpu_sample)
+            except Exception as exc:   # the baseline is reported, never required for the GPU number
+                line["cpu_baseline"] = {"error": repr(exc)}
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

@@ -75,6 +75,8 @@ struct LayerWeights {
   DevMem wq[4], sc[4], zp[4];      // 0 qkv, 1 o, 2 gate_up, 3 down
   DevMem bias_qkv, ln1, ln2;
   W4Linear lin[4];
+  DevMem wt[4], sct[4], zpt[4];    // same linears pre-tiled for the tcgen05 GEMM
+  UmmaW4 ulin[4];
 };
 
 struct PendingLinear {             // raw checkpoint tensors waiting for their siblings
@@ -153,8 +155,43 @@ struct b200_engine {
   // =========================================================================================
   size_t layer_kv_offset(int l) const { return (size_t)l * kv_layer_elems; }
 
-  int linear(const W4Linear& w, const __half* x, int ldx, float* y, int ldy, int T, bool accumulate) {
-    return launch_w4_gemv(w, x, ldx, y, ldy, T, accumulate, stream);
+  // Token-count regime switch: the CUDA-core GEMV streams weights at HBM speed for a handful of
+  // rows; from 5 rows up the FHFMA rate binds and the tcgen05 GEMM takes over.
+  bool use_umma(int T) const { return cfg.gemm_path == 2 || (cfg.gemm_path == 0 && T > 4); }
+
+  // TMA descriptors for the (fixed) activation buffers, one per (buffer, token-tile height).
+  std::map<std::pair<const void*, int>, CUtensorMap> tmaps;
+  int get_map(const void* base, int64_t rows, int64_t cols, int box_rows, const CUtensorMap** out) {
+    auto key = std::make_pair(base, box_rows);
+    auto it = tmaps.find(key);
+    if (it == tmaps.end()) {
+      CUtensorMap m;
+      int rc = make_tensor_map_f16(&m, base, rows, cols, cols, box_rows);
+      if (rc) return rc;
+      it = tmaps.emplace(key, m).first;
+    }
+    *out = &it->second;
+    return B200_OK;
+  }
+
+  int linear(const LayerWeights& lw, int i, const __half* x, int64_t x_rows, float* y, int ldy, int T, bool accumulate) {
+    const W4Linear& w = lw.lin[i];
+    if (!use_umma(T)) return launch_w4_gemv(w, x, w.K, y, ldy, T, accumulate, stream);
+    const int nt = umma_pick_nt(T);
+    const CUtensorMap* mx;
+    int rc = get_map(x, x_rows, w.K, nt, &mx);
+    if (rc) return rc;
+    return launch_umma_w4(lw.ulin[i], *mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, 1, 0, stream);
+  }
+
+  int lm_head(const __half* head, int n_rows) {
+    if (!use_umma(n_rows) || V % 128 != 0)
+      return launch_f16_gemv(head, xn_last.as<__half>(), H, logits.as<float>(), V, n_rows, H, V, false, stream);
+    const int nt = umma_pick_nt(n_rows);
+    const CUtensorMap *mx, *mw;
+    int rc;
+    if ((rc = get_map(xn_last.as<__half>(), cfg.max_seqs, H, nt, &mx)) || (rc = get_map(head, V, H, 128, &mw))) return rc;
+    return launch_umma_f16(*mw, H, V, *mx, nt, n_rows, logits.as<float>(), V, kUmmaStoreF32, stream);
   }
 
   // One forward pass over T token rows whose metadata already sits in the d_* buffers; samples one
@@ -168,24 +205,23 @@ struct b200_engine {
       __half* vc = v_cache.as<__half>() + layer_kv_offset(l);
       if ((rc = launch_rmsnorm(h.as<float>(), nullptr, 0, 0, w.ln1.as<__half>(), cfg.rms_eps, nullptr, T, H,
                                xn.as<__half>(), stream))) return rc;
-      if ((rc = linear(w.lin[0], xn.as<__half>(), H, qkv.as<float>(), QKV, T, false))) return rc;
+      if ((rc = linear(w, 0, xn.as<__half>(), Tmax, qkv.as<float>(), QKV, T, false))) return rc;
       if ((rc = launch_rope_kv(qkv.as<float>(), d_pos.as<int32_t>(), d_slot.as<int32_t>(), cos_t.as<float>(),
                                sin_t.as<float>(), T, NH, NKV, qh.as<__half>(), kc, vc, stream))) return rc;
       if ((rc = launch_paged_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
                                   d_btrow.as<int32_t>(), d_ctx.as<int32_t>(), T, NH, NKV, attn.as<__half>(),
                                   stream))) return rc;
-      if ((rc = linear(w.lin[1], attn.as<__half>(), NH * kHeadDim, h.as<float>(), H, T, true))) return rc;
+      if ((rc = linear(w, 1, attn.as<__half>(), Tmax, h.as<float>(), H, T, true))) return rc;
       if ((rc = launch_rmsnorm(h.as<float>(), nullptr, 0, 0, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H,
                                xn.as<__half>(), stream))) return rc;
-      if ((rc = linear(w.lin[2], xn.as<__half>(), H, gu.as<float>(), 2 * I, T, false))) return rc;
+      if ((rc = linear(w, 2, xn.as<__half>(), Tmax, gu.as<float>(), 2 * I, T, false))) return rc;
       if ((rc = launch_swiglu(gu.as<float>(), T, I, act.as<__half>(), stream))) return rc;
-      if ((rc = linear(w.lin[3], act.as<__half>(), I, h.as<float>(), H, T, true))) return rc;
+      if ((rc = linear(w, 3, act.as<__half>(), Tmax, h.as<float>(), H, T, true))) return rc;
     }
     if ((rc = launch_rmsnorm(h.as<float>(), nullptr, 0, 0, final_norm.as<__half>(), cfg.rms_eps, rows, n_rows, H,
                              xn_last.as<__half>(), stream))) return rc;
     const __half* head = cfg.tie_embeddings ? embed.as<__half>() : lm_head_w.as<__half>();
-    if ((rc = launch_f16_gemv(head, xn_last.as<__half>(), H, logits.as<float>(), V, n_rows, H, V, false, stream)))
-      return rc;
+    if ((rc = lm_head(head, n_rows))) return rc;
     if (want_sample) {
       if ((rc = launch_sample(logits.as<float>(), n_rows, V, d_temp.as<float>(), d_topp.as<float>(),
                               d_seed.as<uint32_t>(), d_step.as<int32_t>(), d_next.as<int32_t>(), stream))) return rc;
@@ -566,6 +602,25 @@ int32_t b200_engine_finalize(b200_engine* e) {
     B200_CUDA(cudaMemcpy(e->cos_t.p, cs.data(), cs.size() * 4, cudaMemcpyHostToDevice));
     B200_CUDA(cudaMemcpy(e->sin_t.p, sn.data(), sn.size() * 4, cudaMemcpyHostToDevice));
   }
+  // tiled weight copies for the tcgen05 GEMM
+  if (c.gemm_path != 1) {
+    for (int l = 0; l < e->L; ++l) {
+      LayerWeights& w = e->layers[l];
+      for (int i = 0; i < 4; ++i) {
+        const W4Linear& a = w.lin[i];
+        B200_REQUIRE(a.N % 128 == 0 && a.K % 64 == 0, "tcgen05 GEMM needs out_features % 128 == 0 and in_features % 64 == 0");
+        if ((rc = w.wt[i].alloc((size_t)a.N * a.K / 2)) || (rc = w.sct[i].alloc((size_t)a.N * (a.K / a.G) * 2)) ||
+            (rc = w.zpt[i].alloc((size_t)a.N * (a.K / a.G) * 2)))
+          return rc;
+        if ((rc = launch_umma_tile_w4(a.wq, a.sc, a.zp, a.K, a.N, a.G, w.wt[i].as<uint4>(), w.sct[i].as<__half>(),
+                                      w.zpt[i].as<__half>(), e->stream)))
+          return rc;
+        w.ulin[i].wt = w.wt[i].as<uint4>(); w.ulin[i].sct = w.sct[i].as<__half>(); w.ulin[i].zpt = w.zpt[i].as<__half>();
+        w.ulin[i].bias = a.bias; w.ulin[i].K = a.K; w.ulin[i].N = a.N; w.ulin[i].G = a.G;
+      }
+    }
+    B200_CUDA(cudaStreamSynchronize(e->stream));
+  }
   // KV pool
   e->max_blocks_per_seq = (c.max_model_len + 1 + kBlockTokens - 1) / kBlockTokens + 1;
   const size_t block_bytes_all_layers = (size_t)2 * e->L * e->NKV * kBlockTokens * kHeadDim * 2;
@@ -613,7 +668,7 @@ void b200_engine_destroy(b200_engine* e) {
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (auto& g : e->decode_graphs) cudaGraphExecDestroy(g.second);
   for (auto& w : e->layers) {
-    for (int i = 0; i < 4; ++i) { w.wq[i].release(); w.sc[i].release(); w.zp[i].release(); }
+    for (int i = 0; i < 4; ++i) { w.wq[i].release(); w.sc[i].release(); w.zp[i].release(); w.wt[i].release(); w.sct[i].release(); w.zpt[i].release(); }
     w.bias_qkv.release(); w.ln1.release(); w.ln2.release();
   }
   for (auto& kv : e->pending) { kv.second.qweight.release(); kv.second.qzeros.release(); kv.second.scales.release(); }
