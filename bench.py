@@ -166,21 +166,18 @@ def dominant_kernel_roofline(a, dims, hbm_peak, peak_src):
     wq = dev(rng.integers(0, 2**31, size=(N, K // 8), dtype=np.int32))
     sc = dev(np.full((N, K // G), 0.003, dtype=np.float16))
     zp = dev(np.full((N, K // G), 1032.0, dtype=np.float16))
-    wt = torch.empty(N * K // 8, dtype=torch.int32, device="cuda")
-    sct = torch.empty(N * (K // G), dtype=torch.float16, device="cuda")
-    zpt = torch.empty_like(sct)
+    chunks = torch.empty(lib.b200_op_w4_tile_bytes(K, N, G), dtype=torch.uint8, device="cuda")
     x = dev(rng.standard_normal((T, K)).astype(np.float16))
     y = torch.empty((T, N), dtype=torch.float32, device="cuda")
     st = torch.cuda.Stream()
     sp = C.c_void_p(st.cuda_stream)
-    _lib.check(lib.b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, ptr(wt), ptr(sct), ptr(zpt), sp))
+    _lib.check(lib.b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, ptr(chunks), sp))
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
-    use_umma = T > 4 and a.gemm_path != 1
+    use_umma = a.gemm_path != 1
 
     def launch():
         if use_umma:
-            _lib.check(lib.b200_op_w4_gemm_umma(ptr(wt), ptr(sct), ptr(zpt), ptr(x), K, ptr(y), N, None, T, K, N, G, 0,
-                                                1, 0, sp))
+            _lib.check(lib.b200_op_w4_gemm_umma(ptr(chunks), ptr(x), K, ptr(y), N, None, T, K, N, G, 0, 1, 0, sp))
         else:
             _lib.check(lib.b200_op_w4_gemv(ptr(wq), ptr(sc), ptr(zp), ptr(x), K, ptr(y), N, None, T, K, N, G, 0, sp))
 

@@ -143,17 +143,25 @@ int32_t b200_op_awq_dequant(const uint32_t* wq, const void* sc, const void* zp, 
 int32_t b200_op_w4_gemv(const uint32_t* wq, const void* sc, const void* zp, const void* x, int32_t ldx,
                         float* y, int32_t ldy, const void* bias, int32_t B, int32_t K, int32_t N, int32_t G,
                         int32_t accumulate, void* stream);
-/* Kernel layout -> the tiled layout the tcgen05 GEMM streams: wt uint4 [N/128, K/64, 2, 128],
- * sct / zpt fp16 [N/128, K/G, 128].  N % 128 == 0, K % 64 == 0. */
+/* Kernel layout -> the chunk layout the tcgen05 GEMM streams with TMA bulk copies: for every
+ * (128-row tile, quantisation group) one contiguous chunk [scales fp16 x128][1024+zero fp16 x128]
+ * [packed k tiles].  `chunks` must hold b200_op_w4_tile_bytes(K, N, G) bytes.  N % 128 == 0,
+ * G in {64, 128}. */
 int32_t b200_op_w4_tile(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N, int32_t G,
-                        void* wt, void* sct, void* zpt, void* stream);
+                        void* chunks, void* stream);
+int64_t b200_op_w4_tile_bytes(int32_t K, int32_t N, int32_t G);
 /* tcgen05/TMEM W4A16 GEMM, same result contract as b200_op_w4_gemv for any T (token tiles of up to
- * 256).  n_splits > 1: split-K; y then receives n_splits partial tensors, partial s at
- * y + s * part_stride (bias and accumulate must be 0 / NULL), to be summed by the consumer
- * (b200_op_rmsnorm does). */
-int32_t b200_op_w4_gemm_umma(const void* wt, const void* sct, const void* zpt, const void* x, int32_t ldx,
-                             float* y, int32_t ldy, const void* bias, int32_t T, int32_t K, int32_t N, int32_t G,
-                             int32_t accumulate, int32_t n_splits, int64_t part_stride, void* stream);
+ * 256).  n_splits > 1: split-K over whole quantisation groups; y then receives n_splits partial
+ * tensors, partial s at y + s * part_stride (bias and accumulate must be NULL / 0), to be summed by the
+ * consumer (b200_op_rmsnorm and b200_op_rope_kv do).  n_splits must equal
+ * b200_op_w4_effective_splits(K, G, n_splits). */
+int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, float* y, int32_t ldy,
+                             const void* bias, int32_t T, int32_t K, int32_t N, int32_t G, int32_t accumulate,
+                             int32_t n_splits, int64_t part_stride, void* stream);
+int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits);
+/* Profiling aid: when dev_buf is non-NULL the tcgen05 GEMM writes 8 x uint64 SM-clock stamps per CTA
+ * (entry, set-up done, first tiles ready, last MMA issued, accumulator ready, epilogue done, exit). */
+void b200_debug_umma_trace(void* dev_buf);
 /* tcgen05/TMEM GEMM with dense fp16 weights W[N, K] fed by TMA (lm_head); N % 128 == 0, K % 64 == 0. */
 int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T,
                               int32_t K, int32_t N, int32_t accumulate, void* stream);
@@ -165,11 +173,14 @@ int32_t b200_op_f16_gemv(const void* w, const void* x, int32_t ldx, float* y, in
 int32_t b200_op_rmsnorm(float* h, const float* parts, int32_t n_parts, int64_t part_stride,
                         const void* gamma, float eps, const int32_t* rows, int32_t n_rows, int32_t H,
                         void* xn, void* stream);
-/* qkv fp32 [T, (nh + 2 nkv) * 128] -> q fp16 [T, nh * 128] (rotated), K/V written (K rotated) into the
- * paged cache at slot[t] (= block * 16 + offset, -1 = skip).  cos/sin fp32 [max_pos, 64]. */
-int32_t b200_op_rope_kv(const float* qkv, const int32_t* pos, const int32_t* slot, const float* cos_t,
-                        const float* sin_t, int32_t T, int32_t n_heads, int32_t n_kv, void* q_out,
-                        void* k_cache, void* v_cache, void* stream);
+/* qkv fp32 [T, (nh + 2 nkv) * 128], given as the sum of n_parts >= 1 tensors (part p at
+ * qkv + p * part_stride) plus an optional fp16 bias -> q fp16 [T, nh * 128] (rotated), K/V written
+ * (K rotated) into the paged cache at slot[t] (= block * 16 + offset, -1 = skip).
+ * cos/sin fp32 [max_pos, 64]. */
+int32_t b200_op_rope_kv(const float* qkv, int32_t n_parts, int64_t part_stride, const void* bias,
+                        const int32_t* pos, const int32_t* slot, const float* cos_t, const float* sin_t,
+                        int32_t T, int32_t n_heads, int32_t n_kv, void* q_out, void* k_cache, void* v_cache,
+                        void* stream);
 /* Paged GQA attention, one query row per t: out fp16 [T, nh * 128].  Row t attends to the first
  * ctx_len[t] tokens of block table row bt_row[t].  K/V cache fp16 [n_blocks, n_kv, 16, 128]. */
 int32_t b200_op_paged_attn(const void* q, const void* k_cache, const void* v_cache,

@@ -12,11 +12,17 @@ def lib():
     return _lib.load()
 
 
+_live = []      # device tensors made by dev() stay alive until the next check(): `ptr(dev(x))` in a
+                # call expression must not hand the kernel memory that torch has already recycled
+
+
 def dev(a, dtype=None):
     t = torch.from_numpy(np.ascontiguousarray(a))
     if dtype is not None:
         t = t.to(dtype)
-    return t.cuda()
+    t = t.cuda()
+    _live.append(t)
+    return t
 
 
 def ptr(t):
@@ -30,6 +36,7 @@ def stream():
 def check(code):
     _lib.check(code)
     torch.cuda.synchronize()
+    del _live[:]
 
 
 def repack(qweight, qzeros, scales, G=128):

@@ -154,8 +154,14 @@ def test_rope_kv_write_matches_oracle():
     kc = torch.zeros((n_blocks, n_kv, 16, 128), dtype=torch.float16, device="cuda")
     vc = torch.zeros_like(kc)
     qo = torch.empty((T, n_heads * 128), dtype=torch.float16, device="cuda")
-    check(lib().b200_op_rope_kv(ptr(dev(qkv)), ptr(dev(pos)), ptr(dev(slot)), ptr(dev(cos.numpy())),
-                                ptr(dev(sin.numpy())), T, n_heads, n_kv, ptr(qo), ptr(kc), ptr(vc), stream()))
+    # the row arrives as 3 split-K partials + bias, summed inside the kernel
+    bias = (rng.standard_normal(qkv.shape[1]) * 0.02).astype(np.float16)
+    parts = rng.standard_normal((3,) + qkv.shape).astype(np.float32)
+    parts[2] = qkv - bias.astype(np.float32) - parts[0] - parts[1]
+    qkv = (parts[0] + parts[1]) + parts[2] + bias.astype(np.float32)        # the kernel's summation order
+    check(lib().b200_op_rope_kv(ptr(dev(parts)), 3, qkv.size, ptr(dev(bias)), ptr(dev(pos)), ptr(dev(slot)),
+                                ptr(dev(cos.numpy())), ptr(dev(sin.numpy())), T, n_heads, n_kv, ptr(qo), ptr(kc), ptr(vc),
+                                stream()))
 
     def rot(x, p):                      # x [..., 128]
         c, s = cos[p].numpy().astype(np.float64), sin[p].numpy().astype(np.float64)
@@ -175,7 +181,7 @@ def test_rope_kv_write_matches_oracle():
     written = np.zeros((n_blocks, 16), bool)
     for s_ in slot[slot >= 0]:
         written[s_ // 16, s_ % 16] = True
-    assert not kcn[~written].any() and not vcn[~written].any()
+    assert not kcn.transpose(0, 2, 1, 3)[~written].any() and not vcn.transpose(0, 2, 1, 3)[~written].any()
 
 
 def test_sampler_greedy_and_top_p():

@@ -15,11 +15,11 @@ TOL = 5e-4
 
 
 def tile(wq, sc, zp, K, N, G=128):
-    wt = torch.empty((N // 128) * (K // 64) * 256 * 4, dtype=torch.int32, device="cuda")
-    sct = torch.empty((N // 128) * (K // G) * 128, dtype=torch.float16, device="cuda")
-    zpt = torch.empty_like(sct)
-    check(lib().b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, ptr(wt), ptr(sct), ptr(zpt), stream()))
-    return wt, sct, zpt
+    nbytes = lib().b200_op_w4_tile_bytes(K, N, G)
+    assert nbytes == (N // 128) * (K // G) * (512 + (G // 64) * 4096)
+    chunks = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    check(lib().b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, ptr(chunks), stream()))
+    return chunks
 
 
 @pytest.mark.parametrize("T", [1, 16, 17, 64, 100, 200, 256, 300, 700])
@@ -28,35 +28,36 @@ def test_w4_umma_matches_oracle(T, K, N):
     rng = np.random.default_rng(T * 7 + K)
     qw, qz, sc = random_awq(rng, K, N)
     wq, s, z = repack(qw, qz, sc)
-    wt, sct, zpt = tile(wq, s, z, K, N)
+    ch = tile(wq, s, z, K, N)
     x = rng.standard_normal((T, K)).astype(np.float16)
     bias = (rng.standard_normal(N) * 0.02).astype(np.float16)
     ref = x.astype(np.float64) @ dequantize_awq(qw, qz, sc, 128).astype(np.float64)
     xd, bd = dev(x), dev(bias)
     y = torch.full((T, N), 7.0, dtype=torch.float32, device="cuda")
-    check(lib().b200_op_w4_gemm_umma(ptr(wt), ptr(sct), ptr(zpt), ptr(xd), K, ptr(y), N, ptr(bd), T, K, N, 128, 0, 1, 0,
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(xd), K, ptr(y), N, ptr(bd), T, K, N, 128, 0, 1, 0,
                                      stream()))
     err = np.abs(y.cpu().numpy() - (ref + bias.astype(np.float64))).max()
     assert err < TOL, err
     # residual-accumulate epilogue
     y0 = rng.standard_normal((T, N)).astype(np.float32)
     y = dev(y0)
-    check(lib().b200_op_w4_gemm_umma(ptr(wt), ptr(sct), ptr(zpt), ptr(xd), K, ptr(y), N, None, T, K, N, 128, 1, 1, 0,
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(xd), K, ptr(y), N, None, T, K, N, 128, 1, 1, 0,
                                      stream()))
     assert np.abs(y.cpu().numpy() - (y0 + ref)).max() < TOL
 
 
-@pytest.mark.parametrize("splits", [2, 5, 12])
+@pytest.mark.parametrize("splits", [2, 5, 12, 70])
 def test_w4_umma_split_k_partials_sum_to_result(splits):
     rng = np.random.default_rng(splits)
     K, N, T = 8960, 1536, 64
+    splits = lib().b200_op_w4_effective_splits(K, 128, splits)
     qw, qz, sc = random_awq(rng, K, N)
     wq, s, z = repack(qw, qz, sc)
-    wt, sct, zpt = tile(wq, s, z, K, N)
+    ch = tile(wq, s, z, K, N)
     x = rng.standard_normal((T, K)).astype(np.float16)
     ref = x.astype(np.float64) @ dequantize_awq(qw, qz, sc, 128).astype(np.float64)
     parts = torch.zeros((splits, T, N), dtype=torch.float32, device="cuda")
-    check(lib().b200_op_w4_gemm_umma(ptr(wt), ptr(sct), ptr(zpt), ptr(dev(x)), K, ptr(parts), N, None, T, K, N, 128, 0,
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(dev(x)), K, ptr(parts), N, None, T, K, N, 128, 0,
                                      splits, T * N, stream()))
     got = parts.cpu().numpy().astype(np.float64).sum(0)
     assert np.abs(got - ref).max() < TOL
@@ -68,12 +69,12 @@ def test_umma_equals_gemv_kernel():
     K, N, T = 1536, 2048, 8
     qw, qz, sc = random_awq(rng, K, N)
     wq, s, z = repack(qw, qz, sc)
-    wt, sct, zpt = tile(wq, s, z, K, N)
+    ch = tile(wq, s, z, K, N)
     xd = dev(rng.standard_normal((T, K)).astype(np.float16))
     y1 = torch.empty((T, N), dtype=torch.float32, device="cuda")
     y2 = torch.empty_like(y1)
     check(lib().b200_op_w4_gemv(ptr(wq), ptr(s), ptr(z), ptr(xd), K, ptr(y1), N, None, T, K, N, 128, 0, stream()))
-    check(lib().b200_op_w4_gemm_umma(ptr(wt), ptr(sct), ptr(zpt), ptr(xd), K, ptr(y2), N, None, T, K, N, 128, 0, 1, 0,
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(xd), K, ptr(y2), N, None, T, K, N, 128, 0, 1, 0,
                                      stream()))
     assert (y1 - y2).abs().max().item() < 1e-4
 
@@ -88,3 +89,36 @@ def test_f16_umma_matches_oracle(T):
     check(lib().b200_op_f16_gemm_umma(ptr(dev(w)), ptr(dev(x)), K, ptr(y), N, T, K, N, 0, stream()))
     ref = x.astype(np.float64) @ w.astype(np.float64).T
     assert np.abs(y.cpu().numpy() - ref).max() < TOL
+
+
+def test_w4_umma_group_size_64():
+    rng = np.random.default_rng(64)
+    K, N, T, G = 1536, 256, 33, 64
+    qw, qz, sc = random_awq(rng, K, N, G=G)
+    wq, s, z = repack(qw, qz, sc, G=G)
+    ch = tile(wq, s, z, K, N, G=G)
+    x = rng.standard_normal((T, K)).astype(np.float16)
+    y = torch.empty((T, N), dtype=torch.float32, device="cuda")
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(dev(x)), K, ptr(y), N, None, T, K, N, G, 0, 1, 0, stream()))
+    ref = x.astype(np.float64) @ dequantize_awq(qw, qz, sc, G).astype(np.float64)
+    assert np.abs(y.cpu().numpy() - ref).max() < TOL
+
+
+def test_w4_umma_is_batch_invariant():
+    """A token's output bits do not depend on which other tokens share the launch (tile height,
+    position in the tile) -- the property continuous batching relies on."""
+    rng = np.random.default_rng(11)
+    K, N = 1536, 2048
+    qw, qz, sc = random_awq(rng, K, N)
+    wq, s, z = repack(qw, qz, sc)
+    ch = tile(wq, s, z, K, N)
+    x = rng.standard_normal((300, K)).astype(np.float16)
+    xd = dev(x)
+    outs = {}
+    for T in (1, 5, 64, 300):
+        y = torch.empty((T, N), dtype=torch.float32, device="cuda")
+        check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(xd), K, ptr(y), N, None, T, K, N, 128, 0, 1, 0, stream()))
+        outs[T] = y.cpu().numpy()
+    for T in (5, 64, 300):
+        assert np.array_equal(outs[T][0], outs[1][0])
+    assert np.array_equal(outs[300][:64], outs[64])

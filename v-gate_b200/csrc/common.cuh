@@ -120,4 +120,12 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
                ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// ---- programmatic dependent launch (PDL) ------------------------------------------------------
+// Every kernel of the step starts with pdl_prologue(): it lets the next kernel in the stream begin
+// launching (its set-up and weight prefetch overlap our execution) and then blocks until the
+// upstream kernel's results are visible.  Both are no-ops for a plain launch.
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_prologue() { grid_dep_launch(); grid_dep_wait(); }
+
 }  // namespace b200

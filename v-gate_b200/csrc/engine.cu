@@ -26,6 +26,10 @@ thread_local std::string g_last_error;
 thread_local int64_t g_launch_count = 0;
 
 void set_last_error(const std::string& msg) { g_last_error = msg; }
+bool pdl_enabled() {
+  static const bool on = [] { const char* v = getenv("VGATE_B200_PDL"); return !(v && v[0] == '0'); }();
+  return on;
+}
 int cuda_fail(cudaError_t err, const char* what, const char* file, int line) {
   g_last_error = std::string("CUDA error ") + cudaGetErrorName(err) + " (" + cudaGetErrorString(err) + ") at " +
                  file + ":" + std::to_string(line) + " in " + what;
@@ -44,6 +48,7 @@ __global__ void advance_decode_kernel(int B, const int32_t* __restrict__ next_id
                                       int32_t* __restrict__ ctx, int32_t* __restrict__ n_gen,
                                       const int32_t* __restrict__ bt_row, const int32_t* __restrict__ block_tables,
                                       int bt_stride, int32_t* __restrict__ out_tokens, int out_stride) {
+  pdl_prologue();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B) return;
   const int tok = next_ids[i];
@@ -75,7 +80,7 @@ struct LayerWeights {
   DevMem wq[4], sc[4], zp[4];      // 0 qkv, 1 o, 2 gate_up, 3 down
   DevMem bias_qkv, ln1, ln2;
   W4Linear lin[4];
-  DevMem wt[4], sct[4], zpt[4];    // same linears pre-tiled for the tcgen05 GEMM
+  DevMem chunks[4];                // same linears in the chunk layout the tcgen05 GEMM streams
   UmmaW4 ulin[4];
 };
 
@@ -155,9 +160,10 @@ struct b200_engine {
   // =========================================================================================
   size_t layer_kv_offset(int l) const { return (size_t)l * kv_layer_elems; }
 
-  // Token-count regime switch: the CUDA-core GEMV streams weights at HBM speed for a handful of
-  // rows; from 5 rows up the FHFMA rate binds and the tcgen05 GEMM takes over.
-  bool use_umma(int T) const { return cfg.gemm_path == 2 || (cfg.gemm_path == 0 && T > 4); }
+  // One GEMM kernel family per engine, whatever the token count: a sequence's bits must not depend
+  // on how many other sequences share its step (continuous batching).  gemm_path 1 selects the
+  // CUDA-core GEMV family (small-batch workers), anything else the tcgen05 GEMM.
+  bool use_umma(int T) const { (void)T; return cfg.gemm_path != 1; }
 
   // TMA descriptors for the (fixed) activation buffers, one per (buffer, token-tile height).
   std::map<std::pair<const void*, int>, CUtensorMap> tmaps;
@@ -174,20 +180,35 @@ struct b200_engine {
     return B200_OK;
   }
 
-  int linear(const LayerWeights& lw, int i, const __half* x, int64_t x_rows, float* y, int ldy, int T, bool accumulate) {
+  // Split-K factors per linear (qkv, o, gate_up, down).  They depend on the weight shape only,
+  // never on the token count, so a sequence's arithmetic is the same in every batch it rides in.
+  int splits[4] = {1, 1, 1, 1};
+  int debug_gemv_mask = getenv("VGATE_B200_DEBUG_GEMV_MASK") ? atoi(getenv("VGATE_B200_DEBUG_GEMV_MASK")) : 0;
+  DevMem parts;                                  // fp32 split-K partials [splits][T][N]
+
+  // y (+)= x . W^T.  Returns in *n_parts_out how many partial tensors were written to `parts`
+  // instead (0: the result is already in y).
+  int linear(const LayerWeights& lw, int i, const __half* x, int64_t x_rows, float* y, int ldy, int T, bool accumulate,
+             int* n_parts_out) {
     const W4Linear& w = lw.lin[i];
-    if (!use_umma(T)) return launch_w4_gemv(w, x, w.K, y, ldy, T, accumulate, stream);
-    const int nt = umma_pick_nt(T);
+    *n_parts_out = 0;
+    if (!use_umma(T) || (debug_gemv_mask >> i & 1)) return launch_w4_gemv(w, x, w.K, y, ldy, T, accumulate, stream);
+    const int nt = umma_pick_nt(T, true);
     const CUtensorMap* mx;
     int rc = get_map(x, x_rows, w.K, nt, &mx);
     if (rc) return rc;
+    const int ns = umma_w4_effective_splits(w.K, w.G, splits[i]);
+    if (ns > 1) {
+      *n_parts_out = ns;
+      return launch_umma_w4(lw.ulin[i], *mx, nt, T, parts.as<float>(), w.N, kUmmaPartialF32, ns, (int64_t)T * w.N, stream);
+    }
     return launch_umma_w4(lw.ulin[i], *mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, 1, 0, stream);
   }
 
   int lm_head(const __half* head, int n_rows) {
-    if (!use_umma(n_rows) || V % 128 != 0)
+    if (!use_umma(n_rows) || V % 128 != 0 || (debug_gemv_mask >> 4 & 1))
       return launch_f16_gemv(head, xn_last.as<__half>(), H, logits.as<float>(), V, n_rows, H, V, false, stream);
-    const int nt = umma_pick_nt(n_rows);
+    const int nt = umma_pick_nt(n_rows, false);
     const CUtensorMap *mx, *mw;
     int rc;
     if ((rc = get_map(xn_last.as<__half>(), cfg.max_seqs, H, nt, &mx)) || (rc = get_map(head, V, H, 128, &mw))) return rc;
@@ -199,27 +220,35 @@ struct b200_engine {
   int forward(int T, int n_rows, const int32_t* rows, bool want_sample = true) {
     int rc;
     if ((rc = launch_embed(embed.as<__half>(), d_ids.as<int32_t>(), T, H, h.as<float>(), stream))) return rc;
+    int pend = 0;                 // split-K partials of the previous projection still to be added into h
+    int64_t pend_stride = 0;
     for (int l = 0; l < L; ++l) {
       LayerWeights& w = layers[l];
       __half* kc = k_cache.as<__half>() + layer_kv_offset(l);
       __half* vc = v_cache.as<__half>() + layer_kv_offset(l);
-      if ((rc = launch_rmsnorm(h.as<float>(), nullptr, 0, 0, w.ln1.as<__half>(), cfg.rms_eps, nullptr, T, H,
-                               xn.as<__half>(), stream))) return rc;
-      if ((rc = linear(w, 0, xn.as<__half>(), Tmax, qkv.as<float>(), QKV, T, false))) return rc;
-      if ((rc = launch_rope_kv(qkv.as<float>(), d_pos.as<int32_t>(), d_slot.as<int32_t>(), cos_t.as<float>(),
-                               sin_t.as<float>(), T, NH, NKV, qh.as<__half>(), kc, vc, stream))) return rc;
+      int np = 0;
+      if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, w.ln1.as<__half>(), cfg.rms_eps,
+                               nullptr, T, H, xn.as<__half>(), stream))) return rc;
+      pend = 0;
+      if ((rc = linear(w, 0, xn.as<__half>(), Tmax, qkv.as<float>(), QKV, T, false, &np))) return rc;
+      if ((rc = launch_rope_kv(np ? parts.as<float>() : qkv.as<float>(), np ? np : 1, (int64_t)T * QKV,
+                               np ? w.bias_qkv.as<__half>() : nullptr, d_pos.as<int32_t>(), d_slot.as<int32_t>(),
+                               cos_t.as<float>(), sin_t.as<float>(), T, NH, NKV, qh.as<__half>(), kc, vc, stream))) return rc;
       if ((rc = launch_paged_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
                                   d_btrow.as<int32_t>(), d_ctx.as<int32_t>(), T, NH, NKV, attn.as<__half>(),
                                   stream))) return rc;
-      if ((rc = linear(w, 1, attn.as<__half>(), Tmax, h.as<float>(), H, T, true))) return rc;
-      if ((rc = launch_rmsnorm(h.as<float>(), nullptr, 0, 0, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H,
-                               xn.as<__half>(), stream))) return rc;
-      if ((rc = linear(w, 2, xn.as<__half>(), Tmax, gu.as<float>(), 2 * I, T, false))) return rc;
+      if ((rc = linear(w, 1, attn.as<__half>(), Tmax, h.as<float>(), H, T, true, &pend))) return rc;
+      pend_stride = (int64_t)T * H;
+      if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps,
+                               nullptr, T, H, xn.as<__half>(), stream))) return rc;
+      pend = 0;
+      if ((rc = linear(w, 2, xn.as<__half>(), Tmax, gu.as<float>(), 2 * I, T, false, &np))) return rc;
+      if (np) { set_last_error("gate_up projection must not be split"); return B200_ERR_STATE; }
       if ((rc = launch_swiglu(gu.as<float>(), T, I, act.as<__half>(), stream))) return rc;
-      if ((rc = linear(w, 3, act.as<__half>(), Tmax, h.as<float>(), H, T, true))) return rc;
+      if ((rc = linear(w, 3, act.as<__half>(), Tmax, h.as<float>(), H, T, true, &pend))) return rc;
     }
-    if ((rc = launch_rmsnorm(h.as<float>(), nullptr, 0, 0, final_norm.as<__half>(), cfg.rms_eps, rows, n_rows, H,
-                             xn_last.as<__half>(), stream))) return rc;
+    if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, final_norm.as<__half>(), cfg.rms_eps,
+                             rows, n_rows, H, xn_last.as<__half>(), stream))) return rc;
     const __half* head = cfg.tie_embeddings ? embed.as<__half>() : lm_head_w.as<__half>();
     if ((rc = lm_head(head, n_rows))) return rc;
     if (want_sample) {
@@ -608,14 +637,12 @@ int32_t b200_engine_finalize(b200_engine* e) {
       LayerWeights& w = e->layers[l];
       for (int i = 0; i < 4; ++i) {
         const W4Linear& a = w.lin[i];
-        B200_REQUIRE(a.N % 128 == 0 && a.K % 64 == 0, "tcgen05 GEMM needs out_features % 128 == 0 and in_features % 64 == 0");
-        if ((rc = w.wt[i].alloc((size_t)a.N * a.K / 2)) || (rc = w.sct[i].alloc((size_t)a.N * (a.K / a.G) * 2)) ||
-            (rc = w.zpt[i].alloc((size_t)a.N * (a.K / a.G) * 2)))
+        B200_REQUIRE(a.N % 128 == 0 && (a.G == 64 || a.G == 128),
+                     "tcgen05 GEMM needs out_features % 128 == 0 and AWQ group size 64 or 128");
+        if ((rc = w.chunks[i].alloc(umma_w4_chunk_bytes(a.K, a.N, a.G)))) return rc;
+        if ((rc = launch_umma_tile_w4(a.wq, a.sc, a.zp, a.K, a.N, a.G, w.chunks[i].as<unsigned char>(), e->stream)))
           return rc;
-        if ((rc = launch_umma_tile_w4(a.wq, a.sc, a.zp, a.K, a.N, a.G, w.wt[i].as<uint4>(), w.sct[i].as<__half>(),
-                                      w.zpt[i].as<__half>(), e->stream)))
-          return rc;
-        w.ulin[i].wt = w.wt[i].as<uint4>(); w.ulin[i].sct = w.sct[i].as<__half>(); w.ulin[i].zpt = w.zpt[i].as<__half>();
+        w.ulin[i].chunks = w.chunks[i].as<unsigned char>();
         w.ulin[i].bias = a.bias; w.ulin[i].K = a.K; w.ulin[i].N = a.N; w.ulin[i].G = a.G;
       }
     }
@@ -645,6 +672,26 @@ int32_t b200_engine_finalize(b200_engine* e) {
       (rc = e->d_temp.alloc(S * 4)) || (rc = e->d_topp.alloc(S * 4)) || (rc = e->d_seed.alloc(S * 4)) ||
       (rc = e->d_step.alloc(S * 4)) || (rc = e->d_next.alloc(S * 4)) || (rc = e->d_ngen.alloc(S * 4)))
     return rc;
+  // split-K factors: enough CTAs to engage every SM's dequant throughput on the skinny projections
+  // (o, down: 12 row tiles), bounded so partial-sum traffic stays small next to the weight bytes.
+  size_t part_elems = 16;
+  if (c.gemm_path != 1) {
+    const char* ov = getenv("VGATE_B200_SPLITS");      // "qkv,o,gate_up,down" override for tuning
+    int o4[4] = {0, 0, 0, 0};
+    if (ov) sscanf(ov, "%d,%d,%d,%d", &o4[0], &o4[1], &o4[2], &o4[3]);
+    for (int i = 0; i < 4; ++i) {
+      const W4Linear& a = e->layers[0].lin[i];
+      const int tiles = a.N / 128, KG = a.K / a.G;
+      int sp = std::max(1, std::min((148 + tiles / 2) / tiles, KG / 2));
+      if (a.K <= 2048) sp = std::min(sp, 4);
+      if (i == 2) sp = 1;                               // gate_up feeds SwiGLU directly
+      if (o4[i] > 0 && i != 2) sp = o4[i];
+      e->splits[i] = sp;
+      const int eff = umma_w4_effective_splits(a.K, a.G, sp);
+      if (eff > 1) part_elems = std::max(part_elems, (size_t)eff * T * a.N);
+    }
+  }
+  if ((rc = e->parts.alloc(part_elems * 4))) return rc;
   B200_CUDA(cudaDeviceSynchronize());
   e->finalized = true;
   e->worker = std::thread([e] { e->scheduler_loop(); });
@@ -668,14 +715,14 @@ void b200_engine_destroy(b200_engine* e) {
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (auto& g : e->decode_graphs) cudaGraphExecDestroy(g.second);
   for (auto& w : e->layers) {
-    for (int i = 0; i < 4; ++i) { w.wq[i].release(); w.sc[i].release(); w.zp[i].release(); w.wt[i].release(); w.sct[i].release(); w.zpt[i].release(); }
+    for (int i = 0; i < 4; ++i) { w.wq[i].release(); w.sc[i].release(); w.zp[i].release(); w.chunks[i].release(); }
     w.bias_qkv.release(); w.ln1.release(); w.ln2.release();
   }
   for (auto& kv : e->pending) { kv.second.qweight.release(); kv.second.qzeros.release(); kv.second.scales.release(); }
   DevMem* all[] = {&e->embed, &e->lm_head_w, &e->final_norm, &e->cos_t, &e->sin_t, &e->k_cache, &e->v_cache, &e->h,
                    &e->xn, &e->qkv, &e->qh, &e->attn, &e->gu, &e->act, &e->xn_last, &e->logits, &e->d_ids, &e->d_pos,
                    &e->d_slot, &e->d_btrow, &e->d_ctx, &e->d_lastrows, &e->d_bt, &e->d_temp, &e->d_topp, &e->d_seed,
-                   &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens};
+                   &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens, &e->parts};
   for (DevMem* m : all) m->release();
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
@@ -867,7 +914,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
     B200_CUDA(cudaStreamSynchronize(s));
   }
   auto advance = [&]() -> int {
-    advance_decode_kernel<<<(n_seqs + 127) / 128, 128, 0, s>>>(
+    launch_k(advance_decode_kernel, dim3((n_seqs + 127) / 128), dim3(128), 0, s,
         n_seqs, e->d_next.as<int32_t>(), e->d_ids.as<int32_t>(), e->d_pos.as<int32_t>(), e->d_slot.as<int32_t>(),
         e->d_ctx.as<int32_t>(), e->d_ngen.as<int32_t>(), e->d_btrow.as<int32_t>(), e->d_bt.as<int32_t>(),
         e->max_blocks_per_seq, e->d_out_tokens.as<int32_t>(), max_tokens);
@@ -956,31 +1003,40 @@ int32_t b200_op_w4_gemv(const uint32_t* wq, const void* sc, const void* zp, cons
   w.wq = wq; w.sc = (const __half*)sc; w.zp = (const __half*)zp; w.bias = (const __half*)bias; w.K = K; w.N = N; w.G = G;
   return launch_w4_gemv(w, (const __half*)x, ldx, y, ldy, B, accumulate != 0, (cudaStream_t)stream);
 }
-int32_t b200_op_w4_tile(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N, int32_t G, void* wt,
-                        void* sct, void* zpt, void* stream) {
-  return launch_umma_tile_w4(wq, (const __half*)sc, (const __half*)zp, K, N, G, (uint4*)wt, (__half*)sct, (__half*)zpt,
-                             (cudaStream_t)stream);
+int32_t b200_op_w4_tile(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N, int32_t G, void* chunks,
+                        void* stream) {
+  return launch_umma_tile_w4(wq, (const __half*)sc, (const __half*)zp, K, N, G, (unsigned char*)chunks, (cudaStream_t)stream);
 }
-int32_t b200_op_w4_gemm_umma(const void* wt, const void* sct, const void* zpt, const void* x, int32_t ldx, float* y,
-                             int32_t ldy, const void* bias, int32_t T, int32_t K, int32_t N, int32_t G,
-                             int32_t accumulate, int32_t n_splits, int64_t part_stride, void* stream) {
+int64_t b200_op_w4_tile_bytes(int32_t K, int32_t N, int32_t G) {
+  if (K <= 0 || N <= 0 || N % 128 != 0 || (G != 64 && G != 128) || K % G != 0) return B200_ERR_INVALID;
+  return (int64_t)umma_w4_chunk_bytes(K, N, G);
+}
+int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, float* y, int32_t ldy, const void* bias,
+                             int32_t T, int32_t K, int32_t N, int32_t G, int32_t accumulate, int32_t n_splits,
+                             int64_t part_stride, void* stream) {
   B200_REQUIRE(T >= 0 && n_splits >= 1, "w4_gemm_umma: T >= 0, n_splits >= 1");
   B200_REQUIRE(n_splits == 1 || (!accumulate && !bias), "w4_gemm_umma: split-K output is raw partials");
+  B200_REQUIRE(n_splits == umma_w4_effective_splits(K, G, n_splits), "w4_gemm_umma: n_splits must divide the groups evenly enough (use b200_op_w4_effective_splits)");
   if (T == 0) return B200_OK;
   UmmaW4 w;
-  w.wt = (const uint4*)wt; w.sct = (const __half*)sct; w.zpt = (const __half*)zpt; w.bias = (const __half*)bias;
-  w.K = K; w.N = N; w.G = G;
-  const int nt = umma_pick_nt(T);
+  w.chunks = (const unsigned char*)chunks; w.bias = (const __half*)bias; w.K = K; w.N = N; w.G = G;
+  const int nt = umma_pick_nt(T, true);
   CUtensorMap mx;
-  int rc = make_tensor_map_f16(&mx, x, T, K, ldx, nt);
+  const char* xr = getenv("VGATE_B200_DEBUG_XROWS");     // debug: map more rows than T (stale rows, as in the engine)
+  int rc = make_tensor_map_f16(&mx, x, xr ? atoi(xr) : T, K, ldx, nt);
   if (rc) return rc;
   const int mode = n_splits > 1 ? kUmmaPartialF32 : accumulate ? kUmmaAccumF32 : kUmmaStoreF32;
   return launch_umma_w4(w, mx, nt, T, y, ldy, mode, n_splits, part_stride, (cudaStream_t)stream);
 }
+void b200_debug_umma_trace(void* dev_buf) { umma_set_trace((unsigned long long*)dev_buf); }
+int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits) {
+  if (K <= 0 || G <= 0 || K % G != 0 || n_splits < 1) return B200_ERR_INVALID;
+  return umma_w4_effective_splits(K, G, n_splits);
+}
 int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T, int32_t K,
                               int32_t N, int32_t accumulate, void* stream) {
   if (T == 0) return B200_OK;
-  const int nt = umma_pick_nt(T);
+  const int nt = umma_pick_nt(T, false);
   CUtensorMap mx, mw;
   int rc = make_tensor_map_f16(&mx, x, T, K, ldx, nt);
   if (rc) return rc;
@@ -996,10 +1052,11 @@ int32_t b200_op_rmsnorm(float* h, const float* parts, int32_t n_parts, int64_t p
   return launch_rmsnorm(h, parts, n_parts, part_stride, (const __half*)gamma, eps, rows, n_rows, H, (__half*)xn,
                         (cudaStream_t)stream);
 }
-int32_t b200_op_rope_kv(const float* qkv, const int32_t* pos, const int32_t* slot, const float* cos_t, const float* sin_t,
-                        int32_t T, int32_t n_heads, int32_t n_kv, void* q_out, void* k_cache, void* v_cache, void* stream) {
-  return launch_rope_kv(qkv, pos, slot, cos_t, sin_t, T, n_heads, n_kv, (__half*)q_out, (__half*)k_cache, (__half*)v_cache,
-                        (cudaStream_t)stream);
+int32_t b200_op_rope_kv(const float* qkv, int32_t n_parts, int64_t part_stride, const void* bias, const int32_t* pos,
+                        const int32_t* slot, const float* cos_t, const float* sin_t, int32_t T, int32_t n_heads,
+                        int32_t n_kv, void* q_out, void* k_cache, void* v_cache, void* stream) {
+  return launch_rope_kv(qkv, n_parts, part_stride, (const __half*)bias, pos, slot, cos_t, sin_t, T, n_heads, n_kv,
+                        (__half*)q_out, (__half*)k_cache, (__half*)v_cache, (cudaStream_t)stream);
 }
 int32_t b200_op_paged_attn(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_tables,
                            int32_t bt_stride, const int32_t* bt_row, const int32_t* ctx_len, int32_t T, int32_t n_heads,

@@ -30,6 +30,22 @@ int cuda_fail(cudaError_t err, const char* what, const char* file, int line);
 // Every launcher returns B200_OK or an error code and bumps the launch counter.
 extern thread_local int64_t g_launch_count;
 
+// Kernel launch with the programmatic-stream-serialization attribute (PDL) unless disabled
+// (VGATE_B200_PDL=0): the kernel may start while its predecessor drains; kernels order themselves
+// with griddepcontrol.wait (common.cuh pdl_prologue).
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // AWQ linear in kernel layout (see b200_op_awq_repack).
 struct W4Linear {
   const uint32_t* wq = nullptr;  // [N, K/8]
@@ -41,18 +57,19 @@ struct W4Linear {
 
 // AWQ linear pre-tiled for the tcgen05 GEMM producers (ops_umma.cu).
 struct UmmaW4 {
-  const uint4* wt = nullptr;     // [N/128][K/64][2][128] uint4
-  const __half* sct = nullptr;   // [N/128][K/G][128]
-  const __half* zpt = nullptr;   // [N/128][K/G][128]  (1024 + zero)
+  const unsigned char* chunks = nullptr;   // [N/128][K/G] chunks: scales, zeros, packed k tiles (see ops_umma.cu)
   const __half* bias = nullptr;
   int K = 0, N = 0, G = 128;
 };
 enum { kUmmaStoreF32 = 0, kUmmaAccumF32 = 1, kUmmaPartialF32 = 2 };
 
-int launch_umma_tile_w4(const uint32_t* wq, const __half* sc, const __half* zp, int K, int N, int G, uint4* wt,
-                        __half* sct, __half* zpt, cudaStream_t s);
+size_t umma_w4_chunk_bytes(int K, int N, int G);
+int umma_w4_effective_splits(int K, int G, int n_splits);
+int launch_umma_tile_w4(const uint32_t* wq, const __half* sc, const __half* zp, int K, int N, int G,
+                        unsigned char* chunks, cudaStream_t s);
 int make_tensor_map_f16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows);
-int umma_pick_nt(int T);
+int umma_pick_nt(int T, bool w4);
+void umma_set_trace(unsigned long long* dev_buf);
 int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T, float* y, int ldy, int mode,
                    int n_splits, int64_t part_stride, cudaStream_t s);
 int launch_umma_f16(const CUtensorMap& map_w, int K, int N, const CUtensorMap& map_x, int nt_sel, int T, float* y,
@@ -68,7 +85,7 @@ int launch_f16_gemv(const __half* w, const __half* x, int ldx, float* y, int ldy
                     bool accumulate, cudaStream_t s);
 int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_stride, const __half* gamma, float eps,
                    const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s);
-int launch_rope_kv(const float* qkv, const int32_t* pos, const int32_t* slot, const float* cos_t,
+int launch_rope_kv(const float* qkv, int n_parts, int64_t part_stride, const __half* bias, const int32_t* pos, const int32_t* slot, const float* cos_t,
                    const float* sin_t, int T, int n_heads, int n_kv, __half* q_out, __half* k_cache,
                    __half* v_cache, cudaStream_t s);
 int launch_paged_attn(const __half* q, const __half* k_cache, const __half* v_cache, const int32_t* block_tables,

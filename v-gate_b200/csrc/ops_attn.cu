@@ -36,6 +36,7 @@ paged_attn_kernel(const __half* __restrict__ q, const __half* __restrict__ k_cac
                   const int32_t* __restrict__ ctx_len, int n_heads, int n_kv, __half* __restrict__ out) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = AttnSmem<GQ>;
+  pdl_prologue();
   const int j = blockIdx.x, t = blockIdx.y, tid = threadIdx.x;
   const int len = ctx_len[t];
   __half* orow = out + ((size_t)t * n_heads + (size_t)j * GQ) * kHeadDim;
@@ -190,8 +191,8 @@ static int launch_gq(const __half* q, const __half* k_cache, const __half* v_cac
     configured = true;
   }
   dim3 grid(n_kv, T);
-  kern<<<grid, kAttnThreads, AttnSmem<GQ>::kBytes, s>>>(q, k_cache, v_cache, block_tables, bt_stride, bt_row, ctx_len,
-                                                        n_heads, n_kv, out);
+  launch_k(kern, grid, dim3(kAttnThreads), AttnSmem<GQ>::kBytes, s, q, k_cache, v_cache, block_tables, bt_stride, bt_row,
+           ctx_len, n_heads, n_kv, out);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;

@@ -81,6 +81,7 @@ int launch_awq_dequant(const uint32_t* wq, const __half* sc, const __half* zp, i
 // Embedding gather into the fp32 residual stream.
 __global__ void embed_kernel(const __half* __restrict__ table, const int32_t* __restrict__ ids, int H,
                              float* __restrict__ h) {
+  pdl_prologue();
   const int t = blockIdx.x;
   const __half* row = table + (size_t)ids[t] * H;
   for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
@@ -100,7 +101,7 @@ __global__ void embed_kernel(const __half* __restrict__ table, const int32_t* __
 int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s) {
   B200_REQUIRE(H % 8 == 0, "embed: H % 8");
   if (T == 0) return B200_OK;
-  embed_kernel<<<T, 192, 0, s>>>(table, ids, H, h);
+  launch_k(embed_kernel, dim3(T), dim3(192), 0, s, table, ids, H, h);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -118,6 +119,7 @@ __global__ void __launch_bounds__(kNormThreads)
 rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_parts, int64_t part_stride,
                const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows, int H,
                __half* __restrict__ xn) {
+  pdl_prologue();
   const int r = blockIdx.x;
   const int row = rows ? rows[r] : r;
   float4 v[kNormMaxPerThread];
@@ -164,7 +166,7 @@ int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_strid
                    const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s) {
   B200_REQUIRE(H % 4 == 0 && H <= kNormThreads * 4 * kNormMaxPerThread, "rmsnorm: H % 4 == 0 && H <= 8192");
   if (n_rows == 0) return B200_OK;
-  rmsnorm_kernel<<<n_rows, kNormThreads, 0, s>>>(h, parts, n_parts, part_stride, gamma, eps, rows, H, xn);
+  launch_k(rmsnorm_kernel, dim3(n_rows), dim3(kNormThreads), 0, s, h, parts, n_parts, part_stride, gamma, eps, rows, H, xn);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -173,10 +175,13 @@ int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_strid
 // ---------------------------------------------------------------------------------------------
 // RoPE (neox: rotate halves, vLLM qwen2.py:181 get_rope) fused with the paged KV-cache write.
 // One CTA per token; one thread per (head, i < 64) pair.  fp32 in, one rounding to fp16 out.
-__global__ void rope_kv_kernel(const float* __restrict__ qkv, const int32_t* __restrict__ pos,
+// The qkv row may arrive as n_parts split-K partial tensors (summed here in fixed order, plus bias).
+__global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_parts, int64_t part_stride,
+                               const __half* __restrict__ bias, const int32_t* __restrict__ pos,
                                const int32_t* __restrict__ slot, const float* __restrict__ cos_t,
                                const float* __restrict__ sin_t, int n_heads, int n_kv, __half* __restrict__ q_out,
                                __half* __restrict__ k_cache, __half* __restrict__ v_cache) {
+  pdl_prologue();
   const int t = blockIdx.x;
   const int p = pos[t];
   const int sl = slot[t];
@@ -184,7 +189,15 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, const int32_t* __r
   const float* row = qkv + (size_t)t * total_heads * kHeadDim;
   for (int idx = threadIdx.x; idx < total_heads * 64; idx += blockDim.x) {
     const int head = idx >> 6, i = idx & 63;
-    const float x1 = row[head * kHeadDim + i], x2 = row[head * kHeadDim + i + 64];
+    float x1 = row[head * kHeadDim + i], x2 = row[head * kHeadDim + i + 64];
+    for (int pp = 1; pp < n_parts; ++pp) {
+      x1 += row[pp * part_stride + head * kHeadDim + i];
+      x2 += row[pp * part_stride + head * kHeadDim + i + 64];
+    }
+    if (bias) {
+      x1 += __half2float(bias[head * kHeadDim + i]);
+      x2 += __half2float(bias[head * kHeadDim + i + 64]);
+    }
     if (head < n_heads) {
       const float c = cos_t[(size_t)p * 64 + i], sn = sin_t[(size_t)p * 64 + i];
       __half* o = q_out + ((size_t)t * n_heads + head) * kHeadDim;
@@ -208,11 +221,13 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, const int32_t* __r
   }
 }
 
-int launch_rope_kv(const float* qkv, const int32_t* pos, const int32_t* slot, const float* cos_t,
-                   const float* sin_t, int T, int n_heads, int n_kv, __half* q_out, __half* k_cache,
-                   __half* v_cache, cudaStream_t s) {
+int launch_rope_kv(const float* qkv, int n_parts, int64_t part_stride, const __half* bias, const int32_t* pos,
+                   const int32_t* slot, const float* cos_t, const float* sin_t, int T, int n_heads, int n_kv,
+                   __half* q_out, __half* k_cache, __half* v_cache, cudaStream_t s) {
+  B200_REQUIRE(n_parts >= 1, "rope_kv: n_parts >= 1");
   if (T == 0) return B200_OK;
-  rope_kv_kernel<<<T, 256, 0, s>>>(qkv, pos, slot, cos_t, sin_t, n_heads, n_kv, q_out, k_cache, v_cache);
+  launch_k(rope_kv_kernel, dim3(T), dim3(256), 0, s, qkv, n_parts, part_stride, bias, pos, slot, cos_t, sin_t, n_heads,
+           n_kv, q_out, k_cache, v_cache);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -221,6 +236,7 @@ int launch_rope_kv(const float* qkv, const int32_t* pos, const int32_t* slot, co
 // ---------------------------------------------------------------------------------------------
 // SwiGLU: act = fp16(silu(gate) * up), gate|up fp32 (vLLM qwen2.py:106-111 SiluAndMul).
 __global__ void swiglu_kernel(const float* __restrict__ gu, int I, __half* __restrict__ act) {
+  pdl_prologue();
   const int t = blockIdx.y;
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i >= I) return;
@@ -237,7 +253,7 @@ int launch_swiglu(const float* gu, int T, int I, __half* act, cudaStream_t s) {
   B200_REQUIRE(I % 4 == 0, "swiglu: I % 4");
   if (T == 0) return B200_OK;
   dim3 grid((I / 4 + 255) / 256, T);
-  swiglu_kernel<<<grid, 256, 0, s>>>(gu, I, act);
+  launch_k(swiglu_kernel, grid, dim3(256), 0, s, gu, I, act);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;

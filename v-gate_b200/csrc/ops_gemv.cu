@@ -16,6 +16,7 @@ __global__ void __launch_bounds__(kGemvWarps * 32)
 w4_gemv_kernel(const uint32_t* __restrict__ wq, const __half* __restrict__ sc, const __half* __restrict__ zp,
                const __half* __restrict__ bias, const __half* __restrict__ x, int ldx, float* __restrict__ y,
                int ldy, int B, int K, int N, int G, int accumulate) {
+  pdl_prologue();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = blockIdx.x * kGemvWarps + warp;
   if (n >= N) return;
@@ -74,7 +75,7 @@ int launch_w4_gemv(const W4Linear& w, const __half* x, int ldx, float* y, int ld
   const int grid = (w.N + kGemvWarps - 1) / kGemvWarps;
   const int threads = kGemvWarps * 32;
 #define LAUNCH(BT) \
-  w4_gemv_kernel<BT><<<grid, threads, 0, s>>>(w.wq, w.sc, w.zp, w.bias, x, ldx, y, ldy, B, w.K, w.N, w.G, accumulate ? 1 : 0)
+  launch_k(w4_gemv_kernel<BT>, dim3(grid), dim3(threads), 0, s, w.wq, w.sc, w.zp, w.bias, x, ldx, y, ldy, B, w.K, w.N, w.G, accumulate ? 1 : 0)
   if (B == 1) LAUNCH(1);
   else if (B == 2) LAUNCH(2);
   else if (B <= 4) LAUNCH(4);
@@ -90,6 +91,7 @@ template <int BT>
 __global__ void __launch_bounds__(kGemvWarps * 32)
 f16_gemv_kernel(const __half* __restrict__ w, const __half* __restrict__ x, int ldx, float* __restrict__ y, int ldy,
                 int B, int K, int N, int accumulate) {
+  pdl_prologue();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = blockIdx.x * kGemvWarps + warp;
   if (n >= N) return;
@@ -128,7 +130,7 @@ int launch_f16_gemv(const __half* w, const __half* x, int ldx, float* y, int ldy
   if (B == 0) return B200_OK;
   const int grid = (N + kGemvWarps - 1) / kGemvWarps;
   const int threads = kGemvWarps * 32;
-#define LAUNCH(BT) f16_gemv_kernel<BT><<<grid, threads, 0, s>>>(w, x, ldx, y, ldy, B, K, N, accumulate ? 1 : 0)
+#define LAUNCH(BT) launch_k(f16_gemv_kernel<BT>, dim3(grid), dim3(threads), 0, s, w, x, ldx, y, ldy, B, K, N, accumulate ? 1 : 0)
   if (B == 1) LAUNCH(1);
   else if (B == 2) LAUNCH(2);
   else if (B <= 4) LAUNCH(4);

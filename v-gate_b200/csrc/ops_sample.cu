@@ -65,6 +65,7 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   __shared__ unsigned long long hist[256];
   __shared__ unsigned long long s_above, s_target;
   __shared__ int s_bin;
+  pdl_prologue();
   const int r = blockIdx.x, tid = threadIdx.x;
   const float* l = logits + (size_t)r * V;
   const float temp = temperature ? temperature[r] : 0.f;
@@ -161,7 +162,7 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
 int launch_sample(const float* logits, int B, int V, const float* temperature, const float* top_p,
                   const uint32_t* seed, const int32_t* step, int32_t* out, cudaStream_t s) {
   if (B == 0) return B200_OK;
-  sample_kernel<<<B, kSampleThreads, 0, s>>>(logits, V, temperature, top_p, seed, step, out);
+  launch_k(sample_kernel, dim3(B), dim3(kSampleThreads), 0, s, logits, V, temperature, top_p, seed, step, out);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
