@@ -171,7 +171,7 @@ def dominant_kernel_roofline(a, dims, hbm_peak, peak_src):
     y = torch.empty((T, N), dtype=torch.float32, device="cuda")
     st = torch.cuda.Stream()
     sp = C.c_void_p(st.cuda_stream)
-    _lib.check(lib.b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, ptr(chunks), sp))
+    _lib.check(lib.b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, 0, ptr(chunks), sp))
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
     use_umma = a.gemm_path != 1
 

@@ -146,17 +146,20 @@ int32_t b200_op_w4_gemv(const uint32_t* wq, const void* sc, const void* zp, cons
 /* Kernel layout -> the chunk layout the tcgen05 GEMM streams with TMA bulk copies: for every
  * (128-row tile, quantisation group) one contiguous chunk [scales fp16 x128][1024+zero fp16 x128]
  * [packed k tiles].  `chunks` must hold b200_op_w4_tile_bytes(K, N, G) bytes.  N % 128 == 0,
- * G in {64, 128}. */
+ * G in {64, 128}.  pair_rows = N / 2 (a multiple of 64) lays a fused [gate; up] matrix out so that
+ * every tile holds 64 gate rows and the 64 matching up rows (needed by the SwiGLU epilogue); 0 = plain. */
 int32_t b200_op_w4_tile(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N, int32_t G,
-                        void* chunks, void* stream);
+                        int32_t pair_rows, void* chunks, void* stream);
 int64_t b200_op_w4_tile_bytes(int32_t K, int32_t N, int32_t G);
 /* tcgen05/TMEM W4A16 GEMM, same result contract as b200_op_w4_gemv for any T (token tiles of up to
- * 256).  n_splits > 1: split-K over whole quantisation groups; y then receives n_splits partial
- * tensors, partial s at y + s * part_stride (bias and accumulate must be NULL / 0), to be summed by the
- * consumer (b200_op_rmsnorm and b200_op_rope_kv do).  n_splits must equal
+ * 128).  epilogue: 0 store (+bias), 1 accumulate into y, 2 fused SwiGLU -- chunks tiled with
+ * pair_rows = N / 2, y is then an fp16 matrix act[T, N / 2] = silu(gate) * up with row stride ldy halves.
+ * n_splits > 1: split-K over whole quantisation groups; y then receives n_splits partial tensors,
+ * partial s at y + s * part_stride (bias NULL, epilogue 0), to be summed by the consumer
+ * (b200_op_rmsnorm and b200_op_rope_kv do).  n_splits must equal
  * b200_op_w4_effective_splits(K, G, n_splits). */
 int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, float* y, int32_t ldy,
-                             const void* bias, int32_t T, int32_t K, int32_t N, int32_t G, int32_t accumulate,
+                             const void* bias, int32_t T, int32_t K, int32_t N, int32_t G, int32_t epilogue,
                              int32_t n_splits, int64_t part_stride, void* stream);
 int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits);
 /* Profiling aid: when dev_buf is non-NULL the tcgen05 GEMM writes 8 x uint64 SM-clock stamps per CTA

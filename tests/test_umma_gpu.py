@@ -14,11 +14,11 @@ from tests.gpu_util import lib, dev, ptr, stream, check, repack, random_awq  # n
 TOL = 5e-4
 
 
-def tile(wq, sc, zp, K, N, G=128):
+def tile(wq, sc, zp, K, N, G=128, pair_rows=0):
     nbytes = lib().b200_op_w4_tile_bytes(K, N, G)
     assert nbytes == (N // 128) * (K // G) * (512 + (G // 64) * 4096)
     chunks = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
-    check(lib().b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, ptr(chunks), stream()))
+    check(lib().b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, pair_rows, ptr(chunks), stream()))
     return chunks
 
 
@@ -122,3 +122,21 @@ def test_w4_umma_is_batch_invariant():
     for T in (5, 64, 300):
         assert np.array_equal(outs[T][0], outs[1][0])
     assert np.array_equal(outs[300][:64], outs[64])
+
+
+@pytest.mark.parametrize("T", [1, 6, 64, 100, 300])
+def test_w4_umma_fused_swiglu(T):
+    """gate_up GEMM with the SwiGLU epilogue == silu(x Wg) * (x Wu), one fp16 rounding."""
+    rng = np.random.default_rng(T + 5)
+    K, I = 1536, 1280
+    qw, qz, sc = random_awq(rng, K, 2 * I)                 # columns [gate | up]
+    wq, s, z = repack(qw, qz, sc)
+    ch = tile(wq, s, z, K, 2 * I, pair_rows=I)
+    x = rng.standard_normal((T, K)).astype(np.float16)
+    act = torch.zeros((T, I), dtype=torch.float16, device="cuda")
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(dev(x)), K, ptr(act), I, None, T, K, 2 * I, 128, 2, 1, 0, stream()))
+    gu = x.astype(np.float64) @ dequantize_awq(qw, qz, sc, 128).astype(np.float64)
+    g, u = gu[:, :I], gu[:, I:]
+    ref = g / (1 + np.exp(-g)) * u
+    got = act.cpu().numpy().astype(np.float64)
+    assert (np.abs(got - ref) <= 1.5e-3 * np.abs(ref) + 1e-4).all()

@@ -32,7 +32,7 @@ def w4(K, N, T, splits=1, G=128):
     sc = torch.full((N, K // G), 0.003, dtype=torch.float16, device="cuda")
     zp = torch.full((N, K // G), 1032.0, dtype=torch.float16, device="cuda")
     ch = torch.empty(lib.b200_op_w4_tile_bytes(K, N, G), dtype=torch.uint8, device="cuda")
-    _lib.check(lib.b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, ptr(ch), sp))
+    _lib.check(lib.b200_op_w4_tile(ptr(wq), ptr(sc), ptr(zp), K, N, G, 0, ptr(ch), sp))
     x = torch.randn((T, K), device="cuda").half()
     splits = lib.b200_op_w4_effective_splits(K, G, splits)
     y = torch.empty((splits, T, N), dtype=torch.float32, device="cuda")

@@ -62,7 +62,7 @@ SIGNATURES = {
     "b200_op_awq_repack": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "b200_op_awq_dequant": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
     "b200_op_w4_gemv": (_i32, [_vp, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
-    "b200_op_w4_tile": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
+    "b200_op_w4_tile": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "b200_op_w4_tile_bytes": (_i64, [_i32, _i32, _i32]),
     "b200_op_w4_gemm_umma": (_i32, [_vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i64, _vp]),
     "b200_op_w4_effective_splits": (_i32, [_i32, _i32, _i32]),

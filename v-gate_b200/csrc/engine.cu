@@ -184,6 +184,10 @@ struct b200_engine {
   // never on the token count, so a sequence's arithmetic is the same in every batch it rides in.
   int splits[4] = {1, 1, 1, 1};
   int debug_gemv_mask = getenv("VGATE_B200_DEBUG_GEMV_MASK") ? atoi(getenv("VGATE_B200_DEBUG_GEMV_MASK")) : 0;
+  // Timing ablation only (results become garbage): bit 0 rmsnorm, 1 qkv, 2 rope, 3 attention, 4 o,
+  // 5 gate_up, 6 down, 7 lm_head, 8 sample -- the kernel is simply not launched.
+  int debug_skip = getenv("VGATE_B200_DEBUG_SKIP") ? atoi(getenv("VGATE_B200_DEBUG_SKIP")) : 0;
+  bool skip(int bit) const { return (debug_skip >> bit) & 1; }
   DevMem parts;                                  // fp32 split-K partials [splits][T][N]
 
   // y (+)= x . W^T.  Returns in *n_parts_out how many partial tensors were written to `parts`
@@ -202,6 +206,8 @@ struct b200_engine {
       *n_parts_out = ns;
       return launch_umma_w4(lw.ulin[i], *mx, nt, T, parts.as<float>(), w.N, kUmmaPartialF32, ns, (int64_t)T * w.N, stream);
     }
+    if (i == 2)    // gate_up: fused SwiGLU epilogue writes fp16 act [T, I] (y is the act buffer)
+      return launch_umma_w4(lw.ulin[i], *mx, nt, T, y, ldy, kUmmaSwigluF16, 1, 0, stream);
     return launch_umma_w4(lw.ulin[i], *mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, 1, 0, stream);
   }
 
@@ -227,31 +233,35 @@ struct b200_engine {
       __half* kc = k_cache.as<__half>() + layer_kv_offset(l);
       __half* vc = v_cache.as<__half>() + layer_kv_offset(l);
       int np = 0;
-      if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, w.ln1.as<__half>(), cfg.rms_eps,
+      if (!skip(0) && (rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, w.ln1.as<__half>(), cfg.rms_eps,
                                nullptr, T, H, xn.as<__half>(), stream))) return rc;
       pend = 0;
-      if ((rc = linear(w, 0, xn.as<__half>(), Tmax, qkv.as<float>(), QKV, T, false, &np))) return rc;
-      if ((rc = launch_rope_kv(np ? parts.as<float>() : qkv.as<float>(), np ? np : 1, (int64_t)T * QKV,
+      if (!skip(1) && (rc = linear(w, 0, xn.as<__half>(), Tmax, qkv.as<float>(), QKV, T, false, &np))) return rc;
+      if (!skip(2) && (rc = launch_rope_kv(np ? parts.as<float>() : qkv.as<float>(), np ? np : 1, (int64_t)T * QKV,
                                np ? w.bias_qkv.as<__half>() : nullptr, d_pos.as<int32_t>(), d_slot.as<int32_t>(),
                                cos_t.as<float>(), sin_t.as<float>(), T, NH, NKV, qh.as<__half>(), kc, vc, stream))) return rc;
-      if ((rc = launch_paged_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
+      if (!skip(3) && (rc = launch_paged_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
                                   d_btrow.as<int32_t>(), d_ctx.as<int32_t>(), T, NH, NKV, attn.as<__half>(),
                                   stream))) return rc;
-      if ((rc = linear(w, 1, attn.as<__half>(), Tmax, h.as<float>(), H, T, true, &pend))) return rc;
+      if (!skip(4) && (rc = linear(w, 1, attn.as<__half>(), Tmax, h.as<float>(), H, T, true, &pend))) return rc;
       pend_stride = (int64_t)T * H;
-      if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps,
+      if (!skip(0) && (rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps,
                                nullptr, T, H, xn.as<__half>(), stream))) return rc;
       pend = 0;
-      if ((rc = linear(w, 2, xn.as<__half>(), Tmax, gu.as<float>(), 2 * I, T, false, &np))) return rc;
+      if (use_umma(T) && !(debug_gemv_mask >> 2 & 1)) {
+        if (!skip(5) && (rc = linear(w, 2, xn.as<__half>(), Tmax, reinterpret_cast<float*>(act.p), I, T, false, &np))) return rc;
+      } else {
+        if ((rc = linear(w, 2, xn.as<__half>(), Tmax, gu.as<float>(), 2 * I, T, false, &np))) return rc;
+        if ((rc = launch_swiglu(gu.as<float>(), T, I, act.as<__half>(), stream))) return rc;
+      }
       if (np) { set_last_error("gate_up projection must not be split"); return B200_ERR_STATE; }
-      if ((rc = launch_swiglu(gu.as<float>(), T, I, act.as<__half>(), stream))) return rc;
-      if ((rc = linear(w, 3, act.as<__half>(), Tmax, h.as<float>(), H, T, true, &pend))) return rc;
+      if (!skip(6) && (rc = linear(w, 3, act.as<__half>(), Tmax, h.as<float>(), H, T, true, &pend))) return rc;
     }
     if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, final_norm.as<__half>(), cfg.rms_eps,
                              rows, n_rows, H, xn_last.as<__half>(), stream))) return rc;
     const __half* head = cfg.tie_embeddings ? embed.as<__half>() : lm_head_w.as<__half>();
-    if ((rc = lm_head(head, n_rows))) return rc;
-    if (want_sample) {
+    if (!skip(7) && (rc = lm_head(head, n_rows))) return rc;
+    if (want_sample && !skip(8)) {
       if ((rc = launch_sample(logits.as<float>(), n_rows, V, d_temp.as<float>(), d_topp.as<float>(),
                               d_seed.as<uint32_t>(), d_step.as<int32_t>(), d_next.as<int32_t>(), stream))) return rc;
     }
@@ -637,10 +647,11 @@ int32_t b200_engine_finalize(b200_engine* e) {
       LayerWeights& w = e->layers[l];
       for (int i = 0; i < 4; ++i) {
         const W4Linear& a = w.lin[i];
-        B200_REQUIRE(a.N % 128 == 0 && (a.G == 64 || a.G == 128),
-                     "tcgen05 GEMM needs out_features % 128 == 0 and AWQ group size 64 or 128");
+        B200_REQUIRE(a.N % 128 == 0 && (a.G == 64 || a.G == 128) && e->I % 64 == 0,
+                     "tcgen05 GEMM needs out_features % 128 == 0, intermediate % 64 == 0 and AWQ group size 64 or 128");
         if ((rc = w.chunks[i].alloc(umma_w4_chunk_bytes(a.K, a.N, a.G)))) return rc;
-        if ((rc = launch_umma_tile_w4(a.wq, a.sc, a.zp, a.K, a.N, a.G, w.chunks[i].as<unsigned char>(), e->stream)))
+        if ((rc = launch_umma_tile_w4(a.wq, a.sc, a.zp, a.K, a.N, a.G, i == 2 ? e->I : 0,
+                                      w.chunks[i].as<unsigned char>(), e->stream)))
           return rc;
         w.ulin[i].chunks = w.chunks[i].as<unsigned char>();
         w.ulin[i].bias = a.bias; w.ulin[i].K = a.K; w.ulin[i].N = a.N; w.ulin[i].G = a.G;
@@ -1003,19 +1014,22 @@ int32_t b200_op_w4_gemv(const uint32_t* wq, const void* sc, const void* zp, cons
   w.wq = wq; w.sc = (const __half*)sc; w.zp = (const __half*)zp; w.bias = (const __half*)bias; w.K = K; w.N = N; w.G = G;
   return launch_w4_gemv(w, (const __half*)x, ldx, y, ldy, B, accumulate != 0, (cudaStream_t)stream);
 }
-int32_t b200_op_w4_tile(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N, int32_t G, void* chunks,
-                        void* stream) {
-  return launch_umma_tile_w4(wq, (const __half*)sc, (const __half*)zp, K, N, G, (unsigned char*)chunks, (cudaStream_t)stream);
+int32_t b200_op_w4_tile(const uint32_t* wq, const void* sc, const void* zp, int32_t K, int32_t N, int32_t G,
+                        int32_t pair_rows, void* chunks, void* stream) {
+  return launch_umma_tile_w4(wq, (const __half*)sc, (const __half*)zp, K, N, G, pair_rows, (unsigned char*)chunks,
+                             (cudaStream_t)stream);
 }
 int64_t b200_op_w4_tile_bytes(int32_t K, int32_t N, int32_t G) {
   if (K <= 0 || N <= 0 || N % 128 != 0 || (G != 64 && G != 128) || K % G != 0) return B200_ERR_INVALID;
   return (int64_t)umma_w4_chunk_bytes(K, N, G);
 }
 int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, float* y, int32_t ldy, const void* bias,
-                             int32_t T, int32_t K, int32_t N, int32_t G, int32_t accumulate, int32_t n_splits,
+                             int32_t T, int32_t K, int32_t N, int32_t G, int32_t epilogue, int32_t n_splits,
                              int64_t part_stride, void* stream) {
-  B200_REQUIRE(T >= 0 && n_splits >= 1, "w4_gemm_umma: T >= 0, n_splits >= 1");
-  B200_REQUIRE(n_splits == 1 || (!accumulate && !bias), "w4_gemm_umma: split-K output is raw partials");
+  const int accumulate = epilogue == 1;
+  B200_REQUIRE(T >= 0 && n_splits >= 1 && epilogue >= 0 && epilogue <= 2, "w4_gemm_umma: T >= 0, n_splits >= 1, epilogue in 0..2");
+  B200_REQUIRE(n_splits == 1 || (epilogue == 0 && !bias), "w4_gemm_umma: split-K output is raw partials");
+  B200_REQUIRE(epilogue != 2 || !bias, "w4_gemm_umma: SwiGLU epilogue takes no bias");
   B200_REQUIRE(n_splits == umma_w4_effective_splits(K, G, n_splits), "w4_gemm_umma: n_splits must divide the groups evenly enough (use b200_op_w4_effective_splits)");
   if (T == 0) return B200_OK;
   UmmaW4 w;
@@ -1025,7 +1039,7 @@ int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, flo
   const char* xr = getenv("VGATE_B200_DEBUG_XROWS");     // debug: map more rows than T (stale rows, as in the engine)
   int rc = make_tensor_map_f16(&mx, x, xr ? atoi(xr) : T, K, ldx, nt);
   if (rc) return rc;
-  const int mode = n_splits > 1 ? kUmmaPartialF32 : accumulate ? kUmmaAccumF32 : kUmmaStoreF32;
+  const int mode = n_splits > 1 ? kUmmaPartialF32 : epilogue == 2 ? kUmmaSwigluF16 : accumulate ? kUmmaAccumF32 : kUmmaStoreF32;
   return launch_umma_w4(w, mx, nt, T, y, ldy, mode, n_splits, part_stride, (cudaStream_t)stream);
 }
 void b200_debug_umma_trace(void* dev_buf) { umma_set_trace((unsigned long long*)dev_buf); }

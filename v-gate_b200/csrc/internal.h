@@ -61,11 +61,11 @@ struct UmmaW4 {
   const __half* bias = nullptr;
   int K = 0, N = 0, G = 128;
 };
-enum { kUmmaStoreF32 = 0, kUmmaAccumF32 = 1, kUmmaPartialF32 = 2 };
+enum { kUmmaStoreF32 = 0, kUmmaAccumF32 = 1, kUmmaPartialF32 = 2, kUmmaSwigluF16 = 3 };
 
 size_t umma_w4_chunk_bytes(int K, int N, int G);
 int umma_w4_effective_splits(int K, int G, int n_splits);
-int launch_umma_tile_w4(const uint32_t* wq, const __half* sc, const __half* zp, int K, int N, int G,
+int launch_umma_tile_w4(const uint32_t* wq, const __half* sc, const __half* zp, int K, int N, int G, int pair_rows,
                         unsigned char* chunks, cudaStream_t s);
 int make_tensor_map_f16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows);
 int umma_pick_nt(int T, bool w4);

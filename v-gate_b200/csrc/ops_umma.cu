@@ -40,7 +40,7 @@ constexpr int kChunkStride = 512 + 2 * 4096;     // ring slot: scales 256 B + ze
 constexpr int kMaxStages = 8, kMaxRing = 8;
 constexpr int kTileABytes = kUmmaM * kUmmaBK * 2;          // 16 KB
 
-enum UmmaMode : int { kStoreF32 = 0, kAccumF32 = 1, kPartialF32 = 2 };
+enum UmmaMode : int { kStoreF32 = 0, kAccumF32 = 1, kPartialF32 = 2, kSwigluF16 = 3 };
 
 // ---- PTX wrappers -------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* map, int x, int y, uint64_t* bar) {
@@ -299,18 +299,47 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       const float bn = (p.mode == kStoreF32 && p.bias) ? __half2float(p.bias[n]) : 0.f;
       float* ybase = p.y + (p.mode == kPartialF32 ? (size_t)split * p.part_stride : 0);
       if (p.mode == kAccumF32) grid_dep_wait();                        // y is read-modify-written
-#pragma unroll 1
-      for (int c = 0; c < kColsPerWarp; c += CW) {
+      if constexpr (kW4 && NT <= 128) if (p.mode == kSwigluF16) {
+        // Fused SwiGLU (vLLM qwen2.py:106-111 SiluAndMul): the tile holds 64 gate rows (TMEM lanes
+        // 0..63) and the matching 64 up rows (lanes 64..127).  The up warps hand their values over
+        // through shared memory (the activation stages are idle once the accumulator is complete),
+        // the gate warps compute fp16(silu(g) * u) and store act[b, 64 * nt + row].
+        float* exch = reinterpret_cast<float*>(smem);                  // [NT cols][64 rows] fp32
         uint32_t v[CW];
-        tmem_ld<CW>(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(col0 + c), v);
+        tmem_ld<CW>(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)col0, v);
+        if (q >= 2) {
 #pragma unroll
-        for (int j = 0; j < CW; ++j) {
-          const int b = tok0 + col0 + c + j;
-          if (b < p.T) {
-            float* yp = ybase + (size_t)b * p.ldy + n;
-            const float acc = __uint_as_float(v[j]);
-            if (p.mode == kAccumF32) *yp += acc;
-            else *yp = acc + bn;
+          for (int j = 0; j < CW; ++j) exch[(col0 + j) * 64 + (q - 2) * 32 + lane] = __uint_as_float(v[j]);
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");
+        if (q < 2) {
+          __half* act = reinterpret_cast<__half*>(p.y);
+          const int nout = nt * 64 + q * 32 + lane;
+#pragma unroll
+          for (int j = 0; j < CW; ++j) {
+            const int b = tok0 + col0 + j;
+            if (b < p.T) {
+              const float g = __uint_as_float(v[j]);
+              const float u = exch[(col0 + j) * 64 + q * 32 + lane];
+              act[(size_t)b * p.ldy + nout] = __float2half_rn(g / (1.f + expf(-g)) * u);
+            }
+          }
+        }
+      }
+      if (p.mode != kSwigluF16) {
+#pragma unroll 1
+        for (int c = 0; c < kColsPerWarp; c += CW) {
+          uint32_t v[CW];
+          tmem_ld<CW>(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(col0 + c), v);
+#pragma unroll
+          for (int j = 0; j < CW; ++j) {
+            const int b = tok0 + col0 + c + j;
+            if (b < p.T) {
+              float* yp = ybase + (size_t)b * p.ldy + n;
+              const float acc = __uint_as_float(v[j]);
+              if (p.mode == kAccumF32) *yp += acc;
+              else *yp = acc + bn;
+            }
           }
         }
       }
@@ -393,8 +422,10 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 // kernel layout A (wq [N, K/8], sc/zp [N, K/G]) -> chunk layout streamed by the TMA ring above:
 //   chunk(nt, g) = [sc fp16 x128][zp fp16 x128][k tile 0: half 0 uint4 x128, half 1 uint4 x128][k tile 1 ...]
 // where row r of the tile is output feature nt*128 + r and a uint4 holds 32 consecutive k of that row.
+// pair_rows > 0 (fused SwiGLU, W = [gate; up] with pair_rows rows each): tile nt row r takes gate row
+// 64 nt + r for r < 64 and up row 64 nt + r - 64 otherwise, so gate_i and up_i land in one tile.
 __global__ void umma_tile_w4_kernel(const uint32_t* __restrict__ wq, const __half* __restrict__ sc,
-                                    const __half* __restrict__ zp, int K, int N, int G,
+                                    const __half* __restrict__ zp, int K, int N, int G, int pair_rows,
                                     unsigned char* __restrict__ chunks) {
   const int KG = K / G, tpg = G / 64;
   const size_t chunk_bytes = 512 + (size_t)tpg * 4096;
@@ -402,7 +433,7 @@ __global__ void umma_tile_w4_kernel(const uint32_t* __restrict__ wq, const __hal
   const int g = (int)(cidx % KG), nt = (int)(cidx / KG);
   unsigned char* ch = chunks + cidx * chunk_bytes;
   const int r = threadIdx.x;                            // 128 threads
-  const size_t row = (size_t)nt * 128 + r;
+  const size_t row = pair_rows > 0 ? (size_t)(r < 64 ? 0 : pair_rows) + (size_t)nt * 64 + (r & 63) : (size_t)nt * 128 + r;
   reinterpret_cast<__half*>(ch)[r] = sc[row * KG + g];
   reinterpret_cast<__half*>(ch + 256)[r] = zp[row * KG + g];
   for (int t = 0; t < tpg; ++t)
@@ -414,10 +445,11 @@ __global__ void umma_tile_w4_kernel(const uint32_t* __restrict__ wq, const __hal
 
 size_t umma_w4_chunk_bytes(int K, int N, int G) { return (size_t)(N / 128) * (K / G) * (512 + (size_t)(G / 64) * 4096); }
 
-int launch_umma_tile_w4(const uint32_t* wq, const __half* sc, const __half* zp, int K, int N, int G,
+int launch_umma_tile_w4(const uint32_t* wq, const __half* sc, const __half* zp, int K, int N, int G, int pair_rows,
                         unsigned char* chunks, cudaStream_t s) {
   B200_REQUIRE(N % 128 == 0 && K % G == 0 && (G == 64 || G == 128), "umma_tile_w4: N % 128, K % G, G in {64, 128}");
-  umma_tile_w4_kernel<<<(unsigned)((N / 128) * (K / G)), 128, 0, s>>>(wq, sc, zp, K, N, G, chunks);
+  B200_REQUIRE(pair_rows == 0 || (pair_rows * 2 == N && pair_rows % 64 == 0), "umma_tile_w4: pair_rows must be N / 2 and a multiple of 64");
+  umma_tile_w4_kernel<<<(unsigned)((N / 128) * (K / G)), 128, 0, s>>>(wq, sc, zp, K, N, G, pair_rows, chunks);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -506,6 +538,7 @@ int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T,
                    int n_splits, int64_t part_stride, cudaStream_t s) {
   B200_REQUIRE(w.N % 128 == 0 && w.K % w.G == 0 && (w.G == 64 || w.G == 128), "umma_w4: N % 128, K % G, G in {64, 128}");
   B200_REQUIRE(n_splits >= 1 && (n_splits == 1 || mode == kPartialF32), "umma_w4: split-K needs partial mode");
+  B200_REQUIRE(mode != kSwigluF16 || nt_sel <= 128, "umma_w4: SwiGLU epilogue needs a token tile <= 128");
   if (T == 0) return B200_OK;
   UmmaParams p{};
   p.trace = g_umma_trace;
