@@ -165,6 +165,8 @@ int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits);
 /* Profiling aid: when dev_buf is non-NULL the tcgen05 GEMM writes 8 x uint64 SM-clock stamps per CTA
  * (entry, set-up done, first tiles ready, last MMA issued, accumulator ready, epilogue done, exit). */
 void b200_debug_umma_trace(void* dev_buf);
+/* Same for the attention kernel (entry, copies issued, wait start, tile landed, scores, softmax, loop end). */
+void b200_debug_attn_trace(void* dev_buf);
 /* tcgen05/TMEM GEMM with dense fp16 weights W[N, K] fed by TMA (lm_head); N % 128 == 0, K % 64 == 0. */
 int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T,
                               int32_t K, int32_t N, int32_t accumulate, void* stream);
@@ -185,11 +187,26 @@ int32_t b200_op_rope_kv(const float* qkv, int32_t n_parts, int64_t part_stride, 
                         int32_t T, int32_t n_heads, int32_t n_kv, void* q_out, void* k_cache, void* v_cache,
                         void* stream);
 /* Paged GQA attention, one query row per t: out fp16 [T, nh * 128].  Row t attends to the first
- * ctx_len[t] tokens of block table row bt_row[t].  K/V cache fp16 [n_blocks, n_kv, 16, 128]. */
+ * ctx_len[t] tokens of block table row bt_row[t].  K/V cache fp16 [n_blocks, n_kv, 16, 128].
+ * n_splits > 1 spreads the 64-token chunks of every row round-robin over n_splits CTAs
+ * (flash-decoding); the partial results meet in `scratch` (b200_op_attn_scratch_bytes) and are
+ * merged in split order by the last CTA to finish, tracked by `counters` (int32 [T, n_kv], all zero
+ * before the call and again after it).  n_splits == 1 needs neither. */
 int32_t b200_op_paged_attn(const void* q, const void* k_cache, const void* v_cache,
                            const int32_t* block_tables, int32_t bt_stride, const int32_t* bt_row,
-                           const int32_t* ctx_len, int32_t T, int32_t n_heads, int32_t n_kv, void* out,
-                           void* stream);
+                           const int32_t* ctx_len, int32_t T, int32_t n_heads, int32_t n_kv, int32_t n_splits,
+                           float* scratch, int32_t* counters, void* out, void* stream);
+int64_t b200_op_attn_scratch_bytes(int32_t T, int32_t n_heads, int32_t n_kv, int32_t n_splits);
+/* Decode step: b200_op_rope_kv + b200_op_paged_attn in one kernel.  Every row is the single new
+ * token of a distinct sequence at position pos[t] (ctx_len[t] = pos[t] + 1): its q is rotated in the
+ * kernel, its k (rotated) and v are written to the paged cache at slot[t] and take part in the
+ * attention.  qkv is given like in b200_op_rope_kv (n_parts partial tensors + optional bias). */
+int32_t b200_op_attn_decode_fused(const float* qkv, int32_t n_parts, int64_t part_stride, const void* bias,
+                                  const int32_t* pos, const int32_t* slot, const float* cos_t, const float* sin_t,
+                                  void* k_cache, void* v_cache, const int32_t* block_tables, int32_t bt_stride,
+                                  const int32_t* bt_row, const int32_t* ctx_len, int32_t T, int32_t n_heads,
+                                  int32_t n_kv, int32_t n_splits, float* scratch, int32_t* counters, void* out,
+                                  void* stream);
 /* gu fp32 [T, 2 I] (gate | up) -> act fp16 [T, I] = silu(gate) * up. */
 int32_t b200_op_swiglu(const float* gu, int32_t T, int32_t I, void* act, void* stream);
 /* h fp32 [T, H] = embed fp16 [V, H] rows ids[t]. */

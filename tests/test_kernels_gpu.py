@@ -120,27 +120,87 @@ def _paged_setup(rng, n_seqs, ctx_lens, n_kv, n_blocks):
     return kc, vc, bt, dense_k, dense_v
 
 
-@pytest.mark.parametrize("n_heads,n_kv", [(12, 2), (28, 4), (4, 4)])
-def test_paged_attention_matches_oracle(n_heads, n_kv):
-    rng = np.random.default_rng(n_heads)
-    ctx_lens = [1, 15, 16, 17, 64, 65, 200, 333]
-    n_seqs = len(ctx_lens)
-    kc, vc, bt, dk, dv = _paged_setup(rng, n_seqs, ctx_lens, n_kv, n_blocks=64)
-    q = rng.standard_normal((n_seqs, n_heads, 128)).astype(np.float16)
-    out = torch.empty((n_seqs, n_heads * 128), dtype=torch.float16, device="cuda")
-    check(lib().b200_op_paged_attn(ptr(dev(q)), ptr(dev(kc)), ptr(dev(vc)), ptr(dev(bt)), bt.shape[1],
-                                   ptr(dev(np.arange(n_seqs, dtype=np.int32))),
-                                   ptr(dev(np.array(ctx_lens, dtype=np.int32))), n_seqs, n_heads, n_kv, ptr(out),
-                                   stream()))
-    got = out.cpu().numpy().astype(np.float64).reshape(n_seqs, n_heads, 128)
+def _attn_ref(q, dk, dv, n_heads, n_kv):
     grp = n_heads // n_kv
-    for s in range(n_seqs):
+    out = np.zeros((len(dk), n_heads, 128))
+    for s in range(len(dk)):
         for h in range(n_heads):
             k, v = dk[s][h // grp].astype(np.float64), dv[s][h // grp].astype(np.float64)
             sc = k @ q[s, h].astype(np.float64) / np.sqrt(128.0)
             p = np.exp(sc - sc.max())
-            ref = (p / p.sum()) @ v
-            assert np.abs(got[s, h] - ref).max() < 3e-3, (s, h)
+            out[s, h] = (p / p.sum()) @ v
+    return out
+
+
+@pytest.mark.parametrize("n_splits", [1, 3, 8])
+@pytest.mark.parametrize("n_heads,n_kv", [(12, 2), (28, 4), (4, 4)])
+def test_paged_attention_matches_oracle(n_heads, n_kv, n_splits):
+    rng = np.random.default_rng(n_heads)
+    ctx_lens = [1, 15, 16, 17, 64, 65, 200, 333, 0, 640]
+    n_seqs = len(ctx_lens)
+    kc, vc, bt, dk, dv = _paged_setup(rng, n_seqs, [max(c, 1) for c in ctx_lens], n_kv, n_blocks=128)
+    q = rng.standard_normal((n_seqs, n_heads, 128)).astype(np.float16)
+    out = torch.full((n_seqs, n_heads * 128), 7.0, dtype=torch.float16, device="cuda")
+    scratch = torch.empty(lib().b200_op_attn_scratch_bytes(n_seqs, n_heads, n_kv, n_splits) // 4, dtype=torch.float32,
+                          device="cuda")
+    counters = torch.zeros(n_seqs * n_kv, dtype=torch.int32, device="cuda")
+    for rep in range(2):                # twice: the arrival counters must clean up after themselves
+        check(lib().b200_op_paged_attn(ptr(dev(q)), ptr(dev(kc)), ptr(dev(vc)), ptr(dev(bt)), bt.shape[1],
+                                       ptr(dev(np.arange(n_seqs, dtype=np.int32))),
+                                       ptr(dev(np.array(ctx_lens, dtype=np.int32))), n_seqs, n_heads, n_kv, n_splits,
+                                       ptr(scratch), ptr(counters), ptr(out), stream()))
+        assert not counters.any().item()
+    got = out.cpu().numpy().astype(np.float64).reshape(n_seqs, n_heads, 128)
+    ref = _attn_ref(q, dk, dv, n_heads, n_kv)
+    for s in range(n_seqs):
+        if ctx_lens[s] == 0:
+            assert not got[s].any()              # empty context: zeros
+        else:
+            assert np.abs(got[s] - ref[s]).max() < 3e-3, s
+
+
+@pytest.mark.parametrize("n_splits,n_parts", [(1, 1), (8, 4)])
+def test_fused_decode_attention_matches_rope_plus_attention(n_splits, n_parts):
+    """The fused decode kernel == b200_op_rope_kv followed by b200_op_paged_attn: same q rotation, same
+    cache contents afterwards, same attention output."""
+    rng = np.random.default_rng(17 + n_splits)
+    n_heads, n_kv, n_blocks = 12, 2, 96
+    ctx_lens = [1, 16, 17, 64, 65, 129, 300, 512]           # context INCLUDING the new token
+    T = len(ctx_lens)
+    kc, vc, bt, _, _ = _paged_setup(rng, T, ctx_lens, n_kv, n_blocks)
+    pos = np.array([c - 1 for c in ctx_lens], dtype=np.int32)
+    slot = np.array([bt[i, p // 16] * 16 + p % 16 for i, p in enumerate(pos)], dtype=np.int32)
+    cos, sin = rope_table(Qwen2Dims(), 4096)
+    width = (n_heads + 2 * n_kv) * 128
+    parts = rng.standard_normal((n_parts, T, width)).astype(np.float32)
+    bias = (rng.standard_normal(width) * 0.05).astype(np.float16)
+    btrow, ctx = np.arange(T, dtype=np.int32), np.array(ctx_lens, dtype=np.int32)
+    cosd, sind, btd, posd, slotd, partsd, biasd = dev(cos.numpy()), dev(sin.numpy()), dev(bt), dev(pos), dev(slot), dev(parts), dev(bias)
+    btrowd, ctxd = dev(btrow), dev(ctx)
+    # reference path: rope kernel then plain attention, on its own copy of the cache
+    kc1, vc1 = dev(kc).clone(), dev(vc).clone()
+    qo = torch.empty((T, n_heads * 128), dtype=torch.float16, device="cuda")
+    out1 = torch.empty_like(qo)
+    check(lib().b200_op_rope_kv(ptr(partsd), n_parts, T * width, ptr(biasd), ptr(posd), ptr(slotd), ptr(cosd), ptr(sind), T,
+                                n_heads, n_kv, ptr(qo), ptr(kc1), ptr(vc1), stream()))
+    cosd, sind, btd, posd, slotd, partsd, biasd = dev(cos.numpy()), dev(sin.numpy()), dev(bt), dev(pos), dev(slot), dev(parts), dev(bias)
+    btrowd, ctxd = dev(btrow), dev(ctx)
+    check(lib().b200_op_paged_attn(ptr(qo), ptr(kc1), ptr(vc1), ptr(btd), bt.shape[1], ptr(btrowd), ptr(ctxd), T, n_heads,
+                                   n_kv, 1, None, None, ptr(out1), stream()))
+    # fused path
+    kc2, vc2 = dev(kc).clone(), dev(vc).clone()
+    out2 = torch.empty_like(qo)
+    scratch = torch.empty(lib().b200_op_attn_scratch_bytes(T, n_heads, n_kv, n_splits) // 4, dtype=torch.float32, device="cuda")
+    counters = torch.zeros(T * n_kv, dtype=torch.int32, device="cuda")
+    cosd, sind, btd, posd, slotd, partsd, biasd = dev(cos.numpy()), dev(sin.numpy()), dev(bt), dev(pos), dev(slot), dev(parts), dev(bias)
+    btrowd, ctxd = dev(btrow), dev(ctx)
+    check(lib().b200_op_attn_decode_fused(ptr(partsd), n_parts, T * width, ptr(biasd), ptr(posd), ptr(slotd), ptr(cosd),
+                                          ptr(sind), ptr(kc2), ptr(vc2), ptr(btd), bt.shape[1], ptr(btrowd), ptr(ctxd), T,
+                                          n_heads, n_kv, n_splits, ptr(scratch), ptr(counters), ptr(out2), stream()))
+    assert torch.equal(kc1, kc2) and torch.equal(vc1, vc2)              # cache writes are bit-identical
+    assert not counters.any().item()
+    d = (out1.float() - out2.float()).abs().max().item()
+    assert d < (1e-6 if n_splits == 1 else 2e-3), d                      # merge order differs only when split
 
 
 def test_rope_kv_write_matches_oracle():

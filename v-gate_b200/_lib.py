@@ -67,11 +67,15 @@ SIGNATURES = {
     "b200_op_w4_gemm_umma": (_i32, [_vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i64, _vp]),
     "b200_op_w4_effective_splits": (_i32, [_i32, _i32, _i32]),
     "b200_debug_umma_trace": (None, [_vp]),
+    "b200_debug_attn_trace": (None, [_vp]),
     "b200_op_f16_gemm_umma": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200_op_f16_gemv": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200_op_rmsnorm": (_i32, [_vp, _vp, _i32, _i64, _vp, _f32, _vp, _i32, _i32, _vp, _vp]),
     "b200_op_rope_kv": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
-    "b200_op_paged_attn": (_i32, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
+    "b200_op_paged_attn": (_i32, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "b200_op_attn_scratch_bytes": (_i64, [_i32, _i32, _i32, _i32]),
+    "b200_op_attn_decode_fused": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32,
+                                         _i32, _i32, _vp, _vp, _vp, _vp]),
     "b200_op_swiglu": (_i32, [_vp, _i32, _i32, _vp, _vp]),
     "b200_op_embed": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp]),
     "b200_op_sample": (_i32, [_vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp]),

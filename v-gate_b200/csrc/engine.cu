@@ -189,6 +189,8 @@ struct b200_engine {
   int debug_skip = getenv("VGATE_B200_DEBUG_SKIP") ? atoi(getenv("VGATE_B200_DEBUG_SKIP")) : 0;
   bool skip(int bit) const { return (debug_skip >> bit) & 1; }
   DevMem parts;                                  // fp32 split-K partials [splits][T][N]
+  DevMem attn_scratch, attn_counters;            // flash-decoding partials + per-(row, kv head) arrival counters
+  static constexpr int kDecodeSplits = 8;        // KV splits of the decode attention (64-token chunks, round-robin)
 
   // y (+)= x . W^T.  Returns in *n_parts_out how many partial tensors were written to `parts`
   // instead (0: the result is already in y).
@@ -223,7 +225,9 @@ struct b200_engine {
 
   // One forward pass over T token rows whose metadata already sits in the d_* buffers; samples one
   // token for each of the n_rows "last" rows into d_next.  `rows` == nullptr: row r is token r.
-  int forward(int T, int n_rows, const int32_t* rows, bool want_sample = true) {
+  // decode_rows: every row is the single new token of a distinct sequence (enables the fused
+  // RoPE + KV-write + split-KV attention kernel).
+  int forward(int T, int n_rows, const int32_t* rows, bool decode_rows, bool want_sample = true) {
     int rc;
     if ((rc = launch_embed(embed.as<__half>(), d_ids.as<int32_t>(), T, H, h.as<float>(), stream))) return rc;
     int pend = 0;                 // split-K partials of the previous projection still to be added into h
@@ -237,12 +241,23 @@ struct b200_engine {
                                nullptr, T, H, xn.as<__half>(), stream))) return rc;
       pend = 0;
       if (!skip(1) && (rc = linear(w, 0, xn.as<__half>(), Tmax, qkv.as<float>(), QKV, T, false, &np))) return rc;
-      if (!skip(2) && (rc = launch_rope_kv(np ? parts.as<float>() : qkv.as<float>(), np ? np : 1, (int64_t)T * QKV,
-                               np ? w.bias_qkv.as<__half>() : nullptr, d_pos.as<int32_t>(), d_slot.as<int32_t>(),
-                               cos_t.as<float>(), sin_t.as<float>(), T, NH, NKV, qh.as<__half>(), kc, vc, stream))) return rc;
-      if (!skip(3) && (rc = launch_paged_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
-                                  d_btrow.as<int32_t>(), d_ctx.as<int32_t>(), T, NH, NKV, attn.as<__half>(),
-                                  stream))) return rc;
+      const float* qsrc = np ? parts.as<float>() : qkv.as<float>();
+      const __half* qbias = np ? w.bias_qkv.as<__half>() : nullptr;
+      if (decode_rows && T <= cfg.max_seqs) {
+        if (!skip(3) && (rc = launch_attn_decode_fused(qsrc, np ? np : 1, (int64_t)T * QKV, qbias, d_pos.as<int32_t>(),
+                                                        d_slot.as<int32_t>(), cos_t.as<float>(), sin_t.as<float>(), kc, vc,
+                                                        d_bt.as<int32_t>(), max_blocks_per_seq, d_btrow.as<int32_t>(),
+                                                        d_ctx.as<int32_t>(), T, NH, NKV, kDecodeSplits,
+                                                        attn_scratch.as<float>(), attn_counters.as<int32_t>(),
+                                                        attn.as<__half>(), stream))) return rc;
+      } else {
+        if (!skip(2) && (rc = launch_rope_kv(qsrc, np ? np : 1, (int64_t)T * QKV, qbias, d_pos.as<int32_t>(),
+                                             d_slot.as<int32_t>(), cos_t.as<float>(), sin_t.as<float>(), T, NH, NKV,
+                                             qh.as<__half>(), kc, vc, stream))) return rc;
+        if (!skip(3) && (rc = launch_paged_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
+                                                d_btrow.as<int32_t>(), d_ctx.as<int32_t>(), T, NH, NKV, 1, nullptr, nullptr,
+                                                attn.as<__half>(), stream))) return rc;
+      }
       if (!skip(4) && (rc = linear(w, 1, attn.as<__half>(), Tmax, h.as<float>(), H, T, true, &pend))) return rc;
       pend_stride = (int64_t)T * H;
       if (!skip(0) && (rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps,
@@ -344,7 +359,7 @@ struct b200_engine {
       return rc;
     const int64_t launches0 = g_launch_count;
     B200_CUDA(cudaEventRecord(ev0, stream));
-    if ((rc = forward(T, n, d_lastrows.as<int32_t>()))) return rc;
+    if ((rc = forward(T, n, d_lastrows.as<int32_t>(), !is_prefill))) return rc;
     B200_CUDA(cudaEventRecord(ev1, stream));
     std::vector<int32_t> next(n);
     B200_CUDA(cudaMemcpyAsync(next.data(), d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
@@ -703,6 +718,10 @@ int32_t b200_engine_finalize(b200_engine* e) {
     }
   }
   if ((rc = e->parts.alloc(part_elems * 4))) return rc;
+  if ((rc = e->attn_scratch.alloc(attn_scratch_floats(c.max_seqs, e->NH, e->NKV, b200_engine::kDecodeSplits) * 4)) ||
+      (rc = e->attn_counters.alloc((size_t)c.max_seqs * e->NKV * 4)))
+    return rc;
+  B200_CUDA(cudaMemset(e->attn_counters.p, 0, e->attn_counters.bytes));
   B200_CUDA(cudaDeviceSynchronize());
   e->finalized = true;
   e->worker = std::thread([e] { e->scheduler_loop(); });
@@ -733,7 +752,7 @@ void b200_engine_destroy(b200_engine* e) {
   DevMem* all[] = {&e->embed, &e->lm_head_w, &e->final_norm, &e->cos_t, &e->sin_t, &e->k_cache, &e->v_cache, &e->h,
                    &e->xn, &e->qkv, &e->qh, &e->attn, &e->gu, &e->act, &e->xn_last, &e->logits, &e->d_ids, &e->d_pos,
                    &e->d_slot, &e->d_btrow, &e->d_ctx, &e->d_lastrows, &e->d_bt, &e->d_temp, &e->d_topp, &e->d_seed,
-                   &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens, &e->parts};
+                   &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens, &e->parts, &e->attn_scratch, &e->attn_counters};
   for (DevMem* m : all) m->release();
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
@@ -904,7 +923,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
         (rc = e->upload_i32(e->d_btrow, btrow)) || (rc = e->upload_i32(e->d_ctx, ctx)) ||
         (rc = e->upload_i32(e->d_lastrows, lastrows)))
       return rc;
-    if ((rc = e->forward(ns * n_prompt, ns, e->d_lastrows.as<int32_t>()))) return rc;
+    if ((rc = e->forward(ns * n_prompt, ns, e->d_lastrows.as<int32_t>(), false))) return rc;
     B200_CUDA(cudaMemcpyAsync(first_tokens.data() + s0, e->d_next.p, (size_t)ns * 4, cudaMemcpyDeviceToHost, s));
     if (logits_out && n_logit_steps > 0)
       B200_CUDA(cudaMemcpy2DAsync(logits_out + (size_t)s0 * n_logit_steps * e->V, (size_t)n_logit_steps * e->V * 4,
@@ -936,7 +955,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
   auto step_once = [&]() -> int {
     int r2;
     if ((r2 = advance())) return r2;
-    return e->forward(n_seqs, n_seqs, nullptr);
+    return e->forward(n_seqs, n_seqs, nullptr, true);
   };
   B200_CUDA(cudaEventRecord(e->ev0, s));
   // step 1 runs eagerly: it loads every kernel of the decode configuration before any capture
@@ -1043,6 +1062,7 @@ int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, flo
   return launch_umma_w4(w, mx, nt, T, y, ldy, mode, n_splits, part_stride, (cudaStream_t)stream);
 }
 void b200_debug_umma_trace(void* dev_buf) { umma_set_trace((unsigned long long*)dev_buf); }
+void b200_debug_attn_trace(void* dev_buf) { attn_set_trace((unsigned long long*)dev_buf); }
 int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits) {
   if (K <= 0 || G <= 0 || K % G != 0 || n_splits < 1) return B200_ERR_INVALID;
   return umma_w4_effective_splits(K, G, n_splits);
@@ -1074,9 +1094,23 @@ int32_t b200_op_rope_kv(const float* qkv, int32_t n_parts, int64_t part_stride, 
 }
 int32_t b200_op_paged_attn(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_tables,
                            int32_t bt_stride, const int32_t* bt_row, const int32_t* ctx_len, int32_t T, int32_t n_heads,
-                           int32_t n_kv, void* out, void* stream) {
+                           int32_t n_kv, int32_t n_splits, float* scratch, int32_t* counters, void* out, void* stream) {
   return launch_paged_attn((const __half*)q, (const __half*)k_cache, (const __half*)v_cache, block_tables, bt_stride,
-                           bt_row, ctx_len, T, n_heads, n_kv, (__half*)out, (cudaStream_t)stream);
+                           bt_row, ctx_len, T, n_heads, n_kv, n_splits, scratch, counters, (__half*)out,
+                           (cudaStream_t)stream);
+}
+int64_t b200_op_attn_scratch_bytes(int32_t T, int32_t n_heads, int32_t n_kv, int32_t n_splits) {
+  if (T < 0 || n_kv <= 0 || n_heads % n_kv != 0 || n_splits < 1) return B200_ERR_INVALID;
+  return (int64_t)attn_scratch_floats(T, n_heads, n_kv, n_splits) * 4;
+}
+int32_t b200_op_attn_decode_fused(const float* qkv, int32_t n_parts, int64_t part_stride, const void* bias,
+                                  const int32_t* pos, const int32_t* slot, const float* cos_t, const float* sin_t,
+                                  void* k_cache, void* v_cache, const int32_t* block_tables, int32_t bt_stride,
+                                  const int32_t* bt_row, const int32_t* ctx_len, int32_t T, int32_t n_heads, int32_t n_kv,
+                                  int32_t n_splits, float* scratch, int32_t* counters, void* out, void* stream) {
+  return launch_attn_decode_fused(qkv, n_parts, part_stride, (const __half*)bias, pos, slot, cos_t, sin_t, (__half*)k_cache,
+                                  (__half*)v_cache, block_tables, bt_stride, bt_row, ctx_len, T, n_heads, n_kv, n_splits,
+                                  scratch, counters, (__half*)out, (cudaStream_t)stream);
 }
 int32_t b200_op_swiglu(const float* gu, int32_t T, int32_t I, void* act, void* stream) {
   return launch_swiglu(gu, T, I, (__half*)act, (cudaStream_t)stream);

@@ -90,7 +90,14 @@ int launch_rope_kv(const float* qkv, int n_parts, int64_t part_stride, const __h
                    __half* v_cache, cudaStream_t s);
 int launch_paged_attn(const __half* q, const __half* k_cache, const __half* v_cache, const int32_t* block_tables,
                       int bt_stride, const int32_t* bt_row, const int32_t* ctx_len, int T, int n_heads, int n_kv,
-                      __half* out, cudaStream_t s);
+                      int n_splits, float* scratch, int32_t* counters, __half* out, cudaStream_t s);
+int launch_attn_decode_fused(const float* qkv, int n_parts, int64_t part_stride, const __half* bias, const int32_t* pos,
+                             const int32_t* slot, const float* cos_t, const float* sin_t, __half* k_cache,
+                             __half* v_cache, const int32_t* block_tables, int bt_stride, const int32_t* bt_row,
+                             const int32_t* ctx_len, int T, int n_heads, int n_kv, int n_splits, float* scratch,
+                             int32_t* counters, __half* out, cudaStream_t s);
+void attn_set_trace(unsigned long long* dev_buf);
+size_t attn_scratch_floats(int T, int n_heads, int n_kv, int n_splits);
 int launch_swiglu(const float* gu, int T, int I, __half* act, cudaStream_t s);
 int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s);
 int launch_sample(const float* logits, int B, int V, const float* temperature, const float* top_p,
