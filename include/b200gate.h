@@ -197,6 +197,22 @@ int32_t b200_op_paged_attn(const void* q, const void* k_cache, const void* v_cac
                            const int32_t* ctx_len, int32_t T, int32_t n_heads, int32_t n_kv, int32_t n_splits,
                            float* scratch, int32_t* counters, void* out, void* stream);
 int64_t b200_op_attn_scratch_bytes(int32_t T, int32_t n_heads, int32_t n_kv, int32_t n_splits);
+/* b200_op_paged_attn without the scratch and counters arguments, for callers that cannot allocate
+ * device memory (a serving loop that must never hit a device-wide sync, a host that exposes no
+ * allocator, a frozen memory pool).  It has no counterpart in the reference.  The split-KV partials
+ * and the arrival counters live in arrays built into the library (about 4.3 MB on every GPU that
+ * loads it, for the life of the process), so the sizes are capped:
+ *     T * n_heads * n_splits <= 8192   and   T * n_kv <= 2048
+ * (e.g. 64 rows x 12 heads x 8 splits); larger calls fail with B200_ERR_CAPACITY and should use
+ * b200_op_paged_attn.  The call itself allocates nothing and frees nothing.  The first call on each
+ * device looks up the arrays' device addresses with that device current -- make that call before any
+ * stream capture.  All calls on a device share the arrays, which keep whatever the previous call left
+ * behind; the counters are cleared on the stream before each launch, the partials need no clearing.
+ * Two calls that overlap on the GPU (different streams) race on the shared arrays: serialise them. */
+int32_t b200_op_paged_attn_noalloc(const void* q, const void* k_cache, const void* v_cache,
+                                   const int32_t* block_tables, int32_t bt_stride, const int32_t* bt_row,
+                                   const int32_t* ctx_len, int32_t T, int32_t n_heads, int32_t n_kv,
+                                   int32_t n_splits, void* out, void* stream);
 /* Decode step: b200_op_rope_kv + b200_op_paged_attn in one kernel.  Every row is the single new
  * token of a distinct sequence at position pos[t] (ctx_len[t] = pos[t] + 1): its q is rotated in the
  * kernel, its k (rotated) and v are written to the paged cache at slot[t] and take part in the

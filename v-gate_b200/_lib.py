@@ -74,6 +74,7 @@ SIGNATURES = {
     "b200_op_rope_kv": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "b200_op_paged_attn": (_i32, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "b200_op_attn_scratch_bytes": (_i64, [_i32, _i32, _i32, _i32]),
+    "b200_op_paged_attn_noalloc": (_i32, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
     "b200_op_attn_decode_fused": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32,
                                          _i32, _i32, _vp, _vp, _vp, _vp]),
     "b200_op_swiglu": (_i32, [_vp, _i32, _i32, _vp, _vp]),

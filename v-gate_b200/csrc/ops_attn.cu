@@ -16,6 +16,8 @@
 // reshape_and_cache): q / k / v of the new token arrive as fp32 split-K partials of the qkv
 // projection; every CTA rotates its own q heads, and the CTA that owns the chunk holding the new
 // position rotates k, writes k / v to the paged cache and patches them into its staged tile.
+#include <mutex>
+
 #include "common.cuh"
 #include "internal.h"
 
@@ -378,4 +380,64 @@ int launch_attn_decode_fused(const float* qkv, int n_parts, int64_t part_stride,
   return dispatch(p, T, true, s);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Split-KV attention for callers that must not allocate.
+//
+// b200_op_paged_attn needs the caller to bring a scratch buffer and arrival counters.  Some callers
+// cannot: code running inside a latency-critical serving loop where a cudaMalloc would synchronise
+// the whole device, a plugin host that hands out no allocator, or a process whose memory pool is
+// already carved up and frozen.  For them the scratch lives in the library image itself, as
+// file-scope __device__ arrays of a fixed, modest size.  Every GPU that loads the library carries
+// these ~4.3 MB until the process exits.
+constexpr int kStaticScratchUnits = 8192;                          // rows * n_heads * n_splits
+constexpr int kStaticCounters = 2048;                              // rows * n_kv_heads
+static __device__ __align__(256) float g_static_attn_scratch[(size_t)kStaticScratchUnits * kPartFloats];
+static __device__ __align__(256) int32_t g_static_attn_counters[kStaticCounters];
+
+constexpr int kMaxDevices = 64;
+static float* g_static_scratch_ptr[kMaxDevices];                   // device addresses, resolved once per device
+static int32_t* g_static_counters_ptr[kMaxDevices];
+static std::mutex g_static_mu;
+
 }  // namespace b200
+
+extern "C" int32_t b200_op_paged_attn_noalloc(const void* q, const void* k_cache, const void* v_cache,
+                                              const int32_t* block_tables, int32_t bt_stride, const int32_t* bt_row,
+                                              const int32_t* ctx_len, int32_t T, int32_t n_heads, int32_t n_kv,
+                                              int32_t n_splits, void* out, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(T >= 0 && n_kv > 0 && n_heads > 0 && n_heads % n_kv == 0 && n_splits >= 1, "paged_attn_noalloc: shape");
+  if ((int64_t)T * n_heads * n_splits > kStaticScratchUnits || (int64_t)T * n_kv > kStaticCounters) {
+    set_last_error("paged_attn_noalloc: rows * n_heads * n_splits = " + std::to_string((int64_t)T * n_heads * n_splits) +
+                   " exceeds the built-in scratch (" + std::to_string(kStaticScratchUnits) + "), or rows * n_kv_heads = " +
+                   std::to_string((int64_t)T * n_kv) + " exceeds the built-in counters (" + std::to_string(kStaticCounters) +
+                   "); use b200_op_paged_attn with caller-provided scratch");
+    return B200_ERR_CAPACITY;
+  }
+  int dev = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kMaxDevices, "paged_attn_noalloc: device ordinal out of range");
+  float* scratch;
+  int32_t* counters;
+  {
+    // In host code the array names are host-side handles, not device addresses: ask the runtime for
+    // the address the current device gave them.  Done once per device, on the first call there.
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_scratch_ptr[dev]) {
+      void *ps = nullptr, *pc = nullptr;
+      B200_CUDA(cudaGetSymbolAddress(&ps, g_static_attn_scratch));
+      B200_CUDA(cudaGetSymbolAddress(&pc, g_static_attn_counters));
+      g_static_counters_ptr[dev] = static_cast<int32_t*>(pc);
+      g_static_scratch_ptr[dev] = static_cast<float*>(ps);
+    }
+    scratch = g_static_scratch_ptr[dev];
+    counters = g_static_counters_ptr[dev];
+  }
+  if (T == 0) return B200_OK;
+  // The arrival counters must read zero when the kernel starts.  A finished call leaves them zero, but
+  // an aborted one might not, and all calls share the array: clear the part this call uses.
+  B200_CUDA(cudaMemsetAsync(counters, 0, (size_t)T * n_kv * sizeof(int32_t), (cudaStream_t)stream));
+  return launch_paged_attn((const __half*)q, (const __half*)k_cache, (const __half*)v_cache, block_tables, bt_stride,
+                           bt_row, ctx_len, T, n_heads, n_kv, n_splits, scratch, counters, (__half*)out,
+                           (cudaStream_t)stream);
+}
