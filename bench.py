@@ -101,6 +101,25 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def reduce_over_ranks(values, op="max", device="cpu"):
+    """Element-wise max / sum over ranks of a small list of floats (identity when not distributed).
+    The timing rule of the bench contract: a multi-GPU time is the MAX over ranks."""
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor(list(values), dtype=torch.float64, device=device)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+    return t.tolist()
+
+
+def aggregate_throughput(tokens_per_rank, seconds_this_rank, device="cpu"):
+    """Whole-job tokens/s: all ranks' tokens divided by the slowest rank's time (weak scaling, one
+    independent replica per rank, no data-path collective)."""
+    total = reduce_over_ranks([tokens_per_rank], "sum", device)[0]
+    worst = reduce_over_ranks([seconds_this_rank], "max", device)[0]
+    return total / worst, worst
+
+
 def make_prompts(rng, a, vocab):
     return rng.integers(0, vocab, size=(a.batch, a.prompt_len), dtype=np.int32)
 
@@ -250,12 +269,9 @@ def run_b200(a):
 
     # device-timed whole-step time (CUDA events on the engine's stream), max over ranks
     dev_time = gpu_prefill + gpu_decode
-    tt = torch.tensor([dev_time, wall, gpu_decode, gpu_prefill], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    dev_time, wall, gpu_decode_max, gpu_prefill_max = tt.tolist()
     tokens_per_rank = a.batch * a.new_tokens * a.steps
-    value = world * tokens_per_rank / dev_time
+    value, _ = aggregate_throughput(tokens_per_rank, dev_time, device="cuda")
+    dev_time, wall, gpu_decode_max, gpu_prefill_max = reduce_over_ranks([dev_time, wall, gpu_decode, gpu_prefill], "max", "cuda")
 
     # ---- e2e: the public API, called the way V-Gate calls it ----
     # B200Backend.generate([one prompt], sampling_params) from one thread per in-flight request
@@ -288,10 +304,8 @@ def run_b200(a):
             tpots += [r["metrics"]["gen_time"] / r["num_tokens"] for r in results]   # vgate/batcher.py:431
         barrier()
         pool.shutdown()
-        t_e = torch.tensor([tot_t], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * tot_n / t_e.item(), "unit": UNIT,
+        e2e_value, _ = aggregate_throughput(tot_n, tot_t, device="cuda")
+        e2e = {"value": e2e_value, "unit": UNIT,
                "h2d_bytes_per_step": int(a.batch * a.prompt_len * 4),       # prompt token ids
                "d2h_bytes_per_step": int(a.batch * a.new_tokens * 4),       # sampled ids, read back every decode step
                "tpot_ms_p50": float(np.median(tpots) * 1e3),
