@@ -55,3 +55,19 @@ def random_awq(rng, K, N, G=128, w_std=0.02):
     qzeros = rng.integers(0, 2**32, size=(K // G, N // 8), dtype=np.uint32).view(np.int32)
     scales = ((w_std / 6.52) * (0.5 + rng.random((K // G, N), dtype=np.float32))).astype(np.float16)
     return qweight, qzeros, scales
+
+
+def swizzle_kv(a):
+    """Logical K/V blocks [..., 16 tokens, 128 dims] -> the cache's physical row layout: 16-byte chunk c
+    of the row at token offset r is stored at chunk position c ^ (r & 7) (csrc/common.cuh kv_swz)."""
+    a = np.asarray(a)
+    out = np.empty_like(a)
+    v = a.reshape(a.shape[:-2] + (16, 16, 8))
+    o = out.reshape(v.shape)
+    for r in range(16):
+        for c in range(16):
+            o[..., r, c ^ (r & 7), :] = v[..., r, c, :]
+    return out
+
+
+unswizzle_kv = swizzle_kv        # the XOR permutation is its own inverse

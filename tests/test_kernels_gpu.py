@@ -10,7 +10,7 @@ from oracle import sampler as osampler
 
 pytestmark = pytest.mark.gpu
 
-from tests.gpu_util import lib, dev, ptr, stream, check, repack, random_awq  # noqa: E402
+from tests.gpu_util import lib, dev, ptr, stream, check, repack, random_awq, swizzle_kv, unswizzle_kv  # noqa: E402
 
 
 @pytest.mark.parametrize("K,N", [(1536, 2048), (8960, 1536), (256, 64)])
@@ -145,7 +145,7 @@ def test_paged_attention_matches_oracle(n_heads, n_kv, n_splits):
                           device="cuda")
     counters = torch.zeros(n_seqs * n_kv, dtype=torch.int32, device="cuda")
     for rep in range(2):                # twice: the arrival counters must clean up after themselves
-        check(lib().b200_op_paged_attn(ptr(dev(q)), ptr(dev(kc)), ptr(dev(vc)), ptr(dev(bt)), bt.shape[1],
+        check(lib().b200_op_paged_attn(ptr(dev(q)), ptr(dev(swizzle_kv(kc))), ptr(dev(swizzle_kv(vc))), ptr(dev(bt)), bt.shape[1],
                                        ptr(dev(np.arange(n_seqs, dtype=np.int32))),
                                        ptr(dev(np.array(ctx_lens, dtype=np.int32))), n_seqs, n_heads, n_kv, n_splits,
                                        ptr(scratch), ptr(counters), ptr(out), stream()))
@@ -156,7 +156,7 @@ def test_paged_attention_matches_oracle(n_heads, n_kv, n_splits):
         if ctx_lens[s] == 0:
             assert not got[s].any()              # empty context: zeros
         else:
-            assert np.abs(got[s] - ref[s]).max() < 3e-3, s
+            assert np.abs(got[s] - ref[s]).max() < 4e-3, s          # P is rounded to fp16 for the tensor-core PV
 
 
 @pytest.mark.parametrize("n_splits,n_parts", [(1, 1), (8, 4)])
@@ -178,7 +178,7 @@ def test_fused_decode_attention_matches_rope_plus_attention(n_splits, n_parts):
     cosd, sind, btd, posd, slotd, partsd, biasd = dev(cos.numpy()), dev(sin.numpy()), dev(bt), dev(pos), dev(slot), dev(parts), dev(bias)
     btrowd, ctxd = dev(btrow), dev(ctx)
     # reference path: rope kernel then plain attention, on its own copy of the cache
-    kc1, vc1 = dev(kc).clone(), dev(vc).clone()
+    kc1, vc1 = dev(swizzle_kv(kc)).clone(), dev(swizzle_kv(vc)).clone()
     qo = torch.empty((T, n_heads * 128), dtype=torch.float16, device="cuda")
     out1 = torch.empty_like(qo)
     check(lib().b200_op_rope_kv(ptr(partsd), n_parts, T * width, ptr(biasd), ptr(posd), ptr(slotd), ptr(cosd), ptr(sind), T,
@@ -188,7 +188,7 @@ def test_fused_decode_attention_matches_rope_plus_attention(n_splits, n_parts):
     check(lib().b200_op_paged_attn(ptr(qo), ptr(kc1), ptr(vc1), ptr(btd), bt.shape[1], ptr(btrowd), ptr(ctxd), T, n_heads,
                                    n_kv, 1, None, None, ptr(out1), stream()))
     # fused path
-    kc2, vc2 = dev(kc).clone(), dev(vc).clone()
+    kc2, vc2 = dev(swizzle_kv(kc)).clone(), dev(swizzle_kv(vc)).clone()
     out2 = torch.empty_like(qo)
     scratch = torch.empty(lib().b200_op_attn_scratch_bytes(T, n_heads, n_kv, n_splits) // 4, dtype=torch.float32, device="cuda")
     counters = torch.zeros(T * n_kv, dtype=torch.int32, device="cuda")
@@ -228,7 +228,8 @@ def test_rope_kv_write_matches_oracle():
         x1, x2 = x[..., :64].astype(np.float64), x[..., 64:].astype(np.float64)
         return np.concatenate([x1 * c - x2 * s, x2 * c + x1 * s], -1)
 
-    kcn, vcn, qon = kc.cpu().numpy(), vc.cpu().numpy(), qo.cpu().numpy().reshape(T, n_heads, 128)
+    kcn, vcn = unswizzle_kv(kc.cpu().numpy()), unswizzle_kv(vc.cpu().numpy())      # physical rows -> logical
+    qon = qo.cpu().numpy().reshape(T, n_heads, 128)
     for t in range(T):
         row = qkv[t].reshape(n_heads + 2 * n_kv, 128)
         assert np.abs(qon[t].astype(np.float64) - rot(row[:n_heads], pos[t])).max() < 4e-3

@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 from tests.gpu_util import lib, ptr, stream, check  # noqa: E402
 from vgate_b200 import _lib  # noqa: E402
 
-TOL = 3e-3          # the tolerance of the attention parity tests (one fp16 rounding of O(1) values)
+TOL = 4e-3          # the tolerance of the attention parity tests (tests/test_kernels_gpu.py)
 
 
 def _case(rng, ctx_lens, n_heads, n_kv):

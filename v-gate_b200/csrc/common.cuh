@@ -120,6 +120,12 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
                ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// ---- paged KV cache row layout ----------------------------------------------------------------
+// A cached row (one token, one kv head) is 128 fp16 = sixteen 16-byte chunks.  Chunk c of the row at
+// token offset r inside its block is stored at chunk position c ^ (r & 7): a bulk copy of the block
+// then lands in shared memory already in the bank-conflict-free layout ldmatrix wants.
+__host__ __device__ __forceinline__ int kv_swz(int r, int dim) { return ((((dim >> 3) ^ (r & 7)) << 3) | (dim & 7)); }
+
 // ---- programmatic dependent launch (PDL) ------------------------------------------------------
 // Every kernel of the step starts with pdl_prologue(): it lets the next kernel in the stream begin
 // launching (its set-up and weight prefetch overlap our execution) and then blocks until the

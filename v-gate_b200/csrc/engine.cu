@@ -190,7 +190,9 @@ struct b200_engine {
   bool skip(int bit) const { return (debug_skip >> bit) & 1; }
   DevMem parts;                                  // fp32 split-K partials [splits][T][N]
   DevMem attn_scratch, attn_counters;            // flash-decoding partials + per-(row, kv head) arrival counters
-  static constexpr int kDecodeSplits = 8;        // KV splits of the decode attention (64-token chunks, round-robin)
+  // KV splits of the decode attention across CTAs.  1: the four warps of a CTA already take different
+  // 64-token chunks, and a split count that followed the batch size would make bits batch-dependent.
+  static constexpr int kDecodeSplits = 1;
 
   // y (+)= x . W^T.  Returns in *n_parts_out how many partial tensors were written to `parts`
   // instead (0: the result is already in y).

@@ -24,21 +24,21 @@
 namespace b200 {
 
 constexpr int kAttnThreads = 128;
+constexpr int kAttnWarps = 4;
 constexpr int kChunkTokens = 64;
 constexpr int kChunkBlocks = kChunkTokens / kBlockTokens;            // 4
 constexpr int kKvBlockBytes = kBlockTokens * kHeadDim * 2;           // 4096
-constexpr int kStageBytes = kChunkTokens * kHeadDim * 2;             // 16384 per K or V tile
+constexpr int kTileBytes = kChunkTokens * kHeadDim * 2;              // 16384 per K or V tile
 constexpr int kPartFloats = kHeadDim + 2;                            // acc[128], max, sum
 
-template <int GQ>
+// Shared memory: per warp one K tile + one V tile (a warp owns whole 64-token chunks), then the
+// query tile [16 rows][128] fp16 (rows >= GQ are zero) and the new token's k / v (fused mode).
 struct AttnSmem {
-  static constexpr int kOffK = 0;
-  static constexpr int kOffV = kStageBytes;
-  static constexpr int kOffQ = 2 * kStageBytes;                      // [GQ][128] half
-  static constexpr int kOffP = kOffQ + GQ * kHeadDim * 2;            // [GQ][64] float
-  static constexpr int kOffM = kOffP + GQ * kChunkTokens * 4;        // m[GQ], l[GQ], corr[GQ]
-  static constexpr int kOffBar = (kOffM + 3 * GQ * 4 + 15) / 16 * 16;
-  static constexpr int kBytes = kOffBar + 16;
+  static constexpr int kOffTiles = 0;                                // kAttnWarps x (K 16 KB + V 16 KB)
+  static constexpr int kOffQ = kAttnWarps * 2 * kTileBytes;          // 4 KB
+  static constexpr int kOffNew = kOffQ + 16 * kHeadDim * 2;          // k[128], v[128] fp16
+  static constexpr int kOffBar = kOffNew + 2 * kHeadDim * 2;
+  static constexpr int kBytes = kOffBar + kAttnWarps * 8;
 };
 
 static unsigned long long* g_attn_trace = nullptr;     // profiling aid: 8 x uint64 clock stamps per CTA
@@ -68,13 +68,37 @@ struct AttnParams {
   __half* out;                   // [T, nh * 128]
 };
 
+__device__ __forceinline__ void ldmatrix_x4(uint32_t saddr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(saddr));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t saddr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(saddr));
+}
+// D (fp32, 16x8) += A (fp16, 16x16, row) * B (fp16, 16x8, col)
+__device__ __forceinline__ void mma_16816(float d[4], const uint32_t a[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// One warp scores whole 64-token chunks with tensor-core MMAs (mma.sync m16n8k16; the 6..8 query
+// heads of the group are the M rows, padded to 16):
+//     S[16 heads, 64 tok] = Q K^T      (A = Q from smem via ldmatrix, B = K rows via ldmatrix)
+//     online softmax in registers (fp32), P rounded to fp16 as the next A operand
+//     O[16 heads, 128]  += P V          (B = V via ldmatrix.trans)
+// Rows of a KV block are stored with their 16-byte chunks XOR-swizzled by (token & 7) -- in the cache
+// itself -- so that the bulk copy needs no re-layout and every ldmatrix is bank-conflict free.
 template <int GQ, bool kFused>
 __global__ void __launch_bounds__(kAttnThreads)
 paged_attn_kernel(const AttnParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  using L = AttnSmem<GQ>;
+  using L = AttnSmem;
+  static_assert(GQ <= 8, "one m16 tile, upper half unused");
   pdl_prologue();
   const int j = blockIdx.x, t = blockIdx.y, split = blockIdx.z, tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
   unsigned long long* tr = p.trace ? p.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
   if (tr && tid == 0) tr[0] = clock64();
   const int n_heads = p.n_heads, n_kv = p.n_kv, S = p.n_splits;
@@ -93,37 +117,38 @@ paged_attn_kernel(const AttnParams p) {
   const int32_t* bt = p.block_tables + (size_t)p.bt_row[t] * p.bt_stride;
   const int nblocks = (len + kBlockTokens - 1) / kBlockTokens;
 
-  __half* q_s = reinterpret_cast<__half*>(smem + L::kOffQ);
-  float* p_s = reinterpret_cast<float*>(smem + L::kOffP);
-  float* m_s = reinterpret_cast<float*>(smem + L::kOffM);
-  float* l_s = m_s + GQ;
-  float* c_s = l_s + GQ;
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + L::kOffBar);
-  __half* Ks_h = reinterpret_cast<__half*>(smem + L::kOffK);
-  __half* Vs_h = reinterpret_cast<__half*>(smem + L::kOffV);
+  unsigned char* q_s = smem + L::kOffQ;
+  __half* new_s = reinterpret_cast<__half*>(smem + L::kOffNew);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + L::kOffBar) + warp;
+  unsigned char* Kt = smem + L::kOffTiles + warp * 2 * kTileBytes;
+  unsigned char* Vt = Kt + kTileBytes;
 
-  if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
-  if (tid < GQ) { m_s[tid] = -INFINITY; l_s[tid] = 0.f; }
-
-  auto issue_chunk = [&](int c) {   // one thread
+  // chunks of this CTA: c = split + S * i; warp w takes i = w, w + 4, ...
+  auto issue_chunk = [&](int c) {   // lane 0 of the owning warp
     const int b0 = c * kChunkBlocks;
     const int nb = min(kChunkBlocks, nblocks - b0);
     mbar_arrive_expect_tx(bar, (uint32_t)nb * 2u * kKvBlockBytes);
     for (int i = 0; i < nb; ++i) {
       const size_t off = ((size_t)bt[b0 + i] * n_kv + j) * (size_t)(kBlockTokens * kHeadDim);
-      bulk_g2s(smem + L::kOffK + i * kKvBlockBytes, p.k_cache + off, kKvBlockBytes, bar);
-      bulk_g2s(smem + L::kOffV + i * kKvBlockBytes, p.v_cache + off, kKvBlockBytes, bar);
+      bulk_g2s(Kt + i * kKvBlockBytes, p.k_cache + off, kKvBlockBytes, bar);
+      bulk_g2s(Vt + i * kKvBlockBytes, p.v_cache + off, kKvBlockBytes, bar);
     }
   };
-  __syncthreads();
-  if (tid == 0) issue_chunk(split);
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+    const int c0 = split + S * warp;
+    if (c0 < nchunks) issue_chunk(c0);
+  }
   if (tr && tid == 0) tr[1] = clock64();
 
-  // ---- queries (and, in fused mode, the new token's k / v) ----
+  // ---- queries -> swizzled smem tile (and, in fused mode, the new token's k / v) ----
+  // q_s row h (256 B), logical 16-byte chunk cc -> physical chunk cc ^ (h & 7)
+  auto q_addr = [&](int h, int dim) { return q_s + h * 256 + ((((dim >> 3) ^ (h & 7)) << 4) | ((dim & 7) << 1)); };
+  for (int i = tid; i < 16 * 16; i += kAttnThreads)                  // zero rows GQ..15 (and everything else first)
+    if ((i >> 4) >= GQ) reinterpret_cast<uint4*>(q_s)[i] = make_uint4(0, 0, 0, 0);
   const int new_pos = len - 1;                      // fused: position of the token being decoded
   const int new_chunk = new_pos / kChunkTokens;
-  float knew1 = 0.f, knew2 = 0.f, vnew = 0.f;       // fused owner: thread tid < 64 holds k pair (tid, tid+64); all hold v[tid]
-  bool owner = false;
   if constexpr (kFused) {
     const int total = (n_heads + 2 * n_kv) * kHeadDim;
     const float* row = p.qkv + (size_t)t * total;
@@ -139,161 +164,197 @@ paged_attn_kernel(const AttnParams p) {
       const int col = (j * GQ + h) * kHeadDim + i;
       const float x1 = load(col), x2 = load(col + 64);
       const float c = p.cos_t[(size_t)ps * 64 + i], sn = p.sin_t[(size_t)ps * 64 + i];
-      q_s[h * kHeadDim + i] = __float2half_rn(x1 * c - x2 * sn);
-      q_s[h * kHeadDim + i + 64] = __float2half_rn(x2 * c + x1 * sn);
+      *reinterpret_cast<__half*>(q_addr(h, i)) = __float2half_rn(x1 * c - x2 * sn);
+      *reinterpret_cast<__half*>(q_addr(h, i + 64)) = __float2half_rn(x2 * c + x1 * sn);
     }
-    owner = (new_chunk % S) == split;
-    if (owner) {
+    if ((new_chunk % S) == split) {                 // this CTA owns the chunk that holds the new token
       const int kcol = (n_heads + j) * kHeadDim, vcol = (n_heads + n_kv + j) * kHeadDim;
-      vnew = load(vcol + tid);
+      const __half vnew = __float2half_rn(load(vcol + tid));
+      new_s[kHeadDim + tid] = vnew;
+      __half k1 = __float2half_rn(0.f), k2 = k1;
       if (tid < 64) {
         const float x1 = load(kcol + tid), x2 = load(kcol + tid + 64);
         const float c = p.cos_t[(size_t)ps * 64 + tid], sn = p.sin_t[(size_t)ps * 64 + tid];
-        knew1 = x1 * c - x2 * sn;
-        knew2 = x2 * c + x1 * sn;
+        k1 = __float2half_rn(x1 * c - x2 * sn);
+        k2 = __float2half_rn(x2 * c + x1 * sn);
+        new_s[tid] = k1;
+        new_s[tid + 64] = k2;
       }
       const int sl = p.slot[t];
-      if (sl >= 0) {
-        const size_t off = (((size_t)(sl / kBlockTokens) * n_kv + j) * kBlockTokens + sl % kBlockTokens) * kHeadDim;
-        p.v_cache[off + tid] = __float2half_rn(vnew);
+      if (sl >= 0) {                                // paged cache write (swizzled row)
+        const int r = sl % kBlockTokens;
+        const size_t rowoff = (((size_t)(sl / kBlockTokens) * n_kv + j) * kBlockTokens + r) * kHeadDim;
+        p.v_cache[rowoff + kv_swz(r, tid)] = vnew;
         if (tid < 64) {
-          p.k_cache[off + tid] = __float2half_rn(knew1);
-          p.k_cache[off + tid + 64] = __float2half_rn(knew2);
+          p.k_cache[rowoff + kv_swz(r, tid)] = k1;
+          p.k_cache[rowoff + kv_swz(r, tid + 64)] = k2;
         }
       }
     }
   } else {
-    const uint4* qg = reinterpret_cast<const uint4*>(p.q + ((size_t)t * n_heads + (size_t)j * GQ) * kHeadDim);
-    for (int i = tid; i < GQ * 16; i += kAttnThreads) reinterpret_cast<uint4*>(q_s)[i] = qg[i];
+    const __half* qg = p.q + ((size_t)t * n_heads + (size_t)j * GQ) * kHeadDim;
+    for (int i = tid; i < GQ * 16; i += kAttnThreads) {              // 16-byte chunks
+      const int h = i >> 4, cc = i & 15;
+      *reinterpret_cast<uint4*>(q_s + h * 256 + ((cc ^ (h & 7)) << 4)) = *reinterpret_cast<const uint4*>(qg + h * kHeadDim + cc * 8);
+    }
+  }
+  __syncthreads();
+
+  // Q as the MMA A operand: 8 k-steps x {a0a1, a2a3, a4a5, a6a7}
+  uint32_t qa[8][4];
+  {
+    const int mj = lane >> 3, mr = lane & 7;        // ldmatrix.x4: lane -> (matrix, row)
+    const int h = (mj & 1) * 8 + mr;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      const int cc = 2 * ks + (mj >> 1);
+      ldmatrix_x4(smem_u32(q_s + h * 256 + ((cc ^ (h & 7)) << 4)), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
+    }
   }
 
-  float acc[GQ];
+  const int g = lane >> 2, tq = lane & 3;           // MMA fragment coordinates
+  float o[16][2];                                   // O[row g][dims 8 dn + 2 tq, +1]  (rows g + 8 are padding)
 #pragma unroll
-  for (int h = 0; h < GQ; ++h) acc[h] = 0.f;
-  constexpr int HH = (GQ + 1) / 2;          // heads scored per thread (two thread halves)
-  const int tok = tid & 63, hg = tid >> 6;
-  const float scale = 0.08838834764831845f; // 1 / sqrt(128)
-  const uint4* q_s4 = reinterpret_cast<const uint4*>(q_s);
+  for (int dn = 0; dn < 16; ++dn) o[dn][0] = o[dn][1] = 0.f;
+  float m_run = -INFINITY, l_run = 0.f;             // running max / sum of row g (replicated over the quad)
+  const float scale = 0.08838834764831845f;         // 1 / sqrt(128)
 
   int it = 0;
-  for (int c = split; c < nchunks; c += S, ++it) {
+  for (int c = split + S * warp; c < nchunks; c += S * kAttnWarps, ++it) {
     if (it > 0) {
-      __syncthreads();                      // everyone is done with the previous tile
-      if (tid == 0) issue_chunk(c);
+      __syncwarp();
+      if (lane == 0) issue_chunk(c);
     }
     if (tr && tid == 0 && it == 0) tr[2] = clock64();
     mbar_wait(bar, (uint32_t)it & 1u);
     if (tr && tid == 0 && it == 0) tr[3] = clock64();
     const int nvalid = min(kChunkTokens, len - c * kChunkTokens);
+    const int nb = (nvalid + kBlockTokens - 1) / kBlockTokens;
     if constexpr (kFused) {
-      if (owner && c == new_chunk) {        // the cache row of the new token is not in HBM yet: patch the tile
-        const int rrow = new_pos - c * kChunkTokens;
-        Vs_h[rrow * kHeadDim + tid] = __float2half_rn(vnew);
-        if (tid < 64) {
-          Ks_h[rrow * kHeadDim + tid] = __float2half_rn(knew1);
-          Ks_h[rrow * kHeadDim + tid + 64] = __float2half_rn(knew2);
+      if (c == new_chunk) {                         // the cache row of the new token is not in HBM yet: patch the tile
+        const int rr = new_pos - c * kChunkTokens, r = rr % kBlockTokens;
+        unsigned char* kr = Kt + (rr / kBlockTokens) * kKvBlockBytes + r * 256;
+        unsigned char* vr = Vt + (rr / kBlockTokens) * kKvBlockBytes + r * 256;
+        if (lane < 16) {
+          *reinterpret_cast<uint4*>(kr + ((lane ^ (r & 7)) << 4)) = reinterpret_cast<const uint4*>(new_s)[lane];
+          *reinterpret_cast<uint4*>(vr + ((lane ^ (r & 7)) << 4)) = reinterpret_cast<const uint4*>(new_s + kHeadDim)[lane];
         }
+        __syncwarp();
       }
     }
-    __syncthreads();                        // q_s (first pass) and the patched rows are visible
 
-    // ---- scores: thread = (token, half of the head group) ----
-    {
-      const uint4* Ks = reinterpret_cast<const uint4*>(Ks_h);
-      float sacc[HH];
+    // ---- S = Q K^T : 8 token tiles of 8 ----
+    float sc[8][2];
 #pragma unroll
-      for (int i = 0; i < HH; ++i) sacc[i] = 0.f;
-      if (tok < nvalid) {
+    for (int nt = 0; nt < 8; ++nt) {
+      float d[4] = {0.f, 0.f, 0.f, 0.f};
+      if (nt * 8 < nvalid) {
+        const int mj = lane >> 3, tok = nt * 8 + (lane & 7);
+        const uint32_t rowaddr = smem_u32(Kt + (tok >> 4) * kKvBlockBytes + (tok & 15) * 256);
 #pragma unroll
-        for (int s = 0; s < 16; ++s) {
-          const int cc = (s + tok) & 15;                       // rotated start: conflict-free 16 B reads
-          const uint4 kv = Ks[tok * 16 + cc];
-#pragma unroll
-          for (int i = 0; i < HH; ++i) {
-            const int h = hg * HH + i;
-            if (h < GQ) {
-              const uint4 qv = q_s4[h * 16 + cc];
-              sacc[i] = fhfma2(kv.x, qv.x, sacc[i]);
-              sacc[i] = fhfma2(kv.y, qv.y, sacc[i]);
-              sacc[i] = fhfma2(kv.z, qv.z, sacc[i]);
-              sacc[i] = fhfma2(kv.w, qv.w, sacc[i]);
-            }
-          }
+        for (int k2 = 0; k2 < 4; ++k2) {            // two k-steps per ldmatrix.x4
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4(rowaddr + ((((4 * k2 + mj) ^ (tok & 7))) << 4), b0, b1, b2, b3);
+          mma_16816(d, qa[2 * k2], b0, b1);
+          mma_16816(d, qa[2 * k2 + 1], b2, b3);
         }
       }
-#pragma unroll
-      for (int i = 0; i < HH; ++i) {
-        const int h = hg * HH + i;
-        if (h < GQ) p_s[h * kChunkTokens + tok] = tok < nvalid ? sacc[i] * scale : -INFINITY;
-      }
+      const int t0 = nt * 8 + 2 * tq;
+      sc[nt][0] = t0 < nvalid ? d[0] * scale : -INFINITY;
+      sc[nt][1] = t0 + 1 < nvalid ? d[1] * scale : -INFINITY;
     }
-    __syncthreads();
     if (tr && tid == 0 && it == 0) tr[4] = clock64();
 
-    // ---- online softmax: warp w owns heads w, w+4 ----
-    {
-      const int warp = tid >> 5, lane = tid & 31;
-      for (int h = warp; h < GQ; h += kAttnThreads / 32) {
-        const float s0 = p_s[h * kChunkTokens + lane], s1 = p_s[h * kChunkTokens + lane + 32];
-        const float m_old = m_s[h];
-        const float m_new = fmaxf(m_old, warp_max(fmaxf(s0, s1)));
-        const float p0 = expf(s0 - m_new), p1 = expf(s1 - m_new);
-        const float sum = warp_sum(p0 + p1);
-        p_s[h * kChunkTokens + lane] = p0;
-        p_s[h * kChunkTokens + lane + 32] = p1;
-        if (lane == 0) {
-          const float corr = expf(m_old - m_new);
-          c_s[h] = corr;
-          l_s[h] = l_s[h] * corr + sum;
-          m_s[h] = m_new;
-        }
-      }
+    // ---- online softmax for row g (the quad holds the row's 64 scores) ----
+    float mx = -INFINITY;
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) mx = fmaxf(mx, fmaxf(sc[nt][0], sc[nt][1]));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+    const float m_new = fmaxf(m_run, mx);
+    const float corr = expf(m_run - m_new);
+    float sum = 0.f;
+    uint32_t pa[4][4];                              // P as A operand: 4 k-steps of 16 tokens; rows g + 8 are zero
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      const float p0 = expf(sc[nt][0] - m_new), p1 = expf(sc[nt][1] - m_new);
+      sum += p0 + p1;
+      pa[nt >> 1][(nt & 1) * 2] = pack_half2(p0, p1);
+      pa[nt >> 1][(nt & 1) * 2 + 1] = 0u;
     }
-    __syncthreads();
+    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+    sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+    l_run = l_run * corr + sum;
+    m_run = m_new;
+#pragma unroll
+    for (int dn = 0; dn < 16; ++dn) { o[dn][0] *= corr; o[dn][1] *= corr; }
     if (tr && tid == 0 && it == 0) tr[5] = clock64();
 
-    // ---- PV: thread owns output dim d = tid for all GQ heads ----
-    {
+    // ---- O += P V : k-step kt = KV block kt of the chunk ----
 #pragma unroll
-      for (int h = 0; h < GQ; ++h) acc[h] *= c_s[h];
-      const int n4 = nvalid & ~3;
-      for (int tk = 0; tk < n4; tk += 4) {
-        const float v0 = __half2float(Vs_h[(tk + 0) * kHeadDim + tid]);
-        const float v1 = __half2float(Vs_h[(tk + 1) * kHeadDim + tid]);
-        const float v2 = __half2float(Vs_h[(tk + 2) * kHeadDim + tid]);
-        const float v3 = __half2float(Vs_h[(tk + 3) * kHeadDim + tid]);
+    for (int kt = 0; kt < 4; ++kt) {
+      if (kt < nb) {
+        const int mj = lane >> 3, r = (mj & 1) * 8 + (lane & 7);
+        const uint32_t rowaddr = smem_u32(Vt + kt * kKvBlockBytes + r * 256);
 #pragma unroll
-        for (int h = 0; h < GQ; ++h) {
-          const float4 pv = *reinterpret_cast<const float4*>(p_s + h * kChunkTokens + tk);
-          acc[h] = fmaf(pv.x, v0, acc[h]);
-          acc[h] = fmaf(pv.y, v1, acc[h]);
-          acc[h] = fmaf(pv.z, v2, acc[h]);
-          acc[h] = fmaf(pv.w, v3, acc[h]);
+        for (int d2 = 0; d2 < 8; ++d2) {            // two 8-dim tiles per ldmatrix.x4.trans
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4_trans(rowaddr + (((2 * d2 + (mj >> 1)) ^ (r & 7)) << 4), b0, b1, b2, b3);
+          float d[4] = {o[2 * d2][0], o[2 * d2][1], 0.f, 0.f};
+          mma_16816(d, pa[kt], b0, b1);
+          o[2 * d2][0] = d[0]; o[2 * d2][1] = d[1];
+          float e[4] = {o[2 * d2 + 1][0], o[2 * d2 + 1][1], 0.f, 0.f};
+          mma_16816(e, pa[kt], b2, b3);
+          o[2 * d2 + 1][0] = e[0]; o[2 * d2 + 1][1] = e[1];
         }
-      }
-      for (int tk = n4; tk < nvalid; ++tk) {
-        const float v0 = __half2float(Vs_h[tk * kHeadDim + tid]);
-#pragma unroll
-        for (int h = 0; h < GQ; ++h) acc[h] = fmaf(p_s[h * kChunkTokens + tk], v0, acc[h]);
       }
     }
   }
-
   if (tr && tid == 0) tr[6] = clock64();
-  if (n_active == 1) {                      // single split: finish locally
-    __syncthreads();
+
+  // ---- merge the four warps in shared memory (their tiles are free now) ----
+  __syncthreads();
+  float* mrg = reinterpret_cast<float*>(smem + L::kOffTiles) + (size_t)warp * (8 * kPartFloats);   // [8 rows][130]
+  if (g < GQ) {
 #pragma unroll
-    for (int h = 0; h < GQ; ++h) orow[h * kHeadDim + tid] = __float2half_rn(acc[h] / l_s[h]);
+    for (int dn = 0; dn < 16; ++dn) {
+      mrg[g * kPartFloats + dn * 8 + 2 * tq] = o[dn][0];
+      mrg[g * kPartFloats + dn * 8 + 2 * tq + 1] = o[dn][1];
+    }
+    if (tq == 0) { mrg[g * kPartFloats + kHeadDim] = m_run; mrg[g * kPartFloats + kHeadDim + 1] = l_run; }
+  }
+  __syncthreads();
+  const float* all = reinterpret_cast<const float*>(smem + L::kOffTiles);
+  float num[GQ], den[GQ], mxh[GQ];
+#pragma unroll
+  for (int h = 0; h < GQ; ++h) {
+    float M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < kAttnWarps; ++w) M = fmaxf(M, all[(w * 8 + h) * kPartFloats + kHeadDim]);
+    float nu = 0.f, de = 0.f;
+#pragma unroll
+    for (int w = 0; w < kAttnWarps; ++w) {          // fixed warp order: deterministic
+      const float* pw = all + (w * 8 + h) * kPartFloats;
+      const float wgt = expf(pw[kHeadDim] - M);     // a warp without chunks has max = -inf -> weight 0
+      nu = fmaf(pw[tid], wgt, nu);
+      de = fmaf(pw[kHeadDim + 1], wgt, de);
+    }
+    num[h] = nu; den[h] = de; mxh[h] = M;
+  }
+  if (n_active == 1) {                              // single split: finished
+#pragma unroll
+    for (int h = 0; h < GQ; ++h) orow[h * kHeadDim + tid] = __float2half_rn(num[h] / den[h]);
     return;
   }
 
-  // ---- publish this split's partial, then let the last split to arrive merge all of them ----
+  // ---- several splits: publish this CTA's partial; the last CTA to arrive merges them all ----
   float* base = p.scratch + ((size_t)(t * n_kv + j) * S) * GQ * kPartFloats;
   float* mine = base + (size_t)split * GQ * kPartFloats;
-  __syncthreads();
 #pragma unroll
-  for (int h = 0; h < GQ; ++h) mine[h * kPartFloats + tid] = acc[h];
-  if (tid < GQ) { mine[tid * kPartFloats + kHeadDim] = m_s[tid]; mine[tid * kPartFloats + kHeadDim + 1] = l_s[tid]; }
+  for (int h = 0; h < GQ; ++h) {
+    mine[h * kPartFloats + tid] = num[h];
+    if (tid == 0) { mine[h * kPartFloats + kHeadDim] = mxh[h]; mine[h * kPartFloats + kHeadDim + 1] = den[h]; }
+  }
   __threadfence();
   __syncthreads();
   __shared__ int s_last;
@@ -305,18 +366,30 @@ paged_attn_kernel(const AttnParams p) {
   __syncthreads();
   if (!s_last) return;
   __threadfence();
+  float pm[GQ][8], pl[GQ][8];                       // S <= 64 in general; merged 8 at a time below
 #pragma unroll
   for (int h = 0; h < GQ; ++h) {
     float M = -INFINITY;
-    for (int s = 0; s < n_active; ++s) M = fmaxf(M, __ldcg(base + ((size_t)s * GQ + h) * kPartFloats + kHeadDim));
-    float num = 0.f, den = 0.f;
-    for (int s = 0; s < n_active; ++s) {            // fixed split order: deterministic
-      const float* ps = base + ((size_t)s * GQ + h) * kPartFloats;
-      const float w = expf(__ldcg(ps + kHeadDim) - M);
-      num = fmaf(__ldcg(ps + tid), w, num);
-      den = fmaf(__ldcg(ps + kHeadDim + 1), w, den);
+    for (int s0 = 0; s0 < n_active; ++s0) M = fmaxf(M, __ldcg(base + ((size_t)s0 * GQ + h) * kPartFloats + kHeadDim));
+    float nu = 0.f, de = 0.f;
+    for (int s0 = 0; s0 < n_active; s0 += 8) {      // fixed split order: deterministic; 8 loads in flight
+      const int nn = min(8, n_active - s0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (k < nn) {
+          const float* ps = base + ((size_t)(s0 + k) * GQ + h) * kPartFloats;
+          pm[h][k] = __ldcg(ps + tid);
+          pl[h][k] = expf(__ldcg(ps + kHeadDim) - M);
+        }
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (k < nn) {
+          const float* ps = base + ((size_t)(s0 + k) * GQ + h) * kPartFloats;
+          nu = fmaf(pm[h][k], pl[h][k], nu);
+          de = fmaf(__ldcg(ps + kHeadDim + 1), pl[h][k], de);
+        }
     }
-    orow[h * kHeadDim + tid] = __float2half_rn(num / den);
+    orow[h * kHeadDim + tid] = __float2half_rn(nu / de);
   }
 }
 
@@ -325,11 +398,11 @@ static int launch_gq(const AttnParams& p, int T, cudaStream_t s) {
   static bool configured = false;   // per process; the attribute is idempotent
   auto kern = paged_attn_kernel<GQ, kFused>;
   if (!configured) {
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnSmem<GQ>::kBytes));
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnSmem::kBytes));
     configured = true;
   }
   dim3 grid(p.n_kv, T, p.n_splits);
-  B200_CUDA(launch_k(kern, grid, dim3(kAttnThreads), (size_t)AttnSmem<GQ>::kBytes, s, p));
+  B200_CUDA(launch_k(kern, grid, dim3(kAttnThreads), (size_t)AttnSmem::kBytes, s, p));
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;

@@ -209,13 +209,13 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_parts, int64
         const int j = head - n_heads;
         const float c = cos_t[(size_t)p * 64 + i], sn = sin_t[(size_t)p * 64 + i];
         __half* o = k_cache + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
-        o[i] = __float2half_rn(x1 * c - x2 * sn);
-        o[i + 64] = __float2half_rn(x2 * c + x1 * sn);
+        o[kv_swz(off, i)] = __float2half_rn(x1 * c - x2 * sn);       // swizzled row layout, see common.cuh
+        o[kv_swz(off, i + 64)] = __float2half_rn(x2 * c + x1 * sn);
       } else {
         const int j = head - n_heads - n_kv;
         __half* o = v_cache + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
-        o[i] = __float2half_rn(x1);
-        o[i + 64] = __float2half_rn(x2);
+        o[kv_swz(off, i)] = __float2half_rn(x1);
+        o[kv_swz(off, i + 64)] = __float2half_rn(x2);
       }
     }
   }
