@@ -21,4 +21,4 @@ def run(T, ctx, n_splits, n_heads=12, n_kv=2):
     d=t[:,1:7]-t[:,0:1]
     names=['copies issued','wait start','tile landed','scores done','softmax done','loop end']
     print(f'T={T} ctx={ctx} splits={n_splits} active ctas={len(t)}: '+', '.join(f'{n} {np.median(d[:,i]):.0f}' for i,n in enumerate(names)))
-run(64,256,8); run(64,256,1); run(8,256,8); run(64,64,1)
+run(64,256,1); run(64,384,1); run(8,256,1)

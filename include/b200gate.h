@@ -167,6 +167,10 @@ int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits);
 void b200_debug_umma_trace(void* dev_buf);
 /* Same for the attention kernel (entry, copies issued, wait start, tile landed, scores, softmax, loop end). */
 void b200_debug_attn_trace(void* dev_buf);
+/* In-situ timeline: while `buf` (device, capacity x 4 uint64) and `counter` (device uint32, zeroed by the
+ * caller) are installed, block 0 of every kernel appends {kernel id | grid, entry, ready, exit} in
+ * %globaltimer nanoseconds.  NULL buf switches it off.  Works under CUDA-graph replay. */
+void b200_debug_timeline(void* buf, void* counter, uint32_t capacity);
 /* tcgen05/TMEM GEMM with dense fp16 weights W[N, K] fed by TMA (lm_head); N % 128 == 0, K % 64 == 0. */
 int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T,
                               int32_t K, int32_t N, int32_t accumulate, void* stream);

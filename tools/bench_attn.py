@@ -62,8 +62,8 @@ def bench(T, ctx, n_splits, fused, n_heads=12, n_kv=2, n_copies=8, reps=20):
 if __name__ == "__main__":
     print(torch.cuda.get_device_name())
     for ctx in (128, 256, 384, 1024):
-        for sp_ in (1, 8):
-            bench(64, ctx, sp_, False)
-        bench(64, ctx, 8, True)
-    bench(8, 256, 8, True)
-    bench(128, 256, 8, True)
+        bench(64, ctx, 1, False)
+        bench(64, ctx, 1, True)
+    bench(8, 256, 1, True)
+    bench(128, 256, 1, True)
+    bench(256, 256, 1, True)

@@ -120,6 +120,13 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
                ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// ---- RoPE rotation (neox halves), one definition so that every kernel rounds identically -----------
+// (left to the compiler, x1*c - x2*s may or may not be contracted into an FMA, per call site)
+__device__ __forceinline__ void rope_rotate(float x1, float x2, float c, float s, float& o1, float& o2) {
+  o1 = __fmaf_rn(x1, c, -__fmul_rn(x2, s));
+  o2 = __fmaf_rn(x2, c, __fmul_rn(x1, s));
+}
+
 // ---- paged KV cache row layout ----------------------------------------------------------------
 // A cached row (one token, one kv head) is 128 fp16 = sixteen 16-byte chunks.  Chunk c of the row at
 // token offset r inside its block is stored at chunk position c ^ (r & 7): a bulk copy of the block
@@ -133,5 +140,44 @@ __host__ __device__ __forceinline__ int kv_swz(int r, int dim) { return ((((dim 
 __device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_prologue() { grid_dep_launch(); grid_dep_wait(); }
+
+// ---- in-situ timeline (profiling aid, off unless b200_debug_timeline() installed a buffer) --------
+// Block (0,0,0) thread 0 of every kernel records %globaltimer (32 ns ticks on B200) at entry, after
+// the PDL dependency wait, and at exit: 4 x uint64 per launch {kernel id, entry, ready, exit}.
+struct Timeline { unsigned long long* buf; unsigned int* ctr; unsigned int cap; };
+static __device__ Timeline d_tl;                 // one copy per translation unit, set by its tl_set_*()
+#define B200_DEFINE_TL_SETTER(name)                                                         \
+  void name(unsigned long long* buf, unsigned int* ctr, unsigned int cap) {               \
+    Timeline t{buf, ctr, cap};                                                              \
+    cudaMemcpyToSymbol(d_tl, &t, sizeof(t));                                                \
+  }
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+enum KernelId { kKidEmbed = 1, kKidRmsnorm, kKidRope, kKidAttn, kKidSwiglu, kKidW4Gemv, kKidF16Gemv, kKidUmmaW4,
+                kKidUmmaF16, kKidSample, kKidAdvance };
+// PDL prologue + timeline entry; returns the timeline slot (or ~0u).
+__device__ __forceinline__ unsigned kernel_prologue(int kid) {
+  unsigned slot = ~0u;
+  const bool rec = d_tl.buf && threadIdx.x == 0 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
+  unsigned long long t0 = 0;
+  if (rec) t0 = gtime();
+  grid_dep_launch();
+  grid_dep_wait();
+  if (rec) {
+    slot = atomicAdd(d_tl.ctr, 1u);
+    if (slot < d_tl.cap) {
+      d_tl.buf[4 * slot] = (unsigned long long)kid | ((unsigned long long)gridDim.x << 8) | ((unsigned long long)gridDim.y << 28) | ((unsigned long long)gridDim.z << 48);
+      d_tl.buf[4 * slot + 1] = t0;
+      d_tl.buf[4 * slot + 2] = gtime();
+    } else slot = ~0u;
+  }
+  return slot;
+}
+__device__ __forceinline__ void kernel_epilogue(unsigned slot) {
+  if (slot != ~0u) d_tl.buf[4 * slot + 3] = gtime();
+}
 
 }  // namespace b200

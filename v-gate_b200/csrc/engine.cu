@@ -36,6 +36,13 @@ int cuda_fail(cudaError_t err, const char* what, const char* file, int line) {
   return B200_ERR_CUDA;
 }
 
+B200_DEFINE_TL_SETTER(tl_set_engine)
+void tl_set_basic(unsigned long long*, unsigned int*, unsigned int);
+void tl_set_gemv(unsigned long long*, unsigned int*, unsigned int);
+void tl_set_attn(unsigned long long*, unsigned int*, unsigned int);
+void tl_set_sample(unsigned long long*, unsigned int*, unsigned int);
+void tl_set_umma(unsigned long long*, unsigned int*, unsigned int);
+
 static double now_s() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -48,7 +55,7 @@ __global__ void advance_decode_kernel(int B, const int32_t* __restrict__ next_id
                                       int32_t* __restrict__ ctx, int32_t* __restrict__ n_gen,
                                       const int32_t* __restrict__ bt_row, const int32_t* __restrict__ block_tables,
                                       int bt_stride, int32_t* __restrict__ out_tokens, int out_stride) {
-  pdl_prologue();
+  const unsigned tl = kernel_prologue(kKidAdvance);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B) return;
   const int tok = next_ids[i];
@@ -61,6 +68,7 @@ __global__ void advance_decode_kernel(int B, const int32_t* __restrict__ next_id
   const int blk = p / kBlockTokens;
   slot[i] = blk < bt_stride ? block_tables[(size_t)bt_row[i] * bt_stride + blk] * kBlockTokens + p % kBlockTokens : -1;
   ctx[i] = p + 1;
+  kernel_epilogue(tl);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1065,6 +1073,11 @@ int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, flo
 }
 void b200_debug_umma_trace(void* dev_buf) { umma_set_trace((unsigned long long*)dev_buf); }
 void b200_debug_attn_trace(void* dev_buf) { attn_set_trace((unsigned long long*)dev_buf); }
+void b200_debug_timeline(void* buf, void* counter, uint32_t capacity) {
+  auto* b = (unsigned long long*)buf; auto* c = (unsigned int*)counter;
+  tl_set_engine(b, c, capacity); tl_set_basic(b, c, capacity); tl_set_gemv(b, c, capacity); tl_set_attn(b, c, capacity);
+  tl_set_sample(b, c, capacity); tl_set_umma(b, c, capacity);
+}
 int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits) {
   if (K <= 0 || G <= 0 || K % G != 0 || n_splits < 1) return B200_ERR_INVALID;
   return umma_w4_effective_splits(K, G, n_splits);

@@ -23,6 +23,8 @@
 
 namespace b200 {
 
+B200_DEFINE_TL_SETTER(tl_set_attn)
+
 constexpr int kAttnThreads = 128;
 constexpr int kAttnWarps = 4;
 constexpr int kChunkTokens = 64;
@@ -96,7 +98,7 @@ paged_attn_kernel(const AttnParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = AttnSmem;
   static_assert(GQ <= 8, "one m16 tile, upper half unused");
-  pdl_prologue();
+  const unsigned tl = kernel_prologue(kKidAttn);
   const int j = blockIdx.x, t = blockIdx.y, split = blockIdx.z, tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
   unsigned long long* tr = p.trace ? p.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
@@ -150,37 +152,68 @@ paged_attn_kernel(const AttnParams p) {
   const int new_pos = len - 1;                      // fused: position of the token being decoded
   const int new_chunk = new_pos / kChunkTokens;
   if constexpr (kFused) {
+    // Everything this thread needs is loaded up front -- split-K partials of its q pairs and of
+    // the new k / v, bias, cos / sin -- so the prologue costs two dependent L2 round trips (position,
+    // then data), not one per partial.
     const int total = (n_heads + 2 * n_kv) * kHeadDim;
     const float* row = p.qkv + (size_t)t * total;
-    auto load = [&](int col) {
-      float v = row[col];
-      for (int pp = 1; pp < p.n_parts; ++pp) v += row[pp * p.part_stride + col];
-      if (p.bias) v += __half2float(p.bias[col]);
-      return v;
-    };
+    constexpr int kMaxParts = 4;                                   // loaded in one batch; more are added after
+    constexpr int kPairs = (GQ * 64 + kAttnThreads - 1) / kAttnThreads;      // rotation pairs per thread (3 for GQ = 6)
+    constexpr int NE = 2 * kPairs + 3;                             // + v[tid], k pair (tid & 63)
     const int ps = p.pos[t];
-    for (int idx = tid; idx < GQ * 64; idx += kAttnThreads) {
-      const int h = idx >> 6, i = idx & 63;
-      const int col = (j * GQ + h) * kHeadDim + i;
-      const float x1 = load(col), x2 = load(col + 64);
-      const float c = p.cos_t[(size_t)ps * 64 + i], sn = p.sin_t[(size_t)ps * 64 + i];
-      *reinterpret_cast<__half*>(q_addr(h, i)) = __float2half_rn(x1 * c - x2 * sn);
-      *reinterpret_cast<__half*>(q_addr(h, i + 64)) = __float2half_rn(x2 * c + x1 * sn);
+    const int sl = p.slot[t];
+    const bool own = (new_chunk % S) == split;                     // this CTA owns the chunk that holds the new token
+    int cols[NE];
+#pragma unroll
+    for (int q3 = 0; q3 < kPairs; ++q3) {
+      const int idx = min(tid + q3 * kAttnThreads, GQ * 64 - 1);
+      cols[2 * q3] = (j * GQ + (idx >> 6)) * kHeadDim + (idx & 63);
+      cols[2 * q3 + 1] = cols[2 * q3] + 64;
     }
-    if ((new_chunk % S) == split) {                 // this CTA owns the chunk that holds the new token
-      const int kcol = (n_heads + j) * kHeadDim, vcol = (n_heads + n_kv + j) * kHeadDim;
-      const __half vnew = __float2half_rn(load(vcol + tid));
-      new_s[kHeadDim + tid] = vnew;
-      __half k1 = __float2half_rn(0.f), k2 = k1;
-      if (tid < 64) {
-        const float x1 = load(kcol + tid), x2 = load(kcol + tid + 64);
-        const float c = p.cos_t[(size_t)ps * 64 + tid], sn = p.sin_t[(size_t)ps * 64 + tid];
-        k1 = __float2half_rn(x1 * c - x2 * sn);
-        k2 = __float2half_rn(x2 * c + x1 * sn);
-        new_s[tid] = k1;
-        new_s[tid + 64] = k2;
+    cols[2 * kPairs] = (n_heads + n_kv + j) * kHeadDim + tid;                 // v
+    cols[2 * kPairs + 1] = (n_heads + j) * kHeadDim + (tid & 63);            // k (first half of the pair)
+    cols[2 * kPairs + 2] = cols[2 * kPairs + 1] + 64;
+    float part[NE][kMaxParts], bia[NE], cs[kPairs + 1], sn[kPairs + 1];
+#pragma unroll
+    for (int e = 0; e < NE; ++e) {
+#pragma unroll
+      for (int pp = 0; pp < kMaxParts; ++pp)
+        part[e][pp] = pp < p.n_parts ? __ldcg(row + (size_t)pp * p.part_stride + cols[e]) : 0.f;
+      bia[e] = p.bias ? __half2float(p.bias[cols[e]]) : 0.f;
+    }
+#pragma unroll
+    for (int q3 = 0; q3 <= kPairs; ++q3) {
+      const int i = q3 < kPairs ? (min(tid + q3 * kAttnThreads, GQ * 64 - 1) & 63) : (tid & 63);
+      cs[q3] = p.cos_t[(size_t)ps * 64 + i];
+      sn[q3] = p.sin_t[(size_t)ps * 64 + i];
+    }
+    float val[NE];
+#pragma unroll
+    for (int e = 0; e < NE; ++e) {
+      float v = part[e][0];
+#pragma unroll
+      for (int pp = 1; pp < kMaxParts; ++pp) v += part[e][pp];                // fixed order: deterministic
+      for (int pp = kMaxParts; pp < p.n_parts; ++pp) v += __ldcg(row + (size_t)pp * p.part_stride + cols[e]);
+      val[e] = v + bia[e];
+    }
+#pragma unroll
+    for (int q3 = 0; q3 < kPairs; ++q3) {
+      const int idx = tid + q3 * kAttnThreads;
+      if (idx < GQ * 64) {
+        const int h = idx >> 6, i = idx & 63;
+        float r1, r2;
+        rope_rotate(val[2 * q3], val[2 * q3 + 1], cs[q3], sn[q3], r1, r2);
+        *reinterpret_cast<__half*>(q_addr(h, i)) = __float2half_rn(r1);
+        *reinterpret_cast<__half*>(q_addr(h, i + 64)) = __float2half_rn(r2);
       }
-      const int sl = p.slot[t];
+    }
+    if (own) {
+      const __half vnew = __float2half_rn(val[2 * kPairs]);
+      new_s[kHeadDim + tid] = vnew;
+      float r1, r2;
+      rope_rotate(val[2 * kPairs + 1], val[2 * kPairs + 2], cs[kPairs], sn[kPairs], r1, r2);
+      const __half k1 = __float2half_rn(r1), k2 = __float2half_rn(r2);
+      if (tid < 64) { new_s[tid] = k1; new_s[tid + 64] = k2; }
       if (sl >= 0) {                                // paged cache write (swizzled row)
         const int r = sl % kBlockTokens;
         const size_t rowoff = (((size_t)(sl / kBlockTokens) * n_kv + j) * kBlockTokens + r) * kHeadDim;
@@ -344,6 +377,7 @@ paged_attn_kernel(const AttnParams p) {
   if (n_active == 1) {                              // single split: finished
 #pragma unroll
     for (int h = 0; h < GQ; ++h) orow[h * kHeadDim + tid] = __float2half_rn(num[h] / den[h]);
+    kernel_epilogue(tl);
     return;
   }
 

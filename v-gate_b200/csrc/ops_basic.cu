@@ -5,6 +5,8 @@
 
 namespace b200 {
 
+B200_DEFINE_TL_SETTER(tl_set_basic)
+
 __constant__ int kAwqOrder[8] = {0, 4, 1, 5, 2, 6, 3, 7};
 
 // ---------------------------------------------------------------------------------------------
@@ -81,7 +83,7 @@ int launch_awq_dequant(const uint32_t* wq, const __half* sc, const __half* zp, i
 // Embedding gather into the fp32 residual stream.
 __global__ void embed_kernel(const __half* __restrict__ table, const int32_t* __restrict__ ids, int H,
                              float* __restrict__ h) {
-  pdl_prologue();
+  const unsigned tl = kernel_prologue(kKidEmbed);
   const int t = blockIdx.x;
   const __half* row = table + (size_t)ids[t] * H;
   for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
@@ -96,6 +98,7 @@ __global__ void embed_kernel(const __half* __restrict__ table, const int32_t* __
     *reinterpret_cast<float4*>(h + (size_t)t * H + i) = a;
     *reinterpret_cast<float4*>(h + (size_t)t * H + i + 4) = b;
   }
+  kernel_epilogue(tl);
 }
 
 int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s) {
@@ -119,7 +122,7 @@ __global__ void __launch_bounds__(kNormThreads)
 rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_parts, int64_t part_stride,
                const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows, int H,
                __half* __restrict__ xn) {
-  pdl_prologue();
+  const unsigned tl = kernel_prologue(kKidRmsnorm);
   const int r = blockIdx.x;
   const int row = rows ? rows[r] : r;
   float4 v[kNormMaxPerThread];
@@ -130,9 +133,17 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
     const int i = threadIdx.x + it * kNormThreads;
     if (i < nvec) {
       float4 a = *reinterpret_cast<const float4*>(h + (size_t)row * H + 4 * i);
-      for (int p = 0; p < n_parts; ++p) {
-        const float4 b = *reinterpret_cast<const float4*>(parts + p * part_stride + (size_t)row * H + 4 * i);
-        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+      // partials: issue the loads four at a time before adding (one L2 round trip per four parts),
+      // then add in the fixed order p = 0, 1, 2, ... so the sum is deterministic
+      for (int p0 = 0; p0 < n_parts; p0 += 4) {
+        float4 b[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          b[k] = p0 + k < n_parts
+                     ? __ldcg(reinterpret_cast<const float4*>(parts + (size_t)(p0 + k) * part_stride + (size_t)row * H + 4 * i))
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
       }
       if (n_parts > 0) *reinterpret_cast<float4*>(h + (size_t)row * H + 4 * i) = a;
       v[it] = a;
@@ -160,6 +171,7 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
       *reinterpret_cast<uint2*>(xn + (size_t)r * H + 4 * i) = o;
     }
   }
+  kernel_epilogue(tl);
 }
 
 int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_stride, const __half* gamma, float eps,
@@ -181,7 +193,7 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_parts, int64
                                const int32_t* __restrict__ slot, const float* __restrict__ cos_t,
                                const float* __restrict__ sin_t, int n_heads, int n_kv, __half* __restrict__ q_out,
                                __half* __restrict__ k_cache, __half* __restrict__ v_cache) {
-  pdl_prologue();
+  const unsigned tl = kernel_prologue(kKidRope);
   const int t = blockIdx.x;
   const int p = pos[t];
   const int sl = slot[t];
@@ -189,10 +201,17 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_parts, int64
   const float* row = qkv + (size_t)t * total_heads * kHeadDim;
   for (int idx = threadIdx.x; idx < total_heads * 64; idx += blockDim.x) {
     const int head = idx >> 6, i = idx & 63;
-    float x1 = row[head * kHeadDim + i], x2 = row[head * kHeadDim + i + 64];
-    for (int pp = 1; pp < n_parts; ++pp) {
-      x1 += row[pp * part_stride + head * kHeadDim + i];
-      x2 += row[pp * part_stride + head * kHeadDim + i + 64];
+    float x1 = 0.f, x2 = 0.f;
+    for (int p0 = 0; p0 < n_parts; p0 += 4) {          // loads first, then adds in fixed order
+      float a[4], b[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const bool ok = p0 + k < n_parts;
+        a[k] = ok ? __ldcg(row + (size_t)(p0 + k) * part_stride + head * kHeadDim + i) : 0.f;
+        b[k] = ok ? __ldcg(row + (size_t)(p0 + k) * part_stride + head * kHeadDim + i + 64) : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { x1 += a[k]; x2 += b[k]; }
     }
     if (bias) {
       x1 += __half2float(bias[head * kHeadDim + i]);
@@ -201,16 +220,20 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_parts, int64
     if (head < n_heads) {
       const float c = cos_t[(size_t)p * 64 + i], sn = sin_t[(size_t)p * 64 + i];
       __half* o = q_out + ((size_t)t * n_heads + head) * kHeadDim;
-      o[i] = __float2half_rn(x1 * c - x2 * sn);
-      o[i + 64] = __float2half_rn(x2 * c + x1 * sn);
+      float r1, r2;
+      rope_rotate(x1, x2, c, sn, r1, r2);
+      o[i] = __float2half_rn(r1);
+      o[i + 64] = __float2half_rn(r2);
     } else if (sl >= 0) {
       const int blk = sl / kBlockTokens, off = sl % kBlockTokens;
       if (head < n_heads + n_kv) {
         const int j = head - n_heads;
         const float c = cos_t[(size_t)p * 64 + i], sn = sin_t[(size_t)p * 64 + i];
         __half* o = k_cache + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
-        o[kv_swz(off, i)] = __float2half_rn(x1 * c - x2 * sn);       // swizzled row layout, see common.cuh
-        o[kv_swz(off, i + 64)] = __float2half_rn(x2 * c + x1 * sn);
+        float r1, r2;
+        rope_rotate(x1, x2, c, sn, r1, r2);
+        o[kv_swz(off, i)] = __float2half_rn(r1);                     // swizzled row layout, see common.cuh
+        o[kv_swz(off, i + 64)] = __float2half_rn(r2);
       } else {
         const int j = head - n_heads - n_kv;
         __half* o = v_cache + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
@@ -219,6 +242,7 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_parts, int64
       }
     }
   }
+  kernel_epilogue(tl);
 }
 
 int launch_rope_kv(const float* qkv, int n_parts, int64_t part_stride, const __half* bias, const int32_t* pos,
@@ -236,7 +260,7 @@ int launch_rope_kv(const float* qkv, int n_parts, int64_t part_stride, const __h
 // ---------------------------------------------------------------------------------------------
 // SwiGLU: act = fp16(silu(gate) * up), gate|up fp32 (vLLM qwen2.py:106-111 SiluAndMul).
 __global__ void swiglu_kernel(const float* __restrict__ gu, int I, __half* __restrict__ act) {
-  pdl_prologue();
+  const unsigned tl = kernel_prologue(kKidSwiglu);
   const int t = blockIdx.y;
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i >= I) return;
@@ -247,6 +271,7 @@ __global__ void swiglu_kernel(const float* __restrict__ gu, int I, __half* __res
   o.x = pack_half2(f(g.x, u.x), f(g.y, u.y));
   o.y = pack_half2(f(g.z, u.z), f(g.w, u.w));
   *reinterpret_cast<uint2*>(act + (size_t)t * I + i) = o;
+  kernel_epilogue(tl);
 }
 
 int launch_swiglu(const float* gu, int T, int I, __half* act, cudaStream_t s) {

@@ -9,6 +9,8 @@
 
 namespace b200 {
 
+B200_DEFINE_TL_SETTER(tl_set_gemv)
+
 constexpr int kGemvWarps = 8;
 
 template <int BT>
@@ -16,7 +18,7 @@ __global__ void __launch_bounds__(kGemvWarps * 32)
 w4_gemv_kernel(const uint32_t* __restrict__ wq, const __half* __restrict__ sc, const __half* __restrict__ zp,
                const __half* __restrict__ bias, const __half* __restrict__ x, int ldx, float* __restrict__ y,
                int ldy, int B, int K, int N, int G, int accumulate) {
-  pdl_prologue();
+  (void)kernel_prologue(kKidW4Gemv);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = blockIdx.x * kGemvWarps + warp;
   if (n >= N) return;
@@ -91,7 +93,7 @@ template <int BT>
 __global__ void __launch_bounds__(kGemvWarps * 32)
 f16_gemv_kernel(const __half* __restrict__ w, const __half* __restrict__ x, int ldx, float* __restrict__ y, int ldy,
                 int B, int K, int N, int accumulate) {
-  pdl_prologue();
+  (void)kernel_prologue(kKidF16Gemv);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = blockIdx.x * kGemvWarps + warp;
   if (n >= N) return;

@@ -13,6 +13,8 @@
 
 namespace b200 {
 
+B200_DEFINE_TL_SETTER(tl_set_sample)
+
 constexpr int kSampleThreads = 1024;
 
 __device__ __forceinline__ uint32_t float_key(float f) {   // order-preserving float -> uint32
@@ -65,7 +67,7 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   __shared__ unsigned long long hist[256];
   __shared__ unsigned long long s_above, s_target;
   __shared__ int s_bin;
-  pdl_prologue();
+  const unsigned tl = kernel_prologue(kKidSample);
   const int r = blockIdx.x, tid = threadIdx.x;
   const float* l = logits + (size_t)r * V;
   const float temp = temperature ? temperature[r] : 0.f;
@@ -76,6 +78,7 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   best = block_argmax(best, red);
   if (temp < 1e-5f) {
     if (tid == 0) out[r] = best.i;
+    kernel_epilogue(tl);
     return;
   }
   // x_i = l_i / T exactly as the reference divides (sampler.py:232)
@@ -157,6 +160,7 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   }
   draw = block_argmax(draw, red);
   if (tid == 0) out[r] = draw.i;
+  kernel_epilogue(tl);
 }
 
 int launch_sample(const float* logits, int B, int V, const float* temperature, const float* top_p,

@@ -29,6 +29,8 @@
 
 namespace b200 {
 
+B200_DEFINE_TL_SETTER(tl_set_umma)
+
 constexpr int kUmmaM = 128;          // weight rows per CTA tile
 constexpr int kUmmaBK = 64;          // k per pipeline stage = one 128-byte swizzle row of fp16
 constexpr int kProducerWarps = 16;   // four warpgroups; warpgroup g owns A stage g and k tiles it = g (mod 4)
@@ -212,7 +214,13 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
   UmmaSmem* sb = reinterpret_cast<UmmaSmem*>(smem + Cfg::kBarOff);
   constexpr uint32_t kTmemCols = Cfg::kTmemCols;
 
-  grid_dep_launch();        // the next kernel may start its own set-up / weight prefetch now
+  // PDL: the next kernel may start its own set-up / weight prefetch now (no dependency wait here:
+  // the weight stream below does not depend on the upstream kernel)
+  unsigned tl = ~0u;
+  unsigned long long tl_t0 = 0;
+  const bool tl_rec = d_tl.buf && threadIdx.x == 0 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
+  if (tl_rec) tl_t0 = gtime();
+  grid_dep_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nt = blockIdx.x;                 // weight-row tile
   const int tok0 = blockIdx.y * NT;          // token tile
@@ -416,6 +424,15 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
   __syncthreads();
   if (warp == kWarpMma) tmem_dealloc(tmem, kTmemCols);
   if (tr && threadIdx.x == 0) tr[6] = clock64();
+  if (tl_rec) {
+    tl = atomicAdd(d_tl.ctr, 1u);
+    if (tl < d_tl.cap) {
+      d_tl.buf[4 * tl] = (unsigned long long)(kW4 ? kKidUmmaW4 : kKidUmmaF16) | ((unsigned long long)gridDim.x << 8) | ((unsigned long long)gridDim.y << 28) | ((unsigned long long)gridDim.z << 48);
+      d_tl.buf[4 * tl + 1] = tl_t0;
+      d_tl.buf[4 * tl + 2] = tl_t0;
+      d_tl.buf[4 * tl + 3] = gtime();
+    }
+  }
 }
 
 // ---- weight tiling (one-time) ---------------------------------------------------------------------
