@@ -165,6 +165,8 @@ int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits);
 /* Profiling aid: when dev_buf is non-NULL the tcgen05 GEMM writes 8 x uint64 SM-clock stamps per CTA
  * (entry, set-up done, first tiles ready, last MMA issued, accumulator ready, epilogue done, exit). */
 void b200_debug_umma_trace(void* dev_buf);
+/* Same, restricted to launches whose grid is (grid_x, *, grid_z) -- to pick one projection inside a step. */
+void b200_debug_umma_trace_grid(void* dev_buf, int32_t grid_x, int32_t grid_z);
 /* Same for the attention kernel (entry, copies issued, wait start, tile landed, scores, softmax, loop end). */
 void b200_debug_attn_trace(void* dev_buf);
 /* In-situ timeline: while `buf` (device, capacity x 4 uint64) and `counter` (device uint32, zeroed by the

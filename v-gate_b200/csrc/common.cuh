@@ -63,15 +63,33 @@ __device__ __forceinline__ float fhfma2(uint32_t a2, uint32_t b2, float c) {
 // along K at load time).  `(w >> 4j) & 0x000f000f | 0x64006400` is then the fp16 pair
 // (1024 + q[2j], 1024 + q[2j+1]).  Subtracting (1024 + z) is exact in fp16 and the one
 // multiply by the scale rounds exactly like the reference's fp16 `(q - z) * s`.
+__device__ __forceinline__ uint32_t lop3_and_or(uint32_t a, uint32_t b, uint32_t c) {   // (a & b) | c in one LOP3
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+// Even nibble pairs (j = 0, 2) are masked in place -> 1024 + q, minus (1024 + z): exact.  Odd pairs
+// (j = 1, 3) are masked one nibble up -> 1024 + 16 q, and one exact FMA (x / 16 - (64 + z)) = q - z
+// replaces the shift.  Either way the fp16 value q - z is exact and the single multiply by the scale
+// rounds exactly like the reference's fp16 (q - z) * s.  13 instructions per 8 weights.
 __device__ __forceinline__ void dequant8(uint32_t w, uint32_t z1024_2, uint32_t s2, uint32_t out[4]) {
   const __half2 z = *reinterpret_cast<const __half2*>(&z1024_2);
   const __half2 s = *reinterpret_cast<const __half2*>(&s2);
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    uint32_t v = ((w >> (4 * j)) & 0x000f000fu) | 0x64006400u;
-    __half2 h = __hmul2(__hsub2(*reinterpret_cast<__half2*>(&v), z), s);
-    out[j] = *reinterpret_cast<uint32_t*>(&h);
-  }
+  const __half2 z64 = __hsub2(z, __float2half2_rn(960.f));           // 64 + zero (exact)
+  const __half2 sixteenth = __float2half2_rn(0.0625f);
+  const uint32_t w8 = w >> 8;
+  uint32_t v0 = lop3_and_or(w, 0x000f000fu, 0x64006400u);             // nibbles 0,4 -> k0,k1
+  uint32_t v1 = lop3_and_or(w, 0x00f000f0u, 0x64006400u);             // nibbles 1,5 -> k2,k3 (x16)
+  uint32_t v2 = lop3_and_or(w8, 0x000f000fu, 0x64006400u);            // nibbles 2,6 -> k4,k5
+  uint32_t v3 = lop3_and_or(w8, 0x00f000f0u, 0x64006400u);            // nibbles 3,7 -> k6,k7 (x16)
+  __half2 h0 = __hmul2(__hsub2(*reinterpret_cast<__half2*>(&v0), z), s);
+  __half2 h1 = __hmul2(__hfma2(*reinterpret_cast<__half2*>(&v1), sixteenth, __hneg2(z64)), s);
+  __half2 h2 = __hmul2(__hsub2(*reinterpret_cast<__half2*>(&v2), z), s);
+  __half2 h3 = __hmul2(__hfma2(*reinterpret_cast<__half2*>(&v3), sixteenth, __hneg2(z64)), s);
+  out[0] = *reinterpret_cast<uint32_t*>(&h0);
+  out[1] = *reinterpret_cast<uint32_t*>(&h1);
+  out[2] = *reinterpret_cast<uint32_t*>(&h2);
+  out[3] = *reinterpret_cast<uint32_t*>(&h3);
 }
 
 __device__ __forceinline__ uint32_t pack_half2(float a, float b) {
@@ -109,10 +127,16 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 // Bounded wait: a pipeline bug must fail loudly (trap -> sticky CUDA error), never hang the GPU.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+// The retry loop is kept out of line and un-unrolled: with a dozen call sites per kernel an inlined,
+// unrolled spin loop multiplies the code size and costs instruction-cache misses on the hot path.
+static __device__ __noinline__ void mbar_wait_slow(uint64_t* bar, uint32_t parity) {
+#pragma unroll 1
   for (uint32_t spin = 0; spin < (1u << 24); ++spin)
     if (mbar_try_wait(bar, parity)) return;
   __trap();
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (!mbar_try_wait(bar, parity)) mbar_wait_slow(bar, parity);
 }
 // global -> shared bulk copy (SASS UBLKCP); bytes % 16 == 0, both addresses 16-byte aligned.
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {

@@ -1071,7 +1071,8 @@ int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, flo
   const int mode = n_splits > 1 ? kUmmaPartialF32 : epilogue == 2 ? kUmmaSwigluF16 : accumulate ? kUmmaAccumF32 : kUmmaStoreF32;
   return launch_umma_w4(w, mx, nt, T, y, ldy, mode, n_splits, part_stride, (cudaStream_t)stream);
 }
-void b200_debug_umma_trace(void* dev_buf) { umma_set_trace((unsigned long long*)dev_buf); }
+void b200_debug_umma_trace(void* dev_buf) { umma_set_trace((unsigned long long*)dev_buf, 0, 0); }
+void b200_debug_umma_trace_grid(void* dev_buf, int32_t grid_x, int32_t grid_z) { umma_set_trace((unsigned long long*)dev_buf, grid_x, grid_z); }
 void b200_debug_attn_trace(void* dev_buf) { attn_set_trace((unsigned long long*)dev_buf); }
 void b200_debug_timeline(void* buf, void* counter, uint32_t capacity) {
   auto* b = (unsigned long long*)buf; auto* c = (unsigned int*)counter;

@@ -69,7 +69,7 @@ int launch_umma_tile_w4(const uint32_t* wq, const __half* sc, const __half* zp, 
                         unsigned char* chunks, cudaStream_t s);
 int make_tensor_map_f16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows);
 int umma_pick_nt(int T, bool w4);
-void umma_set_trace(unsigned long long* dev_buf);
+void umma_set_trace(unsigned long long* dev_buf, int grid_x, int grid_z);
 int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T, float* y, int ldy, int mode,
                    int n_splits, int64_t part_stride, cudaStream_t s);
 int launch_umma_f16(const CUtensorMap& map_w, int K, int N, const CUtensorMap& map_x, int nt_sel, int T, float* y,

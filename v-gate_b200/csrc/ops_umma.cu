@@ -174,7 +174,10 @@ struct UmmaCfg {
 
 // Optional per-CTA cycle trace (debug/profiling aid): 8 x uint64 per CTA, written when non-null.
 static unsigned long long* g_umma_trace = nullptr;
-void umma_set_trace(unsigned long long* dev_buf) { g_umma_trace = dev_buf; }
+static int g_umma_trace_gridx = 0, g_umma_trace_gridz = 0;       // 0 = trace every launch, else only matching grids
+void umma_set_trace(unsigned long long* dev_buf, int grid_x, int grid_z) {
+  g_umma_trace = dev_buf; g_umma_trace_gridx = grid_x; g_umma_trace_gridz = grid_z;
+}
 
 struct UmmaParams {
   unsigned long long* trace;
@@ -299,55 +302,66 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     tc_fence_after();
     if (tr && threadIdx.x == 0) tr[4] = clock64();
     {
+      // Stage the whole [NT tokens x 128 features] fp32 accumulator tile in shared memory (the
+      // activation stages are idle once the accumulator is complete), then write global memory with
+      // 16-byte vectors: a TMEM lane holds one feature for many tokens, and storing it directly costs
+      // one 4-byte store instruction per (token, feature) -- the LSU issue rate then dominates.
       const int q = warp & 3;                                          // TMEM lane quarter this warp may read
-      const int n = nt * kUmmaM + q * 32 + lane;                       // output feature
       constexpr int kColsPerWarp = NT / 4;                             // 16 warps: 4 lane quarters x 4 column groups
       constexpr int CW = kColsPerWarp > 32 ? 32 : kColsPerWarp;
       const int col0 = (warp >> 2) * kColsPerWarp;
-      const float bn = (p.mode == kStoreF32 && p.bias) ? __half2float(p.bias[n]) : 0.f;
-      float* ybase = p.y + (p.mode == kPartialF32 ? (size_t)split * p.part_stride : 0);
-      if (p.mode == kAccumF32) grid_dep_wait();                        // y is read-modify-written
-      if constexpr (kW4 && NT <= 128) if (p.mode == kSwigluF16) {
-        // Fused SwiGLU (vLLM qwen2.py:106-111 SiluAndMul): the tile holds 64 gate rows (TMEM lanes
-        // 0..63) and the matching 64 up rows (lanes 64..127).  The up warps hand their values over
-        // through shared memory (the activation stages are idle once the accumulator is complete),
-        // the gate warps compute fp16(silu(g) * u) and store act[b, 64 * nt + row].
-        float* exch = reinterpret_cast<float*>(smem);                  // [NT cols][64 rows] fp32
+      float* stage = reinterpret_cast<float*>(smem);                   // [NT][128] fp32 = NT * 512 B <= the X ring
+      static_assert(NT * 512 <= Cfg::kStages * Cfg::kStageBytes, "epilogue staging fits in the stage ring");
+#pragma unroll 1
+      for (int c = 0; c < kColsPerWarp; c += CW) {
         uint32_t v[CW];
-        tmem_ld<CW>(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)col0, v);
-        if (q >= 2) {
+        tmem_ld<CW>(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(col0 + c), v);
 #pragma unroll
-          for (int j = 0; j < CW; ++j) exch[(col0 + j) * 64 + (q - 2) * 32 + lane] = __uint_as_float(v[j]);
-        }
-        asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");
-        if (q < 2) {
-          __half* act = reinterpret_cast<__half*>(p.y);
-          const int nout = nt * 64 + q * 32 + lane;
-#pragma unroll
-          for (int j = 0; j < CW; ++j) {
-            const int b = tok0 + col0 + j;
-            if (b < p.T) {
-              const float g = __uint_as_float(v[j]);
-              const float u = exch[(col0 + j) * 64 + q * 32 + lane];
-              act[(size_t)b * p.ldy + nout] = __float2half_rn(g / (1.f + expf(-g)) * u);
-            }
+        for (int j = 0; j < CW; ++j) stage[(col0 + c + j) * 128 + q * 32 + lane] = __uint_as_float(v[j]);
+      }
+      if (tr && threadIdx.x == 0) tr[2] = clock64();                   // (reuses the "first stage ready" slot)
+      asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");
+      const int tid = threadIdx.x;                                     // 0..511
+      if (p.mode == kSwigluF16) {
+        // Fused SwiGLU (vLLM qwen2.py:106-111 SiluAndMul): rows 0..63 of the tile are gate features,
+        // rows 64..127 the matching up features.  One thread = one token x 8 features = one 16-byte store.
+        __half* act = reinterpret_cast<__half*>(p.y);
+        for (int idx = tid; idx < NT * 8; idx += kProducerWarps * 32) {
+          const int bcol = idx >> 3, f8 = (idx & 7) * 8;
+          const int b = tok0 + bcol;
+          if (b < p.T) {
+            const float4 g0 = *reinterpret_cast<const float4*>(stage + bcol * 128 + f8);
+            const float4 g1 = *reinterpret_cast<const float4*>(stage + bcol * 128 + f8 + 4);
+            const float4 u0 = *reinterpret_cast<const float4*>(stage + bcol * 128 + 64 + f8);
+            const float4 u1 = *reinterpret_cast<const float4*>(stage + bcol * 128 + 64 + f8 + 4);
+            auto f = [](float g, float u) { return g / (1.f + expf(-g)) * u; };
+            uint4 o;
+            o.x = pack_half2(f(g0.x, u0.x), f(g0.y, u0.y));
+            o.y = pack_half2(f(g0.z, u0.z), f(g0.w, u0.w));
+            o.z = pack_half2(f(g1.x, u1.x), f(g1.y, u1.y));
+            o.w = pack_half2(f(g1.z, u1.z), f(g1.w, u1.w));
+            *reinterpret_cast<uint4*>(act + (size_t)b * p.ldy + nt * 64 + f8) = o;
           }
         }
-      }
-      if (p.mode != kSwigluF16) {
-#pragma unroll 1
-        for (int c = 0; c < kColsPerWarp; c += CW) {
-          uint32_t v[CW];
-          tmem_ld<CW>(tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(col0 + c), v);
-#pragma unroll
-          for (int j = 0; j < CW; ++j) {
-            const int b = tok0 + col0 + c + j;
-            if (b < p.T) {
-              float* yp = ybase + (size_t)b * p.ldy + n;
-              const float acc = __uint_as_float(v[j]);
-              if (p.mode == kAccumF32) *yp += acc;
-              else *yp = acc + bn;
+      } else {
+        float* ybase = p.y + (p.mode == kPartialF32 ? (size_t)split * p.part_stride : 0) + (size_t)nt * kUmmaM;
+        if (p.mode == kAccumF32) grid_dep_wait();                      // y is read-modify-written
+        for (int idx = tid; idx < NT * 32; idx += kProducerWarps * 32) {
+          const int bcol = idx >> 5, f4 = (idx & 31) * 4;
+          const int b = tok0 + bcol;
+          if (b < p.T) {
+            float4 a = *reinterpret_cast<const float4*>(stage + bcol * 128 + f4);
+            float4* yp = reinterpret_cast<float4*>(ybase + (size_t)b * p.ldy + f4);
+            if (p.mode == kAccumF32) {
+              const float4 o = *yp;
+              a.x += o.x; a.y += o.y; a.z += o.z; a.w += o.w;
+            } else if (p.mode == kStoreF32 && p.bias) {
+              const uint2 bw = *reinterpret_cast<const uint2*>(p.bias + nt * kUmmaM + f4);
+              const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&bw.x));
+              const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&bw.y));
+              a.x += b0.x; a.y += b0.y; a.z += b1.x; a.w += b1.y;
             }
+            *yp = a;
           }
         }
       }
@@ -518,7 +532,9 @@ static int launch_nt(const CUtensorMap& mx, const CUtensorMap& mw, const UmmaPar
     configured = true;
   }
   dim3 grid(p.N / kUmmaM, (p.T + NT - 1) / NT, n_splits);
-  launch_k(kern, grid, dim3(kUmmaThreads), (size_t)smem_bytes, s, mx, mw, p);
+  UmmaParams pp = p;
+  if (g_umma_trace_gridx && ((int)grid.x != g_umma_trace_gridx || (int)grid.z != g_umma_trace_gridz)) pp.trace = nullptr;
+  launch_k(kern, grid, dim3(kUmmaThreads), (size_t)smem_bytes, s, mx, mw, pp);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
