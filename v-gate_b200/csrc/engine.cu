@@ -145,6 +145,9 @@ struct b200_engine {
   DevMem h, xn, qkv, qh, attn, gu, act, xn_last, logits;
   DevMem d_ids, d_pos, d_slot, d_btrow, d_ctx, d_lastrows, d_bt, d_temp, d_topp, d_seed, d_step, d_next, d_ngen;
   DevMem d_out_tokens;
+  DevMem d_tiles;                              // prefill query tiles {row0, nrows, bt_row, ctx0}
+  std::vector<int32_t> h_tiles;
+  int n_q_tiles = 0;                           // tiles describing the rows of the pending prefill pass
   int32_t* hp_i32 = nullptr;                   // pinned staging
   float* hp_f32 = nullptr;
   size_t hp_cap = 0;
@@ -264,9 +267,13 @@ struct b200_engine {
         if (!skip(2) && (rc = launch_rope_kv(qsrc, np ? np : 1, (int64_t)T * QKV, qbias, d_pos.as<int32_t>(),
                                              d_slot.as<int32_t>(), cos_t.as<float>(), sin_t.as<float>(), T, NH, NKV,
                                              qh.as<__half>(), kc, vc, stream))) return rc;
-        if (!skip(3) && (rc = launch_paged_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
-                                                d_btrow.as<int32_t>(), d_ctx.as<int32_t>(), T, NH, NKV, 1, nullptr, nullptr,
-                                                attn.as<__half>(), stream))) return rc;
+        if (n_q_tiles > 0) {       // tiles of <= 16 consecutive query rows share the staged K/V chunks
+          if (!skip(3) && (rc = launch_prefill_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
+                                                    d_tiles.as<int32_t>(), n_q_tiles, NH, NKV, attn.as<__half>(), stream)))
+            return rc;
+        } else if (!skip(3) && (rc = launch_paged_attn(qh.as<__half>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
+                                                       d_btrow.as<int32_t>(), d_ctx.as<int32_t>(), T, NH, NKV, 1, nullptr,
+                                                       nullptr, attn.as<__half>(), stream))) return rc;
       }
       if (!skip(4) && (rc = linear(w, 1, attn.as<__half>(), Tmax, h.as<float>(), H, T, true, &pend))) return rc;
       pend_stride = (int64_t)T * H;
@@ -318,6 +325,22 @@ struct b200_engine {
     r.seq_slot = -1;
   }
 
+  // Group the rows of a prefill pass into query tiles: consecutive rows of one sequence at consecutive
+  // positions, at most 16 per tile.
+  int upload_q_tiles(const std::vector<int32_t>& btrow, const std::vector<int32_t>& ctx) {
+    std::vector<int32_t>& tiles = h_tiles;     // member: must outlive the asynchronous copy
+    tiles.clear();
+    const int T = (int)btrow.size();
+    for (int r = 0; r < T;) {
+      int n = 1;
+      while (n < 16 && r + n < T && btrow[r + n] == btrow[r] && ctx[r + n] == ctx[r] + n) ++n;
+      tiles.insert(tiles.end(), {r, n, btrow[r], ctx[r]});
+      r += n;
+    }
+    n_q_tiles = (int)tiles.size() / 4;
+    return upload_i32(d_tiles, tiles);
+  }
+
   int upload_i32(DevMem& dst, const std::vector<int32_t>& src) {
     if (src.empty()) return B200_OK;
     B200_CUDA(cudaMemcpyAsync(dst.p, src.data(), src.size() * 4, cudaMemcpyHostToDevice, stream));
@@ -364,6 +387,7 @@ struct b200_engine {
     int rc;
     if ((rc = upload_i32(d_ids, ids)) || (rc = upload_i32(d_pos, pos)) || (rc = upload_i32(d_slot, slot)) ||
         (rc = upload_i32(d_btrow, btrow)) || (rc = upload_i32(d_ctx, ctx)) || (rc = upload_i32(d_lastrows, lastrows)) ||
+        (rc = is_prefill ? upload_q_tiles(btrow, ctx) : (n_q_tiles = 0, B200_OK)) ||
         (rc = upload_i32(d_bt, bt)) || (rc = upload_f32(d_temp, temp)) || (rc = upload_f32(d_topp, topp)) ||
         (rc = upload_i32(d_seed, seed)) || (rc = upload_i32(d_step, step)))
       return rc;
@@ -704,7 +728,7 @@ int32_t b200_engine_finalize(b200_engine* e) {
       (rc = e->gu.alloc(T * 2 * e->I * 4)) || (rc = e->act.alloc(T * e->I * 2)) || (rc = e->xn_last.alloc(S * e->H * 2)) ||
       (rc = e->logits.alloc(S * e->V * 4)) || (rc = e->d_ids.alloc(T * 4)) || (rc = e->d_pos.alloc(T * 4)) ||
       (rc = e->d_slot.alloc(T * 4)) || (rc = e->d_btrow.alloc(T * 4)) || (rc = e->d_ctx.alloc(T * 4)) ||
-      (rc = e->d_lastrows.alloc(S * 4)) || (rc = e->d_bt.alloc(S * e->max_blocks_per_seq * 4)) ||
+      (rc = e->d_lastrows.alloc(S * 4)) || (rc = e->d_tiles.alloc(T * 16)) || (rc = e->d_bt.alloc(S * e->max_blocks_per_seq * 4)) ||
       (rc = e->d_temp.alloc(S * 4)) || (rc = e->d_topp.alloc(S * 4)) || (rc = e->d_seed.alloc(S * 4)) ||
       (rc = e->d_step.alloc(S * 4)) || (rc = e->d_next.alloc(S * 4)) || (rc = e->d_ngen.alloc(S * 4)))
     return rc;
@@ -762,7 +786,7 @@ void b200_engine_destroy(b200_engine* e) {
   DevMem* all[] = {&e->embed, &e->lm_head_w, &e->final_norm, &e->cos_t, &e->sin_t, &e->k_cache, &e->v_cache, &e->h,
                    &e->xn, &e->qkv, &e->qh, &e->attn, &e->gu, &e->act, &e->xn_last, &e->logits, &e->d_ids, &e->d_pos,
                    &e->d_slot, &e->d_btrow, &e->d_ctx, &e->d_lastrows, &e->d_bt, &e->d_temp, &e->d_topp, &e->d_seed,
-                   &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens, &e->parts, &e->attn_scratch, &e->attn_counters};
+                   &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens, &e->parts, &e->attn_scratch, &e->attn_counters, &e->d_tiles};
   for (DevMem* m : all) m->release();
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
@@ -931,7 +955,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
     }
     if ((rc = e->upload_i32(e->d_ids, ids)) || (rc = e->upload_i32(e->d_pos, pos)) || (rc = e->upload_i32(e->d_slot, slot)) ||
         (rc = e->upload_i32(e->d_btrow, btrow)) || (rc = e->upload_i32(e->d_ctx, ctx)) ||
-        (rc = e->upload_i32(e->d_lastrows, lastrows)))
+        (rc = e->upload_i32(e->d_lastrows, lastrows)) || (rc = e->upload_q_tiles(btrow, ctx)))
       return rc;
     if ((rc = e->forward(ns * n_prompt, ns, e->d_lastrows.as<int32_t>(), false))) return rc;
     B200_CUDA(cudaMemcpyAsync(first_tokens.data() + s0, e->d_next.p, (size_t)ns * 4, cudaMemcpyDeviceToHost, s));

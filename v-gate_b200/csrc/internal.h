@@ -97,6 +97,10 @@ int launch_attn_decode_fused(const float* qkv, int n_parts, int64_t part_stride,
                              const int32_t* ctx_len, int T, int n_heads, int n_kv, int n_splits, float* scratch,
                              int32_t* counters, __half* out, cudaStream_t s);
 void attn_set_trace(unsigned long long* dev_buf);
+// tiles: int32 [n_tiles, 4] = {row0, nrows <= 16, block-table row, context length of row0}
+int launch_prefill_attn(const __half* q, const __half* k_cache, const __half* v_cache, const int32_t* block_tables,
+                        int bt_stride, const int32_t* tiles, int n_tiles, int n_heads, int n_kv, __half* out,
+                        cudaStream_t s);
 size_t attn_scratch_floats(int T, int n_heads, int n_kv, int n_splits);
 int launch_swiglu(const float* gu, int T, int I, __half* act, cudaStream_t s);
 int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s);

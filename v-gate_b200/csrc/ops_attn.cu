@@ -427,6 +427,221 @@ paged_attn_kernel(const AttnParams p) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Prefill attention: one CTA per (kv head, tile of <= 16 consecutive query tokens of one sequence),
+// one warp per query head of the group.  The K/V chunks of the sequence are staged once per CTA and
+// shared by all heads and all 16 query rows (the per-row kernel above would stage them once per row).
+// Same tensor-core scheme: S = Q K^T with the 16 query tokens as the MMA M rows, causal mask from the
+// row's own context length, online softmax for two rows per thread, O += P V.
+struct QTile { int32_t row0, nrows, bt_row, ctx0; };   // rows [row0, row0 + nrows); row i sees ctx0 + i tokens
+
+struct PrefillAttnParams {
+  const __half* q;               // [T, nh * 128] rotated queries
+  const __half* k_cache;
+  const __half* v_cache;
+  const int32_t* block_tables;
+  int bt_stride;
+  const QTile* tiles;
+  int n_heads, n_kv;
+  __half* out;                   // [T, nh * 128]
+};
+
+template <int GQ>
+struct PrefillSmem {
+  static constexpr int kOffKV = 0;                                   // 2 buffers x (K 16 KB + V 16 KB)
+  static constexpr int kOffQ = 4 * kTileBytes;                       // GQ x [16][128] fp16
+  static constexpr int kOffBar = kOffQ + GQ * 16 * kHeadDim * 2;
+  static constexpr int kBytes = kOffBar + 16;
+};
+
+template <int GQ>
+__global__ void __launch_bounds__(GQ * 32)
+prefill_attn_kernel(const PrefillAttnParams p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  using L = PrefillSmem<GQ>;
+  const unsigned tl = kernel_prologue(kKidAttn);
+  const int j = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const QTile qt = p.tiles[blockIdx.y];
+  const int n_heads = p.n_heads, n_kv = p.n_kv;
+  const int head = j * GQ + warp;
+  const int max_ctx = qt.ctx0 + qt.nrows - 1;
+  const int nchunks = (max_ctx + kChunkTokens - 1) / kChunkTokens;
+  const int nblocks = (max_ctx + kBlockTokens - 1) / kBlockTokens;
+  const int32_t* bt = p.block_tables + (size_t)qt.bt_row * p.bt_stride;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kOffBar);
+
+  auto issue_chunk = [&](int c) {   // thread 0
+    const int buf = c & 1;
+    unsigned char* Kt = smem + L::kOffKV + buf * 2 * kTileBytes;
+    unsigned char* Vt = Kt + kTileBytes;
+    const int b0 = c * kChunkBlocks;
+    const int nb = min(kChunkBlocks, nblocks - b0);
+    mbar_arrive_expect_tx(&bars[buf], (uint32_t)nb * 2u * kKvBlockBytes);
+    for (int i = 0; i < nb; ++i) {
+      const size_t off = ((size_t)bt[b0 + i] * n_kv + j) * (size_t)(kBlockTokens * kHeadDim);
+      bulk_g2s(Kt + i * kKvBlockBytes, p.k_cache + off, kKvBlockBytes, &bars[buf]);
+      bulk_g2s(Vt + i * kKvBlockBytes, p.v_cache + off, kKvBlockBytes, &bars[buf]);
+    }
+  };
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    fence_mbar_init();
+    issue_chunk(0);
+    if (nchunks > 1) issue_chunk(1);
+  }
+
+  // ---- this warp's Q tile: 16 rows x 128 dims, swizzled; rows >= nrows are zero ----
+  unsigned char* q_s = smem + L::kOffQ + warp * (16 * 256);
+  for (int i = lane; i < 16 * 16; i += 32) {
+    const int r = i >> 4, cc = i & 15;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (r < qt.nrows) v = *reinterpret_cast<const uint4*>(p.q + ((size_t)(qt.row0 + r) * n_heads + head) * kHeadDim + cc * 8);
+    *reinterpret_cast<uint4*>(q_s + r * 256 + ((cc ^ (r & 7)) << 4)) = v;
+  }
+  __syncwarp();
+  uint32_t qa[8][4];
+  {
+    const int mj = lane >> 3, mr = lane & 7;
+    const int r = (mj & 1) * 8 + mr;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      const int cc = 2 * ks + (mj >> 1);
+      ldmatrix_x4(smem_u32(q_s + r * 256 + ((cc ^ (r & 7)) << 4)), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
+    }
+  }
+  __syncthreads();                                  // barrier init visible to every warp
+
+  const int g = lane >> 2, tq = lane & 3;
+  float o[16][4];
+#pragma unroll
+  for (int dn = 0; dn < 16; ++dn) o[dn][0] = o[dn][1] = o[dn][2] = o[dn][3] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+  const int ctx_r[2] = {qt.ctx0 + g, qt.ctx0 + g + 8};     // keys visible to rows g and g + 8 (causal)
+  const float scale = 0.08838834764831845f;
+
+  for (int c = 0; c < nchunks; ++c) {
+    const int buf = c & 1;
+    unsigned char* Kt = smem + L::kOffKV + buf * 2 * kTileBytes;
+    unsigned char* Vt = Kt + kTileBytes;
+    mbar_wait(&bars[buf], (uint32_t)(c >> 1) & 1u);
+    const int nvalid = min(kChunkTokens, max_ctx - c * kChunkTokens);
+    const int nb = (nvalid + kBlockTokens - 1) / kBlockTokens;
+
+    float sc[8][4];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      float d[4] = {0.f, 0.f, 0.f, 0.f};
+      if (nt * 8 < nvalid) {
+        const int mj = lane >> 3, tok = nt * 8 + (lane & 7);
+        const uint32_t rowaddr = smem_u32(Kt + (tok >> 4) * kKvBlockBytes + (tok & 15) * 256);
+#pragma unroll
+        for (int k2 = 0; k2 < 4; ++k2) {
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4(rowaddr + ((((4 * k2 + mj) ^ (tok & 7))) << 4), b0, b1, b2, b3);
+          mma_16816(d, qa[2 * k2], b0, b1);
+          mma_16816(d, qa[2 * k2 + 1], b2, b3);
+        }
+      }
+      const int t0 = c * kChunkTokens + nt * 8 + 2 * tq;       // absolute key position
+      sc[nt][0] = t0 < ctx_r[0] ? d[0] * scale : -INFINITY;
+      sc[nt][1] = t0 + 1 < ctx_r[0] ? d[1] * scale : -INFINITY;
+      sc[nt][2] = t0 < ctx_r[1] ? d[2] * scale : -INFINITY;
+      sc[nt][3] = t0 + 1 < ctx_r[1] ? d[3] * scale : -INFINITY;
+    }
+    uint32_t pa[4][4];
+#pragma unroll
+    for (int hr = 0; hr < 2; ++hr) {                            // row g (hr = 0) and row g + 8 (hr = 1)
+      float mx = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) mx = fmaxf(mx, fmaxf(sc[nt][2 * hr], sc[nt][2 * hr + 1]));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      const float m_new = fmaxf(m_run[hr], mx);
+      // a row whose keys are all masked so far (padding rows of a short tile) keeps max = -inf: use 0
+      const float m_use = m_new == -INFINITY ? 0.f : m_new;
+      const float corr = expf(m_run[hr] - m_use);
+      float sum = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const float p0 = expf(sc[nt][2 * hr] - m_use), p1 = expf(sc[nt][2 * hr + 1] - m_use);
+        sum += p0 + p1;
+        pa[nt >> 1][(nt & 1) * 2 + hr] = pack_half2(p0, p1);
+      }
+      sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+      sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+      l_run[hr] = l_run[hr] * corr + sum;
+      m_run[hr] = m_new;
+#pragma unroll
+      for (int dn = 0; dn < 16; ++dn) { o[dn][2 * hr] *= corr; o[dn][2 * hr + 1] *= corr; }
+    }
+#pragma unroll
+    for (int kt = 0; kt < 4; ++kt) {
+      if (kt < nb) {
+        const int mj = lane >> 3, r = (mj & 1) * 8 + (lane & 7);
+        const uint32_t rowaddr = smem_u32(Vt + kt * kKvBlockBytes + r * 256);
+#pragma unroll
+        for (int d2 = 0; d2 < 8; ++d2) {
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4_trans(rowaddr + (((2 * d2 + (mj >> 1)) ^ (r & 7)) << 4), b0, b1, b2, b3);
+          mma_16816(o[2 * d2], pa[kt], b0, b1);
+          mma_16816(o[2 * d2 + 1], pa[kt], b2, b3);
+        }
+      }
+    }
+    __syncthreads();                                            // every warp is done with this buffer
+    if (tid == 0 && c + 2 < nchunks) issue_chunk(c + 2);
+  }
+
+  // ---- write O / l for rows g and g + 8 ----
+#pragma unroll
+  for (int hr = 0; hr < 2; ++hr) {
+    const int r = g + 8 * hr;
+    if (r < qt.nrows) {
+      const float inv = 1.f / l_run[hr];
+      __half* orow = p.out + ((size_t)(qt.row0 + r) * n_heads + head) * kHeadDim;
+#pragma unroll
+      for (int dn = 0; dn < 16; ++dn)
+        *reinterpret_cast<uint32_t*>(orow + dn * 8 + 2 * tq) = pack_half2(o[dn][2 * hr] * inv, o[dn][2 * hr + 1] * inv);
+    }
+  }
+  kernel_epilogue(tl);
+}
+
+template <int GQ>
+static int launch_prefill_gq(const PrefillAttnParams& p, int n_tiles, cudaStream_t s) {
+  static bool configured = false;
+  auto kern = prefill_attn_kernel<GQ>;
+  if (!configured) {
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PrefillSmem<GQ>::kBytes));
+    configured = true;
+  }
+  dim3 grid(p.n_kv, n_tiles);
+  B200_CUDA(launch_k(kern, grid, dim3(GQ * 32), (size_t)PrefillSmem<GQ>::kBytes, s, p));
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+int launch_prefill_attn(const __half* q, const __half* k_cache, const __half* v_cache, const int32_t* block_tables,
+                        int bt_stride, const int32_t* tiles, int n_tiles, int n_heads, int n_kv, __half* out,
+                        cudaStream_t s) {
+  B200_REQUIRE(n_kv > 0 && n_heads % n_kv == 0, "prefill_attn: n_heads % n_kv");
+  B200_REQUIRE(n_tiles <= 65535, "prefill_attn: at most 65535 query tiles per launch");
+  if (n_tiles == 0) return B200_OK;
+  PrefillAttnParams p{};
+  p.q = q; p.k_cache = k_cache; p.v_cache = v_cache; p.block_tables = block_tables; p.bt_stride = bt_stride;
+  p.tiles = reinterpret_cast<const QTile*>(tiles); p.n_heads = n_heads; p.n_kv = n_kv; p.out = out;
+#define CASE(G) case G: return launch_prefill_gq<G>(p, n_tiles, s)
+  switch (n_heads / n_kv) {
+    CASE(1); CASE(2); CASE(3); CASE(4); CASE(5); CASE(6); CASE(7); CASE(8);
+    default:
+      set_last_error("prefill_attn: n_heads / n_kv_heads must be in 1..8");
+      return B200_ERR_INVALID;
+  }
+#undef CASE
+}
+
 template <int GQ, bool kFused>
 static int launch_gq(const AttnParams& p, int T, cudaStream_t s) {
   static bool configured = false;   // per process; the attribute is idempotent

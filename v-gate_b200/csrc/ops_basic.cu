@@ -133,17 +133,17 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
     const int i = threadIdx.x + it * kNormThreads;
     if (i < nvec) {
       float4 a = *reinterpret_cast<const float4*>(h + (size_t)row * H + 4 * i);
-      // partials: issue the loads four at a time before adding (one L2 round trip per four parts),
-      // then add in the fixed order p = 0, 1, 2, ... so the sum is deterministic
-      for (int p0 = 0; p0 < n_parts; p0 += 4) {
-        float4 b[4];
+      // partials: all loads (up to 16 per batch) are issued before the first add -- one L2 round trip
+      // -- then added in the fixed order p = 0, 1, 2, ... so the sum is deterministic
+      for (int p0 = 0; p0 < n_parts; p0 += 16) {
+        float4 b[16];
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
+        for (int k = 0; k < 16; ++k)
           b[k] = p0 + k < n_parts
                      ? __ldcg(reinterpret_cast<const float4*>(parts + (size_t)(p0 + k) * part_stride + (size_t)row * H + 4 * i))
                      : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
+        for (int k = 0; k < 16; ++k) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
       }
       if (n_parts > 0) *reinterpret_cast<float4*>(h + (size_t)row * H + 4 * i) = a;
       v[it] = a;
