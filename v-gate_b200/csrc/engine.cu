@@ -13,6 +13,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <tuple>
 #include <unordered_map>
 #include <vector>
 
@@ -54,7 +55,8 @@ __global__ void advance_decode_kernel(int B, const int32_t* __restrict__ next_id
                                       int32_t* __restrict__ pos, int32_t* __restrict__ slot,
                                       int32_t* __restrict__ ctx, int32_t* __restrict__ n_gen,
                                       const int32_t* __restrict__ bt_row, const int32_t* __restrict__ block_tables,
-                                      int bt_stride, int32_t* __restrict__ out_tokens, int out_stride) {
+                                      int bt_stride, int32_t* __restrict__ out_tokens, int out_stride,
+                                      int32_t* __restrict__ sample_step) {
   const unsigned tl = kernel_prologue(kKidAdvance);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B) return;
@@ -62,6 +64,7 @@ __global__ void advance_decode_kernel(int B, const int32_t* __restrict__ next_id
   const int g = n_gen[i];
   if (out_tokens && g < out_stride) out_tokens[(size_t)i * out_stride + g] = tok;
   n_gen[i] = g + 1;
+  sample_step[i] += 1;                    // index of the token about to be sampled (RNG counter)
   ids[i] = tok;
   const int p = pos[i] + 1;
   pos[i] = p;
@@ -153,8 +156,15 @@ struct b200_engine {
   size_t hp_cap = 0;
 
   // ---- decode CUDA graphs (generate_batch path) ----
-  std::map<int, cudaGraphExec_t> decode_graphs;
-  std::map<int, int64_t> graph_launches_per_step;
+  struct GraphKey {
+    int n; const void* out; int stride;
+    bool operator<(const GraphKey& o) const { return std::tie(n, out, stride) < std::tie(o.n, o.out, o.stride); }
+  };
+  struct GraphVal { cudaGraphExec_t exec; int64_t launches; };
+  std::map<GraphKey, GraphVal> decode_graphs;  // one captured decode step (advance + forward) per configuration
+  std::map<int, bool> decode_warm;             // batch sizes whose kernels have run eagerly once
+  int poll_waiters = 0;                        // threads blocked in b200_poll (guarded by mu)
+  std::vector<int64_t> last_decode_ids;        // scheduler: request ids of the previous decode step, in row order
 
   // ---- scheduler ----
   std::mutex mu;
@@ -353,7 +363,106 @@ struct b200_engine {
   }
 
   // ---- one scheduler step over `batch`; prefill rows for new requests, one row for running ones.
+  // One decode step for the n sequences whose state sits in the d_* buffers: the advance kernel
+  // consumes the previously sampled token (d_next), then the forward pass samples the next one.
+  // The first step of a batch size runs eagerly (loads every kernel), later ones replay a CUDA graph.
+  int decode_step(int n, int32_t* out_tokens, int out_stride) {
+    auto eager = [&]() -> int {
+      B200_CUDA(launch_k(advance_decode_kernel, dim3((n + 127) / 128), dim3(128), 0, stream, n, d_next.as<int32_t>(),
+                         d_ids.as<int32_t>(), d_pos.as<int32_t>(), d_slot.as<int32_t>(), d_ctx.as<int32_t>(),
+                         d_ngen.as<int32_t>(), d_btrow.as<int32_t>(), d_bt.as<int32_t>(), max_blocks_per_seq,
+                         out_tokens, out_stride, d_step.as<int32_t>()));
+      g_launch_count += 1;
+      return forward(n, n, nullptr, true);
+    };
+    if (!cfg.use_cuda_graphs || !decode_warm[n]) {
+      decode_warm[n] = true;
+      return eager();
+    }
+    const GraphKey key{n, out_tokens, out_stride};
+    auto it = decode_graphs.find(key);
+    if (it == decode_graphs.end()) {
+      if (decode_graphs.size() >= 64) {               // bound the cache
+        for (auto& g : decode_graphs) cudaGraphExecDestroy(g.second.exec);
+        decode_graphs.clear();
+      }
+      cudaGraph_t g = nullptr;
+      B200_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+      const int64_t before = g_launch_count;
+      const int rc = eager();
+      const int64_t per_step = g_launch_count - before;
+      g_launch_count = before;
+      const cudaError_t ce = cudaStreamEndCapture(stream, &g);
+      if (rc != B200_OK) { if (g) cudaGraphDestroy(g); return rc; }
+      B200_CUDA(ce);
+      cudaGraphExec_t exec = nullptr;
+      B200_CUDA(cudaGraphInstantiate(&exec, g, 0));
+      B200_CUDA(cudaGraphDestroy(g));
+      it = decode_graphs.emplace(key, GraphVal{exec, per_step}).first;
+    }
+    B200_CUDA(cudaGraphLaunch(it->second.exec, stream));
+    g_launch_count += it->second.launches;
+    return B200_OK;
+  }
+
+  // Scheduler decode step.  When the batch is the same set of sequences as in the previous decode
+  // step nothing is uploaded: the device already holds their state and the sampled tokens.
+  int run_decode(const std::vector<std::shared_ptr<Request>>& batch) {
+    const int n = (int)batch.size();
+    std::vector<int64_t> idsig(n);
+    for (int r = 0; r < n; ++r) idsig[r] = batch[r]->id;
+    int rc;
+    int64_t ctx_sum = 0;
+    for (int r = 0; r < n; ++r) ctx_sum += (int64_t)batch[r]->prompt.size() + (int64_t)batch[r]->out.size();
+    if (idsig != last_decode_ids) {
+      // state BEFORE the advance kernel: last token in d_next, position one behind
+      std::vector<int32_t> next(n), pos(n), btrow(n), step(n), seed(n), bt((size_t)cfg.max_seqs * max_blocks_per_seq, 0);
+      std::vector<float> temp(n), topp(n);
+      for (int r = 0; r < n; ++r) {
+        Request& q = *batch[r];
+        const int n_ctx = (int)q.prompt.size() + (int)q.out.size();
+        next[r] = q.out.back();
+        pos[r] = n_ctx - 2;
+        btrow[r] = q.seq_slot;
+        step[r] = (int32_t)q.out.size() - 1;
+        seed[r] = (int32_t)q.seed;
+        temp[r] = q.temperature;
+        topp[r] = q.top_p;
+        std::copy(q.blocks.begin(), q.blocks.end(), bt.begin() + (size_t)q.seq_slot * max_blocks_per_seq);
+      }
+      if ((rc = upload_i32(d_next, next)) || (rc = upload_i32(d_pos, pos)) || (rc = upload_i32(d_btrow, btrow)) ||
+          (rc = upload_i32(d_step, step)) || (rc = upload_i32(d_seed, seed)) || (rc = upload_i32(d_bt, bt)) ||
+          (rc = upload_f32(d_temp, temp)) || (rc = upload_f32(d_topp, topp)))
+        return rc;
+      B200_CUDA(cudaStreamSynchronize(stream));      // the host vectors above go out of scope
+      last_decode_ids = idsig;
+    }
+    const int64_t launches0 = g_launch_count;
+    B200_CUDA(cudaEventRecord(ev0, stream));
+    if ((rc = decode_step(n, nullptr, 0))) return rc;
+    B200_CUDA(cudaEventRecord(ev1, stream));
+    std::vector<int32_t> next(n);
+    B200_CUDA(cudaMemcpyAsync(next.data(), d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+    B200_CUDA(cudaStreamSynchronize(stream));
+    float ms = 0.f;
+    B200_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+    const double t = now_s();
+    std::lock_guard<std::mutex> lk(mu);
+    stats.kernel_launches += g_launch_count - launches0;
+    stats.steps_decode++; stats.gpu_seconds_decode += ms * 1e-3; stats.decode_batch_sum += n;
+    stats.hbm_bytes_decode += decode_step_bytes(n, ctx_sum);
+    stats.tokens_generated += n;
+    for (int r = 0; r < n; ++r) {
+      Request& q = *batch[r];
+      q.out.push_back(next[r]);
+      q.t_last = t;
+    }
+    return B200_OK;
+  }
+
   int run_step(const std::vector<std::shared_ptr<Request>>& batch, bool is_prefill) {
+    if (!is_prefill) return run_decode(batch);
+    last_decode_ids.clear();                         // a prefill pass overwrites the d_* state
     std::vector<int32_t> ids, pos, slot, btrow, ctx, lastrows, bt, step;
     std::vector<float> temp, topp;
     std::vector<int32_t> seed;
@@ -475,15 +584,19 @@ struct b200_engine {
       if (rc != B200_OK) { fail_all(g_last_error); continue; }
       if (is_prefill) for (auto& r : admitted) running.push_back(r);
       // retire finished sequences
+      bool any_done = false;
       for (auto it = running.begin(); it != running.end();) {
         Request& r = **it;
         const bool eos = cfg.eos_token_id >= 0 && !r.out.empty() && r.out.back() == cfg.eos_token_id;
         if ((int)r.out.size() >= r.max_tokens || eos) {
           r.state = ReqState::FINISHED; release_request_resources(r); stats.requests_finished++;
           it = running.erase(it);
+          any_done = true;
         } else ++it;
       }
-      cv_done.notify_all();
+      // waking every blocked b200_wait caller on every step costs more than the step's bookkeeping;
+      // only finished requests and streaming pollers need to hear about it
+      if (any_done || poll_waiters > 0) cv_done.notify_all();
     }
   }
 };
@@ -777,7 +890,7 @@ void b200_engine_destroy(b200_engine* e) {
   if (e->worker.joinable()) e->worker.join();
   cudaSetDevice(e->cfg.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
-  for (auto& g : e->decode_graphs) cudaGraphExecDestroy(g.second);
+  for (auto& g : e->decode_graphs) cudaGraphExecDestroy(g.second.exec);
   for (auto& w : e->layers) {
     for (int i = 0; i < 4; ++i) { w.wq[i].release(); w.sc[i].release(); w.zp[i].release(); w.chunks[i].release(); }
     w.bias_qkv.release(); w.ln1.release(); w.ln2.release();
@@ -857,7 +970,11 @@ int32_t b200_poll(b200_engine* e, int64_t rid, int32_t* out_ids, int32_t cap, in
   if (it == e->table.end()) { set_last_error("unknown request id"); return B200_ERR_NOT_FOUND; }
   std::shared_ptr<Request> r = it->second;
   auto ready = [&] { return r->out.size() > r->n_polled || (r->state != ReqState::WAITING && r->state != ReqState::RUNNING); };
-  if (timeout_ms > 0) e->cv_done.wait_for(lk, std::chrono::milliseconds(timeout_ms), ready);
+  if (timeout_ms > 0) {
+    e->poll_waiters++;
+    e->cv_done.wait_for(lk, std::chrono::milliseconds(timeout_ms), ready);
+    e->poll_waiters--;
+  }
   const int avail = (int)(r->out.size() - r->n_polled);
   const int n = std::min(avail, std::max(cap, 0));
   if (out_ids && n > 0) std::memcpy(out_ids, r->out.data() + r->n_polled, (size_t)n * 4);
@@ -977,60 +1094,20 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
       return rc;
     B200_CUDA(cudaStreamSynchronize(s));
   }
-  auto advance = [&]() -> int {
-    launch_k(advance_decode_kernel, dim3((n_seqs + 127) / 128), dim3(128), 0, s,
-        n_seqs, e->d_next.as<int32_t>(), e->d_ids.as<int32_t>(), e->d_pos.as<int32_t>(), e->d_slot.as<int32_t>(),
-        e->d_ctx.as<int32_t>(), e->d_ngen.as<int32_t>(), e->d_btrow.as<int32_t>(), e->d_bt.as<int32_t>(),
-        e->max_blocks_per_seq, e->d_out_tokens.as<int32_t>(), max_tokens);
-    g_launch_count += 1;
-    B200_CUDA(cudaGetLastError());
-    return B200_OK;
-  };
-  auto step_once = [&]() -> int {
-    int r2;
-    if ((r2 = advance())) return r2;
-    return e->forward(n_seqs, n_seqs, nullptr, true);
-  };
+  e->last_decode_ids.clear();
   B200_CUDA(cudaEventRecord(e->ev0, s));
-  // step 1 runs eagerly: it loads every kernel of the decode configuration before any capture
-  int t = 1;
-  if (t < max_tokens) {
-    if ((rc = step_once())) return rc;
-    if (logits_out && t < n_logit_steps)
-      B200_CUDA(cudaMemcpy2DAsync(logits_out + (size_t)t * e->V, (size_t)n_logit_steps * e->V * 4, e->logits.p,
-                                  (size_t)e->V * 4, (size_t)e->V * 4, n_seqs, cudaMemcpyDeviceToHost, s));
-    ++t;
-  }
-  cudaGraphExec_t graph = nullptr;
-  if (e->cfg.use_cuda_graphs && t < max_tokens) {
-    auto it = e->decode_graphs.find(n_seqs);
-    if (it != e->decode_graphs.end()) graph = it->second;
-    else {
-      cudaGraph_t g = nullptr;
-      B200_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
-      const int64_t before = g_launch_count;
-      rc = step_once();
-      const int64_t per_step = g_launch_count - before;
-      g_launch_count = before;
-      cudaError_t ce = cudaStreamEndCapture(s, &g);
-      if (rc != B200_OK) { if (g) cudaGraphDestroy(g); return rc; }
-      B200_CUDA(ce);
-      B200_CUDA(cudaGraphInstantiate(&graph, g, 0));
-      B200_CUDA(cudaGraphDestroy(g));
-      e->decode_graphs[n_seqs] = graph;
-      e->graph_launches_per_step[n_seqs] = per_step;
-    }
-  }
-  for (; t < max_tokens; ++t) {
-    if (graph) {
-      B200_CUDA(cudaGraphLaunch(graph, s));
-      g_launch_count += e->graph_launches_per_step[n_seqs];
-    } else if ((rc = step_once())) return rc;
+  for (int t = 1; t < max_tokens; ++t) {
+    if ((rc = e->decode_step(n_seqs, e->d_out_tokens.as<int32_t>(), max_tokens))) return rc;
     if (logits_out && t < n_logit_steps)
       B200_CUDA(cudaMemcpy2DAsync(logits_out + (size_t)t * e->V, (size_t)n_logit_steps * e->V * 4, e->logits.p,
                                   (size_t)e->V * 4, (size_t)e->V * 4, n_seqs, cudaMemcpyDeviceToHost, s));
   }
-  if ((rc = advance())) return rc;     // record the last sampled token
+  // record the last sampled token
+  B200_CUDA(launch_k(advance_decode_kernel, dim3((n_seqs + 127) / 128), dim3(128), 0, s, n_seqs, e->d_next.as<int32_t>(),
+                     e->d_ids.as<int32_t>(), e->d_pos.as<int32_t>(), e->d_slot.as<int32_t>(), e->d_ctx.as<int32_t>(),
+                     e->d_ngen.as<int32_t>(), e->d_btrow.as<int32_t>(), e->d_bt.as<int32_t>(), e->max_blocks_per_seq,
+                     e->d_out_tokens.as<int32_t>(), max_tokens, e->d_step.as<int32_t>()));
+  g_launch_count += 1;
   B200_CUDA(cudaEventRecord(e->ev1, s));
   B200_CUDA(cudaMemcpyAsync(out_ids, e->d_out_tokens.p, (size_t)n_seqs * max_tokens * 4, cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaStreamSynchronize(s));
