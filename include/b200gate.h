@@ -176,6 +176,12 @@ void b200_debug_timeline(void* buf, void* counter, uint32_t capacity);
 /* tcgen05/TMEM GEMM with dense fp16 weights W[N, K] fed by TMA (lm_head); N % 128 == 0, K % 64 == 0. */
 int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T,
                               int32_t K, int32_t N, int32_t accumulate, void* stream);
+/* Greedy lm_head (vLLM sampler.py:223-236 greedy branch over LogitsProcessor output): out[t] =
+ * argmax_n x[t] . W[n]  (highest logit, lowest index on ties) without writing the [T, N] logits: the
+ * GEMM epilogue reduces every 128-row tile to {max, argmax}, a second kernel finishes per token.
+ * scratch: device, (N / 128) * T * 8 bytes.  N % 128 == 0, K % 64 == 0. */
+int32_t b200_op_lm_head_argmax(const void* w, const void* x, int32_t ldx, int32_t T, int32_t K, int32_t N,
+                               float* scratch, int32_t* out, void* stream);
 /* Same contract with dense fp16 weights W[N, K] (lm_head). */
 int32_t b200_op_f16_gemv(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t B,
                          int32_t K, int32_t N, int32_t accumulate, void* stream);

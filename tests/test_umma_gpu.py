@@ -91,6 +91,28 @@ def test_f16_umma_matches_oracle(T):
     assert np.abs(y.cpu().numpy() - ref).max() < TOL
 
 
+@pytest.mark.parametrize("T", [1, 17, 64, 130])
+def test_lm_head_argmax_equals_argmax_of_logits(T):
+    """Fused greedy lm_head: bit-identical choice to argmax over the logits the store epilogue writes
+    (first maximum wins), including exact ties planted in different 128-row tiles."""
+    rng = np.random.default_rng(100 + T)
+    K, N = 1536, 8192
+    w = (rng.standard_normal((N, K)) * 0.02).astype(np.float16)
+    w[4000] = w[77]                                  # equal logits in tiles 0 and 31 -> the lower index must win
+    w[77 + 128] = w[77]
+    x = rng.standard_normal((T, K)).astype(np.float16)
+    x[0] = (w[77].astype(np.float32) * 40).astype(np.float16)       # row 0 points at the tied rows
+    wd, xd = dev(w), dev(x)
+    y = torch.empty((T, N), dtype=torch.float32, device="cuda")
+    check(lib().b200_op_f16_gemm_umma(ptr(wd), ptr(xd), K, ptr(y), N, T, K, N, 0, stream()))
+    scratch = torch.empty((N // 128, T, 2), dtype=torch.float32, device="cuda")
+    out = torch.full((T,), -1, dtype=torch.int32, device="cuda")
+    check(lib().b200_op_lm_head_argmax(ptr(wd), ptr(xd), K, T, K, N, ptr(scratch), ptr(out), stream()))
+    logits = y.cpu().numpy()
+    assert np.array_equal(out.cpu().numpy(), logits.argmax(-1).astype(np.int32))     # numpy: first maximum
+    assert out[0].item() == 77
+
+
 def test_w4_umma_group_size_64():
     rng = np.random.default_rng(64)
     K, N, T, G = 1536, 256, 33, 64

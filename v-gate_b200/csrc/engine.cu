@@ -146,6 +146,8 @@ struct b200_engine {
   // ---- activations / metadata ----
   int Tmax = 0;
   DevMem h, xn, qkv, qh, attn, gu, act, xn_last, logits;
+  DevMem amax;                                 // greedy lm_head: float2 {tile max, argmax} [V/128][max_seqs]
+  bool greedy_only = false;                    // every row of the pending pass is greedy: skip the logits, fuse argmax
   DevMem d_ids, d_pos, d_slot, d_btrow, d_ctx, d_lastrows, d_bt, d_temp, d_topp, d_seed, d_step, d_next, d_ngen;
   DevMem d_out_tokens;
   DevMem d_tiles;                              // prefill query tiles {row0, nrows, bt_row, ctx0}
@@ -157,8 +159,8 @@ struct b200_engine {
 
   // ---- decode CUDA graphs (generate_batch path) ----
   struct GraphKey {
-    int n; const void* out; int stride;
-    bool operator<(const GraphKey& o) const { return std::tie(n, out, stride) < std::tie(o.n, o.out, o.stride); }
+    int n; const void* out; int stride; bool greedy;
+    bool operator<(const GraphKey& o) const { return std::tie(n, out, stride, greedy) < std::tie(o.n, o.out, o.stride, o.greedy); }
   };
   struct GraphVal { cudaGraphExec_t exec; int64_t launches; };
   std::map<GraphKey, GraphVal> decode_graphs;  // one captured decode step (advance + forward) per configuration
@@ -236,13 +238,20 @@ struct b200_engine {
     return launch_umma_w4(lw.ulin[i], *mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, 1, 0, stream);
   }
 
-  int lm_head(const __half* head, int n_rows) {
+  // *fused_argmax: the GEMM epilogue reduced each 128-row vocabulary tile to {max, argmax} (amax) instead
+  // of writing logits; the caller finishes with launch_argmax_reduce.
+  int lm_head(const __half* head, int n_rows, bool want_argmax, bool* fused_argmax) {
+    *fused_argmax = false;
     if (!use_umma(n_rows) || V % 128 != 0 || (debug_gemv_mask >> 4 & 1))
       return launch_f16_gemv(head, xn_last.as<__half>(), H, logits.as<float>(), V, n_rows, H, V, false, stream);
     const int nt = umma_pick_nt(n_rows, false);
     const CUtensorMap *mx, *mw;
     int rc;
     if ((rc = get_map(xn_last.as<__half>(), cfg.max_seqs, H, nt, &mx)) || (rc = get_map(head, V, H, 128, &mw))) return rc;
+    if (want_argmax) {
+      *fused_argmax = true;
+      return launch_umma_f16(*mw, H, V, *mx, nt, n_rows, amax.as<float>(), cfg.max_seqs, kUmmaArgmaxF32, stream);
+    }
     return launch_umma_f16(*mw, H, V, *mx, nt, n_rows, logits.as<float>(), V, kUmmaStoreF32, stream);
   }
 
@@ -302,10 +311,13 @@ struct b200_engine {
     if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, pend_stride, final_norm.as<__half>(), cfg.rms_eps,
                              rows, n_rows, H, xn_last.as<__half>(), stream))) return rc;
     const __half* head = cfg.tie_embeddings ? embed.as<__half>() : lm_head_w.as<__half>();
-    if (!skip(7) && (rc = lm_head(head, n_rows))) return rc;
+    bool fused = false;
+    if (!skip(7) && (rc = lm_head(head, n_rows, want_sample && greedy_only, &fused))) return rc;
     if (want_sample && !skip(8)) {
-      if ((rc = launch_sample(logits.as<float>(), n_rows, V, d_temp.as<float>(), d_topp.as<float>(),
-                              d_seed.as<uint32_t>(), d_step.as<int32_t>(), d_next.as<int32_t>(), stream))) return rc;
+      if (fused) {
+        if ((rc = launch_argmax_reduce(amax.as<float>(), V / 128, cfg.max_seqs, n_rows, d_next.as<int32_t>(), stream))) return rc;
+      } else if ((rc = launch_sample(logits.as<float>(), n_rows, V, d_temp.as<float>(), d_topp.as<float>(),
+                                     d_seed.as<uint32_t>(), d_step.as<int32_t>(), d_next.as<int32_t>(), stream))) return rc;
     }
     return B200_OK;
   }
@@ -375,11 +387,11 @@ struct b200_engine {
       g_launch_count += 1;
       return forward(n, n, nullptr, true);
     };
-    if (!cfg.use_cuda_graphs || !decode_warm[n]) {
-      decode_warm[n] = true;
+    if (!cfg.use_cuda_graphs || !decode_warm[2 * n + (greedy_only ? 1 : 0)]) {
+      decode_warm[2 * n + (greedy_only ? 1 : 0)] = true;
       return eager();
     }
-    const GraphKey key{n, out_tokens, out_stride};
+    const GraphKey key{n, out_tokens, out_stride, greedy_only};
     auto it = decode_graphs.find(key);
     if (it == decode_graphs.end()) {
       if (decode_graphs.size() >= 64) {               // bound the cache
@@ -413,7 +425,11 @@ struct b200_engine {
     for (int r = 0; r < n; ++r) idsig[r] = batch[r]->id;
     int rc;
     int64_t ctx_sum = 0;
-    for (int r = 0; r < n; ++r) ctx_sum += (int64_t)batch[r]->prompt.size() + (int64_t)batch[r]->out.size();
+    greedy_only = true;
+    for (int r = 0; r < n; ++r) {
+      ctx_sum += (int64_t)batch[r]->prompt.size() + (int64_t)batch[r]->out.size();
+      greedy_only = greedy_only && batch[r]->temperature < 1e-5f;
+    }
     if (idsig != last_decode_ids) {
       // state BEFORE the advance kernel: last token in d_next, position one behind
       std::vector<int32_t> next(n), pos(n), btrow(n), step(n), seed(n), bt((size_t)cfg.max_seqs * max_blocks_per_seq, 0);
@@ -469,6 +485,7 @@ struct b200_engine {
     const int n = (int)batch.size();
     bt.assign((size_t)cfg.max_seqs * max_blocks_per_seq, 0);
     int64_t ctx_sum = 0;
+    greedy_only = true;
     for (int r = 0; r < n; ++r) {
       Request& q = *batch[r];
       const int n_ctx = (int)q.prompt.size() + (int)q.out.size();   // tokens known so far
@@ -482,6 +499,7 @@ struct b200_engine {
       }
       ctx_sum += n_ctx;
       lastrows.push_back((int)ids.size() - 1);
+      greedy_only = greedy_only && q.temperature < 1e-5f;
       temp.push_back(q.temperature);
       topp.push_back(q.top_p);
       seed.push_back((int32_t)q.seed);
@@ -839,7 +857,7 @@ int32_t b200_engine_finalize(b200_engine* e) {
   if ((rc = e->h.alloc(T * e->H * 4)) || (rc = e->xn.alloc(T * e->H * 2)) || (rc = e->qkv.alloc(T * e->QKV * 4)) ||
       (rc = e->qh.alloc(T * e->NH * kHeadDim * 2)) || (rc = e->attn.alloc(T * e->NH * kHeadDim * 2)) ||
       (rc = e->gu.alloc(T * 2 * e->I * 4)) || (rc = e->act.alloc(T * e->I * 2)) || (rc = e->xn_last.alloc(S * e->H * 2)) ||
-      (rc = e->logits.alloc(S * e->V * 4)) || (rc = e->d_ids.alloc(T * 4)) || (rc = e->d_pos.alloc(T * 4)) ||
+      (rc = e->logits.alloc(S * e->V * 4)) || (rc = e->amax.alloc(((size_t)e->V / 128 + 1) * S * 8)) || (rc = e->d_ids.alloc(T * 4)) || (rc = e->d_pos.alloc(T * 4)) ||
       (rc = e->d_slot.alloc(T * 4)) || (rc = e->d_btrow.alloc(T * 4)) || (rc = e->d_ctx.alloc(T * 4)) ||
       (rc = e->d_lastrows.alloc(S * 4)) || (rc = e->d_tiles.alloc(T * 16)) || (rc = e->d_bt.alloc(S * e->max_blocks_per_seq * 4)) ||
       (rc = e->d_temp.alloc(S * 4)) || (rc = e->d_topp.alloc(S * 4)) || (rc = e->d_seed.alloc(S * 4)) ||
@@ -897,7 +915,7 @@ void b200_engine_destroy(b200_engine* e) {
   }
   for (auto& kv : e->pending) { kv.second.qweight.release(); kv.second.qzeros.release(); kv.second.scales.release(); }
   DevMem* all[] = {&e->embed, &e->lm_head_w, &e->final_norm, &e->cos_t, &e->sin_t, &e->k_cache, &e->v_cache, &e->h,
-                   &e->xn, &e->qkv, &e->qh, &e->attn, &e->gu, &e->act, &e->xn_last, &e->logits, &e->d_ids, &e->d_pos,
+                   &e->xn, &e->qkv, &e->qh, &e->attn, &e->gu, &e->act, &e->xn_last, &e->logits, &e->amax, &e->d_ids, &e->d_pos,
                    &e->d_slot, &e->d_btrow, &e->d_ctx, &e->d_lastrows, &e->d_bt, &e->d_temp, &e->d_topp, &e->d_seed,
                    &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens, &e->parts, &e->attn_scratch, &e->attn_counters, &e->d_tiles};
   for (DevMem* m : all) m->release();
@@ -1074,6 +1092,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
         (rc = e->upload_i32(e->d_btrow, btrow)) || (rc = e->upload_i32(e->d_ctx, ctx)) ||
         (rc = e->upload_i32(e->d_lastrows, lastrows)) || (rc = e->upload_q_tiles(btrow, ctx)))
       return rc;
+    e->greedy_only = !(logits_out && n_logit_steps > 0);
     if ((rc = e->forward(ns * n_prompt, ns, e->d_lastrows.as<int32_t>(), false))) return rc;
     B200_CUDA(cudaMemcpyAsync(first_tokens.data() + s0, e->d_next.p, (size_t)ns * 4, cudaMemcpyDeviceToHost, s));
     if (logits_out && n_logit_steps > 0)
@@ -1097,6 +1116,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
   e->last_decode_ids.clear();
   B200_CUDA(cudaEventRecord(e->ev0, s));
   for (int t = 1; t < max_tokens; ++t) {
+    e->greedy_only = !(logits_out && t < n_logit_steps);      // logits are materialised only when asked for
     if ((rc = e->decode_step(n_seqs, e->d_out_tokens.as<int32_t>(), max_tokens))) return rc;
     if (logits_out && t < n_logit_steps)
       B200_CUDA(cudaMemcpy2DAsync(logits_out + (size_t)t * e->V, (size_t)n_logit_steps * e->V * 4, e->logits.p,
@@ -1193,6 +1213,18 @@ int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* 
   if (rc) return rc;
   if ((rc = make_tensor_map_f16(&mw, w, N, K, K, 128))) return rc;
   return launch_umma_f16(mw, K, N, mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, (cudaStream_t)stream);
+}
+int32_t b200_op_lm_head_argmax(const void* w, const void* x, int32_t ldx, int32_t T, int32_t K, int32_t N, float* scratch,
+                               int32_t* out, void* stream) {
+  if (T == 0) return B200_OK;
+  B200_REQUIRE(scratch && out, "lm_head_argmax: null scratch / out");
+  const int nt = umma_pick_nt(T, false);
+  CUtensorMap mx, mw;
+  int rc = make_tensor_map_f16(&mx, x, T, K, ldx, nt);
+  if (rc) return rc;
+  if ((rc = make_tensor_map_f16(&mw, w, N, K, K, 128))) return rc;
+  if ((rc = launch_umma_f16(mw, K, N, mx, nt, T, scratch, T, kUmmaArgmaxF32, (cudaStream_t)stream))) return rc;
+  return launch_argmax_reduce(scratch, N / 128, T, T, out, (cudaStream_t)stream);
 }
 int32_t b200_op_f16_gemv(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t B, int32_t K,
                          int32_t N, int32_t accumulate, void* stream) {

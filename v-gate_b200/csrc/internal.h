@@ -61,7 +61,7 @@ struct UmmaW4 {
   const __half* bias = nullptr;
   int K = 0, N = 0, G = 128;
 };
-enum { kUmmaStoreF32 = 0, kUmmaAccumF32 = 1, kUmmaPartialF32 = 2, kUmmaSwigluF16 = 3 };
+enum { kUmmaStoreF32 = 0, kUmmaAccumF32 = 1, kUmmaPartialF32 = 2, kUmmaSwigluF16 = 3, kUmmaArgmaxF32 = 4 };
 
 size_t umma_w4_chunk_bytes(int K, int N, int G);
 int umma_w4_effective_splits(int K, int G, int n_splits);
@@ -104,6 +104,8 @@ int launch_prefill_attn(const __half* q, const __half* k_cache, const __half* v_
 size_t attn_scratch_floats(int T, int n_heads, int n_kv, int n_splits);
 int launch_swiglu(const float* gu, int T, int I, __half* act, cudaStream_t s);
 int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s);
+// part: float2 {max, bits(argmax)} [n_tiles, ld] from the kUmmaArgmaxF32 epilogue
+int launch_argmax_reduce(const float* part, int n_tiles, int ld, int B, int32_t* out, cudaStream_t s);
 int launch_sample(const float* logits, int B, int V, const float* temperature, const float* top_p,
                   const uint32_t* seed, const int32_t* step, int32_t* out, cudaStream_t s);
 

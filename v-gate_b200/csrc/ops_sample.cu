@@ -172,4 +172,31 @@ int launch_sample(const float* logits, int B, int V, const float* temperature, c
   return B200_OK;
 }
 
+// Greedy decoding without materialised logits: the lm_head GEMM epilogue (ops_umma.cu, kUmmaArgmaxF32)
+// leaves, per 128-row vocabulary tile and token, the tile maximum and its lowest index as
+// float2 {value, bits(index)} in part[tile * ld + token]; this kernel finishes the argmax per token with
+// the same tie rule as sample_kernel (highest value, then lowest index).
+__global__ void __launch_bounds__(kSampleThreads)
+argmax_reduce_kernel(const float2* __restrict__ part, int n_tiles, int ld, int32_t* __restrict__ out) {
+  __shared__ ArgMax red[kSampleThreads / 32];
+  const unsigned tl = kernel_prologue(kKidSample);
+  const int r = blockIdx.x;
+  ArgMax best{-INFINITY, 0x7fffffff};
+  for (int t = threadIdx.x; t < n_tiles; t += kSampleThreads) {
+    const float2 v = __ldcg(part + (size_t)t * ld + r);
+    best = better(best, ArgMax{v.x, __float_as_int(v.y)});
+  }
+  best = block_argmax(best, red);
+  if (threadIdx.x == 0) out[r] = best.i;
+  kernel_epilogue(tl);
+}
+
+int launch_argmax_reduce(const float* part, int n_tiles, int ld, int B, int32_t* out, cudaStream_t s) {
+  if (B == 0) return B200_OK;
+  launch_k(argmax_reduce_kernel, dim3(B), dim3(kSampleThreads), 0, s, reinterpret_cast<const float2*>(part), n_tiles, ld, out);
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 }  // namespace b200

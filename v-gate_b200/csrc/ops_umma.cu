@@ -42,7 +42,7 @@ constexpr int kChunkStride = 512 + 2 * 4096;     // ring slot: scales 256 B + ze
 constexpr int kMaxStages = 8, kMaxRing = 8;
 constexpr int kTileABytes = kUmmaM * kUmmaBK * 2;          // 16 KB
 
-enum UmmaMode : int { kStoreF32 = 0, kAccumF32 = 1, kPartialF32 = 2, kSwigluF16 = 3 };
+enum UmmaMode : int { kStoreF32 = 0, kAccumF32 = 1, kPartialF32 = 2, kSwigluF16 = 3, kArgmaxF32 = 4 };
 
 // ---- PTX wrappers -------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* map, int x, int y, uint64_t* bar) {
@@ -343,6 +343,26 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             *reinterpret_cast<uint4*>(act + (size_t)b * p.ldy + nt * 64 + f8) = o;
           }
         }
+      } else if (p.mode == kArgmaxF32) {
+        // Greedy lm_head: per token the maximum of this tile's 128 features and its lowest index, as
+        // float2 {value, bits(row index)} at y[tile * ldy + token]; finished by argmax_reduce_kernel.
+        // The [T, V] fp32 logits (39 MB at batch 64) are never written.
+        float2* part = reinterpret_cast<float2*>(p.y);
+        for (int bcol = warp; bcol < NT && tok0 + bcol < p.T; bcol += kProducerWarps) {
+          const float4 a = *reinterpret_cast<const float4*>(stage + bcol * 128 + lane * 4);
+          float m = a.x;
+          int mi = lane * 4;
+          if (a.y > m) { m = a.y; mi = lane * 4 + 1; }
+          if (a.z > m) { m = a.z; mi = lane * 4 + 2; }
+          if (a.w > m) { m = a.w; mi = lane * 4 + 3; }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const float om = __shfl_xor_sync(0xffffffffu, m, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, mi, o);
+            if (om > m || (om == m && oi < mi)) { m = om; mi = oi; }
+          }
+          if (lane == 0) part[(size_t)nt * p.ldy + tok0 + bcol] = make_float2(m, __int_as_float(nt * kUmmaM + mi));
+        }
       } else {
         float* ybase = p.y + (p.mode == kPartialF32 ? (size_t)split * p.part_stride : 0) + (size_t)nt * kUmmaM;
         if (p.mode == kAccumF32) grid_dep_wait();                      // y is read-modify-written
@@ -385,14 +405,22 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     if (elect_one()) {
       prefetch_tensormap(&map_x);
       if (!kW4) prefetch_tensormap(&map_w);
+      // fp16 weights (lm_head): the first ring of weight tiles does not depend on the upstream kernel
+      const int pre = kW4 ? 0 : min(nst, kStages);
+      for (int gi = 0; gi < pre; ++gi) {
+        mbar_arrive_expect_tx(&sb->full[gi], (uint32_t)(kXInStage + kTileBBytes));
+        tma_load_2d(smem + gi * kStageBytes, &map_w, (kt0 + gi) * kUmmaBK, nt * kUmmaM, &sb->full[gi]);
+      }
       grid_dep_wait();                         // activations come from the upstream kernel
       for (int gi = 0; gi < nst; ++gi) {
         const int s = gi % kStages;
         const int nt_here = min(tps, nkt - gi * tps);
-        mbar_wait(&sb->empty[s], ((uint32_t)(gi / kStages) & 1u) ^ 1u);
         unsigned char* stage = smem + s * kStageBytes;
-        mbar_arrive_expect_tx(&sb->full[s], (uint32_t)(kXInStage + nt_here * kTileBBytes));
-        if (!kW4) tma_load_2d(stage, &map_w, (kt0 + gi) * kUmmaBK, nt * kUmmaM, &sb->full[s]);
+        if (gi >= pre) {
+          mbar_wait(&sb->empty[s], ((uint32_t)(gi / kStages) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&sb->full[s], (uint32_t)(kXInStage + nt_here * kTileBBytes));
+          if (!kW4) tma_load_2d(stage, &map_w, (kt0 + gi) * kUmmaBK, nt * kUmmaM, &sb->full[s]);
+        }
         for (int t = 0; t < nt_here; ++t)
           tma_load_2d(stage + kXInStage + t * kTileBBytes, &map_x, (kt0 + gi * tps + t) * kUmmaBK, tok0, &sb->full[s]);
       }
