@@ -169,10 +169,18 @@ void b200_debug_umma_trace(void* dev_buf);
 void b200_debug_umma_trace_grid(void* dev_buf, int32_t grid_x, int32_t grid_z);
 /* Same for the attention kernel (entry, copies issued, wait start, tile landed, scores, softmax, loop end). */
 void b200_debug_attn_trace(void* dev_buf);
+/* Persistent decode kernel: per CTA and phase (layer * 7 + phase) two %globaltimer stamps {work start, arrival};
+ * dev_buf: n_ctas * n_layers * 7 * 2 uint64, NULL switches it off.  Read at launch (baked into captured graphs). */
+void b200_debug_mega_trace(void* dev_buf);
 /* In-situ timeline: while `buf` (device, capacity x 4 uint64) and `counter` (device uint32, zeroed by the
  * caller) are installed, block 0 of every kernel appends {kernel id | grid, entry, ready, exit} in
  * %globaltimer nanoseconds.  NULL buf switches it off.  Works under CUDA-graph replay. */
 void b200_debug_timeline(void* buf, void* counter, uint32_t capacity);
+/* Microbenchmark of the persistent kernel's phase boundary: n_ctas (<= 148) co-resident CTAs run n_phases
+ * rounds of {write payload_floats, arrive on a flag, wait for all, read the neighbour CTA's floats}.
+ * flags: device, n_phases x uint32; buf: device, 2 * n_ctas * payload_floats floats; sink: device, 1 float. */
+int32_t b200_debug_gridsync_bench(void* flags, int32_t n_phases, float* buf, int32_t payload_floats, int32_t n_ctas,
+                                  float* sink, void* stream);
 /* tcgen05/TMEM GEMM with dense fp16 weights W[N, K] fed by TMA (lm_head); N % 128 == 0, K % 64 == 0. */
 int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T,
                               int32_t K, int32_t N, int32_t accumulate, void* stream);

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200gate.so")
-SOURCES = ["ops_basic.cu", "ops_gemv.cu", "ops_attn.cu", "ops_sample.cu", "ops_umma.cu", "engine.cu"]
+SOURCES = ["ops_basic.cu", "ops_gemv.cu", "ops_attn.cu", "ops_sample.cu", "ops_umma.cu", "ops_mega.cu", "engine.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "-Xcompiler", "-pthread",

@@ -1,0 +1,81 @@
+// Residual-sum + RMSNorm arithmetic shared by rmsnorm_kernel (ops_basic.cu: one 4-CTA cluster per row) and
+// the persistent decode kernel (ops_mega.cu: the four warpgroups of one CTA per row).  A row is cut in
+// four quarters; 128 threads own a quarter; every quarter's warps contribute one partial sum of squares
+// each, and the 16 partials are added in one fixed order, so both callers produce the same bits.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kNormCluster = 4;        // quarters per row
+constexpr int kNormThreads = 128;      // threads per quarter
+constexpr int kNormWarps = kNormThreads / 32;
+constexpr int kNormMaxPerThread = 4;   // H <= 4 quarters * 128 threads * 4 floats * 4 = 8192
+
+// v = h[row] + sum_p parts[p][row] over this thread's float4s of quarter q (fixed p order), h updated in
+// place when n_parts > 0.  Returns the warp's sum of squares (same value in every lane).
+__device__ __forceinline__ float rms_quarter_load(float* __restrict__ h, const float* __restrict__ parts, const int n_parts,
+                                                  const int64_t part_stride, const int row, const int q, const int H,
+                                                  const int tid, float4 (&v)[kNormMaxPerThread]) {
+  const int HQ = H / kNormCluster;
+  const size_t in_off = (size_t)row * H + (size_t)q * HQ;
+  const int nvec = HQ / 4;
+  float ss = 0.f;
+#pragma unroll
+  for (int it = 0; it < kNormMaxPerThread; ++it) {
+    const int i = tid + it * kNormThreads;
+    if (i < nvec) {
+      float4 a = *reinterpret_cast<const float4*>(h + in_off + 4 * i);
+      // partials: all loads (up to 16 per batch) are issued before the first add -- one L2 round trip
+      // -- then added in the fixed order p = 0, 1, 2, ... so the sum is deterministic
+      for (int p0 = 0; p0 < n_parts; p0 += 16) {
+        float4 b[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          b[k] = p0 + k < n_parts
+                     ? __ldcg(reinterpret_cast<const float4*>(parts + (size_t)(p0 + k) * part_stride + in_off + 4 * i))
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
+      }
+      if (n_parts > 0) *reinterpret_cast<float4*>(h + in_off + 4 * i) = a;
+      v[it] = a;
+      // explicit FMAs: the two callers must not be contracted differently by the compiler
+      ss = __fmaf_rn(a.x, a.x, ss); ss = __fmaf_rn(a.y, a.y, ss); ss = __fmaf_rn(a.z, a.z, ss); ss = __fmaf_rn(a.w, a.w, ss);
+    }
+  }
+  return warp_sum(ss);
+}
+
+// red[quarter][warp] -> 1 / rms of the row
+__device__ __forceinline__ float rms_scale(const float (*red)[kNormWarps], const int H, const float eps) {
+  float tot = 0.f;
+#pragma unroll
+  for (int c = 0; c < kNormCluster; ++c)
+#pragma unroll
+    for (int w = 0; w < kNormWarps; ++w) tot += red[c][w];
+  return rsqrtf(__fadd_rn(__fdiv_rn(tot, (float)H), eps));
+}
+
+// xn[r] quarter q = fp16(v * rs * gamma)
+__device__ __forceinline__ void rms_quarter_store(const float4 (&v)[kNormMaxPerThread], const float rs,
+                                                  const __half* __restrict__ gamma, __half* __restrict__ xn, const int r,
+                                                  const int q, const int H, const int tid) {
+  const int HQ = H / kNormCluster;
+  const int nvec = HQ / 4;
+#pragma unroll
+  for (int it = 0; it < kNormMaxPerThread; ++it) {
+    const int i = tid + it * kNormThreads;
+    if (i < nvec) {
+      const uint2 gw = *reinterpret_cast<const uint2*>(gamma + (size_t)q * HQ + 4 * i);
+      const float2 g0 = __half22float2(*reinterpret_cast<const __half2*>(&gw.x));
+      const float2 g1 = __half22float2(*reinterpret_cast<const __half2*>(&gw.y));
+      uint2 o;
+      o.x = pack_half2(__fmul_rn(__fmul_rn(v[it].x, rs), g0.x), __fmul_rn(__fmul_rn(v[it].y, rs), g0.y));
+      o.y = pack_half2(__fmul_rn(__fmul_rn(v[it].z, rs), g1.x), __fmul_rn(__fmul_rn(v[it].w, rs), g1.y));
+      *reinterpret_cast<uint2*>(xn + (size_t)r * H + (size_t)q * HQ + 4 * i) = o;
+    }
+  }
+}
+
+}  // namespace b200

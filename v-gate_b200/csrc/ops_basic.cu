@@ -1,6 +1,7 @@
 // Small memory-bound kernels of the decode/prefill path: AWQ repack + dequant, embedding gather,
 // fused residual-sum + RMSNorm, RoPE + paged KV write, SwiGLU.
 #include "common.cuh"
+#include "norm.cuh"
 #include "internal.h"
 
 namespace b200 {
@@ -118,11 +119,6 @@ int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h
 // The sum of squares is exchanged through distributed shared memory: every warp pushes its partial
 // into all four CTAs, one cluster barrier, then every CTA adds the 16 values in the same order.
 // Follows vLLM qwen2.py:287-312 (RMSNorm with fused residual add), arithmetic in fp32.
-constexpr int kNormCluster = 4;
-constexpr int kNormThreads = 128;
-constexpr int kNormWarps = kNormThreads / 32;
-constexpr int kNormMaxPerThread = 4;   // H <= 4 CTAs * 128 threads * 4 floats * 4 = 8192
-
 __global__ void __cluster_dims__(kNormCluster, 1, 1) __launch_bounds__(kNormThreads)
 rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_parts, int64_t part_stride,
                const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows, int H,
@@ -132,34 +128,8 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
   const int r = blockIdx.x / kNormCluster;
   const int q = blockIdx.x % kNormCluster;            // == %cluster_ctarank for a 1-D cluster
   const int row = rows ? rows[r] : r;
-  const int HQ = H / kNormCluster;
-  const size_t in_off = (size_t)row * H + (size_t)q * HQ;
   float4 v[kNormMaxPerThread];
-  float ss = 0.f;
-  const int nvec = HQ / 4;
-#pragma unroll
-  for (int it = 0; it < kNormMaxPerThread; ++it) {
-    const int i = threadIdx.x + it * kNormThreads;
-    if (i < nvec) {
-      float4 a = *reinterpret_cast<const float4*>(h + in_off + 4 * i);
-      // partials: all loads (up to 16 per batch) are issued before the first add -- one L2 round trip
-      // -- then added in the fixed order p = 0, 1, 2, ... so the sum is deterministic
-      for (int p0 = 0; p0 < n_parts; p0 += 16) {
-        float4 b[16];
-#pragma unroll
-        for (int k = 0; k < 16; ++k)
-          b[k] = p0 + k < n_parts
-                     ? __ldcg(reinterpret_cast<const float4*>(parts + (size_t)(p0 + k) * part_stride + in_off + 4 * i))
-                     : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int k = 0; k < 16; ++k) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
-      }
-      if (n_parts > 0) *reinterpret_cast<float4*>(h + in_off + 4 * i) = a;
-      v[it] = a;
-      ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
-    }
-  }
-  ss = warp_sum(ss);
+  const float ss = rms_quarter_load(h, parts, n_parts, part_stride, row, q, H, threadIdx.x, v);
   if ((threadIdx.x & 31) < kNormCluster) {            // lane c pushes this warp's partial into CTA c
     const uint32_t local = smem_u32(&red[q][threadIdx.x >> 5]);
     uint32_t remote;
@@ -167,25 +137,8 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
     asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(ss) : "memory");
   }
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-  float tot = 0.f;
-#pragma unroll
-  for (int c = 0; c < kNormCluster; ++c)
-#pragma unroll
-    for (int w = 0; w < kNormWarps; ++w) tot += red[c][w];
-  const float rs = rsqrtf(tot / (float)H + eps);
-#pragma unroll
-  for (int it = 0; it < kNormMaxPerThread; ++it) {
-    const int i = threadIdx.x + it * kNormThreads;
-    if (i < nvec) {
-      const uint2 gw = *reinterpret_cast<const uint2*>(gamma + (size_t)q * HQ + 4 * i);
-      const float2 g0 = __half22float2(*reinterpret_cast<const __half2*>(&gw.x));
-      const float2 g1 = __half22float2(*reinterpret_cast<const __half2*>(&gw.y));
-      uint2 o;
-      o.x = pack_half2(v[it].x * rs * g0.x, v[it].y * rs * g0.y);
-      o.y = pack_half2(v[it].z * rs * g1.x, v[it].w * rs * g1.y);
-      *reinterpret_cast<uint2*>(xn + (size_t)r * H + (size_t)q * HQ + 4 * i) = o;
-    }
-  }
+  const float rs = rms_scale(red, H, eps);
+  rms_quarter_store(v, rs, gamma, xn, r, q, H, threadIdx.x);
   kernel_epilogue(tl);
 }
 
