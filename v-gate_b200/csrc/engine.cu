@@ -352,9 +352,11 @@ struct b200_engine {
   // the SMs, so the chains fill each other's bubbles; the weights of a layer are fetched from HBM by
   // the first chain and hit the 126 MB L2 for the others.  Bits do not change: every kernel computes
   // a row independently of the other rows of its launch (the batch-invariance property tested in
-  // tests/test_engine_gpu.py).  VGATE_B200_LANES overrides (1 = single chain).
+  // tests/test_engine_gpu.py).  MEASURED SLOWER (batch 64: 1.26 ms with 1 lane, 1.52 with 2, 2.24 with 4):
+  // the GEMM kernels are bound by L2->SM traffic (weights + the activation tile every CTA re-reads), which
+  // every extra lane pays again.  Kept as an opt-in experiment: VGATE_B200_LANES=2..4.
   static constexpr int kMaxLanes = 4;
-  int n_lanes_cfg = getenv("VGATE_B200_LANES") ? std::max(1, std::min(kMaxLanes, atoi(getenv("VGATE_B200_LANES")))) : 2;
+  int n_lanes_cfg = getenv("VGATE_B200_LANES") ? std::max(1, std::min(kMaxLanes, atoi(getenv("VGATE_B200_LANES")))) : 1;
   cudaStream_t lane_stream[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t lane_fork = nullptr, lane_join[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
   DevMem lane_parts;                             // split-K partials of lanes 1.. (lane 0 uses `parts`)
