@@ -183,13 +183,15 @@ __device__ __forceinline__ unsigned long long gtime() {
 enum KernelId { kKidEmbed = 1, kKidRmsnorm, kKidRope, kKidAttn, kKidSwiglu, kKidW4Gemv, kKidF16Gemv, kKidUmmaW4,
                 kKidUmmaF16, kKidSample, kKidAdvance };
 // PDL prologue + timeline entry; returns the timeline slot (or ~0u).
+// kWait = false: the kernel places griddepcontrol.wait itself (after work that does not depend on upstream).
+template <bool kWait = true>
 __device__ __forceinline__ unsigned kernel_prologue(int kid) {
   unsigned slot = ~0u;
   const bool rec = d_tl.buf && threadIdx.x == 0 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
   unsigned long long t0 = 0;
   if (rec) t0 = gtime();
   grid_dep_launch();
-  grid_dep_wait();
+  if constexpr (kWait) grid_dep_wait();
   if (rec) {
     slot = atomicAdd(d_tl.ctr, 1u);
     if (slot < d_tl.cap) {

@@ -951,6 +951,10 @@ int32_t b200_engine_finalize(b200_engine* e) {
       (rc = e->d_temp.alloc(S * 4)) || (rc = e->d_topp.alloc(S * 4)) || (rc = e->d_seed.alloc(S * 4)) ||
       (rc = e->d_step.alloc(S * 4)) || (rc = e->d_next.alloc(S * 4)) || (rc = e->d_ngen.alloc(S * 4)))
     return rc;
+  // metadata is read speculatively by the decode attention before its dependency wait: never garbage
+  for (DevMem* m : {&e->d_ids, &e->d_pos, &e->d_slot, &e->d_btrow, &e->d_ctx, &e->d_lastrows, &e->d_tiles, &e->d_bt, &e->d_step,
+                    &e->d_next, &e->d_ngen})
+    B200_CUDA(cudaMemset(m->p, 0, m->bytes));
   // split-K factors: enough CTAs to engage every SM's dequant throughput on the skinny projections
   // (o, down: 12 row tiles), bounded so partial-sum traffic stays small next to the weight bytes.
   size_t part_elems = 16;

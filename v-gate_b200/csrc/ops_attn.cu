@@ -15,10 +15,11 @@ template <int GQ, bool kFused>
 __global__ void __launch_bounds__(kAttnThreads)
 paged_attn_kernel(const AttnParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const unsigned tl = kernel_prologue(kKidAttn);
+  // fused decode mode: the unit prefetches K/V before it waits for the upstream qkv projection
+  const unsigned tl = kernel_prologue<!kFused>(kKidAttn);
   unsigned long long* tr = p.trace ? p.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
   uint32_t bar_uses = 0;
-  paged_attn_unit<GQ, kFused, 0, true>(p, smem, blockIdx.x, blockIdx.y, blockIdx.z, tr, bar_uses);
+  paged_attn_unit<GQ, kFused, 0, true, kFused>(p, smem, blockIdx.x, blockIdx.y, blockIdx.z, tr, bar_uses);
   kernel_epilogue(tl);
 }
 

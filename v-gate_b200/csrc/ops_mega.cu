@@ -110,7 +110,7 @@ decode_layers_kernel(const __grid_constant__ CUtensorMap map_xn, const __grid_co
     for (int s = 0; s < MegaCfg::kRing; ++s) { mbar_init(&sb->pk_full[s], 1); mbar_init(&sb->pk_empty[s], 128); }
     mbar_init(&sb->tmem_full, 1);
     mbar_init(acc_empty, 1);
-    for (int w = 0; w < kAttnWarps; ++w) mbar_init(reinterpret_cast<uint64_t*>(smem + AttnSmem::kOffBar) + w, 1);
+    for (int w = 0; w < kAttnTileWarps; ++w) mbar_init(reinterpret_cast<uint64_t*>(smem + AttnSmem::kOffBar) + w, 1);
     fence_mbar_init();
   }
   if (warp == kWarpMma) tmem_alloc(&sb->tmem_base, MegaCfg::kTmemCols);
