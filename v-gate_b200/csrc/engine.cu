@@ -244,8 +244,12 @@ struct b200_engine {
 
   // y (+)= x . W^T.  Returns in *n_parts_out how many partial tensors were written to `pbuf`
   // instead (0: the result is already in y).
+  // split_k: decode passes split K over more CTAs (few token rows, every SM needed); prefill passes have
+  // token tiles enough and write the result once (at 12 800 tokens the partials of the down projection
+  // alone were 0.9 GB written and read back per layer).  Which of the two a token goes through is decided
+  // by its request's state (prompt token or generated token), never by what else is in the batch.
   int linear(const LayerWeights& lw, int i, const __half* x, int64_t x_rows, float* y, int ldy, int T, bool accumulate,
-             int* n_parts_out, cudaStream_t st, float* pbuf) {
+             int* n_parts_out, cudaStream_t st, float* pbuf, bool split_k) {
     const W4Linear& w = lw.lin[i];
     *n_parts_out = 0;
     if (!use_umma(T) || (debug_gemv_mask >> i & 1)) return launch_w4_gemv(w, x, w.K, y, ldy, T, accumulate, st);
@@ -253,7 +257,7 @@ struct b200_engine {
     const CUtensorMap* mx;
     int rc = get_map(x, x_rows, w.K, nt, &mx);
     if (rc) return rc;
-    const int ns = umma_w4_effective_splits(w.K, w.G, splits[i]);
+    const int ns = split_k ? umma_w4_effective_splits(w.K, w.G, splits[i]) : 1;
     if (ns > 1) {
       *n_parts_out = ns;
       return launch_umma_w4(lw.ulin[i], *mx, nt, T, pbuf, w.N, kUmmaPartialF32, ns, (int64_t)T * w.N, st);
@@ -311,7 +315,7 @@ struct b200_engine {
       if (!skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln1.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st)))
         return rc;
       pend = 0;
-      if (!skip(1) && (rc = linear(w, 0, xx, xrows, qq, QKV, T, false, &np, st, pbuf))) return rc;
+      if (!skip(1) && (rc = linear(w, 0, xx, xrows, qq, QKV, T, false, &np, st, pbuf, decode_rows))) return rc;
       const float* qsrc = np ? pbuf : qq;
       const __half* qbias = np ? w.bias_qkv.as<__half>() : nullptr;
       if (decode_rows && T <= cfg.max_seqs) {
@@ -329,18 +333,18 @@ struct b200_engine {
         } else if (!skip(3) && (rc = launch_paged_attn(qhh, kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq, btrow, ctx, T, NH,
                                                        NKV, 1, nullptr, nullptr, aa, st))) return rc;
       }
-      if (!skip(4) && (rc = linear(w, 1, aa, xrows, hh, H, T, true, &pend, st, pbuf))) return rc;
+      if (!skip(4) && (rc = linear(w, 1, aa, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows))) return rc;
       if (!skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st)))
         return rc;
       pend = 0;
       if (use_umma(T) && !(debug_gemv_mask >> 2 & 1)) {
-        if (!skip(5) && (rc = linear(w, 2, xx, xrows, reinterpret_cast<float*>(cc), I, T, false, &np, st, pbuf))) return rc;
+        if (!skip(5) && (rc = linear(w, 2, xx, xrows, reinterpret_cast<float*>(cc), I, T, false, &np, st, pbuf, decode_rows))) return rc;
       } else {
-        if ((rc = linear(w, 2, xx, xrows, gu.as<float>() + (size_t)r0 * 2 * I, 2 * I, T, false, &np, st, pbuf))) return rc;
+        if ((rc = linear(w, 2, xx, xrows, gu.as<float>() + (size_t)r0 * 2 * I, 2 * I, T, false, &np, st, pbuf, decode_rows))) return rc;
         if ((rc = launch_swiglu(gu.as<float>() + (size_t)r0 * 2 * I, T, I, cc, st))) return rc;
       }
       if (np) { set_last_error("gate_up projection must not be split"); return B200_ERR_STATE; }
-      if (!skip(6) && (rc = linear(w, 3, cc, xrows, hh, H, T, true, &pend, st, pbuf))) return rc;
+      if (!skip(6) && (rc = linear(w, 3, cc, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows))) return rc;
     }
     *pend_out = pend;
     return B200_OK;

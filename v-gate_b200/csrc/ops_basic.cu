@@ -119,26 +119,33 @@ int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h
 // The sum of squares is exchanged through distributed shared memory: every warp pushes its partial
 // into all four CTAs, one cluster barrier, then every CTA adds the 16 values in the same order.
 // Follows vLLM qwen2.py:287-312 (RMSNorm with fused residual add), arithmetic in fp32.
+template <bool kOneRow>       // kOneRow: exactly one row per cluster (decode, short prefill): no loop carried state
 __global__ void __cluster_dims__(kNormCluster, 1, 1) __launch_bounds__(kNormThreads)
 rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_parts, int64_t part_stride,
-               const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows, int H,
+               const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows, int n_rows, int H,
                __half* __restrict__ xn) {
-  __shared__ float red[kNormCluster][kNormWarps];
+  // red is double-buffered by row parity: a CTA may push the partials of its next row while a slower
+  // CTA of the cluster still reads the previous row's (one cluster barrier per row is then enough:
+  // nobody can be two rows ahead of a CTA that has not passed the barrier in between)
+  __shared__ float red[2][kNormCluster][kNormWarps];
   const unsigned tl = kernel_prologue(kKidRmsnorm);
-  const int r = blockIdx.x / kNormCluster;
   const int q = blockIdx.x % kNormCluster;            // == %cluster_ctarank for a 1-D cluster
-  const int row = rows ? rows[r] : r;
-  float4 v[kNormMaxPerThread];
-  const float ss = rms_quarter_load(h, parts, n_parts, part_stride, row, q, H, threadIdx.x, v);
-  if ((threadIdx.x & 31) < kNormCluster) {            // lane c pushes this warp's partial into CTA c
-    const uint32_t local = smem_u32(&red[q][threadIdx.x >> 5]);
-    uint32_t remote;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(threadIdx.x & 31));
-    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(ss) : "memory");
+  const int n_clusters = gridDim.x / kNormCluster;
+  int it = 0;
+  for (int r = blockIdx.x / kNormCluster; r < n_rows; r += kOneRow ? n_rows : n_clusters, ++it) {   // prefill: many rows per cluster
+    const int row = rows ? rows[r] : r;
+    float4 v[kNormMaxPerThread];
+    const float ss = rms_quarter_load(h, parts, n_parts, part_stride, row, q, H, threadIdx.x, v);
+    if ((threadIdx.x & 31) < kNormCluster) {          // lane c pushes this warp's partial into CTA c
+      const uint32_t local = smem_u32(&red[it & 1][q][threadIdx.x >> 5]);
+      uint32_t remote;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(threadIdx.x & 31));
+      asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(ss) : "memory");
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    const float rs = rms_scale(red[it & 1], H, eps);
+    rms_quarter_store(v, rs, gamma, xn, r, q, H, threadIdx.x);
   }
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-  const float rs = rms_scale(red, H, eps);
-  rms_quarter_store(v, rs, gamma, xn, r, q, H, threadIdx.x);
   kernel_epilogue(tl);
 }
 
@@ -147,7 +154,13 @@ int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_strid
   B200_REQUIRE(H % (4 * kNormCluster) == 0 && H <= kNormCluster * kNormThreads * 4 * kNormMaxPerThread,
                "rmsnorm: H % 16 == 0 && H <= 8192");
   if (n_rows == 0) return B200_OK;
-  launch_k(rmsnorm_kernel, dim3(n_rows * kNormCluster), dim3(kNormThreads), 0, s, h, parts, n_parts, part_stride, gamma, eps, rows, H, xn);
+  const int n_clusters = n_rows < 2048 ? n_rows : 2048;      // beyond that a cluster walks several rows
+  if (n_clusters == n_rows)
+    launch_k(rmsnorm_kernel<true>, dim3(n_clusters * kNormCluster), dim3(kNormThreads), 0, s, h, parts, n_parts, part_stride, gamma,
+             eps, rows, n_rows, H, xn);
+  else
+    launch_k(rmsnorm_kernel<false>, dim3(n_clusters * kNormCluster), dim3(kNormThreads), 0, s, h, parts, n_parts, part_stride, gamma,
+             eps, rows, n_rows, H, xn);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
