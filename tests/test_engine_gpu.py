@@ -168,3 +168,43 @@ def test_backend_contract_on_gpu(monkeypatch):
         assert counts == sorted(counts) and counts[-1] == 6
     finally:
         be.shutdown()
+
+
+def test_lookahead_scheduling_changes_nothing(monkeypatch):
+    """The scheduler launches decode step s + 1 before it has read the tokens of step s
+    (engine.cu run_decode).  Same tokens as without look-ahead for: different max_tokens in one batch,
+    a sequence stopping on EOS mid-way (its over-run token is dropped), requests arriving while others
+    decode, sampled (seeded) requests."""
+    import time
+    from vgate_b200.engine import Engine
+    dims = PRESETS["qwen2.5-1.5b-awq-l2-v8k"]
+    ckpt = synthetic_checkpoint(dims, seed=0)
+    rng = np.random.default_rng(11)
+    prompts = [rng.integers(0, dims.vocab, size=n, dtype=np.int32) for n in (20, 33, 47, 64, 9, 70)]
+    max_toks = [24, 7, 31, 16, 12, 20]
+
+    def run(lookahead, eos):
+        monkeypatch.setenv("VGATE_B200_LOOKAHEAD", "1" if lookahead else "0")
+        eng = Engine(dims, max_seqs=16, max_model_len=256, max_batch_tokens=256, eos_token_id=eos).load_checkpoint(ckpt)
+        try:
+            rids = []
+            for i, (p, m) in enumerate(zip(prompts, max_toks)):
+                temp = 0.8 if i == 4 else 0.0
+                rids.append(eng.submit(p, temperature=temp, top_p=0.9 if i == 4 else 1.0, max_tokens=m, seed=5))
+                if i == 2:
+                    time.sleep(0.02)                 # the rest arrive while the first three decode
+            return [eng.wait(rid, m)[0] for rid, m in zip(rids, max_toks)]
+        finally:
+            eng.close()
+
+    base = run(False, -1)
+    assert [len(o) for o in base] == max_toks
+    for a, b in zip(base, run(True, -1)):
+        assert np.array_equal(a, b)
+    eos = int(base[0][10])                            # a token sequence 0 emits mid-way becomes the EOS id
+    cut_off = run(False, eos)
+    cut_on = run(True, eos)
+    first = int(np.argmax(base[0] == eos))
+    assert len(cut_off[0]) == first + 1 and cut_off[0][-1] == eos
+    for a, b in zip(cut_off, cut_on):
+        assert np.array_equal(a, b)

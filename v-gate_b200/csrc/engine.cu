@@ -509,14 +509,31 @@ struct b200_engine {
     return B200_OK;
   }
 
-  // Scheduler decode step.  When the batch is the same set of sequences as in the previous decode
-  // step nothing is uploaded: the device already holds their state and the sampled tokens.
-  int run_decode(const std::vector<std::shared_ptr<Request>>& batch) {
+  // ---- scheduler decode: one step of look-ahead -------------------------------------------------
+  // A decode step needs nothing from the host when the batch is unchanged (the device holds the state
+  // and the sampled tokens), so step s + 1 is launched BEFORE the tokens of step s are read back: the
+  // host's per-step work (event wait, copy, bookkeeping, waking waiters) overlaps GPU work instead of
+  // separating two steps.  Look-ahead is only taken when no sequence of the batch can reach max_tokens
+  // at step s, nothing waits for admission and no abort is pending.  A sequence that stops at step s on
+  // EOS has one more token computed at s + 1 (inside its reserved KV blocks); it is dropped at collection.  A step that was launched ahead is always collected (its tokens belong to sequences that
+  // did advance) before anything else touches the device state.
+  struct Inflight {
+    bool active = false;
+    std::vector<std::shared_ptr<Request>> batch;
+    std::vector<int64_t> ids;
+    int slot = 0;
+    int64_t ctx_sum = 0, launches = 0;
+  };
+  Inflight inflight;
+  int32_t* hp_next[2] = {nullptr, nullptr};        // pinned, max_seqs tokens each
+  cudaEvent_t ev_a[2] = {nullptr, nullptr}, ev_b[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
+  bool lookahead_enabled = !(getenv("VGATE_B200_LOOKAHEAD") && atoi(getenv("VGATE_B200_LOOKAHEAD")) == 0);
+
+  // Launch one decode step for `batch` (state upload if the batch changed) and queue the copy of its tokens.
+  int launch_decode(const std::vector<std::shared_ptr<Request>>& batch, const std::vector<int64_t>& idsig, int64_t extra_ctx) {
     const int n = (int)batch.size();
-    std::vector<int64_t> idsig(n);
-    for (int r = 0; r < n; ++r) idsig[r] = batch[r]->id;
     int rc;
-    int64_t ctx_sum = 0;
+    int64_t ctx_sum = extra_ctx;
     greedy_only = true;
     for (int r = 0; r < n; ++r) {
       ctx_sum += (int64_t)batch[r]->prompt.size() + (int64_t)batch[r]->out.size();
@@ -545,31 +562,74 @@ struct b200_engine {
       B200_CUDA(cudaStreamSynchronize(stream));      // the host vectors above go out of scope
       last_decode_ids = idsig;
     }
+    const int slot = inflight.slot ^ 1;
     const int64_t launches0 = g_launch_count;
-    B200_CUDA(cudaEventRecord(ev0, stream));
+    B200_CUDA(cudaEventRecord(ev_a[slot], stream));
     if ((rc = decode_step(n, nullptr, 0))) return rc;
-    B200_CUDA(cudaEventRecord(ev1, stream));
-    std::vector<int32_t> next(n);
-    B200_CUDA(cudaMemcpyAsync(next.data(), d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
-    B200_CUDA(cudaStreamSynchronize(stream));
+    B200_CUDA(cudaEventRecord(ev_b[slot], stream));
+    B200_CUDA(cudaMemcpyAsync(hp_next[slot], d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+    B200_CUDA(cudaEventRecord(ev_copied[slot], stream));
+    inflight.active = true; inflight.batch = batch; inflight.ids = idsig; inflight.slot = slot;
+    inflight.ctx_sum = ctx_sum; inflight.launches = g_launch_count - launches0;
+    return B200_OK;
+  }
+
+  // Wait for the step in flight and hand its tokens to the sequences that are still running.
+  int collect_decode() {
+    if (!inflight.active) return B200_OK;
+    Inflight f = std::move(inflight);
+    inflight = Inflight{};
+    inflight.slot = f.slot;
+    B200_CUDA(cudaEventSynchronize(ev_copied[f.slot]));
     float ms = 0.f;
-    B200_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
+    B200_CUDA(cudaEventElapsedTime(&ms, ev_a[f.slot], ev_b[f.slot]));
+    const int n = (int)f.batch.size();
     const double t = now_s();
     std::lock_guard<std::mutex> lk(mu);
-    stats.kernel_launches += g_launch_count - launches0;
+    stats.kernel_launches += f.launches;
     stats.steps_decode++; stats.gpu_seconds_decode += ms * 1e-3; stats.decode_batch_sum += n;
-    stats.hbm_bytes_decode += decode_step_bytes(n, ctx_sum);
-    stats.tokens_generated += n;
+    stats.hbm_bytes_decode += decode_step_bytes(n, f.ctx_sum);
     for (int r = 0; r < n; ++r) {
-      Request& q = *batch[r];
-      q.out.push_back(next[r]);
+      Request& q = *f.batch[r];
+      if (q.state != ReqState::RUNNING) continue;   // aborted while the step was in flight: its token is dropped
+      q.out.push_back(hp_next[f.slot][r]);
       q.t_last = t;
+      stats.tokens_generated++;
     }
+    return B200_OK;
+  }
+
+  int run_decode(const std::vector<std::shared_ptr<Request>>& batch) {
+    const int n = (int)batch.size();
+    std::vector<int64_t> idsig(n);
+    for (int r = 0; r < n; ++r) idsig[r] = batch[r]->id;
+    int rc;
+    if (inflight.active && inflight.ids != idsig && (rc = collect_decode())) return rc;   // a different batch was ahead
+    if (!inflight.active && (rc = launch_decode(batch, idsig, 0))) return rc;
+    // look ahead: may step s + 1 start before the tokens of step s are known?
+    bool ahead = lookahead_enabled;
+    for (int r = 0; r < n && ahead; ++r) ahead = (int)batch[r]->out.size() + 1 < batch[r]->max_tokens;
+    if (ahead) {
+      std::lock_guard<std::mutex> lk(mu);
+      ahead = waiting.empty() && !stop;
+      for (int r = 0; r < n && ahead; ++r) ahead = !batch[r]->abort_requested;
+    }
+    if (!ahead) return collect_decode();
+    // step s is in flight in slot k; launch s + 1 into the other slot, then collect s
+    Inflight cur = std::move(inflight);
+    inflight = Inflight{};
+    inflight.slot = cur.slot;
+    if ((rc = launch_decode(batch, idsig, n))) return rc;          // context one token longer for the roofline accounting
+    Inflight nxt = std::move(inflight);
+    inflight = std::move(cur);
+    if ((rc = collect_decode())) return rc;
+    inflight = std::move(nxt);
     return B200_OK;
   }
 
   int run_step(const std::vector<std::shared_ptr<Request>>& batch, bool is_prefill) {
     if (!is_prefill) return run_decode(batch);
+    { int rc0 = collect_decode(); if (rc0) return rc0; }   // a step launched ahead belongs to the running sequences
     last_decode_ids.clear();                         // a prefill pass overwrites the d_* state
     std::vector<int32_t> ids, pos, slot, btrow, ctx, lastrows, bt, step;
     std::vector<float> temp, topp;
@@ -691,7 +751,7 @@ struct b200_engine {
       lk.unlock();
       const int rc = run_step(batch, is_prefill);
       lk.lock();
-      if (rc != B200_OK) { fail_all(g_last_error); continue; }
+      if (rc != B200_OK) { inflight = Inflight{}; fail_all(g_last_error); continue; }
       if (is_prefill) for (auto& r : admitted) running.push_back(r);
       // retire finished sequences
       bool any_done = false;
@@ -745,7 +805,13 @@ int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
   int rc = B200_OK;
   auto fail = [&](int code) { b200_engine_destroy(e); return code; };
   if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess) {
+      cudaEventCreate(&e->ev0) != cudaSuccess || cudaEventCreate(&e->ev1) != cudaSuccess ||
+      cudaEventCreate(&e->ev_a[0]) != cudaSuccess || cudaEventCreate(&e->ev_a[1]) != cudaSuccess ||
+      cudaEventCreate(&e->ev_b[0]) != cudaSuccess || cudaEventCreate(&e->ev_b[1]) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_copied[0], cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_copied[1], cudaEventDisableTiming) != cudaSuccess ||
+      cudaMallocHost(&e->hp_next[0], (size_t)cfg->max_seqs * 4) != cudaSuccess ||
+      cudaMallocHost(&e->hp_next[1], (size_t)cfg->max_seqs * 4) != cudaSuccess) {
     set_last_error("cudaStreamCreate/cudaEventCreate failed");
     return fail(B200_ERR_CUDA);
   }
@@ -1055,6 +1121,12 @@ void b200_engine_destroy(b200_engine* e) {
     if (e->lane_join[i]) cudaEventDestroy(e->lane_join[i]);
     if (e->lane_stream[i]) cudaStreamDestroy(e->lane_stream[i]);
   }
+  for (int i = 0; i < 2; ++i) {
+    if (e->ev_a[i]) cudaEventDestroy(e->ev_a[i]);
+    if (e->ev_b[i]) cudaEventDestroy(e->ev_b[i]);
+    if (e->ev_copied[i]) cudaEventDestroy(e->ev_copied[i]);
+    if (e->hp_next[i]) cudaFreeHost(e->hp_next[i]);
+  }
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
   if (e->stream) cudaStreamDestroy(e->stream);
@@ -1187,6 +1259,8 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
   struct Release { b200_engine* e; ~Release() { std::lock_guard<std::mutex> lk(e->mu); e->exclusive = false; e->cv_work.notify_all(); } } release{e};
   B200_CUDA(cudaSetDevice(e->cfg.device));
   cudaStream_t s = e->stream;
+  { const int rc0 = e->collect_decode(); if (rc0) return rc0; }   // a look-ahead step of sequences aborted since
+  e->last_decode_ids.clear();
   const int bps = (n_prompt + max_tokens + 1 + kBlockTokens - 1) / kBlockTokens;   // blocks per sequence
   B200_REQUIRE(bps <= e->max_blocks_per_seq, "sequence needs more blocks than max_blocks_per_seq");
   if ((int64_t)bps * n_seqs > e->n_blocks) { set_last_error("KV pool too small for this batch"); return B200_ERR_CAPACITY; }
