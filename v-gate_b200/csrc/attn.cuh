@@ -154,6 +154,40 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
       }
     }
   }
+  // Fused mode: what a thread needs besides the qkv partials -- column indices, bias, and the cos / sin
+  // row of the new token's position -- is loaded here, before the dependency wait when kPreWait (bias is a
+  // weight; the position is ctx_len - 1, possibly still the previous step's: re-checked after the wait).
+  constexpr int kPairs = (GQ * 64 + kAttnThreads - 1) / kAttnThreads;        // rotation pairs per thread (3 for GQ = 6)
+  constexpr int NE = 2 * kPairs + 3;                                          // + v[tid], k pair (tid & 63)
+  int cols[NE];
+  float bia[NE], cs[kPairs + 1], sn[kPairs + 1];
+  int rope_pos = -1;
+  auto load_rope = [&](int ps) {
+    rope_pos = ps;
+#pragma unroll
+    for (int q3 = 0; q3 <= kPairs; ++q3) {
+      const int i = q3 < kPairs ? (min(tid + q3 * kAttnThreads, GQ * 64 - 1) & 63) : (tid & 63);
+      cs[q3] = p.cos_t[(size_t)ps * 64 + i];
+      sn[q3] = p.sin_t[(size_t)ps * 64 + i];
+    }
+  };
+  if constexpr (kFused) {
+#pragma unroll
+    for (int q3 = 0; q3 < kPairs; ++q3) {
+      const int idx = min(tid + q3 * kAttnThreads, GQ * 64 - 1);
+      cols[2 * q3] = (j * GQ + (idx >> 6)) * kHeadDim + (idx & 63);
+      cols[2 * q3 + 1] = cols[2 * q3] + 64;
+    }
+    cols[2 * kPairs] = (n_heads + n_kv + j) * kHeadDim + tid;                 // v
+    cols[2 * kPairs + 1] = (n_heads + j) * kHeadDim + (tid & 63);            // k (first half of the pair)
+    cols[2 * kPairs + 2] = cols[2 * kPairs + 1] + 64;
+#pragma unroll
+    for (int e = 0; e < NE; ++e) bia[e] = p.bias ? __half2float(p.bias[cols[e]]) : 0.f;
+    if constexpr (kPreWait) {
+      const int len0 = __ldcg(p.ctx_len + t);
+      if (len0 > 0) load_rope(len0 - 1);
+    }
+  }
   if constexpr (kPreWait) grid_dep_wait();          // from here on the upstream kernels' results are visible
 
   const int len = kPreWait ? __ldcg(p.ctx_len + t) : p.ctx_len[t];
@@ -214,35 +248,17 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
     const int total = (n_heads + 2 * n_kv) * kHeadDim;
     const float* row = p.qkv + (size_t)t * total;
     constexpr int kMaxParts = 4;                                   // loaded in one batch; more are added after
-    constexpr int kPairs = (GQ * 64 + kAttnThreads - 1) / kAttnThreads;      // rotation pairs per thread (3 for GQ = 6)
-    constexpr int NE = 2 * kPairs + 3;                             // + v[tid], k pair (tid & 63)
     const int ps = p.pos[t];
     const int sl = p.slot[t];
     const bool own = (new_chunk % S) == split;                     // this CTA owns the chunk that holds the new token
-    int cols[NE];
-#pragma unroll
-    for (int q3 = 0; q3 < kPairs; ++q3) {
-      const int idx = min(tid + q3 * kAttnThreads, GQ * 64 - 1);
-      cols[2 * q3] = (j * GQ + (idx >> 6)) * kHeadDim + (idx & 63);
-      cols[2 * q3 + 1] = cols[2 * q3] + 64;
-    }
-    cols[2 * kPairs] = (n_heads + n_kv + j) * kHeadDim + tid;                 // v
-    cols[2 * kPairs + 1] = (n_heads + j) * kHeadDim + (tid & 63);            // k (first half of the pair)
-    cols[2 * kPairs + 2] = cols[2 * kPairs + 1] + 64;
-    float part[NE][kMaxParts], bia[NE], cs[kPairs + 1], sn[kPairs + 1];
+    float part[NE][kMaxParts];
 #pragma unroll
     for (int e = 0; e < NE; ++e) {
 #pragma unroll
       for (int pp = 0; pp < kMaxParts; ++pp)
         part[e][pp] = pp < p.n_parts ? __ldcg(row + (size_t)pp * p.part_stride + cols[e]) : 0.f;
-      bia[e] = p.bias ? __half2float(p.bias[cols[e]]) : 0.f;
     }
-#pragma unroll
-    for (int q3 = 0; q3 <= kPairs; ++q3) {
-      const int i = q3 < kPairs ? (min(tid + q3 * kAttnThreads, GQ * 64 - 1) & 63) : (tid & 63);
-      cs[q3] = p.cos_t[(size_t)ps * 64 + i];
-      sn[q3] = p.sin_t[(size_t)ps * 64 + i];
-    }
+    if (ps != rope_pos) load_rope(ps);                             // not prefetched, or prefetched for a stale position
     float val[NE];
 #pragma unroll
     for (int e = 0; e < NE; ++e) {
@@ -334,24 +350,36 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
     }
 
     // ---- S = Q K^T : 8 token tiles of 8 ----
+    // The eight token tiles are independent accumulation chains; they are issued interleaved (k outer,
+    // tile inner) because a single warp per scheduler has nothing else to hide the MMA latency with, and
+    // there is no "tile has valid tokens" branch for the same reason.  Rows beyond the context (or in
+    // blocks that were not loaded) hold stale data; their scores are replaced by -inf below.
     float sc[8][2];
+    {
+      float d[8][4];
 #pragma unroll
-    for (int nt = 0; nt < 8; ++nt) {
-      float d[4] = {0.f, 0.f, 0.f, 0.f};
-      if (nt * 8 < nvalid) {
-        const int mj = lane >> 3, tok = nt * 8 + (lane & 7);
-        const uint32_t rowaddr = smem_u32(Kt + (tok >> 4) * kKvBlockBytes + (tok & 15) * 256);
+      for (int nt = 0; nt < 8; ++nt) d[nt][0] = d[nt][1] = d[nt][2] = d[nt][3] = 0.f;
+      const int mj = lane >> 3, tl7 = lane & 7;
 #pragma unroll
-        for (int k2 = 0; k2 < 4; ++k2) {            // two k-steps per ldmatrix.x4
-          uint32_t b0, b1, b2, b3;
-          ldmatrix_x4(rowaddr + ((((4 * k2 + mj) ^ (tok & 7))) << 4), b0, b1, b2, b3);
-          mma_16816(d, qa[2 * k2], b0, b1);
-          mma_16816(d, qa[2 * k2 + 1], b2, b3);
+      for (int k2 = 0; k2 < 4; ++k2) {              // two k-steps per ldmatrix.x4
+        uint32_t kb[8][4];
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          const int tok = nt * 8 + tl7;
+          const uint32_t rowaddr = smem_u32(Kt + (tok >> 4) * kKvBlockBytes + (tok & 15) * 256);
+          ldmatrix_x4(rowaddr + ((((4 * k2 + mj) ^ (tok & 7))) << 4), kb[nt][0], kb[nt][1], kb[nt][2], kb[nt][3]);
         }
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) mma_16816(d[nt], qa[2 * k2], kb[nt][0], kb[nt][1]);
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) mma_16816(d[nt], qa[2 * k2 + 1], kb[nt][2], kb[nt][3]);
       }
-      const int t0 = nt * 8 + 2 * tq;
-      sc[nt][0] = t0 < nvalid ? __fmul_rn(d[0], scale) : -INFINITY;
-      sc[nt][1] = t0 + 1 < nvalid ? __fmul_rn(d[1], scale) : -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const int t0 = nt * 8 + 2 * tq;
+        sc[nt][0] = t0 < nvalid ? __fmul_rn(d[nt][0], scale) : -INFINITY;
+        sc[nt][1] = t0 + 1 < nvalid ? __fmul_rn(d[nt][1], scale) : -INFINITY;
+      }
     }
     if (tr && tid == 0 && it == 0) tr[4] = clock64();
 
@@ -387,14 +415,17 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
         const int mj = lane >> 3, r = (mj & 1) * 8 + (lane & 7);
         const uint32_t rowaddr = smem_u32(Vt + kt * kKvBlockBytes + r * 256);
 #pragma unroll
-        for (int d2 = 0; d2 < 8; ++d2) {            // two 8-dim tiles per ldmatrix.x4.trans
-          uint32_t b0, b1, b2, b3;
-          ldmatrix_x4_trans(rowaddr + (((2 * d2 + (mj >> 1)) ^ (r & 7)) << 4), b0, b1, b2, b3);
+        uint32_t vb[8][4];                          // all eight loads first, then sixteen independent MMAs
+#pragma unroll
+        for (int d2 = 0; d2 < 8; ++d2)              // two 8-dim tiles per ldmatrix.x4.trans
+          ldmatrix_x4_trans(rowaddr + (((2 * d2 + (mj >> 1)) ^ (r & 7)) << 4), vb[d2][0], vb[d2][1], vb[d2][2], vb[d2][3]);
+#pragma unroll
+        for (int d2 = 0; d2 < 8; ++d2) {
           float d[4] = {o[2 * d2][0], o[2 * d2][1], 0.f, 0.f};
-          mma_16816(d, pa[kt], b0, b1);
+          mma_16816(d, pa[kt], vb[d2][0], vb[d2][1]);
           o[2 * d2][0] = d[0]; o[2 * d2][1] = d[1];
           float e[4] = {o[2 * d2 + 1][0], o[2 * d2 + 1][1], 0.f, 0.f};
-          mma_16816(e, pa[kt], b2, b3);
+          mma_16816(e, pa[kt], vb[d2][2], vb[d2][3]);
           o[2 * d2 + 1][0] = e[0]; o[2 * d2 + 1][1] = e[1];
         }
       }

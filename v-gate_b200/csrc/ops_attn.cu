@@ -20,6 +20,7 @@ paged_attn_kernel(const AttnParams p) {
   unsigned long long* tr = p.trace ? p.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
   uint32_t bar_uses = 0;
   paged_attn_unit<GQ, kFused, 0, true, kFused>(p, smem, blockIdx.x, blockIdx.y, blockIdx.z, tr, bar_uses);
+  if (tr && threadIdx.x == 0) tr[7] = clock64();
   kernel_epilogue(tl);
 }
 
