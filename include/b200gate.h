@@ -163,11 +163,13 @@ int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, flo
                              int32_t n_splits, int64_t part_stride, void* stream);
 int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits);
 /* Profiling aid: when dev_buf is non-NULL the tcgen05 GEMM writes 8 x uint64 SM-clock stamps per CTA
- * (entry, set-up done, first tiles ready, last MMA issued, accumulator ready, epilogue done, exit). */
+ * (0 entry, 1 set-up done, 2 first stage complete, 3 last MMA issued, 4 accumulator complete, 5 accumulator
+ * staged in shared memory, 6 epilogue done, 7 dependency wait of the activation-TMA warp returned). */
 void b200_debug_umma_trace(void* dev_buf);
 /* Same, restricted to launches whose grid is (grid_x, *, grid_z) -- to pick one projection inside a step. */
 void b200_debug_umma_trace_grid(void* dev_buf, int32_t grid_x, int32_t grid_z);
-/* Same for the attention kernel (entry, copies issued, wait start, tile landed, scores, softmax, loop end). */
+/* Same for the attention kernel (0 entry, 1 dependency wait returned and tiles checked, 2 prologue done, 3 first
+ * K/V tile landed, 4 scores, 5 softmax, 6 chunk loop end, 7 merge + store done). */
 void b200_debug_attn_trace(void* dev_buf);
 /* Persistent decode kernel: per CTA and phase (layer * 7 + phase) two %globaltimer stamps {work start, arrival};
  * dev_buf: n_ctas * n_layers * 7 * 2 uint64, NULL switches it off.  Read at launch (baked into captured graphs). */

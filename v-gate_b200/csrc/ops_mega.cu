@@ -27,7 +27,7 @@ namespace b200 {
 constexpr int kMegaNT = 64;                              // token tile = the whole decode batch
 constexpr int kMegaPhases = 7;
 constexpr int kMegaComputeThreads = kProducerWarps * 32; // 512
-using MegaCfg = UmmaCfg<kMegaNT, true>;
+using MegaCfg = UmmaCfg<kMegaNT, true, false>;   // four stages: stage s belongs to warpgroup s
 
 // Shared memory: [attention tiles / X stages + epilogue staging (aliased)] [weight ring] [barriers]
 struct MegaSmem {

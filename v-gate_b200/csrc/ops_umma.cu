@@ -136,6 +136,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         tma_load_2d(smem + gi * kStageBytes, &map_w, (kt0 + gi) * kUmmaBK, nt * kUmmaM, &sb->full[gi]);
       }
       grid_dep_wait();                         // activations come from the upstream kernel
+      if (tr) tr[7] = clock64();
       for (int gi = 0; gi < nst; ++gi) {
         const int s = gi % kStages;
         const int nt_here = min(tps, nkt - gi * tps);
@@ -153,14 +154,11 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     // ===================== MMA issuer =====================
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc(kUmmaM, NT);
-      long long tw_a = 0, t_is = 0;
       for (int gi = 0; gi < nst; ++gi) {
         const int s = gi % kStages;
         const int nt_here = min(tps, nkt - gi * tps);
-        const long long c0 = tr ? clock64() : 0;
         mbar_wait(&sb->full[s], (uint32_t)(gi / kStages) & 1u);
         tc_fence_after();
-        const long long c1 = tr ? clock64() : 0;
         if (tr && gi == 0) tr[2] = clock64();
         const uint32_t x_addr = smem_u32(smem + s * kStageBytes + kXInStage);
         for (int t = 0; t < nt_here; ++t) {
@@ -178,18 +176,16 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
           }
         }
         umma_commit(&sb->empty[s]);            // the stage is free again when the MMAs above retire
-        if (tr) { const long long c2 = clock64(); tw_a += c1 - c0; t_is += c2 - c1; }
       }
       umma_commit(&sb->tmem_full);             // accumulator complete
-      if (tr) { tr[3] = clock64(); tr[7] = (unsigned long long)tw_a | ((unsigned long long)t_is << 32); }
+      if (tr) tr[3] = clock64();
     }
   }
 
-  if (tr && threadIdx.x == 0) tr[5] = clock64();
+  if (tr && threadIdx.x == 0) tr[6] = clock64();
   tc_fence_before();
   __syncthreads();
   if (warp == kWarpMma) tmem_dealloc(tmem, kTmemCols);
-  if (tr && threadIdx.x == 0) tr[6] = clock64();
   if (tl_rec) {
     tl = atomicAdd(d_tl.ctr, 1u);
     if (tl < d_tl.cap) {

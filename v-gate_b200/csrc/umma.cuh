@@ -132,10 +132,17 @@ struct UmmaSmem {                      // barriers live after the tile rings
 //   W4   : A = fp16 weights in TMEM (64 columns per stage, written by the dequant warpgroups),
 //          X = kTilesPerStage activation tiles in smem (TMA).  Stage = one AWQ group (G = 128: 2 k tiles).
 //   fp16 : A = weight tile in smem (TMA), X = activation tile in smem (TMA).  Stage = 1 k tile.
-template <int NT, bool kW4>
+// kDeep (W4, token tile <= 64): seven stages instead of four, which is what the 512 TMEM columns hold next
+// to the accumulator.  The producer warpgroups dequantise ahead of the dependency wait, so a CTA with up
+// to seven groups (down: 6, qkv / o: 3) has its whole A operand in tensor memory before the activations
+// exist, and gate_up (12) has seven of twelve; seven activation stages (112 KB) are requested at once.
+// Warpgroup w still takes groups w, w + 4, ...; stage = group % 7 is then shared between warpgroups, which
+// is safe for the parity waits because a warpgroup's previous group g - 4 already waited for group
+// g - 4 - 7 to be consumed, so the barrier of stage g % 7 is never more than one phase behind.
+template <int NT, bool kW4, bool kDeep = true>
 struct UmmaCfg {
   static constexpr int kMaxTilesPerStage = kW4 ? 2 : 1;
-  static constexpr int kStages = 4;
+  static constexpr int kStages = (kW4 && kDeep && NT <= 64) ? 7 : 4;
   static constexpr int kRing = kW4 ? 8 : 0;           // two private slots per producer warpgroup
   static constexpr int kTileBBytes = NT * kUmmaBK * 2;
   static constexpr int kStageBytes = (kW4 ? 0 : kTileABytes) + kMaxTilesPerStage * kTileBBytes;
@@ -145,7 +152,7 @@ struct UmmaCfg {
   static constexpr int kRingOff = kStages * kStageBytes;
   static constexpr int kBarOff = kRingOff + kRing * kChunkStride;
   static constexpr int kSmemBytes = kBarOff + (int)sizeof(UmmaSmem) + 1024;
-  static_assert(kStages == 4 && kStages <= kMaxStages && kRing <= kMaxRing, "ring sizes (stage s is owned by warpgroup s)");
+  static_assert(kStages >= 4 && kStages <= kMaxStages && kRing <= kMaxRing, "ring sizes");
   static_assert(kTmemNeed <= 512, "tensor memory budget");
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
@@ -235,7 +242,7 @@ __device__ __forceinline__ void umma_epilogue(const int mode, float* y, const in
 #pragma unroll
       for (int j = 0; j < CW; ++j) stage[(col0 + c + j) * 128 + q * 32 + lane] = __uint_as_float(v[j]);
     }
-    if (tr && threadIdx.x == 0) tr[2] = clock64();                   // (reuses the "first stage ready" slot)
+    if (tr && threadIdx.x == 0) tr[5] = clock64();                   // accumulator staged in shared memory
     asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");
     const int tid = threadIdx.x;                                     // 0..511
     if (mode == kSwigluF16) {
