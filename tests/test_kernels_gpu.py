@@ -1,5 +1,7 @@
 """Parity of every kernel on the path against the CPU oracle, through the C ABI (b200_op_*).
 Integer / index work is bit-exact; floating point within the stated tolerance."""
+import ctypes as C
+
 import numpy as np
 import pytest
 import torch
@@ -82,6 +84,26 @@ def test_rmsnorm_with_partials_and_row_map():
     h_after = hd.cpu().numpy()
     assert np.abs(h_after[rows] - v[rows]).max() < 1e-5
     assert np.array_equal(h_after[[1, 2, 4, 5]], h[[1, 2, 4, 5]])
+
+
+@pytest.mark.parametrize("H", [1536, 256, 2048])
+def test_rmsnorm_prefill_variant_is_bit_identical(H):
+    """Large passes without partials use a warp-per-row kernel; it must produce the bits of the cluster kernel."""
+    rng = np.random.default_rng(5)
+    T = 1500
+    h = (rng.standard_normal((T, H)) * 3).astype(np.float32)
+    g = (1 + 0.1 * rng.standard_normal(H)).astype(np.float16)
+    hd, gd = dev(h), dev(g)
+    big = torch.empty((T, H), dtype=torch.float16, device="cuda")
+    check(lib().b200_op_rmsnorm(ptr(hd), None, 0, 0, ptr(gd), 1e-6, None, T, H, ptr(big), stream()))        # >= 1024 rows
+    small = torch.empty((T, H), dtype=torch.float16, device="cuda")
+    for r0 in (0, 750):                                                                                        # < 1024 rows each
+        check(lib().b200_op_rmsnorm(C.c_void_p(hd.data_ptr() + r0 * H * 4), None, 0, 0, ptr(gd), 1e-6, None, 750, H,
+                                    C.c_void_p(small.data_ptr() + r0 * H * 2), stream()))
+    assert torch.equal(big.view(torch.int16), small.view(torch.int16))
+    v = h.astype(np.float64)
+    ref = v / np.sqrt((v ** 2).mean(-1, keepdims=True) + 1e-6) * g.astype(np.float64)
+    assert np.abs(big.cpu().numpy().astype(np.float64) - ref).max() < 2e-2
 
 
 def test_embed_swiglu():

@@ -149,11 +149,69 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
   kernel_epilogue(tl);
 }
 
+// Prefill variant (no partials, thousands of rows): one WARP per row, every load of the row in flight at
+// once (the cluster kernel keeps only ~185 rows in flight on the whole GPU and is latency-bound there:
+// 88 us for 8192 rows).  Bit-identical to the cluster kernel: lane l plays thread (w * 32 + l) of quarter q
+// for every (q, w), so each of the 16 partial sums goes through the same FMA chain and the same shuffle
+// tree, and they are added in the same order.  H <= 2048 (16 float4 per lane kept for the store).
+constexpr int kNormWarpRowMaxH = 2048;
+__global__ void __launch_bounds__(256)
+rmsnorm_rows_kernel(const float* __restrict__ h, const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows,
+                    int n_rows, int H, __half* __restrict__ xn) {
+  const unsigned tl = kernel_prologue(kKidRmsnorm);
+  const int lane = threadIdx.x & 31;
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r < n_rows) {
+    const int row = rows ? rows[r] : r;
+    const int HQ = H / kNormCluster, nvec = HQ / 4;             // float4 per quarter
+    const int wpq = (nvec + 31) / 32;                           // warps the cluster kernel uses per quarter (<= 4)
+    constexpr int kMaxVec = kNormWarpRowMaxH / 4 / 32;          // 16
+    float4 v[kMaxVec];
+    const float4* src = reinterpret_cast<const float4*>(h + (size_t)row * H);
+#pragma unroll
+    for (int k = 0; k < kMaxVec; ++k) {
+      const int q = k / 4, w = k % 4, i = w * 32 + lane;        // (quarter, warp) slot k; i = thread index in the quarter
+      v[k] = (q < kNormCluster && w < wpq && i < nvec) ? src[q * nvec + i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float red[kNormCluster][kNormWarps];
+#pragma unroll
+    for (int k = 0; k < kMaxVec; ++k) {
+      float ss = 0.f;
+      ss = __fmaf_rn(v[k].x, v[k].x, ss); ss = __fmaf_rn(v[k].y, v[k].y, ss);
+      ss = __fmaf_rn(v[k].z, v[k].z, ss); ss = __fmaf_rn(v[k].w, v[k].w, ss);
+      red[k / 4][k % 4] = warp_sum(ss);
+    }
+    const float rs = rms_scale(red, H, eps);
+    __half* dst = xn + (size_t)r * H;
+#pragma unroll
+    for (int k = 0; k < kMaxVec; ++k) {
+      const int q = k / 4, w = k % 4, i = w * 32 + lane;
+      if (w < wpq && i < nvec) {
+        const int e = (q * nvec + i) * 4;
+        const uint2 gw = *reinterpret_cast<const uint2*>(gamma + e);
+        const float2 g0 = __half22float2(*reinterpret_cast<const __half2*>(&gw.x));
+        const float2 g1 = __half22float2(*reinterpret_cast<const __half2*>(&gw.y));
+        uint2 o;
+        o.x = pack_half2(__fmul_rn(__fmul_rn(v[k].x, rs), g0.x), __fmul_rn(__fmul_rn(v[k].y, rs), g0.y));
+        o.y = pack_half2(__fmul_rn(__fmul_rn(v[k].z, rs), g1.x), __fmul_rn(__fmul_rn(v[k].w, rs), g1.y));
+        *reinterpret_cast<uint2*>(dst + e) = o;
+      }
+    }
+  }
+  kernel_epilogue(tl);
+}
+
 int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_stride, const __half* gamma, float eps,
                    const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s) {
   B200_REQUIRE(H % (4 * kNormCluster) == 0 && H <= kNormCluster * kNormThreads * 4 * kNormMaxPerThread,
                "rmsnorm: H % 16 == 0 && H <= 8192");
   if (n_rows == 0) return B200_OK;
+  if (n_parts == 0 && n_rows >= 1024 && H <= kNormWarpRowMaxH) {     // large prefill pass: warp per row, same bits
+    launch_k(rmsnorm_rows_kernel, dim3((n_rows + 7) / 8), dim3(256), 0, s, (const float*)h, gamma, eps, rows, n_rows, H, xn);
+    g_launch_count += 1;
+    B200_CUDA(cudaGetLastError());
+    return B200_OK;
+  }
   const int n_clusters = n_rows < 2048 ? n_rows : 2048;      // beyond that a cluster walks several rows
   if (n_clusters == n_rows)
     launch_k(rmsnorm_kernel<true>, dim3(n_clusters * kNormCluster), dim3(kNormThreads), 0, s, h, parts, n_parts, part_stride, gamma,
