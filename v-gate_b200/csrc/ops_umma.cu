@@ -98,8 +98,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       // an mbarrier parity wait cannot tell "two phases ahead" from "done".)
       int use = 0;
       for (int gi = wg; gi < nst; gi += 4, ++use) {
-        const int slot = wg + 4 * (use & 1), s = gi % kStages;
-        w4_chunk_to_tmem(smem_u32(ring + slot * kChunkStride), &sb->pk_full[slot], (uint32_t)(use >> 1) & 1u,
+        const int slot = wg + 4 * (use % Cfg::kSlotsPerWg), s = gi % kStages;
+        w4_chunk_to_tmem(smem_u32(ring + slot * kChunkStride), &sb->pk_full[slot], (uint32_t)(use / Cfg::kSlotsPerWg) & 1u,
                          &sb->empty[s], ((uint32_t)(gi / kStages) & 1u) ^ 1u, &sb->full[s], &sb->pk_empty[slot],
                          tmem + lane_base + (uint32_t)(Cfg::kAccCols + 64 * s), r, min(tps, nkt - gi * tps));
       }
@@ -118,8 +118,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       const unsigned char* src = p.chunks + ((size_t)nt * KG + kt0 / tps) * chunk_bytes;
       for (int gi = 0; gi < nst; ++gi) {
         const int use = gi >> 2;                                   // same slot walk as the consuming warpgroup
-        const int slot = (gi & 3) + 4 * (use & 1);
-        mbar_wait(&sb->pk_empty[slot], ((uint32_t)(use >> 1) & 1u) ^ 1u);
+        const int slot = (gi & 3) + 4 * (use % Cfg::kSlotsPerWg);
+        mbar_wait(&sb->pk_empty[slot], ((uint32_t)(use / Cfg::kSlotsPerWg) & 1u) ^ 1u);
         mbar_arrive_expect_tx(&sb->pk_full[slot], chunk_bytes);
         bulk_g2s(ring + slot * kChunkStride, src + (size_t)gi * chunk_bytes, chunk_bytes, &sb->pk_full[slot]);
       }

@@ -17,7 +17,7 @@ constexpr int kWarpTmaX = kProducerWarps + 1;    // activation (and fp16 weight)
 constexpr int kWarpMma = kProducerWarps + 2;     // MMA issuer + TMEM owner
 constexpr int kUmmaThreads = (kProducerWarps + 3) * 32;
 constexpr int kChunkStride = 512 + 2 * 4096;     // ring slot: scales 256 B + zeros 256 B + up to two 4 KB packed k tiles
-constexpr int kMaxStages = 8, kMaxRing = 8;
+constexpr int kMaxStages = 8, kMaxRing = 12;
 constexpr int kTileABytes = kUmmaM * kUmmaBK * 2;          // 16 KB
 
 enum UmmaMode : int { kStoreF32 = 0, kAccumF32 = 1, kPartialF32 = 2, kSwigluF16 = 3, kArgmaxF32 = 4 };
@@ -143,7 +143,11 @@ template <int NT, bool kW4, bool kDeep = true>
 struct UmmaCfg {
   static constexpr int kMaxTilesPerStage = kW4 ? 2 : 1;
   static constexpr int kStages = (kW4 && kDeep && NT <= 64) ? 7 : 4;
-  static constexpr int kRing = kW4 ? 8 : 0;           // two private slots per producer warpgroup
+  // private ring slots per producer warpgroup.  3 (all 12 chunks of a gate_up CTA requested at once) was
+  // measured: no change -- the kernel's stall samples sit in the wait for the first chunk (HBM latency) and
+  // in the wait for the accumulator (12 groups x 256 tensor cycles), not in ring refills.
+  static constexpr int kSlotsPerWg = 2;
+  static constexpr int kRing = kW4 ? 4 * kSlotsPerWg : 0;
   static constexpr int kTileBBytes = NT * kUmmaBK * 2;
   static constexpr int kStageBytes = (kW4 ? 0 : kTileABytes) + kMaxTilesPerStage * kTileBBytes;
   static constexpr int kAccCols = NT < 32 ? 32 : NT;  // TMEM: accumulator, then (W4) the A stages, 64 columns each
