@@ -197,3 +197,48 @@ def test_satisfies_reference_protocol_and_factory(monkeypatch):
     sp = eng.backend.create_sampling_params(0.0, 1.0, 3)
     assert eng.backend.generate(["User: x\nAssistant:"], sp)[0]["num_tokens"] == 3
     eng.backend.shutdown()
+
+
+@pytest.mark.skipif(not has_reference, reason="reference checkout not present on this machine")
+def test_reference_worker_http_route_serves_b200_backend(monkeypatch):
+    """The worker-side caller (vgate/worker_api.py:85-139) over HTTP, unmodified, with the b200 backend bound:
+    wire-dict sampling params, executor hop, JSON response; an engine failure becomes HTTP 500."""
+    fastapi = pytest.importorskip("fastapi")
+    from fastapi.testclient import TestClient
+    monkeypatch.syspath_prepend(REFERENCE)
+    monkeypatch.delenv("VGATE_DRY_RUN", raising=False)
+    for m in [m for m in sys.modules if m == "vgate" or m.startswith("vgate.")]:
+        monkeypatch.delitem(sys.modules, m)
+    import vgate_b200.engine as eng_mod
+    monkeypatch.setattr(eng_mod, "Engine", _StubEngine)
+    monkeypatch.setenv("VGATE_B200_SYNTHETIC", "tiny-awq")
+    sys.modules.pop("vgate_b200.register", None)
+    import vgate_b200.register  # noqa: F401
+    from vgate import worker_api
+    from vgate.config import ModelConfig, WorkerConfig
+    from vgate.engine import VGateEngine
+    eng = VGateEngine(ModelConfig(engine_type="b200", max_model_len=256), WorkerConfig())
+    app = fastapi.FastAPI()
+    app.include_router(worker_api.router)
+    worker_api.set_engine(eng)
+    assert worker_api._serialize_inference is False                 # supports_concurrent_calls honoured
+    try:
+        with TestClient(app) as client:
+            body = {"prompts": ["User: a\nAssistant:", "User: bb\nAssistant:"],
+                    "sampling_params": {"temperature": 0.0, "top_p": 1.0, "max_tokens": 4}}
+            r = client.post("/internal/generate", json=body)
+            assert r.status_code == 200, r.text
+            res = r.json()["results"]
+            assert len(res) == 2
+            for x in res:
+                assert set(x) >= {"text", "token_ids", "num_tokens", "metrics"} and x["num_tokens"] == 4
+                assert len(x["token_ids"]) == 4 and set(x["metrics"]) == {"ttft", "gen_time"}
+            # engine failure -> HTTP 500 "Inference failed: <Type>" (worker_api.py:115-128)
+            def boom(*a, **k):
+                raise RuntimeError("device lost")
+            monkeypatch.setattr(eng.backend, "generate", boom)
+            r = client.post("/internal/generate", json=body)
+            assert r.status_code == 500 and "RuntimeError" in r.json()["detail"]
+    finally:
+        worker_api.set_engine(None)
+        eng.backend.shutdown()
