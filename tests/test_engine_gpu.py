@@ -208,3 +208,60 @@ def test_lookahead_scheduling_changes_nothing(monkeypatch):
     assert len(cut_off[0]) == first + 1 and cut_off[0][-1] == eos
     for a, b in zip(cut_off, cut_on):
         assert np.array_equal(a, b)
+
+
+def test_full_context_2048_matches_oracle():
+    """The reference's max_model_len (vllm_backend.py:61-86: 2048): a sequence that fills it exactly.
+    prompt 2030 + 18 new tokens on a small model; the logits of the last positions (32 KV chunks, 128 KV
+    blocks per head) stay within tolerance of the fp32 oracle and the tokens equal the fp16-class oracle."""
+    from vgate_b200.engine import Engine
+    dims = PRESETS["tiny-awq"]
+    ckpt = synthetic_checkpoint(dims, seed=3)
+    rng = np.random.default_rng(21)
+    prompts = rng.integers(0, dims.vocab, size=(2, 2030), dtype=np.int32)
+    n_new = 18
+    eng = Engine(dims, max_seqs=4, max_model_len=2048, max_batch_tokens=4096).load_checkpoint(ckpt)
+    try:
+        toks, logits, _ = eng.generate_batch(prompts, n_new, n_logit_steps=n_new)
+        with pytest.raises(Exception):
+            eng.submit(prompts[0], 0.0, 1.0, n_new + 1)                 # one token past max_model_len
+    finally:
+        eng.close()
+    ref32 = _oracle(dims, ckpt, "fp32")
+    ref_toks, ref_logits = ref32.generate_greedy(prompts, n_new, return_logits=True)
+    ref_logits = np.asarray(ref_logits)
+    for b in range(2):                       # compare while the trajectories agree (teacher forcing is not available)
+        n_same = 0
+        while n_same < n_new and toks[b, n_same] == ref_toks[b][n_same]:
+            n_same += 1
+        upto = min(n_new, n_same + 1)
+        assert upto >= 1
+        assert np.abs(logits[b, :upto] - ref_logits[b, :upto]).max() < LOGIT_TOL, b
+
+
+def test_more_requests_than_sequences_and_kv_blocks():
+    """Admission control: 3x more requests than max_seqs, and a KV pool that holds only a few of them at a
+    time; everything completes, FIFO, with the tokens each request produces alone."""
+    from vgate_b200.engine import Engine
+    dims = PRESETS["tiny-awq"]
+    ckpt = synthetic_checkpoint(dims, seed=4)
+    rng = np.random.default_rng(22)
+    prompts = [rng.integers(0, dims.vocab, size=int(n), dtype=np.int32) for n in rng.integers(1, 120, size=24)]
+    news = [int(n) for n in rng.integers(1, 40, size=24)]
+    big = Engine(dims, max_seqs=32, max_model_len=256, max_batch_tokens=512).load_checkpoint(ckpt)
+    try:
+        solo = [big.wait(big.submit(p, 0.0, 1.0, n), n)[0] for p, n in zip(prompts, news)]
+    finally:
+        big.close()
+    kv_tok_bytes = 2 * dims.n_layers * dims.n_kv_heads * dims.head_dim * 2
+    small_eng = Engine(dims, max_seqs=8, max_model_len=256, max_batch_tokens=512,
+                       kv_bytes=kv_tok_bytes * 16 * 40).load_checkpoint(ckpt)      # 40 blocks: ~4 long sequences at once
+    try:
+        rids = [small_eng.submit(p, 0.0, 1.0, n) for p, n in zip(prompts, news)]
+        outs = [small_eng.wait(r, n)[0] for r, n in zip(rids, news)]
+        st = small_eng.stats()
+    finally:
+        small_eng.close()
+    for i, (a, b) in enumerate(zip(outs, solo)):
+        assert np.array_equal(a, b), i
+    assert st["requests_finished"] == 24 and st["kv_blocks_free"] == st["kv_blocks_total"]
