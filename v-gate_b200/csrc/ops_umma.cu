@@ -54,7 +54,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
   // the weight stream below does not depend on the upstream kernel)
   unsigned tl = ~0u;
   unsigned long long tl_t0 = 0;
-  const bool tl_rec = d_tl.buf && threadIdx.x == 0 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
+  const bool tl_rec = threadIdx.x == 0 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && d_tl.buf;
   if (tl_rec) tl_t0 = gtime();
   grid_dep_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
