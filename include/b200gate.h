@@ -174,6 +174,10 @@ void b200_debug_attn_trace(void* dev_buf);
 /* Persistent decode kernel: per CTA and phase (layer * 7 + phase) two %globaltimer stamps {work start, arrival};
  * dev_buf: n_ctas * n_layers * 7 * 2 uint64, NULL switches it off.  Read at launch (baked into captured graphs). */
 void b200_debug_mega_trace(void* dev_buf);
+/* Fused decode MLP kernel: 8 x uint64 SM-clock stamps per CTA of the last launch (0 entry, 1 gate_up accumulator
+ * complete, 2 gate_up columns published, 3 down accumulator complete, 4 down epilogue done, 5 dependency wait returned,
+ * 6 the down unit's column counter reached its target). */
+void b200_debug_mlp_trace(void* dev_buf);
 /* In-situ timeline: while `buf` (device, capacity x 4 uint64) and `counter` (device uint32, zeroed by the
  * caller) are installed, block 0 of every kernel appends {kernel id | grid, entry, ready, exit} in
  * %globaltimer nanoseconds.  NULL buf switches it off.  Works under CUDA-graph replay. */

@@ -43,6 +43,7 @@ void tl_set_gemv(unsigned long long*, unsigned int*, unsigned int);
 void tl_set_attn(unsigned long long*, unsigned int*, unsigned int);
 void tl_set_sample(unsigned long long*, unsigned int*, unsigned int);
 void tl_set_umma(unsigned long long*, unsigned int*, unsigned int);
+void tl_set_mega(unsigned long long*, unsigned int*, unsigned int);
 
 static double now_s() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -218,6 +219,8 @@ struct b200_engine {
   // Persistent decode kernel (ops_mega.cu): all layers of a decode step of <= 64 rows in one launch.
   // Opt-in (VGATE_B200_MEGA=1): measured slower than the per-kernel path so far; same bits.
   bool mega_ok = false;
+  bool mlp_fused_ok = false;                     // gate_up + down as one dataflow kernel in decode steps (opt-in: VGATE_B200_FUSED_MLP=1; measured 2.5 % slower)
+  int mlp_flag_off = 0, mlp_flags_per_layer = 0; // inside mega_flags: [7 L phase flags][L x I/64 column flags]
   DevMem mega_layers, mega_flags;
   int mega_n_flags = 0;
   int decode_layers(int T) {
@@ -337,6 +340,20 @@ struct b200_engine {
       if (!skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st)))
         return rc;
       pend = 0;
+      if (decode_rows && mlp_fused_ok && r0 == 0 && T <= 64 && debug_skip == 0 && debug_gemv_mask == 0) {
+        // gate_up + SwiGLU + down in one launch; down's partials are left pending for the next RMSNorm
+        MlpParams mp{};
+        mp.chunks_gu = w.chunks[2].as<unsigned char>(); mp.chunks_down = w.chunks[3].as<unsigned char>();
+        mp.T = T; mp.H = H; mp.I = I; mp.G = w.lin[3].G;
+        mp.split_down = umma_w4_effective_splits(w.lin[3].K, w.lin[3].G, splits[3]);
+        mp.act = cc; mp.parts = pbuf;
+        mp.flags = mega_flags.as<unsigned int>() + mlp_flag_off + (size_t)l * mlp_flags_per_layer;
+        const CUtensorMap *mxn, *mact;
+        if ((rc = get_map(xx, xrows, H, 64, &mxn)) || (rc = get_map(cc, xrows, I, 64, &mact))) return rc;
+        if ((rc = launch_mlp_fused(*mxn, *mact, mp, st))) return rc;
+        pend = mp.split_down;
+        continue;
+      }
       if (use_umma(T) && !(debug_gemv_mask >> 2 & 1)) {
         if (!skip(5) && (rc = linear(w, 2, xx, xrows, reinterpret_cast<float*>(cc), I, T, false, &np, st, pbuf, decode_rows))) return rc;
       } else {
@@ -1066,7 +1083,12 @@ int32_t b200_engine_finalize(b200_engine* e) {
     e->mega_ok = c.gemm_path != 1 && (mv && atoi(mv) != 0) &&
                  decode_layers_supported(e->NH, e->NKV, e->layers[0].lin[0].G, 1) && e->H % 128 == 0 && e->QKV % 128 == 0 &&
                  (2 * e->I) % 128 == 0 && e->I % e->layers[0].lin[0].G == 0;
-    e->mega_n_flags = decode_layers_flag_count(e->L);
+    const char* fv = getenv("VGATE_B200_FUSED_MLP");
+    e->mlp_fused_ok = c.gemm_path != 1 && !e->mega_ok && (fv && atoi(fv) != 0) && e->n_lanes_cfg == 1 &&
+                      mlp_fused_supported(1, e->H, e->I, e->layers[0].lin[0].G);
+    e->mlp_flag_off = decode_layers_flag_count(e->L);
+    e->mlp_flags_per_layer = e->I / 64;
+    e->mega_n_flags = e->mlp_flag_off + e->L * e->mlp_flags_per_layer;
     if ((rc = e->mega_flags.alloc((size_t)e->mega_n_flags * 4)) || (rc = e->mega_layers.alloc((size_t)e->L * sizeof(MegaLayer))))
       return rc;
     B200_CUDA(cudaMemset(e->mega_flags.p, 0, e->mega_flags.bytes));
@@ -1406,10 +1428,11 @@ void b200_debug_umma_trace(void* dev_buf) { umma_set_trace((unsigned long long*)
 void b200_debug_umma_trace_grid(void* dev_buf, int32_t grid_x, int32_t grid_z) { umma_set_trace((unsigned long long*)dev_buf, grid_x, grid_z); }
 void b200_debug_attn_trace(void* dev_buf) { attn_set_trace((unsigned long long*)dev_buf); }
 void b200_debug_mega_trace(void* dev_buf) { decode_layers_set_trace((unsigned long long*)dev_buf); }
+void b200_debug_mlp_trace(void* dev_buf) { mlp_fused_set_trace((unsigned long long*)dev_buf); }
 void b200_debug_timeline(void* buf, void* counter, uint32_t capacity) {
   auto* b = (unsigned long long*)buf; auto* c = (unsigned int*)counter;
   tl_set_engine(b, c, capacity); tl_set_basic(b, c, capacity); tl_set_gemv(b, c, capacity); tl_set_attn(b, c, capacity);
-  tl_set_sample(b, c, capacity); tl_set_umma(b, c, capacity);
+  tl_set_sample(b, c, capacity); tl_set_umma(b, c, capacity); tl_set_mega(b, c, capacity);
 }
 int32_t b200_debug_gridsync_bench(void* flags, int32_t n_phases, float* buf, int32_t payload_floats, int32_t n_ctas,
                                   float* sink, void* stream) {

@@ -135,6 +135,21 @@ struct MegaParams {
   unsigned long long* trace;                             // debug: [cta][layer * 7 + phase][2] %globaltimer {work start, arrive}
 };
 
+// Fused decode MLP (ops_mega.cu): gate_up + SwiGLU + down in one launch joined by per-column flags.
+struct MlpParams {
+  const unsigned char* chunks_gu;                        // gate/up paired chunk layout
+  const unsigned char* chunks_down;
+  int T, H, I, G;
+  int split_down;                                        // effective split-K of the down projection
+  __half* act;                                           // [T, I] fp16 (written, then read through map_act)
+  float* parts;                                          // [split][T][H] fp32 partials of the down projection
+  unsigned int* flags;                                   // [split_down] counters of published act k tiles, zero at launch
+  unsigned long long* trace;                             // debug: 8 clock64 stamps per CTA (see b200_debug_mlp_trace)
+};
+bool mlp_fused_supported(int T, int H, int I, int G);
+void mlp_fused_set_trace(unsigned long long* dev_buf);
+// maps: xn [rows, H] and act [rows, I], 64-row x 64-column boxes
+int launch_mlp_fused(const CUtensorMap& map_xn, const CUtensorMap& map_act, const MlpParams& P, cudaStream_t s);
 bool decode_layers_supported(int n_heads, int n_kv, int G, int T);
 int decode_layers_flag_count(int n_layers);
 void decode_layers_set_trace(unsigned long long* dev_buf);

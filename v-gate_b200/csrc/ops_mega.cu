@@ -24,6 +24,8 @@
 
 namespace b200 {
 
+B200_DEFINE_TL_SETTER(tl_set_mega)
+
 constexpr int kMegaNT = 64;                              // token tile = the whole decode batch
 constexpr int kMegaPhases = 7;
 constexpr int kMegaComputeThreads = kProducerWarps * 32; // 512
@@ -307,7 +309,255 @@ decode_layers_kernel(const __grid_constant__ CUtensorMap map_xn, const __grid_co
   if (warp == kWarpMma) tmem_dealloc(tmem, MegaCfg::kTmemCols);
 }
 
+// =========================================================================================================
+// Fused MLP for decode (T <= 64 rows): gate_up (+SwiGLU) and down in ONE launch, joined by dataflow.  EXPERIMENT.
+//
+// As separate kernels, down could not begin before the last gate_up CTA had exited and the grid had
+// drained (3.9 us of boundary per layer), and its CTAs could not even be resident -- hence prefetch weights
+// -- while gate_up's were.  Here one CTA per SM first computes its gate_up tile (64 gate + 64 up rows ->
+// 64 columns of `act`), publishes a flag for exactly those columns, and then computes its down unit, whose
+// activation stages wait only for the flags of the two 64-column k tiles they read.  The weight TMA warp
+// streams gate_up's and then down's chunks without ever waiting for activations, and the dequantising
+// warpgroups fill tensor memory with down's A operand while the flags are still in flight.
+// Warp roles and arithmetic are those of umma_gemm_kernel (same device functions, same split-K): the
+// output bits equal the two-kernel path's (tests/test_mega_gpu.py).
+//
+// MEASURED (batch 64, tools/mlp_trace.py): after the dependency resolves, gate_up's accumulator is complete at
+// 5.3 us, its columns are published at 7.5 (epilogue 1.3 + fences / store drain 0.9), the consumers see the
+// counters at 8.6, down's accumulator is complete at 10.9 and its partials are written at 12.4 -- against
+// 14.2 us for the two kernels.  But the grid holds all 148 SMs until its slowest CTA ends, so the next kernels
+// lose their head start, and the decode step comes out 2.5 % SLOWER (1.242 vs 1.212 ms).  Producer -> L2 ->
+// consumer costs ~3.5 us whether the signal is a flag or a kernel boundary.  Opt-in: VGATE_B200_FUSED_MLP=1.
+struct MlpSmem {
+  static constexpr int kOffStages = 0;                   // 4 X stages (64 KB); the epilogue staging aliases them
+  static constexpr int kOffRing = MegaCfg::kStages * MegaCfg::kStageBytes;
+  static constexpr int kOffBar = kOffRing + MegaCfg::kRing * kChunkStride;
+  static constexpr int kOffAccEmpty = kOffBar + (int)sizeof(UmmaSmem);
+  static constexpr int kBytes = kOffAccEmpty + 16 + 1024;
+};
+
+struct MlpUnit { int g, nt, split, kt0, nkt, nst; };     // g: 0 = gate_up, 1 = down
+
+// f(unit) for every unit of this CTA in execution order: its gate_up tiles, then its down units
+template <typename F>
+__device__ __forceinline__ void for_each_mlp_unit(const MlpParams& P, int cta, int G, F&& f) {
+  const int tps = P.G / kUmmaBK;
+  {
+    const int tiles = (2 * P.I) / kUmmaM, nkt = P.H / kUmmaBK;
+    for (int u = cta; u < tiles; u += G) f(MlpUnit{0, u, 0, 0, nkt, (nkt + tps - 1) / tps});
+  }
+  {
+    const int tiles = P.H / kUmmaM, KT = P.I / kUmmaBK, KG = P.I / P.G;
+    const int gps = (KG + P.split_down - 1) / P.split_down;          // same arithmetic as launch_umma_w4
+    const int kt_per_split = gps * tps, nsplit = (KG + gps - 1) / gps;
+    for (int u = (cta + G - 4 % G) % G; u < tiles * nsplit; u += G) {
+      const int nt = u % tiles, split = u / tiles, kt0 = split * kt_per_split;
+      const int nkt = min(kt_per_split, KT - kt0);
+      f(MlpUnit{1, nt, split, kt0, nkt, (nkt + tps - 1) / tps});
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kUmmaThreads, 1)
+mlp_fused_kernel(const __grid_constant__ CUtensorMap map_xn, const __grid_constant__ CUtensorMap map_act, const MlpParams P) {
+  using L = MlpSmem;
+  constexpr int kStages = MegaCfg::kStages, kStageBytes = MegaCfg::kStageBytes, kTileBBytes = MegaCfg::kTileBBytes;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* ring = smem + L::kOffRing;
+  UmmaSmem* sb = reinterpret_cast<UmmaSmem*>(smem + L::kOffBar);
+  uint64_t* acc_empty = reinterpret_cast<uint64_t*>(smem + L::kOffAccEmpty);
+  const int warp = threadIdx.x >> 5;
+  const int cta = blockIdx.x, G = gridDim.x;
+  const int tps = P.G / kUmmaBK;
+  const int down_kt_per_split = ((P.I / P.G + P.split_down - 1) / P.split_down) * tps;   // k tiles per down split
+  unsigned long long* tr = P.trace ? P.trace + 8 * (size_t)cta : nullptr;
+  if (tr && threadIdx.x == 0) tr[0] = clock64();
+  unsigned tl = ~0u;
+  unsigned long long tl_t0 = 0;
+  const bool tl_rec = threadIdx.x == 0 && blockIdx.x == 0 && d_tl.buf;
+  if (tl_rec) tl_t0 = gtime();
+  grid_dep_launch();                 // every CTA of this grid is resident by the time the next kernel may start
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(&sb->full[s], 128 + 1); mbar_init(&sb->empty[s], 1); }
+    for (int s = 0; s < MegaCfg::kRing; ++s) { mbar_init(&sb->pk_full[s], 1); mbar_init(&sb->pk_empty[s], 128); }
+    mbar_init(&sb->tmem_full, 1);
+    mbar_init(acc_empty, 1);
+    fence_mbar_init();
+  }
+  if (warp == kWarpMma) tmem_alloc(&sb->tmem_base, MegaCfg::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sb->tmem_base;
+
+  if (warp < kProducerWarps) {
+    // =============== dequant producers + epilogues ===============
+    const int wg = warp >> 2, r = threadIdx.x & 127;
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    uint32_t n_fill = 0, n_units = 0;
+    for_each_mlp_unit(P, cta, G, [&](const MlpUnit& u) {
+      for (int gi = wg; gi < u.nst; gi += 4, ++n_fill) {
+        const int slot = wg + 4 * (int)(n_fill & 1u);
+        w4_chunk_to_tmem(smem_u32(ring + slot * kChunkStride), &sb->pk_full[slot], (n_fill >> 1) & 1u, &sb->empty[wg],
+                         (n_fill & 1u) ^ 1u, &sb->full[wg], &sb->pk_empty[slot],
+                         tmem + lane_base + (uint32_t)(MegaCfg::kAccCols + 64 * wg), r, min(tps, u.nkt - gi * tps));
+      }
+      mbar_wait(&sb->tmem_full, n_units & 1u);
+      tc_fence_after();
+      if (tr && threadIdx.x == 0) tr[u.g == 0 ? 1 : 3] = clock64();
+      if (u.g == 0)
+        umma_epilogue<kMegaNT>(kSwigluF16, reinterpret_cast<float*>(P.act), P.I, 0, nullptr, P.T, 0, u.nt,
+                               reinterpret_cast<float*>(smem), tmem, nullptr);
+      else
+        umma_epilogue<kMegaNT>(kPartialF32, P.parts, P.H, (size_t)u.split * ((size_t)P.T * P.H), nullptr, P.T, 0, u.nt,
+                               reinterpret_cast<float*>(smem), tmem, nullptr);
+      tc_fence_before();
+      asm volatile("fence.proxy.async;" ::: "memory");   // act (generic stores) is read by other CTAs' TMA; staging vs next X tiles
+      compute_bar();
+      if (threadIdx.x == 0) {
+        mbar_arrive(acc_empty);
+        if (u.g == 0) {
+          // columns [64 nt, 64 nt + 64) of act are visible: count them for the down split whose K range holds them.
+          // (release: ordered after every compute thread's stores through the barrier above; the threads already
+          // issued their generic->async proxy fences)
+          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(P.flags + u.nt / down_kt_per_split) : "memory");
+        }
+        if (tr) tr[u.g == 0 ? 2 : 4] = clock64();
+      }
+      ++n_units;
+    });
+  } else if (warp == kWarpTmaW) {
+    // =============== weight stream ===============
+    if (elect_one()) {
+      uint32_t nf = 0;
+      for_each_mlp_unit(P, cta, G, [&](const MlpUnit& u) {
+        const int K = u.g == 0 ? P.H : P.I;
+        const uint32_t chunk_bytes = 512u + (uint32_t)tps * 4096u;
+        const unsigned char* src = (u.g == 0 ? P.chunks_gu : P.chunks_down) + ((size_t)u.nt * (K / P.G) + u.kt0 / tps) * chunk_bytes;
+        for (int gi = 0; gi < u.nst; ++gi) {
+          const int w = gi & 3;
+          const uint32_t n = (nf >> (8 * w)) & 0xffu;
+          nf = (nf & ~(0xffu << (8 * w))) | (((n + 1) & 0xffu) << (8 * w));
+          const int slot = w + 4 * (int)(n & 1u);
+          mbar_wait(&sb->pk_empty[slot], ((n >> 1) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&sb->pk_full[slot], chunk_bytes);
+          bulk_g2s(ring + slot * kChunkStride, src + (size_t)gi * chunk_bytes, chunk_bytes, &sb->pk_full[slot]);
+        }
+      });
+    }
+  } else if (warp == kWarpTmaX) {
+    // =============== activation tiles: xn after the upstream kernel, act after the producing tiles' flags ===============
+    if (elect_one()) {
+      prefetch_tensormap(&map_xn);
+      prefetch_tensormap(&map_act);
+      grid_dep_wait();
+      if (tr) tr[5] = clock64();
+      uint32_t par = 0, n_units = 0;
+      for_each_mlp_unit(P, cta, G, [&](const MlpUnit& u) {
+        if (n_units > 0) mbar_wait(acc_empty, (n_units - 1) & 1u);     // epilogue staging aliases the X stages
+        for (int gi = 0; gi < u.nst; ++gi) {
+          const int st = gi & 3;
+          const int nt_here = min(tps, u.nkt - gi * tps);
+          if (u.g == 1 && gi == 0) {
+            // one counter per down split: all nkt gate_up tiles whose columns this unit's K range reads (k tile j
+            // == gate_up tile j).  One acquire poll instead of one per tile: an acquire load is an L2 round trip,
+            // and twelve of them in sequence cost 6 us.
+            flag_wait(P.flags + u.split, (unsigned)u.nkt);
+            if (tr) tr[6] = clock64();
+          }
+          mbar_wait(&sb->empty[st], ((par >> st) & 1u) ^ 1u);
+          par ^= 1u << st;
+          unsigned char* stage = smem + st * kStageBytes;
+          mbar_arrive_expect_tx(&sb->full[st], (uint32_t)(nt_here * kTileBBytes));
+          for (int t = 0; t < nt_here; ++t)
+            tma_load_2d(stage + t * kTileBBytes, u.g == 0 ? &map_xn : &map_act, (u.kt0 + gi * tps + t) * kUmmaBK, 0, &sb->full[st]);
+        }
+        ++n_units;
+      });
+    }
+  } else {
+    // =============== MMA issuer ===============
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc(kUmmaM, kMegaNT);
+      uint32_t par = 0, n_units = 0;
+      for_each_mlp_unit(P, cta, G, [&](const MlpUnit& u) {
+        if (n_units > 0) {
+          mbar_wait(acc_empty, (n_units - 1) & 1u);
+          tc_fence_after();
+        }
+        for (int gi = 0; gi < u.nst; ++gi) {
+          const int st = gi & 3;
+          const int nt_here = min(tps, u.nkt - gi * tps);
+          mbar_wait(&sb->full[st], (par >> st) & 1u);
+          par ^= 1u << st;
+          tc_fence_after();
+          const uint32_t x_addr = smem_u32(smem + st * kStageBytes);
+          for (int t = 0; t < nt_here; ++t) {
+            const uint32_t b_addr = x_addr + t * kTileBBytes;
+            const uint32_t a_tmem = tmem + (uint32_t)(MegaCfg::kAccCols + 64 * st + 32 * t);
+#pragma unroll
+            for (int k = 0; k < kUmmaBK / 16; ++k)
+              umma_f16_ts(tmem, a_tmem + k * 8, make_smem_desc(b_addr + k * 32), idesc, (gi | t | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&sb->empty[st]);
+        }
+        umma_commit(&sb->tmem_full);
+        ++n_units;
+      });
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kWarpMma) tmem_dealloc(tmem, MegaCfg::kTmemCols);
+  if (tl_rec) {
+    tl = atomicAdd(d_tl.ctr, 1u);
+    if (tl < d_tl.cap) {
+      d_tl.buf[4 * tl] = (unsigned long long)kKidUmmaW4 | ((unsigned long long)gridDim.x << 8) | (1ull << 28) | (2ull << 48);
+      d_tl.buf[4 * tl + 1] = tl_t0;
+      d_tl.buf[4 * tl + 2] = tl_t0;
+      d_tl.buf[4 * tl + 3] = gtime();
+    }
+  }
+}
+
 // ---- host side ------------------------------------------------------------------------------------------
+static unsigned long long* g_mlp_trace = nullptr;
+void mlp_fused_set_trace(unsigned long long* dev_buf) { g_mlp_trace = dev_buf; }
+
+bool mlp_fused_supported(int T, int H, int I, int G) {
+  return T >= 1 && T <= kMegaNT && (G == 64 || G == 128) && H % kUmmaM == 0 && (2 * I) % kUmmaM == 0 && I % G == 0 && H % G == 0;
+}
+
+int launch_mlp_fused(const CUtensorMap& mxn, const CUtensorMap& mact, const MlpParams& P, cudaStream_t s) {
+  B200_REQUIRE(mlp_fused_supported(P.T, P.H, P.I, P.G) && P.split_down >= 1, "mlp_fused: unsupported shape");
+  static std::mutex mu;
+  static int grid_of_device[64] = {0};
+  int dev = 0, grid = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (dev >= 0 && dev < 64 && grid_of_device[dev] == 0) {
+      B200_CUDA(cudaFuncSetAttribute(mlp_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MlpSmem::kBytes));
+      int sms = 0, per_sm = 0;
+      B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mlp_fused_kernel, kUmmaThreads, MlpSmem::kBytes));
+      B200_REQUIRE(per_sm >= 1 && sms >= 1, "mlp_fused: the kernel does not fit on an SM");
+      grid_of_device[dev] = sms;
+    }
+    grid = dev >= 0 && dev < 64 ? grid_of_device[dev] : 0;
+  }
+  B200_REQUIRE(grid > 0, "mlp_fused: device index");
+  // One CTA per SM: all CTAs are co-resident (nothing else on the stream can hold an SM forever, and the
+  // next kernel is only allowed to start once every CTA of this grid runs), which the column flags rely on.
+  MlpParams PT = P;
+  PT.trace = g_mlp_trace;
+  B200_CUDA(launch_k(mlp_fused_kernel, dim3(grid), dim3(kUmmaThreads), (size_t)MlpSmem::kBytes, s, mxn, mact, PT));
+  g_launch_count += 1;
+  return B200_OK;
+}
+
 bool decode_layers_supported(int n_heads, int n_kv, int G, int T) {
   const int gq = n_kv > 0 ? n_heads / n_kv : 0;
   return T >= 1 && T <= kMegaNT && (G == 64 || G == 128) && (gq == 2 || gq == 4 || gq == 6 || gq == 7 || gq == 8);
