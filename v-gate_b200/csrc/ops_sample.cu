@@ -59,25 +59,81 @@ __device__ ArgMax block_argmax(ArgMax a, ArgMax* red) {
   return red[0];
 }
 
-__global__ void __launch_bounds__(kSampleThreads)
+// One CLUSTER of 8 CTAs per row; each CTA owns a contiguous eighth of the vocabulary.  (One CTA per row --
+// 64 CTAs at batch 64, seven passes over 151 936 logits each, every thread adding 64-bit masses into one
+// shared histogram -- took 1.4 ms per step with the reference's default temperature 0.7 / top_p 0.9: more
+// than the model.)  Per-warp private histograms take the contention out of the mass sums; the eight CTAs
+// exchange their maxima and histograms through distributed shared memory and every CTA then takes the same
+// decisions from the same integer sums, so the result does not depend on how the row is cut.
+constexpr int kSC = 8;                       // CTAs per row
+constexpr int kST = 512;                     // threads per CTA
+constexpr int kSW = kST / 32;
+
+template <typename T>
+__device__ __forceinline__ T dsmem_ld(const T* local, int cta) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local)), "r"(cta));
+  T v;
+  if constexpr (sizeof(T) == 8) {
+    unsigned long long x;
+    asm volatile("ld.shared::cluster.u64 %0, [%1];" : "=l"(x) : "r"(remote) : "memory");
+    v = *reinterpret_cast<T*>(&x);
+  } else {
+    static_assert(sizeof(T) == 4, "dsmem_ld: 4 or 8 bytes");
+    uint32_t x;
+    asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(x) : "r"(remote) : "memory");
+    v = *reinterpret_cast<T*>(&x);
+  }
+  return v;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// CTA-wide argmax, then cluster-wide: every CTA returns the row's result.
+__device__ ArgMax cluster_argmax(ArgMax a, ArgMax* red, ArgMax* xchg) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    ArgMax b{__shfl_xor_sync(0xffffffffu, a.v, o), __shfl_xor_sync(0xffffffffu, a.i, o)};
+    a = better(a, b);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) red[warp] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    ArgMax m = red[0];
+    for (int w = 1; w < kSW; ++w) m = better(m, red[w]);
+    *xchg = m;
+  }
+  cluster_sync_all();
+  ArgMax m{dsmem_ld(&xchg->v, 0), dsmem_ld(&xchg->i, 0)};
+  for (int c = 1; c < kSC; ++c) m = better(m, ArgMax{dsmem_ld(&xchg->v, c), dsmem_ld(&xchg->i, c)});
+  cluster_sync_all();                        // xchg / red may be rewritten after this
+  return m;
+}
+
+__global__ void __cluster_dims__(kSC, 1, 1) __launch_bounds__(kST)
 sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__ temperature,
               const float* __restrict__ top_p, const uint32_t* __restrict__ seed, const int32_t* __restrict__ step,
               int32_t* __restrict__ out) {
-  __shared__ ArgMax red[kSampleThreads / 32];
-  __shared__ unsigned long long hist[256];
-  __shared__ unsigned long long s_above, s_target;
-  __shared__ int s_bin;
+  __shared__ ArgMax red[kSW];
+  __shared__ ArgMax xchg;
+  __shared__ unsigned long long whist[kSW][256];       // per-warp mass histograms
+  __shared__ unsigned long long hist[256];             // this CTA's histogram (read by the other CTAs)
+  __shared__ unsigned long long ghist[256];            // the row's histogram
   const unsigned tl = kernel_prologue(kKidSample);
-  const int r = blockIdx.x, tid = threadIdx.x;
+  const int r = blockIdx.x / kSC, rank = blockIdx.x % kSC, tid = threadIdx.x, warp = tid >> 5;
   const float* l = logits + (size_t)r * V;
+  const int per = (V + kSC - 1) / kSC;
+  const int i0 = rank * per, i1 = min(V, i0 + per);
   const float temp = temperature ? temperature[r] : 0.f;
 
   // pass 0: argmax (greedy result, and the max for the softmax)
   ArgMax best{-INFINITY, 0x7fffffff};
-  for (int i = tid; i < V; i += kSampleThreads) best = better(best, ArgMax{l[i], i});
-  best = block_argmax(best, red);
+  for (int i = i0 + tid; i < i1; i += kST) best = better(best, ArgMax{l[i], i});
+  best = cluster_argmax(best, red, &xchg);
   if (temp < 1e-5f) {
-    if (tid == 0) out[r] = best.i;
+    if (rank == 0 && tid == 0) out[r] = best.i;
     kernel_epilogue(tl);
     return;
   }
@@ -90,59 +146,65 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
     constexpr float kBinsPerUnit = 8.f;     // level 0: linear bins over d = m - x in [0, 32)
     auto bin0 = [&](float x) { return min(255, (int)((m - x) * kBinsPerUnit)); };
     auto mass = [&](float x) { return (unsigned long long)(expf(x - m) * 4294967296.f); };
-    // ---- level 0 ----
-    if (tid < 256) hist[tid] = 0ull;
-    __syncthreads();
-    for (int i = tid; i < V; i += kSampleThreads) {
-      const float x = l[i] / temp;
-      atomicAdd(&hist[bin0(x)], mass(x));
-    }
-    __syncthreads();
-    if (tid == 0) {
-      unsigned long long total = 0;
-      for (int b = 0; b < 256; ++b) total += hist[b];
-      const unsigned long long target = (unsigned long long)((double)p * (double)total);
-      unsigned long long cum = 0;
-      int sel = -1;
-      for (int b = 0; b < 256; ++b) {            // bin 0 holds the most likely tokens
-        if (hist[b] == 0) continue;
-        sel = b;
-        if (cum + hist[b] >= target) break;
-        cum += hist[b];
+    // Sum the masses of this CTA's slice that pass `pred` into bins, combine the eight CTAs: ghist.
+    auto histogram = [&](auto&& bin_of) {
+      for (int b = tid; b < kSW * 256; b += kST) (&whist[0][0])[b] = 0ull;
+      __syncthreads();
+      for (int i = i0 + tid; i < i1; i += kST) {
+        const float x = l[i] / temp;
+        const int b = bin_of(x);
+        if (b >= 0) atomicAdd(&whist[warp][b], mass(x));
       }
-      // total >= target, so the loop always breaks; sel/cum then bracket the threshold bin.
-      s_bin = sel; s_above = cum; s_target = target;
+      __syncthreads();
+      if (tid < 256) {
+        unsigned long long t = 0;
+#pragma unroll
+        for (int w = 0; w < kSW; ++w) t += whist[w][tid];
+        hist[tid] = t;
+      }
+      cluster_sync_all();
+      if (tid < 256) {
+        unsigned long long t = 0;
+#pragma unroll
+        for (int c = 0; c < kSC; ++c) t += dsmem_ld(&hist[tid], c);
+        ghist[tid] = t;
+      }
+      cluster_sync_all();                    // hist may be rewritten; ghist is complete in every CTA
+      __syncthreads();
+    };
+    // ---- level 0 ----
+    histogram([&](float x) { return bin0(x); });
+    unsigned long long above = 0, target = 0;
+    int sel0 = -1;
+    {
+      unsigned long long total = 0;
+      for (int b = 0; b < 256; ++b) total += ghist[b];
+      target = (unsigned long long)((double)p * (double)total);
+      for (int b = 0; b < 256; ++b) {            // bin 0 holds the most likely tokens
+        if (ghist[b] == 0) continue;
+        sel0 = b;
+        if (above + ghist[b] >= target) break;
+        above += ghist[b];
+      }
+      // total >= target, so the loop always breaks; sel0 / above then bracket the threshold bin.
     }
-    __syncthreads();
-    const int sel0 = s_bin;
     // ---- levels 1..4: radix select on the float key inside bin sel0 ----
     uint32_t prefix = 0, pmask = 0;
     for (int level = 0; level < 4; ++level) {
       const int shift = 24 - 8 * level;
-      __syncthreads();
-      if (tid < 256) hist[tid] = 0ull;
-      __syncthreads();
-      for (int i = tid; i < V; i += kSampleThreads) {
-        const float x = l[i] / temp;
-        if (bin0(x) != sel0) continue;
+      histogram([&](float x) {
+        if (bin0(x) != sel0) return -1;
         const uint32_t key = float_key(x);
-        if ((key & pmask) != prefix) continue;
-        atomicAdd(&hist[(key >> shift) & 255u], mass(x));
+        return (key & pmask) != prefix ? -1 : (int)((key >> shift) & 255u);
+      });
+      int sel = -1;
+      for (int b = 255; b >= 0; --b) {           // larger key = more likely
+        if (ghist[b] == 0) continue;
+        sel = b;
+        if (above + ghist[b] >= target) break;
+        above += ghist[b];
       }
-      __syncthreads();
-      if (tid == 0) {
-        unsigned long long cum = s_above;
-        int sel = -1;
-        for (int b = 255; b >= 0; --b) {         // larger key = more likely
-          if (hist[b] == 0) continue;
-          sel = b;
-          if (cum + hist[b] >= s_target) break;
-          cum += hist[b];
-        }
-        s_bin = sel; s_above = cum;
-      }
-      __syncthreads();
-      prefix |= (uint32_t)s_bin << shift;
+      prefix |= (uint32_t)sel << shift;
       pmask |= 255u << shift;
     }
     thr_key = prefix;
@@ -151,22 +213,22 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   // ---- draw: exponential race in log form over the kept set ----
   const uint32_t sd = seed ? seed[r] : 0u, st = step ? (uint32_t)step[r] : 0u;
   ArgMax draw{-INFINITY, 0x7fffffff};
-  for (int i = tid; i < V; i += kSampleThreads) {
+  for (int i = i0 + tid; i < i1; i += kST) {
     const float x = l[i] / temp;
     if (float_key(x) < thr_key) continue;
     const float u = hash_uniform(sd, st, (uint32_t)i);
     const float score = (x - m) - logf(-logf(u));
     draw = better(draw, ArgMax{score, i});
   }
-  draw = block_argmax(draw, red);
-  if (tid == 0) out[r] = draw.i;
+  draw = cluster_argmax(draw, red, &xchg);
+  if (rank == 0 && tid == 0) out[r] = draw.i;
   kernel_epilogue(tl);
 }
 
 int launch_sample(const float* logits, int B, int V, const float* temperature, const float* top_p,
                   const uint32_t* seed, const int32_t* step, int32_t* out, cudaStream_t s) {
   if (B == 0) return B200_OK;
-  launch_k(sample_kernel, dim3(B), dim3(kSampleThreads), 0, s, logits, V, temperature, top_p, seed, step, out);
+  launch_k(sample_kernel, dim3(B * kSC), dim3(kST), 0, s, logits, V, temperature, top_p, seed, step, out);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
