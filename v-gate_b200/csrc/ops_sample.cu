@@ -118,7 +118,10 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
               int32_t* __restrict__ out) {
   __shared__ ArgMax red[kSW];
   __shared__ ArgMax xchg;
-  __shared__ unsigned long long whist[kSW][256];       // per-warp mass histograms
+  // per-warp mass histograms, as (low word, high word) pairs: a 64-bit shared-memory atomicAdd compiles to a
+  // compare-and-swap loop (it was half of the kernel's stall samples); 32-bit adds are native, and the carry
+  // out of the low word is recovered from the value the add returns
+  __shared__ unsigned int wlo[kSW][256], whi[kSW][256];
   __shared__ unsigned long long hist[256];             // this CTA's histogram (read by the other CTAs)
   __shared__ unsigned long long ghist[256];            // the row's histogram
   const unsigned tl = kernel_prologue(kKidSample);
@@ -146,20 +149,26 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
     constexpr float kBinsPerUnit = 8.f;     // level 0: linear bins over d = m - x in [0, 32)
     auto bin0 = [&](float x) { return min(255, (int)((m - x) * kBinsPerUnit)); };
     auto mass = [&](float x) { return (unsigned long long)(expf(x - m) * 4294967296.f); };
+    auto add_mass = [&](int b, unsigned long long mv) {
+      const unsigned int lo = (unsigned int)mv, hi = (unsigned int)(mv >> 32);
+      const unsigned int old = atomicAdd(&wlo[warp][b], lo);
+      const unsigned int carry = old + lo < old ? 1u : 0u;
+      if (hi + carry) atomicAdd(&whi[warp][b], hi + carry);
+    };
     // Sum the masses of this CTA's slice that pass `pred` into bins, combine the eight CTAs: ghist.
     auto histogram = [&](auto&& bin_of) {
-      for (int b = tid; b < kSW * 256; b += kST) (&whist[0][0])[b] = 0ull;
+      for (int b = tid; b < kSW * 256; b += kST) { (&wlo[0][0])[b] = 0u; (&whi[0][0])[b] = 0u; }
       __syncthreads();
       for (int i = i0 + tid; i < i1; i += kST) {
         const float x = l[i] / temp;
         const int b = bin_of(x);
-        if (b >= 0) atomicAdd(&whist[warp][b], mass(x));
+        if (b >= 0) add_mass(b, mass(x));
       }
       __syncthreads();
       if (tid < 256) {
         unsigned long long t = 0;
 #pragma unroll
-        for (int w = 0; w < kSW; ++w) t += whist[w][tid];
+        for (int w = 0; w < kSW; ++w) t += ((unsigned long long)whi[w][tid] << 32) | wlo[w][tid];
         hist[tid] = t;
       }
       cluster_sync_all();
