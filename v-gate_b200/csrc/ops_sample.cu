@@ -68,6 +68,7 @@ __device__ ArgMax block_argmax(ArgMax a, ArgMax* red) {
 constexpr int kSC = 8;                       // CTAs per row
 constexpr int kST = 512;                     // threads per CTA
 constexpr int kSW = kST / 32;
+constexpr int kSampleCand = 4096;            // candidate list per CTA (elements of the threshold bin), 16 KB
 
 template <typename T>
 __device__ __forceinline__ T dsmem_ld(const T* local, int cta) {
@@ -90,7 +91,8 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
-// CTA-wide argmax, then cluster-wide: every CTA returns the row's result.
+// CTA-wide argmax, then cluster-wide: every CTA returns the row's result.  Each call of a kernel uses its own
+// exchange slot, so no barrier is needed after the remote reads -- except before the CTA exits (the caller's job).
 __device__ ArgMax cluster_argmax(ArgMax a, ArgMax* red, ArgMax* xchg) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -108,7 +110,6 @@ __device__ ArgMax cluster_argmax(ArgMax a, ArgMax* red, ArgMax* xchg) {
   cluster_sync_all();
   ArgMax m{dsmem_ld(&xchg->v, 0), dsmem_ld(&xchg->i, 0)};
   for (int c = 1; c < kSC; ++c) m = better(m, ArgMax{dsmem_ld(&xchg->v, c), dsmem_ld(&xchg->i, c)});
-  cluster_sync_all();                        // xchg / red may be rewritten after this
   return m;
 }
 
@@ -117,13 +118,16 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
               const float* __restrict__ top_p, const uint32_t* __restrict__ seed, const int32_t* __restrict__ step,
               int32_t* __restrict__ out) {
   __shared__ ArgMax red[kSW];
-  __shared__ ArgMax xchg;
+  __shared__ ArgMax xchg[2];
   // per-warp mass histograms, as (low word, high word) pairs: a 64-bit shared-memory atomicAdd compiles to a
   // compare-and-swap loop (it was half of the kernel's stall samples); 32-bit adds are native, and the carry
   // out of the low word is recovered from the value the add returns
   __shared__ unsigned int wlo[kSW][256], whi[kSW][256];
-  __shared__ unsigned long long hist[256];             // this CTA's histogram (read by the other CTAs)
+  __shared__ unsigned long long hist[2][256];          // this CTA's histogram (read by the other CTAs), by level parity
   __shared__ unsigned long long ghist[256];            // the row's histogram
+  __shared__ int n_cand;
+  extern __shared__ __align__(16) unsigned char dyn_smem[];
+  float* cand = reinterpret_cast<float*>(dyn_smem);     // x of this CTA's elements in the threshold bin
   const unsigned tl = kernel_prologue(kKidSample);
   const int r = blockIdx.x / kSC, rank = blockIdx.x % kSC, tid = threadIdx.x, warp = tid >> 5;
   const float* l = logits + (size_t)r * V;
@@ -134,9 +138,10 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   // pass 0: argmax (greedy result, and the max for the softmax)
   ArgMax best{-INFINITY, 0x7fffffff};
   for (int i = i0 + tid; i < i1; i += kST) best = better(best, ArgMax{l[i], i});
-  best = cluster_argmax(best, red, &xchg);
+  best = cluster_argmax(best, red, &xchg[0]);
   if (temp < 1e-5f) {
     if (rank == 0 && tid == 0) out[r] = best.i;
+    cluster_sync_all();                      // no CTA exits while another still reads its shared memory
     kernel_epilogue(tl);
     return;
   }
@@ -149,6 +154,7 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
     constexpr float kBinsPerUnit = 8.f;     // level 0: linear bins over d = m - x in [0, 32)
     auto bin0 = [&](float x) { return min(255, (int)((m - x) * kBinsPerUnit)); };
     auto mass = [&](float x) { return (unsigned long long)(expf(x - m) * 4294967296.f); };
+    int n_hist = 0;
     auto add_mass = [&](int b, unsigned long long mv) {
       const unsigned int lo = (unsigned int)mv, hi = (unsigned int)(mv >> 32);
       const unsigned int old = atomicAdd(&wlo[warp][b], lo);
@@ -156,63 +162,107 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
       if (hi + carry) atomicAdd(&whi[warp][b], hi + carry);
     };
     // Sum the masses of this CTA's slice that pass `pred` into bins, combine the eight CTAs: ghist.
-    auto histogram = [&](auto&& bin_of) {
+    auto histogram = [&](bool from_cand, auto&& bin_of) {
       for (int b = tid; b < kSW * 256; b += kST) { (&wlo[0][0])[b] = 0u; (&whi[0][0])[b] = 0u; }
       __syncthreads();
-      for (int i = i0 + tid; i < i1; i += kST) {
-        const float x = l[i] / temp;
-        const int b = bin_of(x);
-        if (b >= 0) add_mass(b, mass(x));
+      if (from_cand) {
+        for (int k = tid; k < n_cand; k += kST) {
+          const float x = cand[k];
+          const int b = bin_of(x);
+          if (b >= 0) add_mass(b, mass(x));
+        }
+      } else {
+        for (int i = i0 + tid; i < i1; i += kST) {
+          const float x = l[i] / temp;
+          const int b = bin_of(x);
+          if (b >= 0) add_mass(b, mass(x));
+        }
       }
       __syncthreads();
+      unsigned long long* mine = hist[n_hist & 1];
       if (tid < 256) {
         unsigned long long t = 0;
 #pragma unroll
         for (int w = 0; w < kSW; ++w) t += ((unsigned long long)whi[w][tid] << 32) | wlo[w][tid];
-        hist[tid] = t;
+        mine[tid] = t;
       }
       cluster_sync_all();
       if (tid < 256) {
         unsigned long long t = 0;
 #pragma unroll
-        for (int c = 0; c < kSC; ++c) t += dsmem_ld(&hist[tid], c);
+        for (int c = 0; c < kSC; ++c) t += dsmem_ld(&mine[tid], c);
         ghist[tid] = t;
       }
-      cluster_sync_all();                    // hist may be rewritten; ghist is complete in every CTA
+      // no second cluster barrier: the next histogram goes to the other buffer, and the one after that is
+      // only written once every CTA has passed the barrier in between
+      ++n_hist;
       __syncthreads();
     };
-    // ---- level 0 ----
-    histogram([&](float x) { return bin0(x); });
-    unsigned long long above = 0, target = 0;
-    int sel0 = -1;
-    {
-      unsigned long long total = 0;
-      for (int b = 0; b < 256; ++b) total += ghist[b];
-      target = (unsigned long long)((double)p * (double)total);
-      for (int b = 0; b < 256; ++b) {            // bin 0 holds the most likely tokens
-        if (ghist[b] == 0) continue;
-        sel0 = b;
-        if (above + ghist[b] >= target) break;
-        above += ghist[b];
+    // The bin (visited in order 0..255, or 255..0 when descending) at which the running mass first reaches
+    // `target`: returns the bin, and adds the mass of the bins before it to `above`.  Warp-parallel (every warp
+    // computes the same): lane j owns eight consecutive bins of the visiting order.
+    auto select_bin = [&](bool descending, unsigned long long& above_io, unsigned long long target_v) {
+      const int lane = tid & 31;
+      unsigned long long h8[8], sum = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int o = lane * 8 + k;
+        h8[k] = ghist[descending ? 255 - o : o];
+        sum += h8[k];
       }
-      // total >= target, so the loop always breaks; sel0 / above then bracket the threshold bin.
+      unsigned long long incl = sum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long up = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += up;
+      }
+      const unsigned hit = __ballot_sync(0xffffffffu, above_io + incl >= target_v && sum != 0);
+      const int src = hit ? __ffs(hit) - 1 : 31;          // (no lane reaches the target: cannot happen, take the last)
+      unsigned long long run = above_io + incl - sum;
+      int sel = -1;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (h8[k] == 0 || sel >= 0) continue;
+        if (run + h8[k] >= target_v) sel = descending ? 255 - (lane * 8 + k) : lane * 8 + k;
+        else run += h8[k];
+      }
+      above_io = __shfl_sync(0xffffffffu, run, src);
+      return __shfl_sync(0xffffffffu, sel, src);
+    };
+    // ---- level 0 ----
+    histogram(false, [&](float x) { return bin0(x); });
+    unsigned long long above = 0, target = 0;
+    {
+      unsigned long long part = 0;
+      for (int b = (tid & 31); b < 256; b += 32) part += ghist[b];
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+      target = (unsigned long long)((double)p * (double)part);   // part == the row's total mass (integer: order-free)
     }
+    const int sel0 = select_bin(false, above, target);           // bin 0 holds the most likely tokens
+    // The elements of the threshold bin (a few percent of the slice) are collected once; the four radix
+    // levels below walk that list instead of the slice.  Sums are integers, so the order is irrelevant.
+    if (tid == 0) n_cand = 0;
+    __syncthreads();
+    for (int i = i0 + tid; i < i1; i += kST) {
+      const float x = l[i] / temp;
+      if (bin0(x) == sel0) {
+        const int k = atomicAdd(&n_cand, 1);
+        if (k < kSampleCand) cand[k] = x;
+      }
+    }
+    __syncthreads();
+    const bool use_cand = n_cand <= kSampleCand;        // else (degenerate rows) the levels rescan the slice
     // ---- levels 1..4: radix select on the float key inside bin sel0 ----
     uint32_t prefix = 0, pmask = 0;
     for (int level = 0; level < 4; ++level) {
       const int shift = 24 - 8 * level;
-      histogram([&](float x) {
+      histogram(use_cand, [&](float x) {
         if (bin0(x) != sel0) return -1;
         const uint32_t key = float_key(x);
         return (key & pmask) != prefix ? -1 : (int)((key >> shift) & 255u);
       });
-      int sel = -1;
-      for (int b = 255; b >= 0; --b) {           // larger key = more likely
-        if (ghist[b] == 0) continue;
-        sel = b;
-        if (above + ghist[b] >= target) break;
-        above += ghist[b];
-      }
+      const int sel = select_bin(true, above, target);           // larger key = more likely
       prefix |= (uint32_t)sel << shift;
       pmask |= 255u << shift;
     }
@@ -229,15 +279,18 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
     const float score = (x - m) - logf(-logf(u));
     draw = better(draw, ArgMax{score, i});
   }
-  draw = cluster_argmax(draw, red, &xchg);
+  draw = cluster_argmax(draw, red, &xchg[1]);
   if (rank == 0 && tid == 0) out[r] = draw.i;
+  cluster_sync_all();                        // no CTA exits while another still reads its shared memory
   kernel_epilogue(tl);
 }
 
 int launch_sample(const float* logits, int B, int V, const float* temperature, const float* top_p,
                   const uint32_t* seed, const int32_t* step, int32_t* out, cudaStream_t s) {
   if (B == 0) return B200_OK;
-  launch_k(sample_kernel, dim3(B * kSC), dim3(kST), 0, s, logits, V, temperature, top_p, seed, step, out);
+  // static + dynamic shared memory exceeds the 48 KB default (host-side attribute, per device, cheap to repeat)
+  B200_CUDA(cudaFuncSetAttribute(sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSampleCand * 4));
+  launch_k(sample_kernel, dim3(B * kSC), dim3(kST), (size_t)kSampleCand * 4, s, logits, V, temperature, top_p, seed, step, out);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
