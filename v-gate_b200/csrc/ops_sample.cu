@@ -135,9 +135,21 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   const int i0 = rank * per, i1 = min(V, i0 + per);
   const float temp = temperature ? temperature[r] : 0.f;
 
+  // f(logit, index) over this CTA's slice, eight coalesced loads in flight per thread (a plain strided loop
+  // is one dependent L2 round trip per element, 37 per thread and pass)
+  auto for_slice = [&](auto&& f) {
+    for (int base = i0 + tid; base < i1; base += 8 * kST) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = base + u * kST < i1 ? __ldg(l + base + u * kST) : 0.f;
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (base + u * kST < i1) f(v[u], base + u * kST);
+    }
+  };
   // pass 0: argmax (greedy result, and the max for the softmax)
   ArgMax best{-INFINITY, 0x7fffffff};
-  for (int i = i0 + tid; i < i1; i += kST) best = better(best, ArgMax{l[i], i});
+  for_slice([&](float v, int i) { best = better(best, ArgMax{v, i}); });
   best = cluster_argmax(best, red, &xchg[0]);
   if (temp < 1e-5f) {
     if (rank == 0 && tid == 0) out[r] = best.i;
@@ -172,11 +184,11 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
           if (b >= 0) add_mass(b, mass(x));
         }
       } else {
-        for (int i = i0 + tid; i < i1; i += kST) {
-          const float x = l[i] / temp;
+        for_slice([&](float v, int) {
+          const float x = v / temp;
           const int b = bin_of(x);
           if (b >= 0) add_mass(b, mass(x));
-        }
+        });
       }
       __syncthreads();
       unsigned long long* mine = hist[n_hist & 1];
@@ -244,13 +256,13 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
     // levels below walk that list instead of the slice.  Sums are integers, so the order is irrelevant.
     if (tid == 0) n_cand = 0;
     __syncthreads();
-    for (int i = i0 + tid; i < i1; i += kST) {
-      const float x = l[i] / temp;
+    for_slice([&](float v, int) {
+      const float x = v / temp;
       if (bin0(x) == sel0) {
         const int k = atomicAdd(&n_cand, 1);
         if (k < kSampleCand) cand[k] = x;
       }
-    }
+    });
     __syncthreads();
     const bool use_cand = n_cand <= kSampleCand;        // else (degenerate rows) the levels rescan the slice
     // ---- levels 1..4: radix select on the float key inside bin sel0 ----
@@ -272,13 +284,13 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   // ---- draw: exponential race in log form over the kept set ----
   const uint32_t sd = seed ? seed[r] : 0u, st = step ? (uint32_t)step[r] : 0u;
   ArgMax draw{-INFINITY, 0x7fffffff};
-  for (int i = i0 + tid; i < i1; i += kST) {
-    const float x = l[i] / temp;
-    if (float_key(x) < thr_key) continue;
+  for_slice([&](float v, int i) {
+    const float x = v / temp;
+    if (float_key(x) < thr_key) return;
     const float u = hash_uniform(sd, st, (uint32_t)i);
     const float score = (x - m) - logf(-logf(u));
     draw = better(draw, ArgMax{score, i});
-  }
+  });
   draw = cluster_argmax(draw, red, &xchg[1]);
   if (rank == 0 && tid == 0) out[r] = draw.i;
   cluster_sync_all();                        // no CTA exits while another still reads its shared memory
