@@ -362,6 +362,16 @@ def run_b200(a):
                 line["cpu_baseline"], _ = cpu_reference_run(a.preset, a.cpu_sample)
             except Exception as exc:   # the baseline is reported, never required for the GPU number
                 line["cpu_baseline"] = {"error": repr(exc)}
+        # informational: the reference's own GPU path (vLLM) measured once on this pool, same checkpoint and
+        # workload, by tools/vllm_b200_baseline.py -- a recorded number, not re-measured by this run
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_vllm_b200_baseline.json")) as f:
+                v = json.load(f)
+            if v.get("batch") == a.batch and v.get("new_tokens") == a.new_tokens and a.preset == v.get("preset"):
+                line["reference_gpu_recorded"] = {"impl": "vllm " + v["vllm_version"], "value": v["tok_per_s"], "unit": "tok/s",
+                                                  "n_gpus": 1, "source": "profiles/r01_vllm_b200_baseline.json"}
+        except Exception:   # noqa: BLE001
+            pass
         print(json.dumps(line), flush=True)
     eng.close()
     if world > 1:
