@@ -162,3 +162,39 @@ def test_w4_umma_fused_swiglu(T):
     ref = g / (1 + np.exp(-g)) * u
     got = act.cpu().numpy().astype(np.float64)
     assert (np.abs(got - ref) <= 1.5e-3 * np.abs(ref) + 1e-4).all()
+
+
+def test_w4_umma_two_row_tiles_per_cta_bitwise():
+    """Large prefill passes run 256 weight rows per CTA (two accumulators sharing the staged activations).
+    Its bits must equal the 128-row kernel's: the first 128 tokens of a 1280-token call (256-row path: N/256 x
+    10 token tiles >= 296 CTAs) against a 128-token call of the same rows (128-row path) -- store + bias,
+    accumulate, and the fused SwiGLU epilogue -- plus a check of the whole result against the oracle."""
+    rng = np.random.default_rng(77)
+    K, N, T = 1536, 8192, 1280
+    qw, qz, sc = random_awq(rng, K, N)
+    wq, s, z = repack(qw, qz, sc)
+    ch = tile(wq, s, z, K, N)
+    chp = tile(wq, s, z, K, N, pair_rows=N // 2)
+    x = rng.standard_normal((T, K)).astype(np.float16)
+    bias = (rng.standard_normal(N) * 0.1).astype(np.float16)
+    xd, bd = dev(x), dev(bias)
+    big = torch.empty((T, N), dtype=torch.float32, device="cuda")
+    small = torch.empty((128, N), dtype=torch.float32, device="cuda")
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(xd), K, ptr(big), N, ptr(bd), T, K, N, 128, 0, 1, 0, stream()))
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(xd), K, ptr(small), N, ptr(bd), 128, K, N, 128, 0, 1, 0, stream()))
+    assert torch.equal(big[:128].view(torch.int32), small.view(torch.int32))
+    ref = x[:256].astype(np.float64) @ dequantize_awq(qw, qz, sc, 128).astype(np.float64) + bias.astype(np.float64)
+    assert np.abs(big[:256].cpu().numpy() - ref).max() < TOL
+    # accumulate
+    y0 = rng.standard_normal((T, N)).astype(np.float32)
+    yb, ys = dev(y0), dev(y0[:128].copy())
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(xd), K, ptr(yb), N, None, T, K, N, 128, 1, 1, 0, stream()))
+    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(xd), K, ptr(ys), N, None, 128, K, N, 128, 1, 1, 0, stream()))
+    assert torch.equal(yb[:128].view(torch.int32), ys.view(torch.int32))
+    # fused SwiGLU (rows paired per tile)
+    ab = torch.zeros((T, N // 2), dtype=torch.float16, device="cuda")
+    as_ = torch.zeros((128, N // 2), dtype=torch.float16, device="cuda")
+    check(lib().b200_op_w4_gemm_umma(ptr(chp), ptr(xd), K, ptr(ab), N // 2, None, T, K, N, 128, 2, 1, 0, stream()))
+    check(lib().b200_op_w4_gemm_umma(ptr(chp), ptr(xd), K, ptr(as_), N // 2, None, 128, K, N, 128, 2, 1, 0, stream()))
+    assert torch.equal(ab[:128].view(torch.int16), as_.view(torch.int16))
+    assert ab[1000:].float().abs().sum().item() > 0

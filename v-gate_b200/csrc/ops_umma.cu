@@ -35,11 +35,11 @@ void umma_set_trace(unsigned long long* dev_buf, int grid_x, int grid_z) {
   g_umma_trace = dev_buf; g_umma_trace_gridx = grid_x; g_umma_trace_gridz = grid_z;
 }
 
-template <int NT, bool kW4>
+template <int NT, bool kW4, int MT = 1>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
 umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                  const UmmaParams p) {
-  using Cfg = UmmaCfg<NT, kW4>;
+  using Cfg = UmmaCfg<NT, kW4, true, MT>;
   constexpr int kStages = Cfg::kStages, kRing = Cfg::kRing;
   constexpr int kTileBBytes = Cfg::kTileBBytes, kStageBytes = Cfg::kStageBytes;
   constexpr int kXInStage = kW4 ? 0 : kTileABytes;           // byte offset of the first X tile inside a stage
@@ -70,7 +70,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
   unsigned long long* tr = p.trace ? p.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
   if (tr && threadIdx.x == 0) tr[0] = clock64();
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) { mbar_init(&sb->full[s], kW4 ? 128 + 1 : 1); mbar_init(&sb->empty[s], 1); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(&sb->full[s], kW4 ? MT * 128 + 1 : 1); mbar_init(&sb->empty[s], 1); }
     for (int s = 0; s < kRing; ++s) { mbar_init(&sb->pk_full[s], 1); mbar_init(&sb->pk_empty[s], 128); }
     mbar_init(&sb->tmem_full, 1);
     fence_mbar_init();
@@ -96,32 +96,40 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       // a thread only ever waits on a barrier whose previous phase it has itself consumed.  (With
       // slots shared between warpgroups a fast warpgroup could wait on a slot two phases ahead, and
       // an mbarrier parity wait cannot tell "two phases ahead" from "done".)
+      // The chunk sequence v = gi * MT + t (group gi, row tile t) is dealt to the warpgroups round-robin; with
+      // MT = 2 a stage holds both tiles of a group (A slot = (gi % 2) * 2 + t = v % 4 = wg, still private).
       int use = 0;
-      for (int gi = wg; gi < nst; gi += 4, ++use) {
+      for (int v = wg; v < nst * MT; v += 4, ++use) {
+        const int gi = v / MT, t = v % MT;
         const int slot = wg + 4 * (use % Cfg::kSlotsPerWg), s = gi % kStages;
         w4_chunk_to_tmem(smem_u32(ring + slot * kChunkStride), &sb->pk_full[slot], (uint32_t)(use / Cfg::kSlotsPerWg) & 1u,
                          &sb->empty[s], ((uint32_t)(gi / kStages) & 1u) ^ 1u, &sb->full[s], &sb->pk_empty[slot],
-                         tmem + lane_base + (uint32_t)(Cfg::kAccCols + 64 * s), r, min(tps, nkt - gi * tps));
+                         tmem + lane_base + (uint32_t)(Cfg::kAccCols + 64 * (s * MT + t)), r, min(tps, nkt - gi * tps));
       }
     }
     // ===================== epilogue: TMEM -> registers -> global =====================
     mbar_wait(&sb->tmem_full, 0);
     tc_fence_after();
     if (tr && threadIdx.x == 0) tr[4] = clock64();
-    umma_epilogue<NT>(p.mode, p.y, p.ldy, p.mode == kPartialF32 ? (size_t)split * p.part_stride : 0, p.bias, p.T, tok0, nt,
-                      reinterpret_cast<float*>(smem), tmem, tr);
+#pragma unroll
+    for (int t = 0; t < MT; ++t) {
+      if (t > 0) asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");   // the staging buffer is reused
+      umma_epilogue<NT>(p.mode, p.y, p.ldy, p.mode == kPartialF32 ? (size_t)split * p.part_stride : 0, p.bias, p.T, tok0,
+                        nt * MT + t, reinterpret_cast<float*>(smem), tmem + (uint32_t)(t * (Cfg::kAccCols / MT)), tr);
+    }
   } else if (warp == kWarpTmaW) {
     // ===================== TMA: packed weight chunks (do not depend on upstream kernels) =====================
     if (kW4 && elect_one()) {
       const int KG = p.K / p.G;
       const uint32_t chunk_bytes = 512u + (uint32_t)tps * 4096u;
-      const unsigned char* src = p.chunks + ((size_t)nt * KG + kt0 / tps) * chunk_bytes;
-      for (int gi = 0; gi < nst; ++gi) {
-        const int use = gi >> 2;                                   // same slot walk as the consuming warpgroup
-        const int slot = (gi & 3) + 4 * (use % Cfg::kSlotsPerWg);
+      for (int v = 0; v < nst * MT; ++v) {
+        const int gi = v / MT, t = v % MT;
+        const unsigned char* src = p.chunks + ((size_t)(nt * MT + t) * KG + kt0 / tps + gi) * chunk_bytes;
+        const int use = v >> 2;                                    // same slot walk as the consuming warpgroup
+        const int slot = (v & 3) + 4 * (use % Cfg::kSlotsPerWg);
         mbar_wait(&sb->pk_empty[slot], ((uint32_t)(use / Cfg::kSlotsPerWg) & 1u) ^ 1u);
         mbar_arrive_expect_tx(&sb->pk_full[slot], chunk_bytes);
-        bulk_g2s(ring + slot * kChunkStride, src + (size_t)gi * chunk_bytes, chunk_bytes, &sb->pk_full[slot]);
+        bulk_g2s(ring + slot * kChunkStride, src, chunk_bytes, &sb->pk_full[slot]);
       }
     }
   } else if (warp == kWarpTmaX) {
@@ -164,10 +172,14 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         for (int t = 0; t < nt_here; ++t) {
           const uint32_t b_addr = x_addr + t * kTileBBytes;
           if constexpr (kW4) {
-            const uint32_t a_tmem = tmem + (uint32_t)(Cfg::kAccCols + 64 * s + 32 * t);
 #pragma unroll
-            for (int k = 0; k < kUmmaBK / 16; ++k)     // 16 k = 8 TMEM columns of A, 32 bytes of the B swizzle row
-              umma_f16_ts(tmem, a_tmem + k * 8, make_smem_desc(b_addr + k * 32), idesc, (gi | t | k) != 0 ? 1u : 0u);
+            for (int m = 0; m < MT; ++m) {             // row tile m: its own accumulator and A slot, the same X tile
+              const uint32_t a_tmem = tmem + (uint32_t)(Cfg::kAccCols + 64 * (s * MT + m) + 32 * t);
+#pragma unroll
+              for (int k = 0; k < kUmmaBK / 16; ++k)   // 16 k = 8 TMEM columns of A, 32 bytes of the B swizzle row
+                umma_f16_ts(tmem + (uint32_t)(m * (Cfg::kAccCols / MT)), a_tmem + k * 8, make_smem_desc(b_addr + k * 32), idesc,
+                            (gi | t | k) != 0 ? 1u : 0u);
+            }
           } else {
             const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
 #pragma unroll
@@ -270,16 +282,16 @@ int make_tensor_map_f16(CUtensorMap* map, const void* base, int64_t rows, int64_
 }
 
 // ---- launch -------------------------------------------------------------------------------------------
-template <int NT, bool kW4>
+template <int NT, bool kW4, int MT = 1>
 static int launch_nt(const CUtensorMap& mx, const CUtensorMap& mw, const UmmaParams& p, int n_splits, cudaStream_t s) {
-  constexpr int smem_bytes = UmmaCfg<NT, kW4>::kSmemBytes;
-  auto kern = umma_gemm_kernel<NT, kW4>;
+  constexpr int smem_bytes = UmmaCfg<NT, kW4, true, MT>::kSmemBytes;
+  auto kern = umma_gemm_kernel<NT, kW4, MT>;
   static bool configured = false;
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     configured = true;
   }
-  dim3 grid(p.N / kUmmaM, (p.T + NT - 1) / NT, n_splits);
+  dim3 grid(p.N / (kUmmaM * MT), (p.T + NT - 1) / NT, n_splits);
   UmmaParams pp = p;
   if (g_umma_trace_gridx && ((int)grid.x != g_umma_trace_gridx || (int)grid.z != g_umma_trace_gridz)) pp.trace = nullptr;
   launch_k(kern, grid, dim3(kUmmaThreads), (size_t)smem_bytes, s, mx, mw, pp);
@@ -295,7 +307,14 @@ static int dispatch_nt(int nt_sel, const CUtensorMap& mx, const CUtensorMap& mw,
     case 16: return launch_nt<16, kW4>(mx, mw, p, n_splits, s);
     case 32: return launch_nt<32, kW4>(mx, mw, p, n_splits, s);
     case 64: return launch_nt<64, kW4>(mx, mw, p, n_splits, s);
-    case 128: return launch_nt<128, kW4>(mx, mw, p, n_splits, s);
+    case 128:
+      if constexpr (kW4) {
+        // large prefill passes: 256 weight rows per CTA (same bits; half the activation traffic through L2)
+        // once that still leaves two waves of CTAs
+        if (n_splits == 1 && p.N % (2 * kUmmaM) == 0 && (int64_t)(p.N / (2 * kUmmaM)) * ((p.T + 127) / 128) >= 2 * 148)
+          return launch_nt<128, kW4, 2>(mx, mw, p, n_splits, s);
+      }
+      return launch_nt<128, kW4>(mx, mw, p, n_splits, s);
     default:
       if constexpr (kW4) { set_last_error("umma_w4: token tile must be <= 128"); return B200_ERR_INVALID; }
       else return launch_nt<256, kW4>(mx, mw, p, n_splits, s);
