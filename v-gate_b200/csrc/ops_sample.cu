@@ -68,7 +68,7 @@ __device__ ArgMax block_argmax(ArgMax a, ArgMax* red) {
 constexpr int kSC = 8;                       // CTAs per row
 constexpr int kST = 512;                     // threads per CTA
 constexpr int kSW = kST / 32;
-constexpr int kSampleCand = 4096;            // candidate list per CTA (elements of the threshold bin), 16 KB
+constexpr int kSampleCand = 4096;            // candidate list per CTA (elements of the threshold bin): x and index, 32 KB
 
 template <typename T>
 __device__ __forceinline__ T dsmem_ld(const T* local, int cta) {
@@ -128,6 +128,7 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   __shared__ int n_cand;
   extern __shared__ __align__(16) unsigned char dyn_smem[];
   float* cand = reinterpret_cast<float*>(dyn_smem);     // x of this CTA's elements in the threshold bin
+  int* cand_i = reinterpret_cast<int*>(dyn_smem + kSampleCand * 4);   // ... and their vocabulary indices
   const unsigned tl = kernel_prologue(kKidSample);
   const int r = blockIdx.x / kSC, rank = blockIdx.x % kSC, tid = threadIdx.x, warp = tid >> 5;
   const float* l = logits + (size_t)r * V;
@@ -161,6 +162,14 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
   const float m = best.v / temp;
   const float p = top_p ? top_p[r] : 1.f;
   uint32_t thr_key = 0;        // keep iff key(x_i) >= thr_key
+  const uint32_t sd = seed ? seed[r] : 0u, st = step ? (uint32_t)step[r] : 0u;
+  ArgMax draw{-INFINITY, 0x7fffffff};
+  auto race = [&](float x, int i) {         // exponential race in log form: argmax of (x - m) + Gumbel(u_i)
+    const float u = hash_uniform(sd, st, (uint32_t)i);
+    const float score = (x - m) - logf(-logf(u));
+    draw = better(draw, ArgMax{score, i});
+  };
+  bool drawn = false;          // the kept set has already been raced (top-p path with a candidate list)
 
   if (p < 1.f) {
     constexpr float kBinsPerUnit = 8.f;     // level 0: linear bins over d = m - x in [0, 32)
@@ -252,15 +261,19 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
       target = (unsigned long long)((double)p * (double)part);   // part == the row's total mass (integer: order-free)
     }
     const int sel0 = select_bin(false, above, target);           // bin 0 holds the most likely tokens
-    // The elements of the threshold bin (a few percent of the slice) are collected once; the four radix
-    // levels below walk that list instead of the slice.  Sums are integers, so the order is irrelevant.
+    // One more pass over the slice does two things.  Elements in bins before sel0 are more likely than anything
+    // in the threshold bin, so they are kept whatever the exact threshold turns out to be: they enter the draw
+    // right away.  The elements of the threshold bin (a few percent of the slice) are collected; the four
+    // radix levels below and the rest of the draw walk that list instead of the slice.
     if (tid == 0) n_cand = 0;
     __syncthreads();
-    for_slice([&](float v, int) {
+    for_slice([&](float v, int i) {
       const float x = v / temp;
-      if (bin0(x) == sel0) {
+      const int b = bin0(x);
+      if (b < sel0) race(x, i);
+      else if (b == sel0) {
         const int k = atomicAdd(&n_cand, 1);
-        if (k < kSampleCand) cand[k] = x;
+        if (k < kSampleCand) { cand[k] = x; cand_i[k] = i; }
       }
     });
     __syncthreads();
@@ -279,18 +292,21 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
       pmask |= 255u << shift;
     }
     thr_key = prefix;
+    if (use_cand) {              // finish the draw with the kept part of the threshold bin
+      for (int k = tid; k < n_cand; k += kST)
+        if (float_key(cand[k]) >= thr_key) race(cand[k], cand_i[k]);
+      drawn = true;
+    } else {
+      draw = ArgMax{-INFINITY, 0x7fffffff};                        // degenerate row: start over with the exact threshold
+    }
   }
 
-  // ---- draw: exponential race in log form over the kept set ----
-  const uint32_t sd = seed ? seed[r] : 0u, st = step ? (uint32_t)step[r] : 0u;
-  ArgMax draw{-INFINITY, 0x7fffffff};
-  for_slice([&](float v, int i) {
-    const float x = v / temp;
-    if (float_key(x) < thr_key) return;
-    const float u = hash_uniform(sd, st, (uint32_t)i);
-    const float score = (x - m) - logf(-logf(u));
-    draw = better(draw, ArgMax{score, i});
-  });
+  // ---- draw over the kept set (no top-p, or a threshold bin too large for the candidate list) ----
+  if (!drawn)
+    for_slice([&](float v, int i) {
+      const float x = v / temp;
+      if (float_key(x) >= thr_key) race(x, i);
+    });
   draw = cluster_argmax(draw, red, &xchg[1]);
   if (rank == 0 && tid == 0) out[r] = draw.i;
   cluster_sync_all();                        // no CTA exits while another still reads its shared memory
@@ -301,8 +317,8 @@ int launch_sample(const float* logits, int B, int V, const float* temperature, c
                   const uint32_t* seed, const int32_t* step, int32_t* out, cudaStream_t s) {
   if (B == 0) return B200_OK;
   // static + dynamic shared memory exceeds the 48 KB default (host-side attribute, per device, cheap to repeat)
-  B200_CUDA(cudaFuncSetAttribute(sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSampleCand * 4));
-  launch_k(sample_kernel, dim3(B * kSC), dim3(kST), (size_t)kSampleCand * 4, s, logits, V, temperature, top_p, seed, step, out);
+  B200_CUDA(cudaFuncSetAttribute(sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSampleCand * 8));
+  launch_k(sample_kernel, dim3(B * kSC), dim3(kST), (size_t)kSampleCand * 8, s, logits, V, temperature, top_p, seed, step, out);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
