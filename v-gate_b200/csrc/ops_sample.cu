@@ -59,13 +59,14 @@ __device__ ArgMax block_argmax(ArgMax a, ArgMax* red) {
   return red[0];
 }
 
-// One CLUSTER of 8 CTAs per row; each CTA owns a contiguous eighth of the vocabulary.  (One CTA per row --
+// One CLUSTER of 4 CTAs per row; each CTA owns a contiguous quarter of the vocabulary.  (One CTA per row --
 // 64 CTAs at batch 64, seven passes over 151 936 logits each, every thread adding 64-bit masses into one
 // shared histogram -- took 1.4 ms per step with the reference's default temperature 0.7 / top_p 0.9: more
-// than the model.)  Per-warp private histograms take the contention out of the mass sums; the eight CTAs
+// than the model.)  Per-warp private histograms take the contention out of the mass sums; the CTAs
 // exchange their maxima and histograms through distributed shared memory and every CTA then takes the same
-// decisions from the same integer sums, so the result does not depend on how the row is cut.
-constexpr int kSC = 8;                       // CTAs per row
+// decisions from the same integer sums, so the result does not depend on how the row is cut.  (Four, not
+// eight: only 33 clusters of 8 fit on the GPU at once -- two waves for 64 rows; 1.32 -> 1.28 ms per step.)
+constexpr int kSC = 4;                       // CTAs per row
 constexpr int kST = 512;                     // threads per CTA
 constexpr int kSW = kST / 32;
 constexpr int kSampleCand = 4096;            // candidate list per CTA (elements of the threshold bin): x and index, 32 KB
