@@ -1010,6 +1010,7 @@ int32_t b200_engine_finalize(b200_engine* e) {
           return rc;
         w.ulin[i].chunks = w.chunks[i].as<unsigned char>();
         w.ulin[i].bias = a.bias; w.ulin[i].K = a.K; w.ulin[i].N = a.N; w.ulin[i].G = a.G;
+        if (i == 3) { w.ulin[2].next_chunks = w.chunks[3].as<unsigned char>(); w.ulin[2].next_bytes = (int64_t)w.chunks[3].bytes; }
       }
     }
     B200_CUDA(cudaStreamSynchronize(e->stream));

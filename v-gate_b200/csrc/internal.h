@@ -60,6 +60,10 @@ struct UmmaW4 {
   const unsigned char* chunks = nullptr;   // [N/128][K/G] chunks: scales, zeros, packed k tiles (see ops_umma.cu)
   const __half* bias = nullptr;
   int K = 0, N = 0, G = 128;
+  // Weights of the linear that runs next and cannot prefetch for itself (down after gate_up: its CTAs need the
+  // SMs gate_up's CTAs occupy).  This kernel's TMA warp asks L2 for them once its own loads are issued.
+  const unsigned char* next_chunks = nullptr;
+  int64_t next_bytes = 0;
 };
 enum { kUmmaStoreF32 = 0, kUmmaAccumF32 = 1, kUmmaPartialF32 = 2, kUmmaSwigluF16 = 3, kUmmaArgmaxF32 = 4 };
 

@@ -131,6 +131,16 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         mbar_arrive_expect_tx(&sb->pk_full[slot], chunk_bytes);
         bulk_g2s(ring + slot * kChunkStride, src, chunk_bytes, &sb->pk_full[slot]);
       }
+      if (p.l2_prefetch) {       // HBM has spare bandwidth here; the next kernel then finds its weights in L2
+        const int64_t n_cta = (int64_t)gridDim.x * gridDim.y * gridDim.z;
+        const int64_t cta = blockIdx.x + (int64_t)gridDim.x * (blockIdx.y + (int64_t)gridDim.y * blockIdx.z);
+        const int64_t per = ((p.l2_prefetch_bytes + n_cta - 1) / n_cta + 4095) & ~(int64_t)4095;
+        const int64_t b0 = cta * per, b1 = b0 + per < p.l2_prefetch_bytes ? b0 + per : p.l2_prefetch_bytes;
+        for (int64_t b = b0; b < b1; b += 4096) {
+          const uint32_t n = (uint32_t)(b1 - b < 4096 ? (b1 - b) & ~(int64_t)15 : 4096);
+          if (n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.l2_prefetch + b), "r"(n) : "memory");
+        }
+      }
     }
   } else if (warp == kWarpTmaX) {
     // ===================== TMA: activation tiles (and fp16 weight tiles) =====================
@@ -343,6 +353,7 @@ int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T,
   UmmaParams p{};
   p.trace = g_umma_trace;
   p.chunks = w.chunks; p.bias = w.bias; p.y = y; p.part_stride = part_stride;
+  p.l2_prefetch = w.next_chunks; p.l2_prefetch_bytes = w.next_bytes;
   p.ldy = ldy; p.T = T; p.K = w.K; p.N = w.N; p.G = w.G; p.mode = mode;
   const int KG = w.K / w.G, tpg = w.G / kUmmaBK;
   const int groups_per_split = (KG + n_splits - 1) / n_splits;     // split boundaries fall on quantisation groups

@@ -176,6 +176,8 @@ struct UmmaParams {
   int ldy, T, K, N, G;
   int kt_per_split;       // k tiles handled by one CTA along grid.z (W4: a multiple of G/64)
   int mode;
+  const unsigned char* l2_prefetch;   // weights of the NEXT kernel to pull into L2 (or null), shared out over the CTAs
+  int64_t l2_prefetch_bytes;
 };
 
 __device__ __forceinline__ uint4 lds128(uint32_t saddr) {
