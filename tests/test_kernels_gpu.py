@@ -225,6 +225,46 @@ def test_fused_decode_attention_matches_rope_plus_attention(n_splits, n_parts):
     assert d < (1e-6 if n_splits == 1 else 2e-3), d                      # merge order differs only when split
 
 
+def test_fused_decode_attention_two_ctas_per_sm_variant_bitwise():
+    """With more CTAs than SMs the decode attention runs three tile-owning warps (two CTAs per SM); the chunks
+    are still dealt to four virtual warps, so its bits equal the four-warp kernel's: 100 rows in one call
+    (200 CTAs -> three-warp kernel) against the same rows in two calls of 50 (four-warp kernel)."""
+    rng = np.random.default_rng(31)
+    n_heads, n_kv, n_blocks = 12, 2, 2700
+    ctx_lens = [int(x) for x in rng.integers(1, 400, size=100)]
+    ctx_lens[:6] = [1, 64, 65, 192, 193, 257]
+    T = len(ctx_lens)
+    kc, vc, bt, _, _ = _paged_setup(rng, T, ctx_lens, n_kv, n_blocks)
+    pos = np.array([c - 1 for c in ctx_lens], dtype=np.int32)
+    slot = np.array([bt[i, p // 16] * 16 + p % 16 for i, p in enumerate(pos)], dtype=np.int32)
+    cos, sin = rope_table(Qwen2Dims(), 4096)
+    width = (n_heads + 2 * n_kv) * 128
+    n_parts = 4
+    parts = rng.standard_normal((n_parts, T, width)).astype(np.float32)
+    bias = (rng.standard_normal(width) * 0.05).astype(np.float16)
+    cosd, sind, btd, biasd = dev(cos.numpy()), dev(sin.numpy()), dev(bt), dev(bias)
+    ctx = np.array(ctx_lens, dtype=np.int32)
+
+    def run(rows):
+        n = len(rows)
+        kcd, vcd = dev(swizzle_kv(kc)).clone(), dev(swizzle_kv(vc)).clone()
+        out = torch.empty((n, n_heads * 128), dtype=torch.float16, device="cuda")
+        pd, sd, cd = dev(pos[rows]), dev(slot[rows]), dev(ctx[rows])
+        brd = dev(np.asarray(rows, dtype=np.int32))
+        prt = dev(np.ascontiguousarray(parts[:, rows]))
+        check(lib().b200_op_attn_decode_fused(ptr(prt), n_parts, n * width, ptr(biasd), ptr(pd), ptr(sd), ptr(cosd), ptr(sind),
+                                              ptr(kcd), ptr(vcd), ptr(btd), bt.shape[1], ptr(brd), ptr(cd), n, n_heads, n_kv,
+                                              1, None, None, ptr(out), stream()))
+        return out, kcd, vcd
+
+    rows = list(range(T))
+    big, kb, vb = run(rows)
+    lo, k1, v1 = run(rows[:50])
+    hi, k2, v2 = run(rows[50:])
+    assert torch.equal(big[:50].view(torch.int16), lo.view(torch.int16))
+    assert torch.equal(big[50:].view(torch.int16), hi.view(torch.int16))
+
+
 def test_rope_kv_write_matches_oracle():
     rng = np.random.default_rng(3)
     n_heads, n_kv, T, n_blocks = 12, 2, 9, 8

@@ -40,13 +40,16 @@ constexpr int kPartFloats = kHeadDim + 2;                            // acc[128]
 
 // Shared memory: per warp one K tile + one V tile (a warp owns whole 64-token chunks), then the
 // query tile [16 rows][128] fp16 (rows >= GQ are zero) and the new token's k / v (fused mode).
-struct AttnSmem {
-  static constexpr int kOffTiles = 0;                                // kAttnTileWarps x (K 16 KB + V 16 KB)
-  static constexpr int kOffQ = kAttnTileWarps * 2 * kTileBytes;      // 4 KB
+template <int NW>                                                    // NW = warps that own a K/V tile pair
+struct AttnSmemT {
+  static constexpr int kOffTiles = 0;                                // NW x (K 16 KB + V 16 KB)
+  static constexpr int kOffQ = NW * 2 * kTileBytes;                  // 4 KB
   static constexpr int kOffNew = kOffQ + 16 * kHeadDim * 2;          // k[128], v[128] fp16
   static constexpr int kOffBar = kOffNew + 2 * kHeadDim * 2;
-  static constexpr int kBytes = kOffBar + kAttnTileWarps * 8;
+  static constexpr int kBytes = kOffBar + NW * 8;
 };
+using AttnSmem = AttnSmemT<4>;
+
 
 
 struct AttnParams {
@@ -111,10 +114,11 @@ __device__ __forceinline__ void attn_bar_sync() {
 // block ids or the block count changed (a sequence crossed into a new block, or the batch changed), the
 // prefetched tile is dropped (its barrier phase is consumed) and the chunk is loaded again.  Requires
 // ctx_len / bt_row / block_tables to hold valid values at all times (the engine zero-fills them).
-template <int GQ, bool kFused, int kBarId, bool kInitBars, bool kPreWait = false>
+template <int GQ, bool kFused, int kBarId, bool kInitBars, bool kPreWait = false, int kPhys = kAttnTileWarps>
 __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned char* smem, const int j, const int t,
                                                 const int split, unsigned long long* tr, uint32_t& bar_uses) {
-  using L = AttnSmem;
+  using L = AttnSmemT<kPhys>;
+  static_assert(kPhys == 3 || kPhys == 4, "physical tile warps");
   static_assert(GQ <= 8, "one m16 tile, upper half unused");
   static_assert(!kPreWait || kInitBars, "the prefetch owns phase 0 of a fresh barrier");
   const int tid = threadIdx.x;
@@ -130,7 +134,7 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
 
   int pre_nb = 0;                                   // lane 0: blocks requested before the wait, and their ids
   int pre_ids[kChunkBlocks] = {0, 0, 0, 0};
-  const bool tile_warp = warp < kAttnTileWarps;
+  const bool tile_warp = warp < kPhys;
   if (lane == 0 && tile_warp) {
     if constexpr (kInitBars) {
       mbar_init(bar, 1);
@@ -318,15 +322,16 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
   }
 
   const int g = lane >> 2, tq = lane & 3;           // MMA fragment coordinates
-  float o[16][2];                                   // O[row g][dims 8 dn + 2 tq, +1]  (rows g + 8 are padding)
-#pragma unroll
-  for (int dn = 0; dn < 16; ++dn) o[dn][0] = o[dn][1] = 0.f;
-  float m_run = -INFINITY, l_run = 0.f;             // running max / sum of row g (replicated over the quad)
   const float scale = 0.08838834764831845f;         // 1 / sqrt(128)
-
+  // The chunks of a (row, kv head, split) are dealt to kAttnTileWarps VIRTUAL warps, c = split + S * (vw + 4 i),
+  // each with its own online-softmax state; the merge below combines the virtual warps in order.  With
+  // kPhys == 4 a physical warp is a virtual warp.  With kPhys == 3 (three tile pairs: ~101 KB, two CTAs per SM,
+  // used when there are more CTAs than SMs) warp 0 also plays virtual warp 3 with a second state -- the
+  // arithmetic, hence the bits, do not depend on kPhys.
+  auto run_chunks = [&](const int vw, const bool first_issued, float (&o)[16][2], float& m_run, float& l_run) {
   int it = 0;
-  for (int c = tile_warp ? split + S * warp : nchunks; c < nchunks; c += S * kAttnTileWarps, ++it) {
-    if (it > 0) {
+  for (int c = split + S * vw; c < nchunks; c += S * kAttnTileWarps, ++it) {
+    if (it > 0 || !first_issued) {
       __syncwarp();
       if (lane == 0) issue_chunk(c);
     }
@@ -431,18 +436,34 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
       }
     }
   }
+  };
+  float oA[16][2], oB[16][2];                       // O[row g][dims 8 dn + 2 tq, +1]  (rows g + 8 are padding)
+#pragma unroll
+  for (int dn = 0; dn < 16; ++dn) oA[dn][0] = oA[dn][1] = oB[dn][0] = oB[dn][1] = 0.f;
+  float mA = -INFINITY, lA = 0.f, mB = -INFINITY, lB = 0.f;   // running max / sum of row g (replicated over the quad)
+  const bool second = kPhys < kAttnTileWarps && warp + kPhys < kAttnTileWarps;
+  if (tile_warp) run_chunks(warp, true, oA, mA, lA);
+  if constexpr (kPhys < kAttnTileWarps) {
+    if (second) run_chunks(warp + kPhys, false, oB, mB, lB);
+  }
   if (tr && tid == 0) tr[6] = clock64();
 
-  // ---- merge the four warps in shared memory (their tiles are free now) ----
+  // ---- merge the four virtual warps in shared memory (the tiles are free now) ----
   attn_bar_sync<kBarId>();
-  float* mrg = reinterpret_cast<float*>(smem + L::kOffTiles) + (size_t)warp * (8 * kPartFloats);   // [8 rows][130]
-  if (g < GQ && tile_warp) {
+  auto put = [&](const int vw, const float (&o)[16][2], const float m_run, const float l_run) {
+    float* mrg = reinterpret_cast<float*>(smem + L::kOffTiles) + (size_t)vw * (8 * kPartFloats);   // [8 rows][130]
+    if (g < GQ) {
 #pragma unroll
-    for (int dn = 0; dn < 16; ++dn) {
-      mrg[g * kPartFloats + dn * 8 + 2 * tq] = o[dn][0];
-      mrg[g * kPartFloats + dn * 8 + 2 * tq + 1] = o[dn][1];
+      for (int dn = 0; dn < 16; ++dn) {
+        mrg[g * kPartFloats + dn * 8 + 2 * tq] = o[dn][0];
+        mrg[g * kPartFloats + dn * 8 + 2 * tq + 1] = o[dn][1];
+      }
+      if (tq == 0) { mrg[g * kPartFloats + kHeadDim] = m_run; mrg[g * kPartFloats + kHeadDim + 1] = l_run; }
     }
-    if (tq == 0) { mrg[g * kPartFloats + kHeadDim] = m_run; mrg[g * kPartFloats + kHeadDim + 1] = l_run; }
+  };
+  if (tile_warp) put(warp, oA, mA, lA);
+  if constexpr (kPhys < kAttnTileWarps) {
+    if (second) put(warp + kPhys, oB, mB, lB);
   }
   attn_bar_sync<kBarId>();
   const float* all = reinterpret_cast<const float*>(smem + L::kOffTiles);

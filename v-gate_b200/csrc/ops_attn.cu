@@ -11,7 +11,7 @@ B200_DEFINE_TL_SETTER(tl_set_attn)
 static unsigned long long* g_attn_trace = nullptr;     // profiling aid: 8 x uint64 clock stamps per CTA
 void attn_set_trace(unsigned long long* dev_buf) { g_attn_trace = dev_buf; }
 
-template <int GQ, bool kFused>
+template <int GQ, bool kFused, int kPhys>
 __global__ void __launch_bounds__(kAttnThreads)
 paged_attn_kernel(const AttnParams p) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -19,7 +19,7 @@ paged_attn_kernel(const AttnParams p) {
   const unsigned tl = kernel_prologue<!kFused>(kKidAttn);
   unsigned long long* tr = p.trace ? p.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
   uint32_t bar_uses = 0;
-  paged_attn_unit<GQ, kFused, 0, true, kFused>(p, smem, blockIdx.x, blockIdx.y, blockIdx.z, tr, bar_uses);
+  paged_attn_unit<GQ, kFused, 0, true, kFused, kPhys>(p, smem, blockIdx.x, blockIdx.y, blockIdx.z, tr, bar_uses);
   if (tr && threadIdx.x == 0) tr[7] = clock64();
   kernel_epilogue(tl);
 }
@@ -239,19 +239,26 @@ int launch_prefill_attn(const __half* q, const __half* k_cache, const __half* v_
 #undef CASE
 }
 
-template <int GQ, bool kFused>
-static int launch_gq(const AttnParams& p, int T, cudaStream_t s) {
-  static bool configured = false;   // per process; the attribute is idempotent
-  auto kern = paged_attn_kernel<GQ, kFused>;
-  if (!configured) {
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnSmem::kBytes));
-    configured = true;
-  }
+template <int GQ, bool kFused, int kPhys>
+static int launch_gq_phys(const AttnParams& p, int T, cudaStream_t s) {
+  auto kern = paged_attn_kernel<GQ, kFused, kPhys>;
+  constexpr int smem_bytes = AttnSmemT<kPhys>::kBytes;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));   // idempotent, host-side
   dim3 grid(p.n_kv, T, p.n_splits);
-  B200_CUDA(launch_k(kern, grid, dim3(kAttnThreads), (size_t)AttnSmem::kBytes, s, p));
+  B200_CUDA(launch_k(kern, grid, dim3(kAttnThreads), (size_t)smem_bytes, s, p));
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
+}
+
+template <int GQ, bool kFused>
+static int launch_gq(const AttnParams& p, int T, cudaStream_t s) {
+  // More CTAs than SMs (decode batches above ~64 rows): three tile-owning warps, ~101 KB, two CTAs per SM --
+  // half the waves.  Same bits as the four-warp kernel (virtual warps, attn.cuh).
+  if constexpr (kFused) {
+    if ((int64_t)p.n_kv * T * p.n_splits > 148) return launch_gq_phys<GQ, kFused, 3>(p, T, s);
+  }
+  return launch_gq_phys<GQ, kFused, 4>(p, T, s);
 }
 
 size_t attn_scratch_floats(int T, int n_heads, int n_kv, int n_splits) {
