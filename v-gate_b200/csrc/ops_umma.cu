@@ -319,9 +319,10 @@ static int dispatch_nt(int nt_sel, const CUtensorMap& mx, const CUtensorMap& mw,
     case 64: return launch_nt<64, kW4>(mx, mw, p, n_splits, s);
     case 128:
       if constexpr (kW4) {
-        // large prefill passes: 256 weight rows per CTA (same bits; half the activation traffic through L2)
-        // once that still leaves two waves of CTAs
-        if (n_splits == 1 && p.N % (2 * kUmmaM) == 0 && (int64_t)(p.N / (2 * kUmmaM)) * ((p.T + 127) / 128) >= 2 * 148)
+        // 256 weight rows per CTA (same bits; half the activation traffic through L2, half the CTAs) as soon as
+        // 128-row tiles would not fit on the GPU in one wave: large prefill passes, and decode batches of 129..256
+        // rows (two token tiles: gate_up 280 CTAs -> 140, down 288 -> 144)
+        if (p.N % (2 * kUmmaM) == 0 && (int64_t)(p.N / kUmmaM) * ((p.T + 127) / 128) * n_splits > 148)
           return launch_nt<128, kW4, 2>(mx, mw, p, n_splits, s);
       }
       return launch_nt<128, kW4>(mx, mw, p, n_splits, s);
