@@ -1,8 +1,13 @@
-"""Import shim: the package sources live in ``v-gate_b200/`` (not a valid Python
-identifier); ``import vgate_b200`` resolves submodules from there."""
-import os as _os
+"""b200gate: a B200-native (sm_100a) worker backend for V-Gate's generate path.
 
-_real = _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))), "v-gate_b200")
-__path__.insert(0, _real)
-with open(_os.path.join(_real, "__init__.py")) as _f:
-    exec(compile(_f.read(), _os.path.join(_real, "__init__.py"), "exec"))
+Public surface (mirrors ``vgate/backends/vllm_backend.py:35-149``):
+    from vgate_b200 import B200Backend
+"""
+__all__ = ["B200Backend"]
+
+
+def __getattr__(name):
+    if name == "B200Backend":
+        from .backend import B200Backend
+        return B200Backend
+    raise AttributeError(name)
