@@ -40,7 +40,7 @@ extern "C" {
 #define B200_OK 0
 #define B200_ERR_INVALID (-1)   /* bad argument / unsupported shape */
 #define B200_ERR_CUDA (-2)      /* a CUDA call failed; engine is poisoned */
-#define B200_ERR_CAPACITY (-3)  /* request can never fit (prompt + max_tokens > max_model_len, KV pool) */
+#define B200_ERR_CAPACITY (-3)  /* request can never fit (prompt >= max_model_len, KV pool) */
 #define B200_ERR_STATE (-4)     /* call made in the wrong engine state */
 #define B200_ERR_NOT_FOUND (-5) /* unknown request id */
 #define B200_ERR_ABORTED (-6)   /* request was aborted or engine shut down */
@@ -105,7 +105,9 @@ int32_t b200_engine_finalize(b200_engine* e);
 void b200_engine_destroy(b200_engine* e);
 
 /* ---- requests ---------------------------------------------------------------------- */
-/* Returns a request id >= 0, or a negative error code.  Greedy iff temperature < 1e-5. */
+/* Returns a request id >= 0, or a negative error code.  Greedy iff temperature < 1e-5.  As in vLLM, a
+ * generation stops when the sequence reaches max_model_len: max_tokens is clamped to
+ * max_model_len - n_prompt, and only a prompt of max_model_len tokens or more is refused. */
 int64_t b200_submit(b200_engine* e, const int32_t* prompt_ids, int32_t n_prompt, float temperature,
                     float top_p, int32_t max_tokens, uint64_t seed);
 /* Blocks until the request finishes; copies up to `cap` generated ids; releases the request. */
@@ -115,6 +117,8 @@ int32_t b200_wait(b200_engine* e, int64_t rid, int32_t* out_ids, int32_t cap, in
  * When *finished becomes 1 the request is released. */
 int32_t b200_poll(b200_engine* e, int64_t rid, int32_t* out_ids, int32_t cap, int32_t* n_new,
                   int32_t* finished, int32_t timeout_ms);
+/* Stops the request and releases it: the caller must not wait on or poll `rid` afterwards (a thread
+ * already blocked in b200_wait / b200_poll on it gets B200_ERR_ABORTED). */
 int32_t b200_abort(b200_engine* e, int64_t rid);
 int32_t b200_stats_get(b200_engine* e, b200_stats* out);
 

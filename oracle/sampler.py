@@ -26,7 +26,14 @@ def hash_uniform(seed: int, step: int, n: int) -> np.ndarray:
     x ^= x >> 15
     x = (x * 0x846CA68B) & 0xFFFFFFFF
     x ^= x >> 16
-    return ((x >> 8).astype(np.float32) + np.float32(0.5)) * np.float32(1.0 / 16777216.0)
+    return uniform_from_bits(x)
+
+
+def uniform_from_bits(x) -> np.ndarray:
+    """32 hash bits -> fp32 strictly inside (0, 1): 23 bits, so that ``(x >> 9) + 0.5`` is exact in
+    fp32 (24 bits would round 16777215.5 up to 2**24 and give u == 1.0, i.e. an Exp(1) draw of 0)."""
+    x = np.asarray(x, dtype=np.uint64)
+    return ((x >> 9).astype(np.float32) + np.float32(0.5)) * np.float32(1.0 / 8388608.0)
 
 
 def top_p_keep_mask(logits: np.ndarray, top_p: float) -> np.ndarray:

@@ -111,6 +111,28 @@ def test_poll_streams_tokens_and_abort(small):
                 break
     st = eng.stats()
     assert st["kv_blocks_free"] == st["kv_blocks_total"]
+    # an aborted request leaves nothing behind: its id is unknown afterwards (abort releases the table entry),
+    # also when nobody ever polls it again (client disconnect, main.py:372-376)
+    rid = eng.submit(p, 0.0, 1.0, 400)
+    eng.poll(rid, cap=8, timeout_ms=2000)
+    eng.abort(rid)
+    import time
+    for _ in range(200):
+        if eng.stats()["running"] == 0:
+            break
+        time.sleep(0.01)
+    with pytest.raises(B200Error) as ei:
+        eng.poll(rid, cap=8, timeout_ms=0)
+    assert ei.value.code == -5                                  # B200_ERR_NOT_FOUND
+    n_fin = eng.stats()["requests_finished"]
+    done = eng.submit(p, 0.0, 1.0, 3)
+    for _ in range(500):
+        if eng.stats()["requests_finished"] > n_fin:
+            break
+        time.sleep(0.01)
+    eng.abort(done)                                             # already finished, never waited on: erased as well
+    with pytest.raises(B200Error):
+        eng.wait(done, 3)
 
 
 def test_sampling_requests_are_seeded(small):
@@ -128,7 +150,13 @@ def test_capacity_and_argument_errors(small):
     dims, ckpt, eng = small
     from vgate_b200.engine import B200Error
     with pytest.raises(B200Error):
-        eng.submit(np.zeros(500, np.int32), 0.0, 1.0, 100)          # prompt + max_tokens > max_model_len
+        eng.submit(np.zeros(512, np.int32), 0.0, 1.0, 4)            # a prompt of max_model_len tokens leaves no room
+    # vLLM semantics: a prompt shorter than max_model_len is accepted and the generation stops when the
+    # sequence reaches max_model_len (500 + 12 = 512), whatever max_tokens asked for
+    out = eng.wait(eng.submit(np.zeros(500, np.int32), 0.0, 1.0, 100), 100)[0]
+    assert len(out) == 12
+    st = eng.stats()
+    assert st["kv_blocks_free"] == st["kv_blocks_total"]
     with pytest.raises(B200Error):
         eng.submit(np.array([dims.vocab], np.int32), 0.0, 1.0, 4)   # token id out of range
     with pytest.raises(B200Error):
@@ -223,8 +251,9 @@ def test_full_context_2048_matches_oracle():
     eng = Engine(dims, max_seqs=4, max_model_len=2048, max_batch_tokens=4096).load_checkpoint(ckpt)
     try:
         toks, logits, _ = eng.generate_batch(prompts, n_new, n_logit_steps=n_new)
-        with pytest.raises(Exception):
-            eng.submit(prompts[0], 0.0, 1.0, n_new + 1)                 # one token past max_model_len
+        # one token past max_model_len is clamped (vLLM stops at max_model_len): the same 18 tokens come back
+        clamped = eng.wait(eng.submit(prompts[0], 0.0, 1.0, n_new + 1), n_new + 1)[0]
+        assert np.array_equal(clamped, toks[0])
     finally:
         eng.close()
     ref32 = _oracle(dims, ckpt, "fp32")

@@ -120,6 +120,42 @@ def test_backend_generate_contract(backend):
     json.dumps(res)                                                            # worker_api.py:139 serialises it
 
 
+def test_generate_releases_every_request_when_one_fails(backend):
+    """A failure in the middle of a multi-prompt call (worker_api.py:77 bodies) must not leave the other
+    requests of that call decoding or parked in the engine's table: they are aborted (= released)."""
+    eng = backend.engine
+    sp = backend.create_sampling_params(0.0, 1.0, 4)
+    real_wait, calls = eng.wait, []
+
+    def flaky_wait(rid, max_tokens):
+        calls.append(rid)
+        if len(calls) == 2:
+            raise RuntimeError("engine failure")
+        return real_wait(rid, max_tokens)
+
+    eng.wait = flaky_wait
+    with pytest.raises(RuntimeError):
+        backend.generate(["a", "b", "c", "d"], sp)
+    # first request was waited on (released by wait); the failing one and the two never waited on are aborted
+    assert sorted(eng.aborted) == sorted(calls[1:2] + [r for r in (calls[1] + 1, calls[1] + 2)])
+    eng.wait = real_wait
+    # a submit that fails half-way aborts what was already submitted
+    eng.aborted.clear()
+    real_submit, n = eng.submit, []
+
+    def flaky_submit(*a, **k):
+        n.append(1)
+        if len(n) == 3:
+            raise ValueError("prompt token id out of range")
+        return real_submit(*a, **k)
+
+    eng.submit = flaky_submit
+    with pytest.raises(ValueError):
+        backend.generate(["a", "b", "c"], sp)
+    assert len(eng.aborted) == 2
+    eng.submit = real_submit
+
+
 def test_backend_accepts_attribute_style_sampling_params(backend):
     sp = SimpleNamespace(temperature=0.0, top_p=1.0, max_tokens=3, seed=11)   # like vllm.SamplingParams
     r = backend.generate(["x"], sp)[0]

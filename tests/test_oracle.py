@@ -6,7 +6,7 @@ import numpy as np
 
 from oracle.awq import unpack_awq, pack_awq, dequantize_awq, AWQ_ORDER
 from oracle.qwen2 import OracleQwen2, Qwen2Dims
-from oracle.sampler import top_p_keep_mask, sample, hash_uniform
+from oracle.sampler import top_p_keep_mask, sample, hash_uniform, uniform_from_bits
 from vgate_b200.weights import ModelDims, synthetic_checkpoint
 
 
@@ -53,6 +53,19 @@ def test_sampler_greedy_and_determinism():
     u = hash_uniform(5, 9, 1000)
     assert u.dtype == np.float32 and (u > 0).all() and (u < 1).all()
     assert abs(u.mean() - 0.5) < 0.05
+
+
+def test_uniform_is_strictly_inside_unit_interval_for_every_hash_value():
+    """The draw is -log(u): u == 1 would give 0 and an infinite race score (a garbage token wins whatever
+    its probability), u == 0 an infinite draw.  Only the top 23 hash bits are used, so all 2**23 distinct
+    inputs (and the two extremes of the discarded low bits) are checked; fp32 arithmetic, as the kernel's."""
+    hi = np.arange(1 << 23, dtype=np.uint64) << np.uint64(9)
+    for low in (0, 0x1FF):
+        u = uniform_from_bits(hi | np.uint64(low))
+        assert u.dtype == np.float32
+        assert float(u.min()) > 0.0 and float(u.max()) < 1.0
+        assert np.isfinite(-np.log(-np.log(u))).all()
+    assert uniform_from_bits(np.uint64(0xFFFFFFFF)) == np.float32(1.0) - np.float32(2.0 ** -24)
 
 
 def _small():

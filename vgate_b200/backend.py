@@ -100,24 +100,28 @@ class B200Backend:
     def generate(self, prompts: List[str], sampling_params: Any) -> List[Dict[str, Any]]:
         """Blocking, batch-shaped entry point; called from executor threads, re-entrant.  The GIL
         is released while waiting inside the C library."""
-        submitted = []
+        pending = []                   # request ids this call still owns (submitted, not yet waited on)
+        results = []
         try:
+            submitted = []
             for p in prompts:
                 submitted.append(self._submit(p, sampling_params))
-        except Exception:
-            for rid, _ in submitted:
+                pending.append(submitted[-1][0])
+            for rid, max_tokens in submitted:
+                ids, ttft, gen_time = self.engine.wait(rid, max_tokens)     # releases the request
+                pending.remove(rid)
+                token_ids = [int(t) for t in ids]
+                results.append({
+                    "text": self.tokenizer.decode(token_ids),
+                    "token_ids": token_ids,
+                    "num_tokens": len(token_ids),
+                    "metrics": {"ttft": float(ttft), "gen_time": float(gen_time)},
+                })
+        finally:
+            # a failed submit or wait: the rest of this call's requests must neither keep decoding nor stay
+            # in the engine's table (abort releases them)
+            for rid in pending:
                 self.engine.abort(rid)
-            raise
-        results = []
-        for rid, max_tokens in submitted:
-            ids, ttft, gen_time = self.engine.wait(rid, max_tokens)
-            token_ids = [int(t) for t in ids]
-            results.append({
-                "text": self.tokenizer.decode(token_ids),
-                "token_ids": token_ids,
-                "num_tokens": len(token_ids),
-                "metrics": {"ttft": float(ttft), "gen_time": float(gen_time)},
-            })
         return results
 
     async def stream_generate(self, prompt: str, sampling_params: Any) -> AsyncIterator[Dict[str, Any]]:

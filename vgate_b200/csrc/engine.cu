@@ -114,6 +114,7 @@ struct Request {
   uint32_t seed = 0;
   ReqState state = ReqState::WAITING;
   bool abort_requested = false;
+  bool detached = false;                       // aborted by its owner: nobody will wait or poll, the scheduler erases it
   int seq_slot = -1;
   std::vector<int32_t> blocks;
   std::vector<int32_t> out;
@@ -178,6 +179,8 @@ struct b200_engine {
   std::thread worker;
   bool stop = false;
   bool exclusive = false;                      // generate_batch owns the device
+  bool stepping = false;                       // the scheduler is inside run_step with mu released (admitted requests
+                                               // are in neither `waiting` nor `running` during a prefill pass)
   int64_t next_id = 1;
   std::deque<std::shared_ptr<Request>> waiting;
   std::vector<std::shared_ptr<Request>> running;
@@ -736,12 +739,16 @@ struct b200_engine {
       for (auto it = running.begin(); it != running.end();) {
         if ((*it)->abort_requested) {
           (*it)->state = ReqState::ABORTED; release_request_resources(**it); stats.requests_aborted++;
+          if ((*it)->detached) table.erase((*it)->id);
           it = running.erase(it);
         } else ++it;
       }
       for (auto it = waiting.begin(); it != waiting.end();) {
-        if ((*it)->abort_requested) { (*it)->state = ReqState::ABORTED; stats.requests_aborted++; it = waiting.erase(it); }
-        else ++it;
+        if ((*it)->abort_requested) {
+          (*it)->state = ReqState::ABORTED; stats.requests_aborted++;
+          if ((*it)->detached) table.erase((*it)->id);
+          it = waiting.erase(it);
+        } else ++it;
       }
       cv_done.notify_all();
       // admit: FIFO, whole prompts, within the token budget, with blocks reserved for the full
@@ -765,9 +772,11 @@ struct b200_engine {
       std::vector<std::shared_ptr<Request>> batch = admitted.empty() ? running : admitted;
       const bool is_prefill = !admitted.empty();
       if (batch.empty()) continue;
+      stepping = true;
       lk.unlock();
       const int rc = run_step(batch, is_prefill);
       lk.lock();
+      stepping = false;
       if (rc != B200_OK) { inflight = Inflight{}; fail_all(g_last_error); continue; }
       if (is_prefill) for (auto& r : admitted) running.push_back(r);
       // retire finished sequences
@@ -1162,11 +1171,14 @@ int64_t b200_submit(b200_engine* e, const int32_t* prompt_ids, int32_t n_prompt,
   B200_REQUIRE(n_prompt > 0 && max_tokens > 0, "n_prompt > 0 && max_tokens > 0");
   B200_REQUIRE(top_p > 0.f && top_p <= 1.f && temperature >= 0.f, "0 < top_p <= 1, temperature >= 0");
   if (!e->finalized) { set_last_error("submit before finalize"); return B200_ERR_STATE; }
-  if (n_prompt + max_tokens > e->cfg.max_model_len) {
-    set_last_error("prompt (" + std::to_string(n_prompt) + ") + max_tokens (" + std::to_string(max_tokens) +
-                   ") exceeds max_model_len " + std::to_string(e->cfg.max_model_len));
+  // vLLM accepts any prompt shorter than max_model_len and stops the generation when the sequence reaches
+  // max_model_len (finish reason "length"); only a prompt that leaves no room for a single token is refused.
+  if (n_prompt >= e->cfg.max_model_len) {
+    set_last_error("prompt (" + std::to_string(n_prompt) + " tokens) does not fit max_model_len " +
+                   std::to_string(e->cfg.max_model_len));
     return B200_ERR_CAPACITY;
   }
+  max_tokens = std::min(max_tokens, e->cfg.max_model_len - n_prompt);
   for (int i = 0; i < n_prompt; ++i)
     if (prompt_ids[i] < 0 || prompt_ids[i] >= e->V) { set_last_error("prompt token id out of range"); return B200_ERR_INVALID; }
   auto r = std::make_shared<Request>();
@@ -1242,9 +1254,15 @@ int32_t b200_abort(b200_engine* e, int64_t rid) {
   auto it = e->table.find(rid);
   if (it == e->table.end()) { set_last_error("unknown request id"); return B200_ERR_NOT_FOUND; }
   Request& r = *it->second;
+  // The caller gives the request up: its table entry (prompt and output vectors) must not outlive it.  A live
+  // request is retired and erased by the scheduler; one that already ended is erased here.  A thread blocked in
+  // b200_wait / b200_poll on the same id holds its own reference and still gets B200_ERR_ABORTED.
   if (r.state == ReqState::WAITING || r.state == ReqState::RUNNING) {
     r.abort_requested = true;
+    r.detached = true;
     e->cv_work.notify_all();
+  } else {
+    e->table.erase(it);
   }
   return B200_OK;
 }
@@ -1273,7 +1291,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
   {
     std::unique_lock<std::mutex> lk(e->mu);
     if (!e->fatal.empty()) { set_last_error("engine failed earlier: " + e->fatal); return B200_ERR_CUDA; }
-    if (e->exclusive || !e->running.empty() || !e->waiting.empty()) {
+    if (e->exclusive || e->stepping || e->inflight.active || !e->running.empty() || !e->waiting.empty()) {
       set_last_error("generate_batch needs an idle engine");
       return B200_ERR_STATE;
     }

@@ -207,12 +207,8 @@ prefill_attn_kernel(const PrefillAttnParams p) {
 
 template <int GQ>
 static int launch_prefill_gq(const PrefillAttnParams& p, int n_tiles, cudaStream_t s) {
-  static bool configured = false;
   auto kern = prefill_attn_kernel<GQ>;
-  if (!configured) {
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PrefillSmem<GQ>::kBytes));
-    configured = true;
-  }
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PrefillSmem<GQ>::kBytes));   // per device: every launch
   dim3 grid(p.n_kv, n_tiles);
   B200_CUDA(launch_k(kern, grid, dim3(GQ * 32), (size_t)PrefillSmem<GQ>::kBytes, s, p));
   g_launch_count += 1;

@@ -25,7 +25,10 @@ __device__ __forceinline__ uint32_t float_key(float f) {   // order-preserving f
 __device__ __forceinline__ float hash_uniform(uint32_t seed, uint32_t step, uint32_t i) {
   uint32_t x = i * 0x9E3779B1u + step * 0x85EBCA77u + seed * 0xC2B2AE3Du;
   x ^= x >> 16; x *= 0x7FEB352Du; x ^= x >> 15; x *= 0x846CA68Bu; x ^= x >> 16;
-  return ((float)(x >> 8) + 0.5f) * (1.0f / 16777216.0f);
+  // 23 hash bits: (x >> 9) + 0.5 <= 8388607.5 is exact in fp32 and the product stays strictly inside (0, 1).
+  // (With 24 bits, 16777215 + 0.5 rounds up to 2^24 and u becomes 1.0: -log(u) = 0 and the token's race
+  // score is +inf whatever its probability.)
+  return ((float)(x >> 9) + 0.5f) * (1.0f / 8388608.0f);
 }
 
 struct ArgMax { float v; int i; };

@@ -296,11 +296,8 @@ template <int NT, bool kW4, int MT = 1>
 static int launch_nt(const CUtensorMap& mx, const CUtensorMap& mw, const UmmaParams& p, int n_splits, cudaStream_t s) {
   constexpr int smem_bytes = UmmaCfg<NT, kW4, true, MT>::kSmemBytes;
   auto kern = umma_gemm_kernel<NT, kW4, MT>;
-  static bool configured = false;
-  if (!configured) {
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    configured = true;
-  }
+  // per device and cheap: set on every launch (a process-wide "configured" flag would leave a second device unset)
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   dim3 grid(p.N / (kUmmaM * MT), (p.T + NT - 1) / NT, n_splits);
   UmmaParams pp = p;
   if (g_umma_trace_gridx && ((int)grid.x != g_umma_trace_gridx || (int)grid.z != g_umma_trace_gridz)) pp.trace = nullptr;
