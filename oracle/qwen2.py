@@ -8,13 +8,16 @@ Follows vLLM 0.22.0 ``vllm/model_executor/models/qwen2.py``:
 The same mathematics as ``transformers.Qwen2ForCausalLM`` -- which is what
 ``tests/golden/make_golden.py`` pins it against.
 
-Two arithmetic modes:
-  ``fp32``  every intermediate in fp32 (the logits oracle; tolerance 2e-2).
-  ``fp16``  fp32 accumulation with activations rounded to fp16 at exactly the
-            points where the CUDA path stores fp16 (normed activations,
-            q/k/v after RoPE, attention output, SwiGLU output).  This is the
-            arithmetic class of the reference (vLLM runs this checkpoint with
-            fp16 activations) and is what greedy-token parity is judged on.
+Arithmetic modes:
+  ``fp32``  every intermediate in fp32.  THE oracle: it is the mode the golden vectors pin
+            (``tests/golden/hf_qwen2.npz``), and the only one a parity gate may use -- logits within
+            2e-2, greedy tokens identical.
+  ``fp16``  diagnostic only, pinned by nothing and gating nothing: fp32 accumulation with the
+            activations rounded to fp16 where the CUDA path stores fp16 (normed activations, q/k/v after
+            RoPE, attention output, SwiGLU output).  Useful to tell rounding-point effects from
+            summation-order effects when a logit differs.
+  ``bf16``  timing only (``bench.py`` CPU legs): weights and matmul operands in bfloat16, the eager
+            CPU arithmetic a PyTorch user of this model would run on the host.
 """
 from dataclasses import dataclass
 import numpy as np
@@ -55,8 +58,9 @@ class OracleQwen2:
     """Batched (equal-length) forward with a dense per-sequence KV cache."""
 
     def __init__(self, dims: Qwen2Dims, ckpt: dict, mode: str = "fp32", max_pos: int = 4096):
-        assert mode in ("fp32", "fp16")
+        assert mode in ("fp32", "fp16", "bf16")
         self.d, self.mode = dims, mode
+        wdt = torch.bfloat16 if mode == "bf16" else torch.float32
         self.cos, self.sin = rope_table(dims, max_pos)
         g = dims.group_size
 
@@ -64,14 +68,14 @@ class OracleQwen2:
             if prefix + ".qweight" in ckpt:
                 w = dequantize_awq(ckpt[prefix + ".qweight"], ckpt[prefix + ".qzeros"],
                                    ckpt[prefix + ".scales"], g)      # fp16 [K, N]
-                return _t(w).float()
-            return _t(ckpt[prefix + ".weight"]).float().t().contiguous()  # HF [N, K] -> [K, N]
+                return _t(w).to(wdt)
+            return _t(ckpt[prefix + ".weight"]).to(wdt).t().contiguous()  # HF [N, K] -> [K, N]
 
         def vec(name):
             return _t(ckpt[name]).float()
 
         self.embed = vec("model.embed_tokens.weight")
-        self.lm_head = self.embed if dims.tie_embeddings else vec("lm_head.weight")
+        self.lm_head = (self.embed if dims.tie_embeddings else vec("lm_head.weight")).to(wdt)
         self.final_norm = vec("model.norm.weight")
         self.layers = []
         for i in range(dims.n_layers):
@@ -97,6 +101,10 @@ class OracleQwen2:
     def _rnd(self, x):
         return x.half().float() if self.mode == "fp16" else x
 
+    def _mm(self, x, w):
+        """x @ w with fp32 result; bf16 mode rounds the left operand to the weights' dtype first."""
+        return (x.to(w.dtype) @ w).float() if w.dtype != torch.float32 else x @ w
+
     def _norm(self, h, w):
         # qwen2.py:287-312 RMSNorm; fp32 throughout, one rounding at the end
         var = h.pow(2).mean(-1, keepdim=True)
@@ -112,8 +120,10 @@ class OracleQwen2:
 
     # -- forward ---------------------------------------------------------
     @torch.no_grad()
-    def forward(self, ids: np.ndarray, return_hidden=False) -> torch.Tensor:
-        """ids int [B, T] appended after the cached prefix -> logits fp32 [B, T, V]."""
+    def forward(self, ids: np.ndarray, return_hidden=False, last_only=False) -> torch.Tensor:
+        """ids int [B, T] appended after the cached prefix -> logits fp32 [B, T, V]
+        ([B, 1, V] with ``last_only``: the LM head is applied to the last position alone, as an engine
+        does for a prompt -- vLLM qwen2.py:553-565 compute_logits on the sampled rows)."""
         d = self.d
         ids_t = _t(np.asarray(ids, dtype=np.int64))
         B, T = ids_t.shape
@@ -121,7 +131,7 @@ class OracleQwen2:
         h = self.embed[ids_t]                                   # [B, T, H] fp32
         for li, L in enumerate(self.layers):
             xn = self._norm(h, L["ln1"])
-            qkv = xn @ L["wqkv"] + L["bqkv"]
+            qkv = self._mm(xn, L["wqkv"]) + L["bqkv"]
             q, k, v = qkv.split([d.n_heads * d.head_dim, d.n_kv_heads * d.head_dim,
                                  d.n_kv_heads * d.head_dim], dim=-1)
             q = self._rnd(self._rope(q.view(B, T, d.n_heads, d.head_dim), pos))
@@ -140,28 +150,32 @@ class OracleQwen2:
             p = torch.softmax(sc, dim=-1)
             ao = torch.einsum("bkgts,bskd->btkgd", p, v).reshape(B, T, d.n_heads * d.head_dim)
             ao = self._rnd(ao)
-            h = h + ao @ L["wo"]
+            h = h + self._mm(ao, L["wo"])
             xn = self._norm(h, L["ln2"])
-            gu = xn @ L["wgu"]
+            gu = self._mm(xn, L["wgu"])
             gte, up = gu.split(d.intermediate, dim=-1)
             act = self._rnd(torch.nn.functional.silu(gte) * up)
-            h = h + act @ L["wd"]
+            h = h + self._mm(act, L["wd"])
         self.n_cached += T
+        if last_only:
+            h = h[:, -1:]
         xn = self._norm(h, self.final_norm)
         if return_hidden:
             return xn
-        return xn @ self.lm_head.t()
+        return self._mm(xn, self.lm_head.t())
 
     @torch.no_grad()
-    def generate_greedy(self, prompt_ids: np.ndarray, max_new_tokens: int, return_logits=False):
-        """prompt_ids int [B, P] -> int32 [B, max_new_tokens] (EOS disabled)."""
+    def generate_greedy(self, prompt_ids: np.ndarray, max_new_tokens: int, return_logits=False, n_logit_steps=None):
+        """prompt_ids int [B, P] -> int32 [B, max_new_tokens] (EOS disabled); with ``return_logits`` also the
+        fp32 logits [B, n_logit_steps or max_new_tokens, V] of the first generated positions."""
         self.reset()
         out, all_logits = [], []
-        logits = self.forward(prompt_ids)[:, -1]
+        n_keep = max_new_tokens if n_logit_steps is None else n_logit_steps
+        logits = self.forward(prompt_ids, last_only=True)[:, -1]
         for _ in range(max_new_tokens):
             nxt = logits.argmax(-1)
             out.append(nxt.numpy().astype(np.int32))
-            if return_logits:
+            if return_logits and len(all_logits) < n_keep:
                 all_logits.append(logits.numpy().copy())
             if len(out) == max_new_tokens:
                 break

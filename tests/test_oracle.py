@@ -94,6 +94,36 @@ def test_qwen2_greedy_matches_transformers(golden_dir):
     assert np.array_equal(toks, g["greedy"])
 
 
+def test_last_only_logits_equal_full_forward():
+    d, ck = _small()
+    m = OracleQwen2(Qwen2Dims(**d.to_dict()), ck, mode="fp32")
+    ids = np.random.default_rng(4).integers(0, d.vocab, (3, 11))
+    full = m.forward(ids).numpy()
+    m.reset()
+    last = m.forward(ids, last_only=True).numpy()
+    assert last.shape == (3, 1, d.vocab) and np.abs(last[:, 0] - full[:, -1]).max() < 1e-5   # BLAS blocking differs with the shape
+
+
+def test_peaked_profile_has_wide_margins_and_walks_the_permutation():
+    """The parity checkpoint: the head row aligned with the residual-carried embedding leads the field by
+    several units (a flat random-init checkpoint has margins below 1e-2 every few dozen steps)."""
+    from vgate_b200.weights import next_token_permutation
+    d = ModelDims(hidden=256, intermediate=512, n_layers=2, n_heads=2, n_kv_heads=1, head_dim=128, vocab=1024,
+                  tie_embeddings=False)
+    ck = synthetic_checkpoint(d, seed=5, profile="peaked")
+    m = OracleQwen2(Qwen2Dims(**d.to_dict()), ck, mode="fp32")
+    prompts = np.random.default_rng(6).integers(0, d.vocab, (4, 9))
+    toks, logits = m.generate_greedy(prompts, 6, return_logits=True)
+    perm = next_token_permutation(d.vocab, 5)
+    assert np.array_equal(toks[:, 0], perm[prompts[:, -1]])
+    assert np.array_equal(toks[:, 1:], perm[toks[:, :-1]])
+    top2 = np.sort(np.partition(logits, -2, axis=-1)[..., -2:], axis=-1)
+    assert (top2[..., 1] - top2[..., 0]).min() > 0.5
+    # the flat profile of the same shape is what the docstring says it is
+    ckf = synthetic_checkpoint(ModelDims(**{**d.to_dict(), "tie_embeddings": True}), seed=5)
+    assert "lm_head.weight" not in ckf and ckf["model.embed_tokens.weight"].std() < 0.03
+
+
 def test_fp16_mode_close_to_fp32():
     d, ck = _small()
     a = OracleQwen2(Qwen2Dims(**d.to_dict()), ck, mode="fp32")

@@ -30,13 +30,20 @@ class ModelDims:
         return asdict(self)
 
 
+PEAKED_EMBED_STD = 1.5       # embedding scale of the ``peaked`` synthetic profile (see synthetic_checkpoint)
+
 # Public HF config.json values.
 QWEN25_1P5B = ModelDims()
 PRESETS = {
     "qwen2.5-1.5b-awq": QWEN25_1P5B,
+    # the same decoder with an untied head: the parity checkpoint (profile "peaked") points the head at a
+    # permutation of the embedding, so greedy decoding walks the vocabulary instead of repeating a token
+    "qwen2.5-1.5b-awq-untied": ModelDims(tie_embeddings=False),
     # reduced-depth / reduced-vocab shapes used by parity tests (same per-layer kernels)
     "qwen2.5-1.5b-awq-l4": ModelDims(n_layers=4),
     "qwen2.5-1.5b-awq-l2-v8k": ModelDims(n_layers=2, vocab=8192),
+    "qwen2.5-1.5b-awq-l2-v8k-untied": ModelDims(n_layers=2, vocab=8192, tie_embeddings=False),
+    "qwen2.5-1.5b-awq-l4-untied": ModelDims(n_layers=4, tie_embeddings=False),
     "tiny-awq": ModelDims(hidden=256, intermediate=512, n_layers=2, n_heads=2, n_kv_heads=1,
                           head_dim=128, vocab=1024),
 }
@@ -56,14 +63,36 @@ def linear_shapes(d: ModelDims):
     ]
 
 
-def synthetic_checkpoint(d: ModelDims, seed: int = 0, w_std: float = 0.02) -> dict:
+def next_token_permutation(vocab: int, seed: int = 0) -> np.ndarray:
+    """The ``peaked`` profile's successor map: token t is followed by ``perm[t]`` (one seeded random
+    permutation of the vocabulary, so greedy decoding walks its cycles)."""
+    return np.random.default_rng(seed + 0x5EED).permutation(vocab).astype(np.int64)
+
+
+def synthetic_checkpoint(d: ModelDims, seed: int = 0, w_std: float = 0.02, profile: str = "flat") -> dict:
     """Seeded random-init AWQ checkpoint (numpy arrays, HF tensor names).
 
     int4 nibbles and zero points are uniform (a uniform random int32 word is
     eight uniform nibbles in any packing order); scales are chosen so that the
     dequantised weights have standard deviation ~``w_std``: (q - z) for uniform
     q, z in [0, 15] has std sqrt(2 * 255 / 12) = 6.52.
+
+    ``profile``:
+      ``flat``    every tensor N(0, w_std^2): the residual stream is all branch output, the logits are
+                  151 936 exchangeable Gaussians (sigma 0.78) and the top-2 margin is below 1e-2 at a few
+                  percent of the steps -- no two correct implementations agree on 32 greedy tokens.  Stress.
+      ``peaked``  the logit statistics of a trained model (one candidate far ahead of the field) with the
+                  same decoder layers: embedding rows have unit scale (PEAKED_EMBED_STD), so the token's own
+                  embedding stays a sizeable part of the residual stream next to the 28 layers' output
+                  (|branches| / |embedding| ~ 2.7: the layers still carry ~88 % of its energy), and the final
+                  norm gain is w_std / PEAKED_EMBED_STD so the logits keep the
+                  flat profile's scale (field sigma 0.78, hence the same absolute error budget).  The head
+                  row aligned with the residual-carried embedding leads the field's maximum by several
+                  units.  With untied embeddings the head is the embedding permuted by
+                  ``next_token_permutation`` (greedy decoding walks a permutation of the vocabulary);
+                  with tied embeddings the leading candidate is the input token itself.
     """
+    assert profile in ("flat", "peaked"), profile
     rng = np.random.default_rng(seed)
     G = d.group_size
     ck = {}
@@ -71,10 +100,18 @@ def synthetic_checkpoint(d: ModelDims, seed: int = 0, w_std: float = 0.02) -> di
     def f16(a):
         return np.asarray(a, dtype=np.float16)
 
-    ck["model.embed_tokens.weight"] = f16(rng.standard_normal((d.vocab, d.hidden), dtype=np.float32) * w_std)
+    peaked = profile == "peaked"
+    e_std = PEAKED_EMBED_STD if peaked else w_std
+    ck["model.embed_tokens.weight"] = f16(rng.standard_normal((d.vocab, d.hidden), dtype=np.float32) * e_std)
     if not d.tie_embeddings:
-        ck["lm_head.weight"] = f16(rng.standard_normal((d.vocab, d.hidden), dtype=np.float32) * w_std)
-    ck["model.norm.weight"] = f16(1.0 + 0.1 * rng.standard_normal(d.hidden, dtype=np.float32))
+        if peaked:
+            head = np.empty_like(ck["model.embed_tokens.weight"])
+            head[next_token_permutation(d.vocab, seed)] = ck["model.embed_tokens.weight"]     # head[perm[t]] = embed[t]
+            ck["lm_head.weight"] = head
+        else:
+            ck["lm_head.weight"] = f16(rng.standard_normal((d.vocab, d.hidden), dtype=np.float32) * w_std)
+    g_final = (w_std / PEAKED_EMBED_STD) if peaked else 1.0
+    ck["model.norm.weight"] = f16(g_final * (1.0 + 0.1 * rng.standard_normal(d.hidden, dtype=np.float32)))
     for i in range(d.n_layers):
         p = f"model.layers.{i}."
         ck[p + "input_layernorm.weight"] = f16(1.0 + 0.1 * rng.standard_normal(d.hidden, dtype=np.float32))
