@@ -36,12 +36,16 @@ def pack_awq(q: np.ndarray) -> np.ndarray:
 
 def dequantize_awq(qweight, qzeros, scales, group_size=128) -> np.ndarray:
     """-> fp16 [K, N] = fp16((q - z) * s)   (awq_triton.py:98-99)."""
-    q = unpack_awq(qweight).astype(np.float16)
-    z = unpack_awq(qzeros).astype(np.float16)
+    q = unpack_awq(qweight)
+    z = unpack_awq(qzeros)
     s = np.asarray(scales, dtype=np.float16)
-    z = np.repeat(z, group_size, axis=0)
-    s = np.repeat(s, group_size, axis=0)
-    return ((q - z) * s).astype(np.float16)
+    K, N = q.shape
+    # Evaluated in fp32 and rounded once: q - z is a small integer and its product with an fp16 scale
+    # (5 x 11 significant bits) is exact in fp32, so the single rounding to fp16 is bit-identical to the
+    # reference's fp16 multiply -- and numpy's fp32 arithmetic is vectorised where its fp16 is emulated.
+    d = q.reshape(K // group_size, group_size, N).astype(np.float32) - z.astype(np.float32)[:, None, :]
+    d *= s.astype(np.float32)[:, None, :]
+    return d.astype(np.float16).reshape(K, N)
 
 
 def awq_linear(x, qweight, qzeros, scales, bias=None, group_size=128):
