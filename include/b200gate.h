@@ -166,31 +166,6 @@ int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, flo
                              const void* bias, int32_t T, int32_t K, int32_t N, int32_t G, int32_t epilogue,
                              int32_t n_splits, int64_t part_stride, void* stream);
 int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits);
-/* Profiling aid: when dev_buf is non-NULL the tcgen05 GEMM writes 8 x uint64 SM-clock stamps per CTA
- * (0 entry, 1 set-up done, 2 first stage complete, 3 last MMA issued, 4 accumulator complete, 5 accumulator
- * staged in shared memory, 6 epilogue done, 7 dependency wait of the activation-TMA warp returned). */
-void b200_debug_umma_trace(void* dev_buf);
-/* Same, restricted to launches whose grid is (grid_x, *, grid_z) -- to pick one projection inside a step. */
-void b200_debug_umma_trace_grid(void* dev_buf, int32_t grid_x, int32_t grid_z);
-/* Same for the attention kernel (0 entry, 1 dependency wait returned and tiles checked, 2 prologue done, 3 first
- * K/V tile landed, 4 scores, 5 softmax, 6 chunk loop end, 7 merge + store done). */
-void b200_debug_attn_trace(void* dev_buf);
-/* Persistent decode kernel: per CTA and phase (layer * 7 + phase) two %globaltimer stamps {work start, arrival};
- * dev_buf: n_ctas * n_layers * 7 * 2 uint64, NULL switches it off.  Read at launch (baked into captured graphs). */
-void b200_debug_mega_trace(void* dev_buf);
-/* Fused decode MLP kernel: 8 x uint64 SM-clock stamps per CTA of the last launch (0 entry, 1 gate_up accumulator
- * complete, 2 gate_up columns published, 3 down accumulator complete, 4 down epilogue done, 5 dependency wait returned,
- * 6 the down unit's column counter reached its target). */
-void b200_debug_mlp_trace(void* dev_buf);
-/* In-situ timeline: while `buf` (device, capacity x 4 uint64) and `counter` (device uint32, zeroed by the
- * caller) are installed, block 0 of every kernel appends {kernel id | grid, entry, ready, exit} in
- * %globaltimer nanoseconds.  NULL buf switches it off.  Works under CUDA-graph replay. */
-void b200_debug_timeline(void* buf, void* counter, uint32_t capacity);
-/* Microbenchmark of the persistent kernel's phase boundary: n_ctas (<= 148) co-resident CTAs run n_phases
- * rounds of {write payload_floats, arrive on a flag, wait for all, read the neighbour CTA's floats}.
- * flags: device, n_phases x uint32; buf: device, 2 * n_ctas * payload_floats floats; sink: device, 1 float. */
-int32_t b200_debug_gridsync_bench(void* flags, int32_t n_phases, float* buf, int32_t payload_floats, int32_t n_ctas,
-                                  float* sink, void* stream);
 /* tcgen05/TMEM GEMM with dense fp16 weights W[N, K] fed by TMA (lm_head); N % 128 == 0, K % 64 == 0. */
 int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T,
                               int32_t K, int32_t N, int32_t accumulate, void* stream);

@@ -1,5 +1,6 @@
 """The C-ABI surface without a GPU: the shared library loads, exports every symbol that
-include/b200gate.h declares, the ctypes table covers the same set, and no compute is needed for that."""
+include/b200gate.h (the boundary) and include/b200gate_debug.h (profiling aids) declare, the ctypes table
+covers the same set, and no compute is needed for that."""
 import ctypes
 import os
 import re
@@ -8,16 +9,21 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "b200gate.h")
+DEBUG_HEADER = os.path.join(ROOT, "include", "b200gate_debug.h")
 
 
-def declared_functions():
-    src = open(HEADER).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", src)))
+def declared_functions(headers=(HEADER, DEBUG_HEADER)):
+    names = set()
+    for h in headers:
+        src = re.sub(r"/\*.*?\*/", "", open(h).read(), flags=re.S)
+        names |= set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", src))
+    return sorted(names)
 
 
 def test_header_declares_the_documented_boundary():
-    names = declared_functions()
+    names = declared_functions((HEADER,))
+    assert not [n for n in names if n.startswith("b200_debug_")]      # profiling aids live in their own header
+    assert all(n.startswith("b200_debug_") for n in declared_functions((DEBUG_HEADER,)))
     for must in ("b200_engine_create", "b200_engine_load_tensor", "b200_engine_finalize", "b200_engine_destroy",
                  "b200_submit", "b200_wait", "b200_poll", "b200_abort", "b200_stats_get", "b200_last_error",
                  "b200_op_awq_dequant", "b200_op_w4_gemv", "b200_op_w4_gemm_umma", "b200_op_f16_gemm_umma",

@@ -136,12 +136,15 @@ class Topology:
                 env = {"VGATE_ROLE": "worker", "VGATE_SERVER__PORT": str(WORKER_PORT_BASE + i)}
                 env.update(self.wenv(i))
                 self.workers.append(_spawn(self.ref, env, os.path.join(self.logs, f"worker-{i}.log"), self.plain))
+            for i, w in enumerate(self.workers):          # /health answers only after load_model (SURVEY appendix A.10)
+                await _wait_healthy(self.endpoints()[i], w, self.ready_timeout)
+            # The gateway starts once the workers answer: a worker that is still loading its model fails the
+            # gateway's health probes (vgate/health_checker.py), is taken out of rotation after failure_threshold
+            # probes and needs success_threshold more rounds of 5 s to come back.
             env = {"VGATE_ROLE": "gateway", "VGATE_SERVER__PORT": str(GATEWAY_PORT),
                    "VGATE_WORKER__ENDPOINTS": json.dumps(self.endpoints())}
             env.update(self.genv)
             self.gateway = _spawn(self.ref, env, os.path.join(self.logs, "gateway.log"), self.plain)
-            for i, w in enumerate(self.workers):          # /health answers only after load_model (SURVEY appendix A.10)
-                await _wait_healthy(self.endpoints()[i], w, self.ready_timeout)
             await _wait_healthy(self.base_url, self.gateway, 60)
             await asyncio.sleep(1.0)                       # the gateway's first health probe
         except BaseException:

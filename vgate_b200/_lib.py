@@ -69,10 +69,7 @@ SIGNATURES = {
     "b200_debug_umma_trace": (None, [_vp]),
     "b200_debug_umma_trace_grid": (None, [_vp, _i32, _i32]),
     "b200_debug_attn_trace": (None, [_vp]),
-    "b200_debug_mega_trace": (None, [_vp]),
-    "b200_debug_mlp_trace": (None, [_vp]),
     "b200_debug_timeline": (None, [_vp, _vp, C.c_uint32]),
-    "b200_debug_gridsync_bench": (_i32, [_vp, _i32, _vp, _i32, _i32, _vp, _vp]),
     "b200_op_f16_gemm_umma": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200_op_lm_head_argmax": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp]),
     "b200_op_f16_gemv": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200gate.so")
-SOURCES = ["ops_basic.cu", "ops_gemv.cu", "ops_attn.cu", "ops_sample.cu", "ops_umma.cu", "ops_mega.cu", "engine.cu"]
+SOURCES = ["ops_basic.cu", "ops_gemv.cu", "ops_attn.cu", "ops_sample.cu", "ops_umma.cu", "engine.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "-Xcompiler", "-pthread",
@@ -23,7 +23,7 @@ def _stale(target, deps):
 def build(verbose=False, force=False):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
-    headers.append(os.path.join(os.path.dirname(HERE), "include", "b200gate.h"))
+    headers += [os.path.join(os.path.dirname(HERE), "include", h) for h in ("b200gate.h", "b200gate_debug.h")]
     srcs = [os.path.join(CSRC, f) for f in SOURCES if os.path.exists(os.path.join(CSRC, f))]
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)

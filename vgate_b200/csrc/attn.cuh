@@ -100,7 +100,7 @@ __device__ __forceinline__ void mma_16816(float d[4], const uint32_t a[4], uint3
 // itself -- so that the bulk copy needs no re-layout and every ldmatrix is bank-conflict free.
 // One unit = one (kv head j, row t, split) of the decode attention; 128 threads (4 warps) cooperate.
 // Called by paged_attn_kernel (one unit per CTA, kBarId 0 = the CTA barrier) and by the persistent
-// decode kernel (ops_mega.cu: warps 0..3 of the CTA, a named barrier, mbarriers that live across units:
+// decode kernel (an experiment that lives in the history, commit 8d75821: warps 0..3 of the CTA, a named barrier, mbarriers that live across units:
 // `bar_uses` counts the completed phases of this warp's barrier; kInitBars = false there).
 template <int kBarId>
 __device__ __forceinline__ void attn_bar_sync() {

@@ -43,7 +43,6 @@ void tl_set_gemv(unsigned long long*, unsigned int*, unsigned int);
 void tl_set_attn(unsigned long long*, unsigned int*, unsigned int);
 void tl_set_sample(unsigned long long*, unsigned int*, unsigned int);
 void tl_set_umma(unsigned long long*, unsigned int*, unsigned int);
-void tl_set_mega(unsigned long long*, unsigned int*, unsigned int);
 
 static double now_s() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -57,12 +56,9 @@ __global__ void advance_decode_kernel(int B, const int32_t* __restrict__ next_id
                                       int32_t* __restrict__ ctx, int32_t* __restrict__ n_gen,
                                       const int32_t* __restrict__ bt_row, const int32_t* __restrict__ block_tables,
                                       int bt_stride, int32_t* __restrict__ out_tokens, int out_stride,
-                                      int32_t* __restrict__ sample_step, unsigned int* __restrict__ phase_flags,
-                                      int n_phase_flags) {
+                                      int32_t* __restrict__ sample_step) {
   const unsigned tl = kernel_prologue(kKidAdvance);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  // the persistent decode kernel of this step expects its phase flags to be zero
-  for (int k = i; k < n_phase_flags; k += gridDim.x * blockDim.x) phase_flags[k] = 0u;
   if (i >= B) return;
   const int tok = next_ids[i];
   const int g = n_gen[i];
@@ -219,30 +215,6 @@ struct b200_engine {
   int debug_skip = getenv("VGATE_B200_DEBUG_SKIP") ? atoi(getenv("VGATE_B200_DEBUG_SKIP")) : 0;
   bool skip(int bit) const { return (debug_skip >> bit) & 1; }
   DevMem parts;                                  // fp32 split-K partials [splits][T][N]
-  // Persistent decode kernel (ops_mega.cu): all layers of a decode step of <= 64 rows in one launch.
-  // Opt-in (VGATE_B200_MEGA=1): measured slower than the per-kernel path so far; same bits.
-  bool mega_ok = false;
-  bool mlp_fused_ok = false;                     // gate_up + down as one dataflow kernel in decode steps (opt-in: VGATE_B200_FUSED_MLP=1; measured 2.5 % slower)
-  int mlp_flag_off = 0, mlp_flags_per_layer = 0; // inside mega_flags: [7 L phase flags][L x I/64 column flags]
-  DevMem mega_layers, mega_flags;
-  int mega_n_flags = 0;
-  int decode_layers(int T) {
-    MegaParams P{};
-    P.layers = mega_layers.as<MegaLayer>(); P.n_layers = L; P.T = T;
-    P.H = H; P.I = I; P.QKV = QKV; P.n_heads = NH; P.n_kv = NKV; P.G = layers[0].lin[0].G;
-    for (int i = 0; i < 4; ++i) P.splits[i] = umma_w4_effective_splits(layers[0].lin[i].K, layers[0].lin[i].G, splits[i]);
-    P.rms_eps = cfg.rms_eps;
-    P.h = h.as<float>(); P.parts = parts.as<float>(); P.xn = xn.as<__half>(); P.attn = attn.as<__half>(); P.act = act.as<__half>();
-    P.pos = d_pos.as<int32_t>(); P.slot = d_slot.as<int32_t>(); P.block_tables = d_bt.as<int32_t>();
-    P.bt_row = d_btrow.as<int32_t>(); P.ctx_len = d_ctx.as<int32_t>(); P.bt_stride = max_blocks_per_seq;
-    P.cos_t = cos_t.as<float>(); P.sin_t = sin_t.as<float>(); P.flags = mega_flags.as<unsigned int>();
-    const CUtensorMap *mxn, *mattn, *mact;
-    int rc;
-    if ((rc = get_map(xn.as<__half>(), Tmax, H, 64, &mxn)) || (rc = get_map(attn.as<__half>(), Tmax, NH * kHeadDim, 64, &mattn)) ||
-        (rc = get_map(act.as<__half>(), Tmax, I, 64, &mact)))
-      return rc;
-    return launch_decode_layers(*mxn, *mattn, *mact, P, stream);
-  }
   DevMem attn_scratch, attn_counters;            // flash-decoding partials + per-(row, kv head) arrival counters
   // KV splits of the decode attention across CTAs.  1: the four warps of a CTA already take different
   // 64-token chunks, and a split count that followed the batch size would make bits batch-dependent.
@@ -307,13 +279,7 @@ struct b200_engine {
     if ((rc = launch_embed(embed.as<__half>(), d_ids.as<int32_t>() + r0, T, H, hh, st))) return rc;
     int pend = 0;                 // split-K partials of the previous projection still to be added into h
     const int64_t pend_stride = (int64_t)T * H;
-    const bool mega = decode_rows && mega_ok && r0 == 0 && T <= 64 && debug_skip == 0 && debug_gemv_mask == 0;
-    if (mega) {
-      if ((rc = decode_layers(T))) return rc;
-      const W4Linear& dn = layers[0].lin[3];
-      pend = umma_w4_effective_splits(dn.K, dn.G, splits[3]);      // down partials of the last layer
-    }
-    for (int l = 0; l < (mega ? 0 : L); ++l) {
+    for (int l = 0; l < L; ++l) {
       LayerWeights& w = layers[l];
       __half* kc = k_cache.as<__half>() + layer_kv_offset(l);
       __half* vc = v_cache.as<__half>() + layer_kv_offset(l);
@@ -343,20 +309,6 @@ struct b200_engine {
       if (!skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st)))
         return rc;
       pend = 0;
-      if (decode_rows && mlp_fused_ok && r0 == 0 && T <= 64 && debug_skip == 0 && debug_gemv_mask == 0) {
-        // gate_up + SwiGLU + down in one launch; down's partials are left pending for the next RMSNorm
-        MlpParams mp{};
-        mp.chunks_gu = w.chunks[2].as<unsigned char>(); mp.chunks_down = w.chunks[3].as<unsigned char>();
-        mp.T = T; mp.H = H; mp.I = I; mp.G = w.lin[3].G;
-        mp.split_down = umma_w4_effective_splits(w.lin[3].K, w.lin[3].G, splits[3]);
-        mp.act = cc; mp.parts = pbuf;
-        mp.flags = mega_flags.as<unsigned int>() + mlp_flag_off + (size_t)l * mlp_flags_per_layer;
-        const CUtensorMap *mxn, *mact;
-        if ((rc = get_map(xx, xrows, H, 64, &mxn)) || (rc = get_map(cc, xrows, I, 64, &mact))) return rc;
-        if ((rc = launch_mlp_fused(*mxn, *mact, mp, st))) return rc;
-        pend = mp.split_down;
-        continue;
-      }
       if (use_umma(T) && !(debug_gemv_mask >> 2 & 1)) {
         if (!skip(5) && (rc = linear(w, 2, xx, xrows, reinterpret_cast<float*>(cc), I, T, false, &np, st, pbuf, decode_rows))) return rc;
       } else {
@@ -370,57 +322,17 @@ struct b200_engine {
     return B200_OK;
   }
 
-  // Decode lanes: the rows of a decode step are cut into n_lanes groups whose layer passes run as
-  // independent kernel chains on separate streams (captured into the same CUDA graph).  A decode step is
-  // bound by the dependent kernel boundaries of one chain (~2.5 us each, 7 per layer), not by HBM or
-  // the SMs, so the chains fill each other's bubbles; the weights of a layer are fetched from HBM by
-  // the first chain and hit the 126 MB L2 for the others.  Bits do not change: every kernel computes
-  // a row independently of the other rows of its launch (the batch-invariance property tested in
-  // tests/test_engine_gpu.py).  MEASURED SLOWER (batch 64: 1.26 ms with 1 lane, 1.52 with 2, 2.24 with 4):
-  // the GEMM kernels are bound by L2->SM traffic (weights + the activation tile every CTA re-reads), which
-  // every extra lane pays again.  Kept as an opt-in experiment: VGATE_B200_LANES=2..4.
-  static constexpr int kMaxLanes = 4;
-  int n_lanes_cfg = getenv("VGATE_B200_LANES") ? std::max(1, std::min(kMaxLanes, atoi(getenv("VGATE_B200_LANES")))) : 1;
-  cudaStream_t lane_stream[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
-  cudaEvent_t lane_fork = nullptr, lane_join[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
-  DevMem lane_parts;                             // split-K partials of lanes 1.. (lane 0 uses `parts`)
-  size_t lane_part_elems = 0;
-  int lanes_for(int T, bool decode_rows) const {
-    if (!decode_rows || mega_ok || !use_umma(T) || lane_part_elems == 0) return 1;
-    return std::max(1, std::min(n_lanes_cfg, T / 16));             // at least 16 rows per lane
-  }
-
   // One forward pass over T token rows whose metadata already sits in the d_* buffers; samples one
   // token for each of the n_rows "last" rows into d_next.  `rows` == nullptr: row r is token r.
   // decode_rows: every row is the single new token of a distinct sequence (enables the fused
   // RoPE + KV-write + split-KV attention kernel).
   int forward(int T, int n_rows, const int32_t* rows, bool decode_rows, bool want_sample = true) {
     int rc;
-    const int nl = lanes_for(T, decode_rows);
-    if (nl == 1) {
+    {
       int pend = 0;
       if ((rc = layers_pass(0, T, decode_rows, stream, parts.as<float>(), &pend))) return rc;
       if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, (int64_t)T * H, final_norm.as<__half>(), cfg.rms_eps,
                                rows, n_rows, H, xn_last.as<__half>(), stream))) return rc;
-    } else {
-      // decode rows: n_rows == T and row r is token r, so each lane normalises its own rows
-      B200_CUDA(cudaEventRecord(lane_fork, stream));
-      const int per = (T + nl - 1) / nl;
-      for (int i = 0; i < nl; ++i) {
-        const int r0 = i * per, Tl = std::min(per, T - r0);
-        if (Tl <= 0) break;
-        cudaStream_t st = i == 0 ? stream : lane_stream[i];
-        float* pbuf = i == 0 ? parts.as<float>() : lane_parts.as<float>() + (size_t)(i - 1) * lane_part_elems;
-        if (i > 0) B200_CUDA(cudaStreamWaitEvent(st, lane_fork, 0));
-        int pend = 0;
-        if ((rc = layers_pass(r0, Tl, true, st, pbuf, &pend))) return rc;
-        if ((rc = launch_rmsnorm(h.as<float>() + (size_t)r0 * H, pbuf, pend, (int64_t)Tl * H, final_norm.as<__half>(),
-                                 cfg.rms_eps, nullptr, Tl, H, xn_last.as<__half>() + (size_t)r0 * H, st))) return rc;
-        if (i > 0) {
-          B200_CUDA(cudaEventRecord(lane_join[i], st));
-          B200_CUDA(cudaStreamWaitEvent(stream, lane_join[i], 0));
-        }
-      }
     }
     const __half* head = cfg.tie_embeddings ? embed.as<__half>() : lm_head_w.as<__half>();
     bool fused = false;
@@ -495,7 +407,7 @@ struct b200_engine {
       B200_CUDA(launch_k(advance_decode_kernel, dim3((n + 127) / 128), dim3(128), 0, stream, n, d_next.as<int32_t>(),
                          d_ids.as<int32_t>(), d_pos.as<int32_t>(), d_slot.as<int32_t>(), d_ctx.as<int32_t>(),
                          d_ngen.as<int32_t>(), d_btrow.as<int32_t>(), d_bt.as<int32_t>(), max_blocks_per_seq,
-                         out_tokens, out_stride, d_step.as<int32_t>(), mega_flags.as<unsigned int>(), mega_n_flags));
+                         out_tokens, out_stride, d_step.as<int32_t>()));
       g_launch_count += 1;
       return forward(n, n, nullptr, true);
     };
@@ -1023,6 +935,16 @@ int32_t b200_engine_finalize(b200_engine* e) {
       }
     }
     B200_CUDA(cudaStreamSynchronize(e->stream));
+    // The GEMV-layout copy (wq / sc / zp) was only the source of the tiling: the tcgen05 family never reads it.
+    // Keeping both layouts resident cost 0.68 GB on the 1.5B model.  (VGATE_B200_DEBUG_GEMV_MASK routes single
+    // projections through the GEMV kernels for debugging and therefore keeps it.)
+    if (e->debug_gemv_mask == 0) {
+      for (auto& w : e->layers)
+        for (int i = 0; i < 4; ++i) {
+          w.wq[i].release(); w.sc[i].release(); w.zp[i].release();
+          w.lin[i].wq = nullptr; w.lin[i].sc = nullptr; w.lin[i].zp = nullptr;
+        }
+    }
   }
   // KV pool
   e->max_blocks_per_seq = (c.max_model_len + 1 + kBlockTokens - 1) / kBlockTokens + 1;
@@ -1069,49 +991,9 @@ int32_t b200_engine_finalize(b200_engine* e) {
       e->splits[i] = sp;
       const int eff = umma_w4_effective_splits(a.K, a.G, sp);
       if (eff > 1) part_elems = std::max(part_elems, (size_t)eff * T * a.N);
-      if (i != 2) part_elems = std::max(part_elems, (size_t)eff * 64 * a.N);    // persistent kernel: always partials
     }
   }
   if ((rc = e->parts.alloc(part_elems * 4))) return rc;
-  if (c.gemm_path != 1) {
-    // decode lanes: partials for up to max_seqs rows per extra lane
-    size_t le = 16;
-    for (int i = 0; i < 4; ++i) {
-      const W4Linear& a = e->layers[0].lin[i];
-      if (i != 2) le = std::max(le, (size_t)umma_w4_effective_splits(a.K, a.G, e->splits[i]) * c.max_seqs * a.N);
-    }
-    e->lane_part_elems = le;
-    if ((rc = e->lane_parts.alloc((size_t)(b200_engine::kMaxLanes - 1) * le * 4))) return rc;
-    B200_CUDA(cudaEventCreateWithFlags(&e->lane_fork, cudaEventDisableTiming));
-    for (int i = 1; i < b200_engine::kMaxLanes; ++i) {
-      B200_CUDA(cudaStreamCreateWithFlags(&e->lane_stream[i], cudaStreamNonBlocking));
-      B200_CUDA(cudaEventCreateWithFlags(&e->lane_join[i], cudaEventDisableTiming));
-    }
-  }
-  {
-    const char* mv = getenv("VGATE_B200_MEGA");
-    e->mega_ok = c.gemm_path != 1 && (mv && atoi(mv) != 0) &&
-                 decode_layers_supported(e->NH, e->NKV, e->layers[0].lin[0].G, 1) && e->H % 128 == 0 && e->QKV % 128 == 0 &&
-                 (2 * e->I) % 128 == 0 && e->I % e->layers[0].lin[0].G == 0;
-    const char* fv = getenv("VGATE_B200_FUSED_MLP");
-    e->mlp_fused_ok = c.gemm_path != 1 && !e->mega_ok && (fv && atoi(fv) != 0) && e->n_lanes_cfg == 1 &&
-                      mlp_fused_supported(1, e->H, e->I, e->layers[0].lin[0].G);
-    e->mlp_flag_off = decode_layers_flag_count(e->L);
-    e->mlp_flags_per_layer = e->I / 64;
-    e->mega_n_flags = e->mlp_flag_off + e->L * e->mlp_flags_per_layer;
-    if ((rc = e->mega_flags.alloc((size_t)e->mega_n_flags * 4)) || (rc = e->mega_layers.alloc((size_t)e->L * sizeof(MegaLayer))))
-      return rc;
-    B200_CUDA(cudaMemset(e->mega_flags.p, 0, e->mega_flags.bytes));
-    std::vector<MegaLayer> tab(e->L);
-    for (int l = 0; l < e->L; ++l) {
-      LayerWeights& w = e->layers[l];
-      for (int i = 0; i < 4; ++i) tab[l].chunks[i] = w.chunks[i].as<unsigned char>();
-      tab[l].bias_qkv = w.bias_qkv.as<__half>(); tab[l].ln1 = w.ln1.as<__half>(); tab[l].ln2 = w.ln2.as<__half>();
-      tab[l].k_cache = e->k_cache.as<__half>() + e->layer_kv_offset(l);
-      tab[l].v_cache = e->v_cache.as<__half>() + e->layer_kv_offset(l);
-    }
-    B200_CUDA(cudaMemcpy(e->mega_layers.p, tab.data(), tab.size() * sizeof(MegaLayer), cudaMemcpyHostToDevice));
-  }
   if ((rc = e->attn_scratch.alloc(attn_scratch_floats(c.max_seqs, e->NH, e->NKV, b200_engine::kDecodeSplits) * 4)) ||
       (rc = e->attn_counters.alloc((size_t)c.max_seqs * e->NKV * 4)))
     return rc;
@@ -1144,15 +1026,10 @@ void b200_engine_destroy(b200_engine* e) {
   }
   for (auto& kv : e->pending) { kv.second.qweight.release(); kv.second.qzeros.release(); kv.second.scales.release(); }
   DevMem* all[] = {&e->embed, &e->lm_head_w, &e->final_norm, &e->cos_t, &e->sin_t, &e->k_cache, &e->v_cache, &e->h,
-                   &e->xn, &e->qkv, &e->qh, &e->attn, &e->gu, &e->act, &e->xn_last, &e->logits, &e->amax, &e->mega_layers, &e->mega_flags, &e->lane_parts, &e->d_ids, &e->d_pos,
+                   &e->xn, &e->qkv, &e->qh, &e->attn, &e->gu, &e->act, &e->xn_last, &e->logits, &e->amax, &e->d_ids, &e->d_pos,
                    &e->d_slot, &e->d_btrow, &e->d_ctx, &e->d_lastrows, &e->d_bt, &e->d_temp, &e->d_topp, &e->d_seed,
                    &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens, &e->parts, &e->attn_scratch, &e->attn_counters, &e->d_tiles};
   for (DevMem* m : all) m->release();
-  if (e->lane_fork) cudaEventDestroy(e->lane_fork);
-  for (int i = 1; i < b200_engine::kMaxLanes; ++i) {
-    if (e->lane_join[i]) cudaEventDestroy(e->lane_join[i]);
-    if (e->lane_stream[i]) cudaStreamDestroy(e->lane_stream[i]);
-  }
   for (int i = 0; i < 2; ++i) {
     if (e->ev_a[i]) cudaEventDestroy(e->ev_a[i]);
     if (e->ev_b[i]) cudaEventDestroy(e->ev_b[i]);
@@ -1377,7 +1254,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
   B200_CUDA(launch_k(advance_decode_kernel, dim3((n_seqs + 127) / 128), dim3(128), 0, s, n_seqs, e->d_next.as<int32_t>(),
                      e->d_ids.as<int32_t>(), e->d_pos.as<int32_t>(), e->d_slot.as<int32_t>(), e->d_ctx.as<int32_t>(),
                      e->d_ngen.as<int32_t>(), e->d_btrow.as<int32_t>(), e->d_bt.as<int32_t>(), e->max_blocks_per_seq,
-                     e->d_out_tokens.as<int32_t>(), max_tokens, e->d_step.as<int32_t>(), (unsigned int*)nullptr, 0));
+                     e->d_out_tokens.as<int32_t>(), max_tokens, e->d_step.as<int32_t>()));
   g_launch_count += 1;
   B200_CUDA(cudaEventRecord(e->ev1, s));
   B200_CUDA(cudaMemcpyAsync(out_ids, e->d_out_tokens.p, (size_t)n_seqs * max_tokens * 4, cudaMemcpyDeviceToHost, s));
@@ -1446,16 +1323,10 @@ int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, flo
 void b200_debug_umma_trace(void* dev_buf) { umma_set_trace((unsigned long long*)dev_buf, 0, 0); }
 void b200_debug_umma_trace_grid(void* dev_buf, int32_t grid_x, int32_t grid_z) { umma_set_trace((unsigned long long*)dev_buf, grid_x, grid_z); }
 void b200_debug_attn_trace(void* dev_buf) { attn_set_trace((unsigned long long*)dev_buf); }
-void b200_debug_mega_trace(void* dev_buf) { decode_layers_set_trace((unsigned long long*)dev_buf); }
-void b200_debug_mlp_trace(void* dev_buf) { mlp_fused_set_trace((unsigned long long*)dev_buf); }
 void b200_debug_timeline(void* buf, void* counter, uint32_t capacity) {
   auto* b = (unsigned long long*)buf; auto* c = (unsigned int*)counter;
   tl_set_engine(b, c, capacity); tl_set_basic(b, c, capacity); tl_set_gemv(b, c, capacity); tl_set_attn(b, c, capacity);
-  tl_set_sample(b, c, capacity); tl_set_umma(b, c, capacity); tl_set_mega(b, c, capacity);
-}
-int32_t b200_debug_gridsync_bench(void* flags, int32_t n_phases, float* buf, int32_t payload_floats, int32_t n_ctas,
-                                  float* sink, void* stream) {
-  return launch_gridsync_bench((unsigned int*)flags, n_phases, buf, payload_floats, n_ctas, sink, (cudaStream_t)stream);
+  tl_set_sample(b, c, capacity); tl_set_umma(b, c, capacity);
 }
 int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits) {
   if (K <= 0 || G <= 0 || K % G != 0 || n_splits < 1) return B200_ERR_INVALID;

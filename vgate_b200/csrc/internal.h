@@ -7,6 +7,7 @@
 #include <string>
 
 #include "../../include/b200gate.h"
+#include "../../include/b200gate_debug.h"
 
 namespace b200 {
 
@@ -106,61 +107,6 @@ int launch_prefill_attn(const __half* q, const __half* k_cache, const __half* v_
                         int bt_stride, const int32_t* tiles, int n_tiles, int n_heads, int n_kv, __half* out,
                         cudaStream_t s);
 size_t attn_scratch_floats(int T, int n_heads, int n_kv, int n_splits);
-// Persistent decode kernel (ops_mega.cu): every layer of one decode step (T <= 64 rows) in one launch.
-struct MegaLayer {                                       // one per layer, in device memory
-  const unsigned char* chunks[4];                        // qkv, o, gate_up (gate/up paired), down in chunk layout
-  const __half* bias_qkv;
-  const __half* ln1;
-  const __half* ln2;
-  __half* k_cache;
-  __half* v_cache;
-};
-
-struct MegaParams {
-  const MegaLayer* layers;
-  int n_layers, T;
-  int H, I, QKV, n_heads, n_kv, G;
-  int splits[4];                                         // requested split-K of qkv, o, gate_up (1), down
-  float rms_eps;
-  float* h;                                              // [T, H] fp32 residual stream (in / out)
-  float* parts;                                          // split-K partials, reused by qkv / o / down
-  __half* xn;
-  __half* attn;
-  __half* act;
-  const int32_t* pos;
-  const int32_t* slot;
-  const int32_t* block_tables;
-  const int32_t* bt_row;
-  const int32_t* ctx_len;
-  int bt_stride;
-  const float* cos_t;
-  const float* sin_t;
-  unsigned int* flags;                                   // [n_layers * 7], zero at launch
-  unsigned long long* trace;                             // debug: [cta][layer * 7 + phase][2] %globaltimer {work start, arrive}
-};
-
-// Fused decode MLP (ops_mega.cu): gate_up + SwiGLU + down in one launch joined by per-column flags.
-struct MlpParams {
-  const unsigned char* chunks_gu;                        // gate/up paired chunk layout
-  const unsigned char* chunks_down;
-  int T, H, I, G;
-  int split_down;                                        // effective split-K of the down projection
-  __half* act;                                           // [T, I] fp16 (written, then read through map_act)
-  float* parts;                                          // [split][T][H] fp32 partials of the down projection
-  unsigned int* flags;                                   // [split_down] counters of published act k tiles, zero at launch
-  unsigned long long* trace;                             // debug: 8 clock64 stamps per CTA (see b200_debug_mlp_trace)
-};
-bool mlp_fused_supported(int T, int H, int I, int G);
-void mlp_fused_set_trace(unsigned long long* dev_buf);
-// maps: xn [rows, H] and act [rows, I], 64-row x 64-column boxes
-int launch_mlp_fused(const CUtensorMap& map_xn, const CUtensorMap& map_act, const MlpParams& P, cudaStream_t s);
-bool decode_layers_supported(int n_heads, int n_kv, int G, int T);
-int decode_layers_flag_count(int n_layers);
-void decode_layers_set_trace(unsigned long long* dev_buf);
-// maps: xn [rows, H], attn [rows, n_heads * 128], act [rows, I] with a 64-row x 64-column box
-int launch_decode_layers(const CUtensorMap& map_xn, const CUtensorMap& map_attn, const CUtensorMap& map_act,
-                         const MegaParams& P, cudaStream_t s);
-int launch_gridsync_bench(unsigned int* flags, int n_phases, float* buf, int payload, int n_ctas, float* sink, cudaStream_t s);
 int launch_swiglu(const float* gu, int T, int I, __half* act, cudaStream_t s);
 int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s);
 // part: float2 {max, bits(argmax)} [n_tiles, ld] from the kUmmaArgmaxF32 epilogue

@@ -5,19 +5,18 @@
 // The weight matrix is the M side so that a 16..256-token batch fills the MMA N dimension and no
 // tensor-core work is wasted on padding; weights stream through exactly once per token tile.
 //
-//   * AWQ int4 weights never touch shared memory as fp16: the packed words of one (128-row tile, quantisation group) plus their
-//     scales and zero points are one contiguous chunk in HBM; a TMA bulk copy (cp.async.bulk) ring
-//     keeps ~50 KB of them in flight per SM, so HBM latency never reaches the math warps.  8
-//     producer warps read the packed words from shared memory, dequantise in registers (lop3
-//     magic-number trick, exact fp16 (q-z)*s) and write the fp16 tile straight into the canonical
-//     K-major SWIZZLE_128B layout that tcgen05.mma consumes (fence.proxy.async, mbarrier arrive).
-//   * dense fp16 weights (tied lm_head): TMA (cp.async.bulk.tensor.2d, SWIZZLE_128B) feeds the same
-//     layout.
+//   * AWQ int4 weights: the packed words of one (128-row tile, quantisation group) plus their scales and zero
+//     points are one contiguous chunk in HBM; one warp keeps a ring of TMA bulk copies (cp.async.bulk) of them in
+//     flight.  16 producer warps (four warpgroups, thread = weight row) read the packed words from shared memory,
+//     dequantise in registers (lop3 magic-number trick, exact fp16 (q - z) * s) and write the fp16 tile to TENSOR
+//     MEMORY with tcgen05.st; the MMA takes its A operand from there (TS mode), so the dequantised weights never
+//     pass through shared memory and the MMA reads only the activation tile from it.
+//   * dense fp16 weights (tied lm_head): TMA (cp.async.bulk.tensor.2d, SWIZZLE_128B) feeds shared memory; SS mode.
 //   * activations: always TMA; rows beyond T are zero-filled by the TMA unit.
-//   * one elected thread issues tcgen05.mma (M=128, N=NT, K=16) x4 per 64-wide k tile;
-//     tcgen05.commit releases the smem stage and, after the last k tile, publishes the accumulator.
-//   * epilogue: tcgen05.ld (32 lanes x 32 bit) -> registers -> fused store / bias / residual add /
-//     split-K partial; 32 lanes write 32 consecutive output features (coalesced).
+//   * one elected thread issues tcgen05.mma (M=128, N=NT, K=16) x4 per 64-wide k tile; one mbarrier per stage
+//     (= one quantisation group); tcgen05.commit releases the stage and, after the last one, publishes the accumulator.
+//   * epilogue: tcgen05.ld -> registers -> fp32 tile staged in shared memory -> 16-byte global stores with the
+//     fused store / bias / residual add / split-K partial / SwiGLU / per-tile argmax.
 //
 // Replaces vLLM's awq_gemm / awq_dequantize+matmul (awq.py:262-286) and the cuBLAS lm_head GEMM.
 #include <mutex>
