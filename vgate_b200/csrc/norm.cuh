@@ -1,5 +1,5 @@
 // Residual-sum + RMSNorm arithmetic shared by rmsnorm_kernel (ops_basic.cu: one 4-CTA cluster per row) and
-// the persistent decode kernel (ops_mega.cu: the four warpgroups of one CTA per row).  A row is cut in
+// the norm tail of the split-K GEMM (ops_umma.cu: the four producer warpgroups of one CTA per row).  A row is cut in
 // four quarters; 128 threads own a quarter; every quarter's warps contribute one partial sum of squares
 // each, and the 16 partials are added in one fixed order, so both callers produce the same bits.
 #pragma once
@@ -14,6 +14,8 @@ constexpr int kNormMaxPerThread = 4;   // H <= 4 quarters * 128 threads * 4 floa
 
 // v = h[row] + sum_p parts[p][row] over this thread's float4s of quarter q (fixed p order), h updated in
 // place when n_parts > 0.  Returns the warp's sum of squares (same value in every lane).
+// kBatch: partial loads in flight per pass (a register budget; the order of the additions does not depend on it).
+template <int kBatch = 16>
 __device__ __forceinline__ float rms_quarter_load(float* __restrict__ h, const float* __restrict__ parts, const int n_parts,
                                                   const int64_t part_stride, const int row, const int q, const int H,
                                                   const int tid, float4 (&v)[kNormMaxPerThread]) {
@@ -28,15 +30,15 @@ __device__ __forceinline__ float rms_quarter_load(float* __restrict__ h, const f
       float4 a = *reinterpret_cast<const float4*>(h + in_off + 4 * i);
       // partials: all loads (up to 16 per batch) are issued before the first add -- one L2 round trip
       // -- then added in the fixed order p = 0, 1, 2, ... so the sum is deterministic
-      for (int p0 = 0; p0 < n_parts; p0 += 16) {
-        float4 b[16];
+      for (int p0 = 0; p0 < n_parts; p0 += kBatch) {
+        float4 b[kBatch];
 #pragma unroll
-        for (int k = 0; k < 16; ++k)
+        for (int k = 0; k < kBatch; ++k)
           b[k] = p0 + k < n_parts
                      ? __ldcg(reinterpret_cast<const float4*>(parts + (size_t)(p0 + k) * part_stride + in_off + 4 * i))
                      : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int k = 0; k < 16; ++k) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
+        for (int k = 0; k < kBatch; ++k) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
       }
       if (n_parts > 0) *reinterpret_cast<float4*>(h + in_off + 4 * i) = a;
       v[it] = a;
