@@ -347,3 +347,40 @@ def test_norm_tail_changes_no_bit(monkeypatch):
         assert np.array_equal(ta, tb)
         assert np.array_equal(la, lb)
     assert out["1"][1] < out["0"][1]              # two norm kernels less per layer and decode step
+
+
+def test_chunked_prefill_interleaves_with_decode_and_changes_nothing(monkeypatch):
+    """Prompts that arrive while other sequences decode are prefilled in chunks that alternate with decode steps
+    (VGATE_B200_PREFILL_CHUNK, here 48 tokens so that a 300-token prompt takes 7 passes): every sequence still
+    produces exactly the tokens it produces alone, prompts cut at arbitrary chunk boundaries included, and the
+    running sequences keep receiving tokens between the chunks."""
+    import time
+    from vgate_b200.engine import Engine
+    dims = PRESETS["qwen2.5-1.5b-awq-l2-v8k"]
+    ckpt = synthetic_checkpoint(dims, seed=6)
+    rng = np.random.default_rng(41)
+    lens = [300, 45, 48, 49, 130, 7]
+    late = [rng.integers(0, dims.vocab, size=n, dtype=np.int32) for n in lens]
+    early = [rng.integers(0, dims.vocab, size=20, dtype=np.int32) for _ in range(4)]
+    monkeypatch.setenv("VGATE_B200_PREFILL_CHUNK", "48")
+    eng = Engine(dims, max_seqs=16, max_model_len=512, max_batch_tokens=256).load_checkpoint(ckpt)
+    try:
+        solo_late = [eng.wait(eng.submit(p, 0.0, 1.0, 10), 10)[0] for p in late]
+        solo_early = [eng.wait(eng.submit(p, 0.0, 1.0, 150), 150)[0] for p in early]
+        st0 = eng.stats()
+        rids_e = [eng.submit(p, 0.0, 1.0, 150) for p in early]
+        while eng.stats()["tokens_generated"] < st0["tokens_generated"] + 40:      # the early ones are decoding
+            time.sleep(0.002)
+        rids_l = [eng.submit(p, 0.0, 1.0, 10) for p in late]
+        out_l = [eng.wait(r, 10)[0] for r in rids_l]
+        out_e = [eng.wait(r, 150)[0] for r in rids_e]
+        st1 = eng.stats()
+    finally:
+        eng.close()
+    for a, b in zip(out_l, solo_late):
+        assert np.array_equal(a, b)
+    for a, b in zip(out_e, solo_early):
+        assert np.array_equal(a, b)
+    # 579 prompt tokens in chunks of <= 48 while four sequences decode: at least 12 prefill passes
+    assert st1["steps_prefill"] - st0["steps_prefill"] >= 12
+    assert st1["kv_blocks_free"] == st1["kv_blocks_total"]

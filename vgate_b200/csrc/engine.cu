@@ -114,6 +114,8 @@ struct Request {
   int seq_slot = -1;
   std::vector<int32_t> blocks;
   std::vector<int32_t> out;
+  int n_prefilled = 0;                         // prompt tokens whose K/V are in the cache (chunked prefill)
+  bool bt_uploaded = false;                    // its block-table row is on the device (blocks never change after admission)
   size_t n_polled = 0;
   double t_submit = 0, t_first = 0, t_last = 0;
 };
@@ -179,7 +181,14 @@ struct b200_engine {
                                                // are in neither `waiting` nor `running` during a prefill pass)
   int64_t next_id = 1;
   std::deque<std::shared_ptr<Request>> waiting;
-  std::vector<std::shared_ptr<Request>> running;
+  std::vector<std::shared_ptr<Request>> prefilling;   // admitted (slot and KV blocks reserved), prompt not fully in the cache yet; FIFO
+  std::vector<std::shared_ptr<Request>> running;      // decoding
+  // Prompt tokens per prefill pass while sequences are decoding: a pass of the whole max_batch_tokens budget
+  // (8192 tokens, ~27 ms) would stall every running sequence for that long on each arrival; with a chunk the
+  // stall is one chunk, and decode steps alternate with the chunks (the policy vLLM's scheduler follows for
+  // vllm_backend.py:105-132 callers).  With nothing decoding the full budget is used.
+  int prefill_chunk = getenv("VGATE_B200_PREFILL_CHUNK") ? std::max(16, atoi(getenv("VGATE_B200_PREFILL_CHUNK"))) : 2048;
+  bool last_step_was_prefill = false;
   std::unordered_map<int64_t, std::shared_ptr<Request>> table;
   b200_stats stats{};
 
@@ -488,6 +497,9 @@ struct b200_engine {
   };
   Inflight inflight;
   int32_t* hp_next[2] = {nullptr, nullptr};        // pinned, max_seqs tokens each
+  int32_t* hp_up[2] = {nullptr, nullptr};          // pinned, 7 x max_seqs words: decode state upload when the batch changes
+  cudaEvent_t ev_up[2] = {nullptr, nullptr};
+  int up_slot = 0;
   cudaEvent_t ev_a[2] = {nullptr, nullptr}, ev_b[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
   bool lookahead_enabled = !(getenv("VGATE_B200_LOOKAHEAD") && atoi(getenv("VGATE_B200_LOOKAHEAD")) == 0);
 
@@ -502,9 +514,15 @@ struct b200_engine {
       greedy_only = greedy_only && batch[r]->temperature < 1e-5f;
     }
     if (idsig != last_decode_ids) {
-      // state BEFORE the advance kernel: last token in d_next, position one behind
-      std::vector<int32_t> next(n), pos(n), btrow(n), step(n), seed(n), bt((size_t)cfg.max_seqs * max_blocks_per_seq, 0);
-      std::vector<float> temp(n), topp(n);
+      // state BEFORE the advance kernel: last token in d_next, position one behind.  Seven small per-row arrays
+      // go through a pinned double buffer (no stream synchronisation: the decode pipeline keeps running while
+      // the host moves on); block-table rows were uploaded when their sequences were admitted.
+      const int k = (up_slot ^= 1);
+      B200_CUDA(cudaEventSynchronize(ev_up[k]));       // the copies that last used this buffer (long done)
+      int32_t* base = hp_up[k];
+      const size_t S = (size_t)cfg.max_seqs;
+      int32_t *next = base, *pos = base + S, *btrow = base + 2 * S, *step = base + 3 * S, *seed = base + 4 * S;
+      float *temp = reinterpret_cast<float*>(base + 5 * S), *topp = reinterpret_cast<float*>(base + 6 * S);
       for (int r = 0; r < n; ++r) {
         Request& q = *batch[r];
         const int n_ctx = (int)q.prompt.size() + (int)q.out.size();
@@ -515,13 +533,11 @@ struct b200_engine {
         seed[r] = (int32_t)q.seed;
         temp[r] = q.temperature;
         topp[r] = q.top_p;
-        std::copy(q.blocks.begin(), q.blocks.end(), bt.begin() + (size_t)q.seq_slot * max_blocks_per_seq);
       }
-      if ((rc = upload_i32(d_next, next)) || (rc = upload_i32(d_pos, pos)) || (rc = upload_i32(d_btrow, btrow)) ||
-          (rc = upload_i32(d_step, step)) || (rc = upload_i32(d_seed, seed)) || (rc = upload_i32(d_bt, bt)) ||
-          (rc = upload_f32(d_temp, temp)) || (rc = upload_f32(d_topp, topp)))
-        return rc;
-      B200_CUDA(cudaStreamSynchronize(stream));      // the host vectors above go out of scope
+      auto up = [&](DevMem& dst, const void* src) { return cudaMemcpyAsync(dst.p, src, (size_t)n * 4, cudaMemcpyHostToDevice, stream); };
+      B200_CUDA(up(d_next, next)); B200_CUDA(up(d_pos, pos)); B200_CUDA(up(d_btrow, btrow)); B200_CUDA(up(d_step, step));
+      B200_CUDA(up(d_seed, seed)); B200_CUDA(up(d_temp, temp)); B200_CUDA(up(d_topp, topp));
+      B200_CUDA(cudaEventRecord(ev_up[k], stream));
       last_decode_ids = idsig;
     }
     const int slot = inflight.slot ^ 1;
@@ -561,7 +577,7 @@ struct b200_engine {
     return B200_OK;
   }
 
-  int run_decode(const std::vector<std::shared_ptr<Request>>& batch) {
+  int run_decode(const std::vector<std::shared_ptr<Request>>& batch, bool allow_ahead) {
     const int n = (int)batch.size();
     std::vector<int64_t> idsig(n);
     for (int r = 0; r < n; ++r) idsig[r] = batch[r]->id;
@@ -569,7 +585,7 @@ struct b200_engine {
     if (inflight.active && inflight.ids != idsig && (rc = collect_decode())) return rc;   // a different batch was ahead
     if (!inflight.active && (rc = launch_decode(batch, idsig, 0))) return rc;
     // look ahead: may step s + 1 start before the tokens of step s are known?
-    bool ahead = lookahead_enabled;
+    bool ahead = lookahead_enabled && allow_ahead;
     for (int r = 0; r < n && ahead; ++r) ahead = (int)batch[r]->out.size() + 1 < batch[r]->max_tokens;
     if (ahead) {
       std::lock_guard<std::mutex> lk(mu);
@@ -589,72 +605,68 @@ struct b200_engine {
     return B200_OK;
   }
 
-  int run_step(const std::vector<std::shared_ptr<Request>>& batch, bool is_prefill) {
-    if (!is_prefill) return run_decode(batch);
+  // One prefill pass: for every chunk the prompt tokens [start, start + count) of its request, K/V written to the
+  // paged cache, attention over everything cached so far (earlier chunks included).  Requests whose prompt ends
+  // in this pass get their first token sampled.  A row's arithmetic depends on its own position and context
+  // only, so a prompt's results do not depend on how it was cut into chunks.
+  struct Chunk { std::shared_ptr<Request> req; int start, count; };
+  int run_prefill(const std::vector<Chunk>& chunks) {
     { int rc0 = collect_decode(); if (rc0) return rc0; }   // a step launched ahead belongs to the running sequences
     last_decode_ids.clear();                         // a prefill pass overwrites the d_* state
-    std::vector<int32_t> ids, pos, slot, btrow, ctx, lastrows, bt, step;
+    std::vector<int32_t> ids, pos, slot, btrow, ctx, lastrows, step, seed;
     std::vector<float> temp, topp;
-    std::vector<int32_t> seed;
-    const int n = (int)batch.size();
-    bt.assign((size_t)cfg.max_seqs * max_blocks_per_seq, 0);
-    int64_t ctx_sum = 0;
+    std::vector<Request*> done;                      // requests whose prompt completes in this pass
+    int rc;
     greedy_only = true;
-    for (int r = 0; r < n; ++r) {
-      Request& q = *batch[r];
-      const int n_ctx = (int)q.prompt.size() + (int)q.out.size();   // tokens known so far
-      const int first = is_prefill ? 0 : n_ctx - 1;
-      for (int p = first; p < n_ctx; ++p) {
-        ids.push_back(p < (int)q.prompt.size() ? q.prompt[p] : q.out[p - q.prompt.size()]);
+    for (const Chunk& c : chunks) {
+      Request& q = *c.req;
+      if (!q.bt_uploaded) {                          // once per sequence: its blocks are reserved for its whole life
+        B200_CUDA(cudaMemcpyAsync(d_bt.as<int32_t>() + (size_t)q.seq_slot * max_blocks_per_seq, q.blocks.data(),
+                                  q.blocks.size() * 4, cudaMemcpyHostToDevice, stream));   // q.blocks outlives the pass
+        q.bt_uploaded = true;
+      }
+      for (int p = c.start; p < c.start + c.count; ++p) {
+        ids.push_back(q.prompt[p]);
         pos.push_back(p);
         slot.push_back(q.blocks[p / kBlockTokens] * kBlockTokens + p % kBlockTokens);
         btrow.push_back(q.seq_slot);
         ctx.push_back(p + 1);
       }
-      ctx_sum += n_ctx;
-      lastrows.push_back((int)ids.size() - 1);
-      greedy_only = greedy_only && q.temperature < 1e-5f;
-      temp.push_back(q.temperature);
-      topp.push_back(q.top_p);
-      seed.push_back((int32_t)q.seed);
-      step.push_back((int32_t)q.out.size());
+      if (c.start + c.count == (int)q.prompt.size()) {
+        done.push_back(&q);
+        lastrows.push_back((int)ids.size() - 1);
+        greedy_only = greedy_only && q.temperature < 1e-5f;
+        temp.push_back(q.temperature);
+        topp.push_back(q.top_p);
+        seed.push_back((int32_t)q.seed);
+        step.push_back(0);
+      }
     }
-    // block tables: only rows of sequences in this batch are read by the kernels
-    for (int r = 0; r < n; ++r) {
-      Request& q = *batch[r];
-      std::copy(q.blocks.begin(), q.blocks.end(), bt.begin() + (size_t)q.seq_slot * max_blocks_per_seq);
-    }
-    const int T = (int)ids.size();
-    int rc;
+    const int T = (int)ids.size(), n = (int)done.size();
     if ((rc = upload_i32(d_ids, ids)) || (rc = upload_i32(d_pos, pos)) || (rc = upload_i32(d_slot, slot)) ||
         (rc = upload_i32(d_btrow, btrow)) || (rc = upload_i32(d_ctx, ctx)) || (rc = upload_i32(d_lastrows, lastrows)) ||
-        (rc = is_prefill ? upload_q_tiles(btrow, ctx) : (n_q_tiles = 0, B200_OK)) ||
-        (rc = upload_i32(d_bt, bt)) || (rc = upload_f32(d_temp, temp)) || (rc = upload_f32(d_topp, topp)) ||
+        (rc = upload_q_tiles(btrow, ctx)) || (rc = upload_f32(d_temp, temp)) || (rc = upload_f32(d_topp, topp)) ||
         (rc = upload_i32(d_seed, seed)) || (rc = upload_i32(d_step, step)))
       return rc;
     const int64_t launches0 = g_launch_count;
     B200_CUDA(cudaEventRecord(ev0, stream));
-    if ((rc = forward(T, n, d_lastrows.as<int32_t>(), !is_prefill))) return rc;
+    if ((rc = forward(T, n, d_lastrows.as<int32_t>(), false, n > 0))) return rc;
     B200_CUDA(cudaEventRecord(ev1, stream));
     std::vector<int32_t> next(n);
-    B200_CUDA(cudaMemcpyAsync(next.data(), d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
-    B200_CUDA(cudaStreamSynchronize(stream));
+    if (n > 0) B200_CUDA(cudaMemcpyAsync(next.data(), d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+    B200_CUDA(cudaStreamSynchronize(stream));        // the host vectors above stay alive until here
     float ms = 0.f;
     B200_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
     const double t = now_s();
     std::lock_guard<std::mutex> lk(mu);
     stats.kernel_launches += g_launch_count - launches0;
-    if (is_prefill) {
-      stats.steps_prefill++; stats.tokens_prefill += T; stats.gpu_seconds_prefill += ms * 1e-3;
-    } else {
-      stats.steps_decode++; stats.gpu_seconds_decode += ms * 1e-3; stats.decode_batch_sum += n;
-      stats.hbm_bytes_decode += decode_step_bytes(n, ctx_sum);
-    }
+    stats.steps_prefill++; stats.tokens_prefill += T; stats.gpu_seconds_prefill += ms * 1e-3;
     stats.tokens_generated += n;
+    for (const Chunk& c : chunks) c.req->n_prefilled = c.start + c.count;
     for (int r = 0; r < n; ++r) {
-      Request& q = *batch[r];
+      Request& q = *done[r];
       q.out.push_back(next[r]);
-      if (q.out.size() == 1) q.t_first = t;
+      q.t_first = t;
       q.t_last = t;
     }
     return B200_OK;
@@ -667,6 +679,7 @@ struct b200_engine {
       if (r.state == ReqState::WAITING || r.state == ReqState::RUNNING) r.state = ReqState::FAILED;
     }
     waiting.clear();
+    prefilling.clear();
     running.clear();
     cv_done.notify_all();
   }
@@ -675,15 +688,17 @@ struct b200_engine {
     cudaSetDevice(cfg.device);
     std::unique_lock<std::mutex> lk(mu);
     while (true) {
-      cv_work.wait(lk, [&] { return stop || (!exclusive && (!waiting.empty() || !running.empty())); });
+      cv_work.wait(lk, [&] { return stop || (!exclusive && (!waiting.empty() || !prefilling.empty() || !running.empty())); });
       if (stop) break;
       // retire aborted requests
-      for (auto it = running.begin(); it != running.end();) {
-        if ((*it)->abort_requested) {
-          (*it)->state = ReqState::ABORTED; release_request_resources(**it); stats.requests_aborted++;
-          if ((*it)->detached) table.erase((*it)->id);
-          it = running.erase(it);
-        } else ++it;
+      for (auto* list : {&running, &prefilling}) {
+        for (auto it = list->begin(); it != list->end();) {
+          if ((*it)->abort_requested) {
+            (*it)->state = ReqState::ABORTED; release_request_resources(**it); stats.requests_aborted++;
+            if ((*it)->detached) table.erase((*it)->id);
+            it = list->erase(it);
+          } else ++it;
+        }
       }
       for (auto it = waiting.begin(); it != waiting.end();) {
         if ((*it)->abort_requested) {
@@ -693,34 +708,49 @@ struct b200_engine {
         } else ++it;
       }
       cv_done.notify_all();
-      // admit: FIFO, whole prompts, within the token budget, with blocks reserved for the full
-      // generation so a running sequence never has to be preempted.
-      std::vector<std::shared_ptr<Request>> admitted;
-      int budget = cfg.max_batch_tokens;
+      // admit: FIFO, a sequence slot and KV blocks reserved for the full generation, so that an admitted
+      // sequence never has to be preempted.
       while (!waiting.empty() && !free_slots.empty()) {
         auto& r = waiting.front();
         const int need_tokens = (int)r->prompt.size() + r->max_tokens;
         const int need_blocks = (need_tokens + kBlockTokens - 1) / kBlockTokens;
-        if ((int)r->prompt.size() > budget && !admitted.empty()) break;
         if ((int)free_blocks.size() < need_blocks) break;
         alloc_blocks(need_blocks, r->blocks);
         r->seq_slot = free_slots.back(); free_slots.pop_back();
         r->state = ReqState::RUNNING;
-        budget -= (int)r->prompt.size();
-        admitted.push_back(r);
+        prefilling.push_back(r);
         waiting.pop_front();
-        if (budget <= 0) break;
       }
-      std::vector<std::shared_ptr<Request>> batch = admitted.empty() ? running : admitted;
-      const bool is_prefill = !admitted.empty();
-      if (batch.empty()) continue;
+      // choose the step: prompt chunks and decode steps alternate while both kinds of work exist
+      const bool do_prefill = !prefilling.empty() && (running.empty() || !last_step_was_prefill);
+      std::vector<Chunk> chunks;
+      std::vector<std::shared_ptr<Request>> batch;
+      if (do_prefill) {
+        int budget = running.empty() ? cfg.max_batch_tokens : std::min(cfg.max_batch_tokens, prefill_chunk);
+        for (auto& r : prefilling) {
+          if (budget <= 0) break;
+          const int take = std::min(budget, (int)r->prompt.size() - r->n_prefilled);
+          chunks.push_back(Chunk{r, r->n_prefilled, take});
+          budget -= take;
+        }
+      } else {
+        batch = running;
+      }
+      if (chunks.empty() && batch.empty()) continue;
+      const bool allow_ahead = prefilling.empty();   // with prompt chunks pending the next step is not a decode step
       stepping = true;
       lk.unlock();
-      const int rc = run_step(batch, is_prefill);
+      const int rc = do_prefill ? run_prefill(chunks) : run_decode(batch, allow_ahead);
       lk.lock();
       stepping = false;
+      last_step_was_prefill = do_prefill;
       if (rc != B200_OK) { inflight = Inflight{}; fail_all(g_last_error); continue; }
-      if (is_prefill) for (auto& r : admitted) running.push_back(r);
+      if (do_prefill) {                              // sequences whose prompt is in the cache start decoding
+        for (auto it = prefilling.begin(); it != prefilling.end();) {
+          if ((*it)->n_prefilled == (int)(*it)->prompt.size()) { running.push_back(*it); it = prefilling.erase(it); }
+          else ++it;
+        }
+      }
       // retire finished sequences
       bool any_done = false;
       for (auto it = running.begin(); it != running.end();) {
@@ -778,6 +808,10 @@ int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
       cudaEventCreate(&e->ev_b[0]) != cudaSuccess || cudaEventCreate(&e->ev_b[1]) != cudaSuccess ||
       cudaEventCreateWithFlags(&e->ev_copied[0], cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&e->ev_copied[1], cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_up[0], cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_up[1], cudaEventDisableTiming) != cudaSuccess ||
+      cudaMallocHost(&e->hp_up[0], (size_t)cfg->max_seqs * 7 * 4) != cudaSuccess ||
+      cudaMallocHost(&e->hp_up[1], (size_t)cfg->max_seqs * 7 * 4) != cudaSuccess ||
       cudaMallocHost(&e->hp_next[0], (size_t)cfg->max_seqs * 4) != cudaSuccess ||
       cudaMallocHost(&e->hp_next[1], (size_t)cfg->max_seqs * 4) != cudaSuccess) {
     set_last_error("cudaStreamCreate/cudaEventCreate failed");
@@ -1066,6 +1100,8 @@ void b200_engine_destroy(b200_engine* e) {
     if (e->ev_b[i]) cudaEventDestroy(e->ev_b[i]);
     if (e->ev_copied[i]) cudaEventDestroy(e->ev_copied[i]);
     if (e->hp_next[i]) cudaFreeHost(e->hp_next[i]);
+    if (e->hp_up[i]) cudaFreeHost(e->hp_up[i]);
+    if (e->ev_up[i]) cudaEventDestroy(e->ev_up[i]);
   }
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
@@ -1179,7 +1215,7 @@ int32_t b200_stats_get(b200_engine* e, b200_stats* out) {
   B200_REQUIRE(e && out, "null argument");
   std::lock_guard<std::mutex> lk(e->mu);
   *out = e->stats;
-  out->running = (int)e->running.size();
+  out->running = (int)(e->running.size() + e->prefilling.size());
   out->waiting = (int)e->waiting.size();
   out->kv_blocks_total = e->n_blocks;
   out->kv_blocks_free = (int)e->free_blocks.size();
@@ -1199,7 +1235,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
   {
     std::unique_lock<std::mutex> lk(e->mu);
     if (!e->fatal.empty()) { set_last_error("engine failed earlier: " + e->fatal); return B200_ERR_CUDA; }
-    if (e->exclusive || e->stepping || e->inflight.active || !e->running.empty() || !e->waiting.empty()) {
+    if (e->exclusive || e->stepping || e->inflight.active || !e->running.empty() || !e->prefilling.empty() || !e->waiting.empty()) {
       set_last_error("generate_batch needs an idle engine");
       return B200_ERR_STATE;
     }
