@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-gateway", action="store_true", help="skip the worker-HTTP / gateway levels (tools/bench_gateway.py)")
     ap.add_argument("--profile", default="peaked", choices=["peaked", "flat"],
                     help="synthetic checkpoint profile (vgate_b200/weights.py); timing does not depend on it, the "
                          "self-check against the oracle needs well-defined greedy tokens")
@@ -295,6 +296,23 @@ def dominant_kernel_roofline(a, dims, hbm_peak, peak_src):
             "timing": f"CUDA events around a graph of {reps} back-to-back launches, mean of 5 replays after 3 warm-up replays"}
 
 
+def gateway_levels(a, world):
+    """tools/bench_gateway.py on this box: `world` b200 workers (CUDA_VISIBLE_DEVICES=i) behind one gateway."""
+    import asyncio
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_gateway", os.path.join(ROOT, "tools", "bench_gateway.py"))
+    bg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bg)
+    ref = bg.find_reference()
+    if ref is None:
+        return {"unavailable": "no V-Gate checkout on this box (tools/bench_gateway.py --stage copies it to baseline/_ref)"}
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    devs = vis.split(",") if vis else [str(i) for i in range(world)]
+    out = asyncio.run(bg.run_b200(ref, os.path.join(ROOT, "gpurun_out", "gateway_logs"), world, a.batch, a.new_tokens, 2,
+                                  a.preset, ["worker_http", "gateway"], devices=devs[:world]))
+    return out
+
+
 def run_b200(a):
     import torch
     import torch.distributed as dist
@@ -390,6 +408,38 @@ def run_b200(a):
                "path": f"B200Backend.generate([prompt], sp) x {a.batch} concurrent threads (one prompt per call, as "
                        "vgate/worker_api.py:112 issues them); continuous batching inside the engine"}
 
+    checks = {}
+    if rank == 0 and not a.no_cpu_baseline and world == 1:
+        # what was timed is also checked: 4 sequences x 8 tokens of the first timed step against the fp32
+        # oracle (the same object the CPU baseline times) -- tokens identical, logits within 2e-2
+        ref = CpuReference(a.preset, a.profile, a.batch, a.prompt_len, a.new_tokens)
+        pr4, tok4 = checked
+        again, logits4, _ = eng.generate_batch(pr4, 8, n_logit_steps=8)
+        ref_toks, ref_logits = ref.fp32().generate_greedy(pr4, 8, return_logits=True)
+        err = float(np.abs(logits4 - np.asarray(ref_logits)).max()) if np.array_equal(again, ref_toks) else float("nan")
+        checks["self_check"] = {"sequences": 4, "tokens": 8, "timed_step_tokens_equal_oracle": bool(np.array_equal(tok4, ref_toks)),
+                              "batch_invariant": bool(np.array_equal(again, tok4)), "logits_max_abs_err": err}
+        assert np.array_equal(tok4, ref_toks), "bench self-check: timed tokens differ from the fp32 oracle"
+        assert np.array_equal(again, tok4), "bench self-check: tokens depend on the batch"
+        assert err < 2e-2, f"bench self-check: logits differ from the fp32 oracle by {err}"
+        checks["cpu_baseline"], _, _ = ref.run(steps=1)
+        del ref
+    # ---- the same workload behind V-Gate: worker HTTP level and ONE gateway in front of `world` workers ----
+    # (north_star: "one worker replica per GPU ... behind one V-Gate gateway").  Unmodified reference processes,
+    # spawned by rank 0 once every rank has released its GPU; skipped when no reference checkout travelled here
+    # (baseline/_ref, git-ignored) or with --no-gateway.
+    levels = None
+    if not a.no_gateway:
+        eng.close()
+        eng = None
+        barrier()
+        if rank == 0:
+            try:
+                levels = gateway_levels(a, world)
+            except Exception as exc:                    # reported, never fatal for the engine-level line
+                levels = {"error": repr(exc)[:300]}
+        barrier()
+
     if rank == 0:
         d_steps = st1["steps_decode"] - st0["steps_decode"]
         d_bytes = st1["hbm_bytes_decode"] - st0["hbm_bytes_decode"]
@@ -411,21 +461,20 @@ def run_b200(a):
         }
         if e2e is not None:
             line["e2e"] = e2e
-        if not a.no_cpu_baseline and world == 1:
-            # what was timed is also checked: 4 sequences x 8 tokens of the first timed step against the fp32
-            # oracle (the same object the CPU baseline times) -- tokens identical, logits within 2e-2
-            ref = CpuReference(a.preset, a.profile, a.batch, a.prompt_len, a.new_tokens)
-            pr4, tok4 = checked
-            again, logits4, _ = eng.generate_batch(pr4, 8, n_logit_steps=8)
-            ref_toks, ref_logits = ref.fp32().generate_greedy(pr4, 8, return_logits=True)
-            err = float(np.abs(logits4 - np.asarray(ref_logits)).max()) if np.array_equal(again, ref_toks) else float("nan")
-            line["self_check"] = {"sequences": 4, "tokens": 8, "timed_step_tokens_equal_oracle": bool(np.array_equal(tok4, ref_toks)),
-                                  "batch_invariant": bool(np.array_equal(again, tok4)), "logits_max_abs_err": err}
-            assert np.array_equal(tok4, ref_toks), "bench self-check: timed tokens differ from the fp32 oracle"
-            assert np.array_equal(again, tok4), "bench self-check: tokens depend on the batch"
-            assert err < 2e-2, f"bench self-check: logits differ from the fp32 oracle by {err}"
-            line["cpu_baseline"], _, _ = ref.run(steps=1)
-            del ref
+        if levels is not None:
+            if "error" in levels or "unavailable" in levels:
+                line["gateway"] = levels
+            else:
+                line["worker_http"] = levels["worker_http_multi"]
+                line["worker_http_single_prompt_bodies"] = levels["worker_http_single"]
+                line["gateway"] = levels["gateway"]
+                lv = {"engine_c_abi": value, "backend_threads": e2e["value"] if e2e else None,
+                      "worker_http": levels["worker_http_multi"]["tok_per_s"], "gateway": levels["gateway"]["tok_per_s"]}
+                line["levels_tok_per_s"] = lv
+                line["binding_level"] = ("gateway (CPU control plane: one event loop, one thread per in-flight request)"
+                                         if lv["gateway"] < 0.9 * lv["worker_http"] else
+                                         "worker HTTP" if lv["worker_http"] < 0.9 * lv["engine_c_abi"] else "engine")
+        line.update(checks)
         # informational: the reference's own GPU path (vLLM) measured once on this pool, same checkpoint and
         # workload, by tools/vllm_b200_baseline.py -- a recorded number, not re-measured by this run
         try:
@@ -437,7 +486,8 @@ def run_b200(a):
         except Exception:   # noqa: BLE001
             pass
         print(json.dumps(line), flush=True)
-    eng.close()
+    if eng is not None:
+        eng.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -270,11 +270,12 @@ async def run_config1(ref_dir, log_dir, latency_ms=None):
             "cores": os.cpu_count(), "gateway": s, "raw": res}
 
 
-async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, levels):
+async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, levels, devices=None):
     threads = n_gpus * batch + 64
+    devices = devices or [str(i) for i in range(n_gpus)]
 
     def wenv(i):
-        return {"CUDA_VISIBLE_DEVICES": str(i), "VGATE_MODEL__ENGINE_TYPE": "b200", "VGATE_DRY_RUN": "false",
+        return {"CUDA_VISIBLE_DEVICES": devices[i], "VGATE_MODEL__ENGINE_TYPE": "b200", "VGATE_DRY_RUN": "false",
                 "VGATE_B200_SYNTHETIC": preset, "VGATE_B200_MAX_SEQS": str(max(batch, 64)),
                 "VGATE_MODEL__MAX_MODEL_LEN": str(128 + max_tokens + 16)}
 
