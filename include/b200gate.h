@@ -121,6 +121,10 @@ int32_t b200_poll(b200_engine* e, int64_t rid, int32_t* out_ids, int32_t cap, in
  * already blocked in b200_wait / b200_poll on it gets B200_ERR_ABORTED). */
 int32_t b200_abort(b200_engine* e, int64_t rid);
 int32_t b200_stats_get(b200_engine* e, b200_stats* out);
+/* Liveness for health probes: B200_OK while the engine serves; B200_ERR_CUDA (b200_last_error() = the first
+ * failure) once a CUDA error has poisoned it and every request was failed.  What /health should report and the
+ * reference's unconditional route cannot (main.py:288-295; probed by vgate/health_checker.py:307-312). */
+int32_t b200_engine_status(b200_engine* e);
 
 /* Synchronous batch generate on the engine's stream for benchmarks and parity tests:
  * all prompts have the same length, greedy, exactly max_tokens each, device-resident

@@ -29,6 +29,9 @@ async def _serve():
         asyncio.get_running_loop().set_default_executor(ThreadPoolExecutor(n, thread_name_prefix="vgate-call"))
     import vgate_b200.register  # noqa: F401  (before main builds its config / engine)
     import main                 # the reference's module, untouched
+    if main.IS_WORKER and os.environ.get("VGATE_B200_WORKER_EXTRAS", "1") != "0":
+        from vgate_b200.worker_stream import install
+        install(main.app, main)                   # /internal/stream and a /health that reflects engine liveness
     import uvicorn
     cfg = uvicorn.Config(main.app, host=main.config.server.host, port=main.config.server.port, log_level="warning")
     await uvicorn.Server(cfg).serve()

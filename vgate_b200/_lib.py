@@ -58,6 +58,7 @@ SIGNATURES = {
     "b200_poll": (_i32, [_vp, _i64, _vp, _i32, _pi32, _pi32, _i32]),
     "b200_abort": (_i32, [_vp, _i64]),
     "b200_stats_get": (_i32, [_vp, C.POINTER(Stats)]),
+    "b200_engine_status": (_i32, [_vp]),
     "b200_generate_batch": (_i32, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _i32, _pf64]),
     "b200_op_awq_repack": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "b200_op_awq_dequant": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),

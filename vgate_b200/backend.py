@@ -144,6 +144,13 @@ class B200Backend:
             if not finished:          # generator closed mid-way (client disconnect, main.py:372-376)
                 self.engine.abort(rid)
 
+    def healthy(self):
+        """(ok, reason): False once the engine has hit a CUDA error and failed its requests (it accepts no new
+        ones); read by the worker's /health (vgate_b200/worker_stream.py) so that probes see a dead engine."""
+        if self.engine is None:
+            return False, "engine not loaded"
+        return self.engine.status()
+
     def shutdown(self) -> None:
         if self.engine is not None:
             self.engine.close()

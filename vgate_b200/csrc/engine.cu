@@ -1222,6 +1222,14 @@ int32_t b200_stats_get(b200_engine* e, b200_stats* out) {
   return B200_OK;
 }
 
+int32_t b200_engine_status(b200_engine* e) {
+  B200_REQUIRE(e, "null engine");
+  std::lock_guard<std::mutex> lk(e->mu);
+  if (!e->fatal.empty()) { set_last_error("engine failed: " + e->fatal); return B200_ERR_CUDA; }
+  if (!e->finalized) { set_last_error("engine not finalized"); return B200_ERR_STATE; }
+  return B200_OK;
+}
+
 int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n_seqs, int32_t n_prompt,
                             int32_t max_tokens, int32_t* out_ids, float* logits_out, int32_t n_logit_steps,
                             double* gpu_seconds) {

@@ -85,6 +85,13 @@ class Engine:
     def abort(self, rid: int):
         self._lib.b200_abort(self._h, rid)
 
+    def status(self):
+        """(True, "") while the engine can serve; (False, reason) once it is poisoned or closed."""
+        if getattr(self, "_h", None) is None or not self._h:
+            return False, "engine closed"
+        code = self._lib.b200_engine_status(self._h)
+        return (True, "") if code == 0 else (False, self._lib.b200_last_error().decode("utf-8", "replace"))
+
     def stats(self) -> dict:
         s = _lib.Stats()
         _lib.check(self._lib.b200_stats_get(self._h, C.byref(s)))

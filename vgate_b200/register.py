@@ -33,6 +33,11 @@ _orig_create = _eng._create_backend
 
 
 def _create_backend(engine_type, worker_config=None):
+    import os
+    if worker_config is not None and _eng._is_remote(worker_config) and os.environ.get("VGATE_B200_REMOTE") == "coalesce":
+        # gateway side: the coalescing / streaming worker hop instead of the reference's RemoteBackend
+        from vgate_b200.remote import CoalescingRemoteBackend
+        return CoalescingRemoteBackend(worker_config)
     if engine_type == "b200" and not (worker_config is not None and _eng._is_remote(worker_config)) and not _eng.DRY_RUN:
         from vgate_b200 import B200Backend
         return B200Backend()
