@@ -48,6 +48,7 @@ extern "C" {
 #define B200_DTYPE_F16 0
 #define B200_DTYPE_I32 1
 #define B200_DTYPE_F32 2
+#define B200_DTYPE_BF16 3
 
 #define B200_ABI_VERSION 1
 
@@ -75,7 +76,11 @@ typedef struct b200_config {
   int32_t eos_token_id;    /* -1 disables EOS (synthetic checkpoints) */
   int32_t use_cuda_graphs; /* 1: capture the decode step per batch bucket */
   int32_t gemm_path;       /* 0 auto, 1 force CUDA-core GEMV, 2 force tcgen05 GEMM */
-  int32_t reserved[8];
+  int32_t act_dtype;       /* 16-bit storage of activations, KV cache, norm weights, biases, embeddings: B200_DTYPE_F16 (default)
+                              or B200_DTYPE_BF16 */
+  int32_t dense_weights;   /* 0: AWQ int4 linears (qweight / qzeros / scales, fp16 activations only);
+                              1: dense 16-bit linears ("...proj.weight" [out, in] in act_dtype) -- Qwen2.5-7B/14B bf16 */
+  int32_t reserved[6];
 } b200_config;
 
 typedef struct b200_stats {

@@ -9,7 +9,7 @@ ABI_VERSION = 1
 
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOT_FOUND, ERR_ABORTED = -1, -2, -3, -4, -5, -6
-DTYPE_F16, DTYPE_I32, DTYPE_F32 = 0, 1, 2
+DTYPE_F16, DTYPE_I32, DTYPE_F32, DTYPE_BF16 = 0, 1, 2, 3
 
 
 class B200Error(RuntimeError):
@@ -25,7 +25,8 @@ class Config(C.Structure):
         ("vocab", C.c_int32), ("group_size", C.c_int32), ("tie_embeddings", C.c_int32), ("rms_eps", C.c_float),
         ("rope_theta", C.c_float), ("max_seqs", C.c_int32), ("max_model_len", C.c_int32),
         ("max_batch_tokens", C.c_int32), ("kv_bytes", C.c_int64), ("eos_token_id", C.c_int32),
-        ("use_cuda_graphs", C.c_int32), ("gemm_path", C.c_int32), ("reserved", C.c_int32 * 8),
+        ("use_cuda_graphs", C.c_int32), ("gemm_path", C.c_int32), ("act_dtype", C.c_int32), ("dense_weights", C.c_int32),
+        ("reserved", C.c_int32 * 6),
     ]
 
 

@@ -74,6 +74,7 @@ struct AttnParams {
   float* scratch;                // [T, n_kv, n_splits, GQ, 130]
   int32_t* counters;             // [T, n_kv], zero before and after every launch
   __half* out;                   // [T, nh * 128]
+  int bf16;                      // 16-bit storage type of q / K / V / out: 0 fp16, 1 bf16
 };
 
 __device__ __forceinline__ void ldmatrix_x4(uint32_t saddr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
@@ -84,11 +85,16 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t saddr, uint32_t& r0, 
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(saddr));
 }
-// D (fp32, 16x8) += A (fp16, 16x16, row) * B (fp16, 16x8, col)
-__device__ __forceinline__ void mma_16816(float d[4], const uint32_t a[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+// D (fp32, 16x8) += A (16-bit, 16x16, row) * B (16-bit, 16x8, col); bf (uniform per launch) selects bf16 operands
+__device__ __forceinline__ void mma_16816(float d[4], const uint32_t a[4], uint32_t b0, uint32_t b1, const bool bf = false) {
+  if (bf)
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  else
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
 // One warp scores whole 64-token chunks with tensor-core MMAs (mma.sync m16n8k16; the 6..8 query
@@ -125,8 +131,9 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
   const int warp = tid >> 5, lane = tid & 31;
   if (tr && tid == 0) tr[0] = clock64();
   const int n_heads = p.n_heads, n_kv = p.n_kv, S = p.n_splits;
+  const bool bf = p.bf16 != 0;
   unsigned char* q_s = smem + L::kOffQ;
-  __half* new_s = reinterpret_cast<__half*>(smem + L::kOffNew);
+  uint16_t* new_s = reinterpret_cast<uint16_t*>(smem + L::kOffNew);
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + L::kOffBar) + warp;
   unsigned char* Kt = smem + L::kOffTiles + warp * 2 * kTileBytes;
   unsigned char* Vt = Kt + kTileBytes;
@@ -186,7 +193,7 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
     cols[2 * kPairs + 1] = (n_heads + j) * kHeadDim + (tid & 63);            // k (first half of the pair)
     cols[2 * kPairs + 2] = cols[2 * kPairs + 1] + 64;
 #pragma unroll
-    for (int e = 0; e < NE; ++e) bia[e] = p.bias ? __half2float(p.bias[cols[e]]) : 0.f;
+    for (int e = 0; e < NE; ++e) bia[e] = p.bias ? from16(reinterpret_cast<const uint16_t*>(p.bias)[cols[e]], bf) : 0.f;
     if constexpr (kPreWait) {
       const int len0 = __ldcg(p.ctx_len + t);
       if (len0 > 0) load_rope(len0 - 1);
@@ -195,7 +202,7 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
   if constexpr (kPreWait) grid_dep_wait();          // from here on the upstream kernels' results are visible
 
   const int len = kPreWait ? __ldcg(p.ctx_len + t) : p.ctx_len[t];
-  __half* orow = p.out + ((size_t)t * n_heads + (size_t)j * GQ) * kHeadDim;
+  uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + ((size_t)t * n_heads + (size_t)j * GQ) * kHeadDim;
   const int nchunks = len > 0 ? (len + kChunkTokens - 1) / kChunkTokens : 0;
   const int n_active = min(S, nchunks);
   const int32_t* bt = p.block_tables + (size_t)(kPreWait ? __ldcg(p.bt_row + t) : p.bt_row[t]) * p.bt_stride;
@@ -231,7 +238,7 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
   if (len <= 0) {
     if (split == 0) {
 #pragma unroll
-      for (int h = 0; h < GQ; ++h) orow[h * kHeadDim + tid] = __float2half_rn(0.f);
+      for (int h = 0; h < GQ; ++h) orow[h * kHeadDim + tid] = 0;
     }
     return;
   }
@@ -279,24 +286,24 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
         const int h = idx >> 6, i = idx & 63;
         float r1, r2;
         rope_rotate(val[2 * q3], val[2 * q3 + 1], cs[q3], sn[q3], r1, r2);
-        *reinterpret_cast<__half*>(q_addr(h, i)) = __float2half_rn(r1);
-        *reinterpret_cast<__half*>(q_addr(h, i + 64)) = __float2half_rn(r2);
+        *reinterpret_cast<uint16_t*>(q_addr(h, i)) = to16(r1, bf);
+        *reinterpret_cast<uint16_t*>(q_addr(h, i + 64)) = to16(r2, bf);
       }
     }
     if (own) {
-      const __half vnew = __float2half_rn(val[2 * kPairs]);
+      const uint16_t vnew = to16(val[2 * kPairs], bf);
       new_s[kHeadDim + tid] = vnew;
       float r1, r2;
       rope_rotate(val[2 * kPairs + 1], val[2 * kPairs + 2], cs[kPairs], sn[kPairs], r1, r2);
-      const __half k1 = __float2half_rn(r1), k2 = __float2half_rn(r2);
+      const uint16_t k1 = to16(r1, bf), k2 = to16(r2, bf);
       if (tid < 64) { new_s[tid] = k1; new_s[tid + 64] = k2; }
       if (sl >= 0) {                                // paged cache write (swizzled row)
         const int r = sl % kBlockTokens;
         const size_t rowoff = (((size_t)(sl / kBlockTokens) * n_kv + j) * kBlockTokens + r) * kHeadDim;
-        p.v_cache[rowoff + kv_swz(r, tid)] = vnew;
+        reinterpret_cast<uint16_t*>(p.v_cache)[rowoff + kv_swz(r, tid)] = vnew;
         if (tid < 64) {
-          p.k_cache[rowoff + kv_swz(r, tid)] = k1;
-          p.k_cache[rowoff + kv_swz(r, tid + 64)] = k2;
+          reinterpret_cast<uint16_t*>(p.k_cache)[rowoff + kv_swz(r, tid)] = k1;
+          reinterpret_cast<uint16_t*>(p.k_cache)[rowoff + kv_swz(r, tid + 64)] = k2;
         }
       }
     }
@@ -375,9 +382,9 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
           ldmatrix_x4(rowaddr + ((((4 * k2 + mj) ^ (tok & 7))) << 4), kb[nt][0], kb[nt][1], kb[nt][2], kb[nt][3]);
         }
 #pragma unroll
-        for (int nt = 0; nt < 8; ++nt) mma_16816(d[nt], qa[2 * k2], kb[nt][0], kb[nt][1]);
+        for (int nt = 0; nt < 8; ++nt) mma_16816(d[nt], qa[2 * k2], kb[nt][0], kb[nt][1], bf);
 #pragma unroll
-        for (int nt = 0; nt < 8; ++nt) mma_16816(d[nt], qa[2 * k2 + 1], kb[nt][2], kb[nt][3]);
+        for (int nt = 0; nt < 8; ++nt) mma_16816(d[nt], qa[2 * k2 + 1], kb[nt][2], kb[nt][3], bf);
       }
 #pragma unroll
       for (int nt = 0; nt < 8; ++nt) {
@@ -402,7 +409,7 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
     for (int nt = 0; nt < 8; ++nt) {
       const float p0 = expf(__fsub_rn(sc[nt][0], m_new)), p1 = expf(__fsub_rn(sc[nt][1], m_new));
       sum = __fadd_rn(sum, __fadd_rn(p0, p1));
-      pa[nt >> 1][(nt & 1) * 2] = pack_half2(p0, p1);
+      pa[nt >> 1][(nt & 1) * 2] = pack16x2(p0, p1, bf);
       pa[nt >> 1][(nt & 1) * 2 + 1] = 0u;
     }
     sum += __shfl_xor_sync(0xffffffffu, sum, 1);
@@ -427,10 +434,10 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
 #pragma unroll
         for (int d2 = 0; d2 < 8; ++d2) {
           float d[4] = {o[2 * d2][0], o[2 * d2][1], 0.f, 0.f};
-          mma_16816(d, pa[kt], vb[d2][0], vb[d2][1]);
+          mma_16816(d, pa[kt], vb[d2][0], vb[d2][1], bf);
           o[2 * d2][0] = d[0]; o[2 * d2][1] = d[1];
           float e[4] = {o[2 * d2 + 1][0], o[2 * d2 + 1][1], 0.f, 0.f};
-          mma_16816(e, pa[kt], vb[d2][2], vb[d2][3]);
+          mma_16816(e, pa[kt], vb[d2][2], vb[d2][3], bf);
           o[2 * d2 + 1][0] = e[0]; o[2 * d2 + 1][1] = e[1];
         }
       }
@@ -485,7 +492,7 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
   }
   if (n_active == 1) {                              // single split: finished
 #pragma unroll
-    for (int h = 0; h < GQ; ++h) orow[h * kHeadDim + tid] = __float2half_rn(num[h] / den[h]);
+    for (int h = 0; h < GQ; ++h) orow[h * kHeadDim + tid] = to16(num[h] / den[h], bf);
     return;
   }
 
@@ -531,7 +538,7 @@ __device__ __forceinline__ void paged_attn_unit(const AttnParams& p, unsigned ch
           de = fmaf(__ldcg(ps + kHeadDim + 1), pl[h][k], de);
         }
     }
-    orow[h * kHeadDim + tid] = __float2half_rn(nu / de);
+    orow[h * kHeadDim + tid] = to16(nu / de, bf);
   }
 }
 

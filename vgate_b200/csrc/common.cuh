@@ -1,5 +1,6 @@
 // Shared device helpers for libb200gate (sm_100a only).
 #pragma once
+#include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -97,6 +98,25 @@ __device__ __forceinline__ uint32_t pack_half2(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// ---- 16-bit activation / weight storage: fp16 (the AWQ path) or bf16 (dense checkpoints) -----------------------
+// `bf` is uniform per launch; the arrays are typed __half* either way (16-bit storage).
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint32_t pack16x2(float a, float b, bool bf) { return bf ? pack_bf16x2(a, b) : pack_half2(a, b); }
+__device__ __forceinline__ uint16_t to16(float a, bool bf) {
+  if (bf) { const __nv_bfloat16 h = __float2bfloat16_rn(a); return *reinterpret_cast<const uint16_t*>(&h); }
+  const __half h = __float2half_rn(a);
+  return *reinterpret_cast<const uint16_t*>(&h);
+}
+__device__ __forceinline__ float from16(uint16_t v, bool bf) {
+  return bf ? __uint_as_float((uint32_t)v << 16) : __half2float(*reinterpret_cast<const __half*>(&v));
+}
+__device__ __forceinline__ float2 unpack16x2(uint32_t w, bool bf) {
+  if (bf) return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+  return __half22float2(*reinterpret_cast<const __half2*>(&w));
+}
 
 // ---- shared-memory addresses, mbarrier, bulk async copies (TMA 1-D) ---------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

@@ -93,6 +93,7 @@ struct LayerWeights {
   W4Linear lin[4];
   DevMem chunks[4];                // same linears in the chunk layout the tcgen05 GEMM streams
   UmmaW4 ulin[4];
+  DevMem dense[4];                 // dense checkpoints: W[N, K] 16-bit (qkv fused row-wise, gate/up paired per 128-row tile)
 };
 
 struct PendingLinear {             // raw checkpoint tensors waiting for their siblings
@@ -133,6 +134,8 @@ struct b200_engine {
 
   // ---- model ----
   int H = 0, I = 0, L = 0, NH = 0, NKV = 0, V = 0, G = 0, QKV = 0;
+  bool bf16 = false;                           // 16-bit storage type (cfg.act_dtype)
+  bool dense = false;                          // dense 16-bit linears instead of AWQ int4 (cfg.dense_weights)
   std::vector<LayerWeights> layers;
   DevMem embed, lm_head_w, final_norm;
   std::map<std::string, PendingLinear> pending;
@@ -198,7 +201,7 @@ struct b200_engine {
   // One GEMM kernel family per engine, whatever the token count: a sequence's bits must not depend
   // on how many other sequences share its step (continuous batching).  gemm_path 1 selects the
   // CUDA-core GEMV family (small-batch workers), anything else the tcgen05 GEMM.
-  bool use_umma(int T) const { (void)T; return cfg.gemm_path != 1; }
+  bool use_umma(int T) const { (void)T; return dense || cfg.gemm_path != 1; }
 
   // TMA descriptors for the (fixed) activation buffers, one per (buffer, token-tile height).
   std::map<std::pair<const void*, int>, CUtensorMap> tmaps;
@@ -232,7 +235,12 @@ struct b200_engine {
     if (!norm_tail_enabled || !use_umma(T) || debug_skip != 0 || debug_gemv_mask != 0) return false;
     for (int i : {1, 3}) {
       const W4Linear& a = layers[0].lin[i];
-      if (umma_w4_effective_splits(a.K, a.G, splits[i]) < 2 || !umma_norm_tail_ok(T, a.K, a.N, a.G, splits[i], cfg.device)) return false;
+      if (dense) {
+        if (umma_dense_effective_splits(a.K, splits[i]) < 2 || umma_pick_nt(T, false) < T ||
+            !umma_dense_norm_tail_ok(T, a.K, a.N, splits[i], cfg.device)) return false;
+      } else if (umma_w4_effective_splits(a.K, a.G, splits[i]) < 2 || !umma_norm_tail_ok(T, a.K, a.N, a.G, splits[i], cfg.device)) {
+        return false;
+      }
     }
     return true;
   }
@@ -253,6 +261,21 @@ struct b200_engine {
              int* n_parts_out, cudaStream_t st, float* pbuf, bool split_k, const UmmaNormTail* tail = nullptr) {
     const W4Linear& w = lw.lin[i];
     *n_parts_out = 0;
+    if (dense) {
+      const int nt = umma_pick_nt(T, false);
+      const CUtensorMap *mx, *mw;
+      int rc;
+      if ((rc = get_map(x, x_rows, w.K, nt, &mx)) || (rc = get_map(lw.dense[i].p, w.N, w.K, 128, &mw))) return rc;
+      const int ns = split_k ? umma_dense_effective_splits(w.K, splits[i]) : 1;
+      if (ns > 1) {
+        *n_parts_out = tail ? 0 : ns;
+        return launch_umma_f16(*mw, w.K, w.N, *mx, nt, T, pbuf, w.N, kUmmaPartialF32, st, ns, (int64_t)T * w.N, nullptr, bf16, tail);
+      }
+      if (tail) { set_last_error("norm tail requested for a projection that is not split"); return B200_ERR_STATE; }
+      if (i == 2) return launch_umma_f16(*mw, w.K, w.N, *mx, nt, T, y, ldy, kUmmaSwigluF16, st, 1, 0, nullptr, bf16);
+      return launch_umma_f16(*mw, w.K, w.N, *mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, st, 1, 0,
+                             accumulate ? nullptr : w.bias, bf16);
+    }
     if (!use_umma(T) || (debug_gemv_mask >> i & 1)) return launch_w4_gemv(w, x, w.K, y, ldy, T, accumulate, st);
     const int nt = umma_pick_nt(T, true);
     const CUtensorMap* mx;
@@ -273,7 +296,7 @@ struct b200_engine {
   // of writing logits; the caller finishes with launch_argmax_reduce.
   int lm_head(const __half* head, int n_rows, bool want_argmax, bool* fused_argmax) {
     *fused_argmax = false;
-    if (!use_umma(n_rows) || V % 128 != 0 || (debug_gemv_mask >> 4 & 1))
+    if (!bf16 && (!use_umma(n_rows) || V % 128 != 0 || (debug_gemv_mask >> 4 & 1)))
       return launch_f16_gemv(head, xn_last.as<__half>(), H, logits.as<float>(), V, n_rows, H, V, false, stream);
     const int nt = umma_pick_nt(n_rows, false);
     const CUtensorMap *mx, *mw;
@@ -281,9 +304,9 @@ struct b200_engine {
     if ((rc = get_map(xn_last.as<__half>(), cfg.max_seqs, H, nt, &mx)) || (rc = get_map(head, V, H, 128, &mw))) return rc;
     if (want_argmax) {
       *fused_argmax = true;
-      return launch_umma_f16(*mw, H, V, *mx, nt, n_rows, amax.as<float>(), cfg.max_seqs, kUmmaArgmaxF32, stream);
+      return launch_umma_f16(*mw, H, V, *mx, nt, n_rows, amax.as<float>(), cfg.max_seqs, kUmmaArgmaxF32, stream, 1, 0, nullptr, bf16);
     }
-    return launch_umma_f16(*mw, H, V, *mx, nt, n_rows, logits.as<float>(), V, kUmmaStoreF32, stream);
+    return launch_umma_f16(*mw, H, V, *mx, nt, n_rows, logits.as<float>(), V, kUmmaStoreF32, stream, 1, 0, nullptr, bf16);
   }
 
   // Embedding + all decoder layers for token rows [r0, r0 + T) on stream `st`; every buffer is indexed
@@ -300,7 +323,7 @@ struct b200_engine {
     const int32_t *pos = d_pos.as<int32_t>() + r0, *slot = d_slot.as<int32_t>() + r0, *btrow = d_btrow.as<int32_t>() + r0,
                   *ctx = d_ctx.as<int32_t>() + r0;
     const int64_t xrows = Tmax - r0;
-    if ((rc = launch_embed(embed.as<__half>(), d_ids.as<int32_t>() + r0, T, H, hh, st))) return rc;
+    if ((rc = launch_embed(embed.as<__half>(), d_ids.as<int32_t>() + r0, T, H, hh, st, bf16))) return rc;
     int pend = 0;                 // split-K partials of the previous projection still to be added into h
     const int64_t pend_stride = (int64_t)T * H;
     const bool tail = decode_rows && r0 == 0 && norm_tail_ok(T);
@@ -310,7 +333,7 @@ struct b200_engine {
       __half* kc = k_cache.as<__half>() + layer_kv_offset(l);
       __half* vc = v_cache.as<__half>() + layer_kv_offset(l);
       int np = 0;
-      if (!normed && !skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln1.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st)))
+      if (!normed && !skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln1.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st, bf16)))
         return rc;
       pend = 0;
       normed = false;
@@ -321,23 +344,23 @@ struct b200_engine {
         if (!skip(3) && (rc = launch_attn_decode_fused(qsrc, np ? np : 1, (int64_t)T * QKV, qbias, pos, slot, cos_t.as<float>(),
                                                         sin_t.as<float>(), kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq, btrow,
                                                         ctx, T, NH, NKV, kDecodeSplits, attn_scratch.as<float>(),
-                                                        attn_counters.as<int32_t>(), aa, st))) return rc;
+                                                        attn_counters.as<int32_t>(), aa, st, bf16))) return rc;
       } else {
         if (!skip(2) && (rc = launch_rope_kv(qsrc, np ? np : 1, (int64_t)T * QKV, qbias, pos, slot, cos_t.as<float>(),
-                                             sin_t.as<float>(), T, NH, NKV, qhh, kc, vc, st))) return rc;
+                                             sin_t.as<float>(), T, NH, NKV, qhh, kc, vc, st, bf16))) return rc;
         if (n_q_tiles > 0) {       // tiles of <= 16 consecutive query rows share the staged K/V chunks
           if (!skip(3) && (rc = launch_prefill_attn(qhh, kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq,
-                                                    d_tiles.as<int32_t>(), n_q_tiles, NH, NKV, aa, st)))
+                                                    d_tiles.as<int32_t>(), n_q_tiles, NH, NKV, aa, st, bf16)))
             return rc;
         } else if (!skip(3) && (rc = launch_paged_attn(qhh, kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq, btrow, ctx, T, NH,
-                                                       NKV, 1, nullptr, nullptr, aa, st))) return rc;
+                                                       NKV, 1, nullptr, nullptr, aa, st, bf16))) return rc;
       }
       UmmaNormTail nt{};
       if (tail) {
         nt.counter = norm_counters.as<unsigned long long>(); nt.h = hh; nt.gamma = w.ln2.as<__half>(); nt.xn = xx; nt.eps = cfg.rms_eps;
       }
       if (!skip(4) && (rc = linear(w, 1, aa, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows, tail ? &nt : nullptr))) return rc;
-      if (!tail && !skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st)))
+      if (!tail && !skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st, bf16)))
         return rc;
       pend = 0;
       if (use_umma(T) && !(debug_gemv_mask >> 2 & 1)) {
@@ -371,7 +394,7 @@ struct b200_engine {
       if ((rc = layers_pass(0, T, decode_rows, stream, parts.as<float>(), &pend))) return rc;
       // decode rows: n_rows == T and row r is token r, which is what the last down projection's norm tail wrote
       if (pend >= 0 && (rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, (int64_t)T * H, final_norm.as<__half>(), cfg.rms_eps,
-                                            rows, n_rows, H, xn_last.as<__half>(), stream))) return rc;
+                                            rows, n_rows, H, xn_last.as<__half>(), stream, bf16))) return rc;
     }
     const __half* head = cfg.tie_embeddings ? embed.as<__half>() : lm_head_w.as<__half>();
     bool fused = false;
@@ -390,9 +413,9 @@ struct b200_engine {
     double w = 0;
     for (int i = 0; i < 4; ++i) {
       const W4Linear& lw = layers[0].lin[i];
-      w += (double)lw.N * lw.K / 2 + 2.0 * lw.N * (lw.K / lw.G) * 2;
+      w += dense ? (double)lw.N * lw.K * 2 : (double)lw.N * lw.K / 2 + 2.0 * lw.N * (lw.K / lw.G) * 2;
     }
-    w = w * L + (double)V * H * 2;
+    w = w * L + (double)V * H * 2;                 // + the LM head (tied or not, it is read once per step)
     const double kv_tok = 2.0 * L * NKV * kHeadDim * 2;
     return w + kv_tok * (double)ctx_sum + kv_tok * B;
   }
@@ -782,7 +805,10 @@ int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
   B200_REQUIRE(cfg->struct_size == (int32_t)sizeof(b200_config), "b200_config.struct_size mismatch");
   B200_REQUIRE(cfg->head_dim == kHeadDim, "head_dim must be 128");
   B200_REQUIRE(cfg->hidden > 0 && cfg->hidden % 128 == 0 && cfg->intermediate % 128 == 0, "hidden/intermediate % 128");
-  B200_REQUIRE(cfg->group_size == 128 || cfg->group_size == 64 || cfg->group_size == 32, "group_size in {32,64,128}");
+  B200_REQUIRE(cfg->dense_weights == 0 || cfg->dense_weights == 1, "dense_weights in {0, 1}");
+  B200_REQUIRE(cfg->act_dtype == B200_DTYPE_F16 || cfg->act_dtype == B200_DTYPE_BF16, "act_dtype is B200_DTYPE_F16 or B200_DTYPE_BF16");
+  B200_REQUIRE(cfg->dense_weights == 1 || cfg->act_dtype == B200_DTYPE_F16, "AWQ int4 linears run with fp16 activations");
+  B200_REQUIRE(cfg->dense_weights == 1 || cfg->group_size == 128 || cfg->group_size == 64 || cfg->group_size == 32, "group_size in {32,64,128}");
   B200_REQUIRE(cfg->n_heads % cfg->n_kv_heads == 0 && cfg->n_heads / cfg->n_kv_heads <= 8, "GQA group <= 8");
   B200_REQUIRE(cfg->max_seqs > 0 && cfg->max_model_len > 0 && cfg->max_batch_tokens > 0, "max_seqs/max_model_len/max_batch_tokens");
   int ndev = 0;
@@ -799,7 +825,8 @@ int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
   auto* e = new b200_engine();
   e->cfg = *cfg;
   e->H = cfg->hidden; e->I = cfg->intermediate; e->L = cfg->n_layers; e->NH = cfg->n_heads; e->NKV = cfg->n_kv_heads;
-  e->V = cfg->vocab; e->G = cfg->group_size; e->QKV = (cfg->n_heads + 2 * cfg->n_kv_heads) * kHeadDim;
+  e->V = cfg->vocab; e->G = cfg->dense_weights ? 128 : cfg->group_size; e->QKV = (cfg->n_heads + 2 * cfg->n_kv_heads) * kHeadDim;
+  e->bf16 = cfg->act_dtype == B200_DTYPE_BF16; e->dense = cfg->dense_weights == 1;
   int rc = B200_OK;
   auto fail = [&](int code) { b200_engine_destroy(e); return code; };
   if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -824,10 +851,14 @@ int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
     LayerWeights& w = e->layers[l];
     for (int i = 0; i < 4 && rc == B200_OK; ++i) {
       const size_t K = Ks[i], N = Ns[i];
+      w.lin[i].K = (int)K; w.lin[i].N = (int)N; w.lin[i].G = e->G;
+      if (e->dense) {
+        if ((rc = w.dense[i].alloc(N * K * 2))) break;
+        continue;
+      }
       if ((rc = w.wq[i].alloc(N * (K / 8) * 4)) || (rc = w.sc[i].alloc(N * (K / e->G) * 2)) ||
           (rc = w.zp[i].alloc(N * (K / e->G) * 2))) break;
       w.lin[i].wq = w.wq[i].as<uint32_t>(); w.lin[i].sc = w.sc[i].as<__half>(); w.lin[i].zp = w.zp[i].as<__half>();
-      w.lin[i].K = (int)K; w.lin[i].N = (int)N; w.lin[i].G = e->G;
     }
     if (rc == B200_OK && !((rc = w.bias_qkv.alloc((size_t)e->QKV * 2)) || (rc = w.ln1.alloc((size_t)e->H * 2)) ||
                            (rc = w.ln2.alloc((size_t)e->H * 2))))
@@ -838,7 +869,11 @@ int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
   if (rc == B200_OK) rc = e->final_norm.alloc((size_t)e->H * 2);
   if (rc != B200_OK) return fail(rc);
   // per layer: 7 linears x 3 tensors + 3 biases + 2 norms; + embed + final norm (+ lm_head)
-  e->tensors_expected = e->L * (7 * 3 + 3 + 2) + 2 + (cfg->tie_embeddings ? 0 : 1);
+  e->tensors_expected = e->L * (7 * (e->dense ? 1 : 3) + 3 + 2) + 2 + (cfg->tie_embeddings ? 0 : 1);
+  if (e->dense) {
+    B200_REQUIRE(e->H % 128 == 0 && e->QKV % 128 == 0 && e->I % 64 == 0 && e->V % 128 == 0,
+                 "dense linears: hidden, qkv width and vocab % 128 == 0, intermediate % 64 == 0");
+  }
   *out = e;
   return B200_OK;
 }
@@ -858,14 +893,15 @@ int32_t b200_engine_load_tensor(b200_engine* e, const char* name_c, const void* 
   const std::string name(name_c);
   size_t count = 1;
   for (int i = 0; i < ndim; ++i) count *= (size_t)shape[i];
-  const size_t esz = dtype == B200_DTYPE_F16 ? 2 : 4;
+  const size_t esz = (dtype == B200_DTYPE_F16 || dtype == B200_DTYPE_BF16) ? 2 : 4;
+  const int32_t dt16 = e->cfg.act_dtype;             // the 16-bit type every non-quantised tensor must have
   auto expect = [&](bool ok, const char* what) {
     if (!ok) set_last_error("load_tensor " + name + ": unexpected " + what);
     return ok;
   };
   int rc;
   if (name == "model.embed_tokens.weight" || name == "lm_head.weight" || name == "model.norm.weight") {
-    if (!expect(dtype == B200_DTYPE_F16, "dtype")) return B200_ERR_INVALID;
+    if (!expect(dtype == dt16, "dtype")) return B200_ERR_INVALID;
     DevMem& dst = name == "model.norm.weight" ? e->final_norm : name == "lm_head.weight" ? e->lm_head_w : e->embed;
     if (name == "lm_head.weight" && e->cfg.tie_embeddings) return B200_OK;   // tied: ignore the duplicate
     if (!expect(count * esz == dst.bytes, "shape")) return B200_ERR_INVALID;
@@ -892,7 +928,7 @@ int32_t b200_engine_load_tensor(b200_engine* e, const char* name_c, const void* 
   LayerWeights& w = e->layers[layer];
   const std::string r(rest);
   if (r == "input_layernorm.weight" || r == "post_attention_layernorm.weight") {
-    if (!expect(dtype == B200_DTYPE_F16 && (int)count == e->H, "dtype/shape")) return B200_ERR_INVALID;
+    if (!expect(dtype == dt16 && (int)count == e->H, "dtype/shape")) return B200_ERR_INVALID;
     if ((rc = copy_to(r[0] == 'i' ? w.ln1 : w.ln2, 0, data, count * 2, e->stream))) return rc;
     e->tensors_loaded++;
     return B200_OK;
@@ -913,11 +949,31 @@ int32_t b200_engine_load_tensor(b200_engine* e, const char* name_c, const void* 
     if (r.compare(0, key.size() + 1, key + ".") != 0) continue;
     const std::string kind = r.substr(key.size() + 1);
     if (kind == "bias") {
-      if (!expect(pj.lin == 0 && dtype == B200_DTYPE_F16 && (int)count == pj.N, "bias")) return B200_ERR_INVALID;
+      if (!expect(pj.lin == 0 && dtype == dt16 && (int)count == pj.N, "bias")) return B200_ERR_INVALID;
       if ((rc = copy_to(w.bias_qkv, (size_t)pj.row_off * 2, data, count * 2, e->stream))) return rc;
       e->tensors_loaded++;
       return B200_OK;
     }
+    if (kind == "weight") {
+      // dense checkpoint: W[N, K] row-major in the activation dtype.  q / k / v are stacked row-wise; gate and up
+      // are interleaved in blocks of 64 rows so that every 128-row GEMM tile holds 64 gate rows and the matching
+      // 64 up rows (the SwiGLU epilogue pairs them).
+      if (!expect(e->dense && dtype == dt16 && ndim == 2 && shape[0] == pj.N && shape[1] == pj.K, "dense weight")) return B200_ERR_INVALID;
+      DevMem& dst = w.dense[pj.lin];
+      const size_t row_bytes = (size_t)pj.K * 2;
+      if (pj.lin == 2) {
+        const size_t blk = 64 * row_bytes;
+        const size_t off = (pj.row_off ? 64 : 0) * row_bytes;       // up rows take the second half of every tile
+        if (off + ((size_t)pj.N / 64 - 1) * 2 * blk + blk > dst.bytes) { set_last_error("tensor larger than its destination"); return B200_ERR_INVALID; }
+        B200_CUDA(cudaMemcpy2DAsync((char*)dst.p + off, 2 * blk, data, blk, blk, (size_t)pj.N / 64, cudaMemcpyHostToDevice, e->stream));
+        B200_CUDA(cudaStreamSynchronize(e->stream));
+      } else if ((rc = copy_to(dst, (size_t)pj.row_off * row_bytes, data, count * 2, e->stream))) {
+        return rc;
+      }
+      e->tensors_loaded++;
+      return B200_OK;
+    }
+    if (e->dense) { set_last_error("load_tensor: " + name + " is an AWQ tensor but the engine was created with dense_weights"); return B200_ERR_INVALID; }
     PendingLinear& pl = e->pending[std::to_string(layer) + "." + key];
     const int K = pj.K, N = pj.N, Gs = e->G;
     if (kind == "qweight") {
@@ -982,7 +1038,9 @@ int32_t b200_engine_finalize(b200_engine* e) {
     B200_CUDA(cudaMemcpy(e->sin_t.p, sn.data(), sn.size() * 4, cudaMemcpyHostToDevice));
   }
   // tiled weight copies for the tcgen05 GEMM
-  if (c.gemm_path != 1) {
+  if (e->dense) {
+    for (auto& w : e->layers) w.lin[0].bias = w.bias_qkv.as<__half>();
+  } else if (c.gemm_path != 1) {
     for (int l = 0; l < e->L; ++l) {
       LayerWeights& w = e->layers[l];
       for (int i = 0; i < 4; ++i) {
@@ -1041,7 +1099,18 @@ int32_t b200_engine_finalize(b200_engine* e) {
   // split-K factors: enough CTAs to engage every SM's dequant throughput on the skinny projections
   // (o, down: 12 row tiles), bounded so partial-sum traffic stays small next to the weight bytes.
   size_t part_elems = 16;
-  if (c.gemm_path != 1) {
+  if (e->dense) {
+    // dense decode passes: enough CTAs to pull the weights at HBM speed (tiles x splits ~ the SM count)
+    for (int i = 0; i < 4; ++i) {
+      const W4Linear& a = e->layers[0].lin[i];
+      const int tiles = a.N / 128, KT = a.K / 64;
+      int sp = std::max(1, std::min((148 + tiles / 2) / tiles, KT / 4));
+      if (i == 2) sp = 1;                               // gate_up feeds SwiGLU directly
+      e->splits[i] = sp;
+      const int eff = umma_dense_effective_splits(a.K, sp);
+      if (eff > 1) part_elems = std::max(part_elems, (size_t)eff * S * a.N);
+    }
+  } else if (c.gemm_path != 1) {
     const char* ov = getenv("VGATE_B200_SPLITS");      // "qkv,o,gate_up,down" override for tuning
     int o4[4] = {0, 0, 0, 0};
     if (ov) sscanf(ov, "%d,%d,%d,%d", &o4[0], &o4[1], &o4[2], &o4[3]);
@@ -1054,7 +1123,7 @@ int32_t b200_engine_finalize(b200_engine* e) {
       if (o4[i] > 0 && i != 2) sp = o4[i];
       e->splits[i] = sp;
       const int eff = umma_w4_effective_splits(a.K, a.G, sp);
-      if (eff > 1) part_elems = std::max(part_elems, (size_t)eff * T * a.N);
+      if (eff > 1) part_elems = std::max(part_elems, (size_t)eff * S * a.N);   // split-K only runs on decode passes (<= max_seqs rows)
     }
   }
   if ((rc = e->parts.alloc(part_elems * 4)) || (rc = e->norm_counters.alloc(2 * sizeof(unsigned long long)))) return rc;
@@ -1086,7 +1155,7 @@ void b200_engine_destroy(b200_engine* e) {
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (auto& g : e->decode_graphs) cudaGraphExecDestroy(g.second.exec);
   for (auto& w : e->layers) {
-    for (int i = 0; i < 4; ++i) { w.wq[i].release(); w.sc[i].release(); w.zp[i].release(); w.chunks[i].release(); }
+    for (int i = 0; i < 4; ++i) { w.wq[i].release(); w.sc[i].release(); w.zp[i].release(); w.chunks[i].release(); w.dense[i].release(); }
     w.bias_qkv.release(); w.ln1.release(); w.ln2.release();
   }
   for (auto& kv : e->pending) { kv.second.qweight.release(); kv.second.qzeros.release(); kv.second.scales.release(); }

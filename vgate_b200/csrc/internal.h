@@ -88,7 +88,10 @@ int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T,
 // May this projection run with the norm tail?  Every CTA of the grid must be resident at once.
 bool umma_norm_tail_ok(int T, int K, int N, int G, int n_splits, int device);
 int launch_umma_f16(const CUtensorMap& map_w, int K, int N, const CUtensorMap& map_x, int nt_sel, int T, float* y,
-                    int ldy, int mode, cudaStream_t s);
+                    int ldy, int mode, cudaStream_t s, int n_splits = 1, int64_t part_stride = 0, const __half* bias = nullptr,
+                    bool bf16 = false, const UmmaNormTail* norm = nullptr);
+int umma_dense_effective_splits(int K, int n_splits);
+bool umma_dense_norm_tail_ok(int T, int K, int N, int n_splits, int device);
 
 int launch_awq_repack(const int32_t* qweight, const int32_t* qzeros, const __half* scales, int K, int N, int G,
                       uint32_t* wq, __half* sc, __half* zp, int row_offset, cudaStream_t s);
@@ -99,26 +102,26 @@ int launch_w4_gemv(const W4Linear& w, const __half* x, int ldx, float* y, int ld
 int launch_f16_gemv(const __half* w, const __half* x, int ldx, float* y, int ldy, int B, int K, int N,
                     bool accumulate, cudaStream_t s);
 int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_stride, const __half* gamma, float eps,
-                   const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s);
+                   const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s, bool bf16 = false);
 int launch_rope_kv(const float* qkv, int n_parts, int64_t part_stride, const __half* bias, const int32_t* pos, const int32_t* slot, const float* cos_t,
                    const float* sin_t, int T, int n_heads, int n_kv, __half* q_out, __half* k_cache,
-                   __half* v_cache, cudaStream_t s);
+                   __half* v_cache, cudaStream_t s, bool bf16 = false);
 int launch_paged_attn(const __half* q, const __half* k_cache, const __half* v_cache, const int32_t* block_tables,
                       int bt_stride, const int32_t* bt_row, const int32_t* ctx_len, int T, int n_heads, int n_kv,
-                      int n_splits, float* scratch, int32_t* counters, __half* out, cudaStream_t s);
+                      int n_splits, float* scratch, int32_t* counters, __half* out, cudaStream_t s, bool bf16 = false);
 int launch_attn_decode_fused(const float* qkv, int n_parts, int64_t part_stride, const __half* bias, const int32_t* pos,
                              const int32_t* slot, const float* cos_t, const float* sin_t, __half* k_cache,
                              __half* v_cache, const int32_t* block_tables, int bt_stride, const int32_t* bt_row,
                              const int32_t* ctx_len, int T, int n_heads, int n_kv, int n_splits, float* scratch,
-                             int32_t* counters, __half* out, cudaStream_t s);
+                             int32_t* counters, __half* out, cudaStream_t s, bool bf16 = false);
 void attn_set_trace(unsigned long long* dev_buf);
 // tiles: int32 [n_tiles, 4] = {row0, nrows <= 16, block-table row, context length of row0}
 int launch_prefill_attn(const __half* q, const __half* k_cache, const __half* v_cache, const int32_t* block_tables,
                         int bt_stride, const int32_t* tiles, int n_tiles, int n_heads, int n_kv, __half* out,
-                        cudaStream_t s);
+                        cudaStream_t s, bool bf16 = false);
 size_t attn_scratch_floats(int T, int n_heads, int n_kv, int n_splits);
 int launch_swiglu(const float* gu, int T, int I, __half* act, cudaStream_t s);
-int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s);
+int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s, bool bf16 = false);
 // part: float2 {max, bits(argmax)} [n_tiles, ld] from the kUmmaArgmaxF32 epilogue
 int launch_argmax_reduce(const float* part, int n_tiles, int ld, int B, int32_t* out, cudaStream_t s);
 int launch_sample(const float* logits, int B, int V, const float* temperature, const float* top_p,

@@ -62,7 +62,7 @@ __device__ __forceinline__ float rms_scale(const float (*red)[kNormWarps], const
 // xn[r] quarter q = fp16(v * rs * gamma)
 __device__ __forceinline__ void rms_quarter_store(const float4 (&v)[kNormMaxPerThread], const float rs,
                                                   const __half* __restrict__ gamma, __half* __restrict__ xn, const int r,
-                                                  const int q, const int H, const int tid) {
+                                                  const int q, const int H, const int tid, const bool bf = false) {
   const int HQ = H / kNormCluster;
   const int nvec = HQ / 4;
 #pragma unroll
@@ -70,11 +70,11 @@ __device__ __forceinline__ void rms_quarter_store(const float4 (&v)[kNormMaxPerT
     const int i = tid + it * kNormThreads;
     if (i < nvec) {
       const uint2 gw = *reinterpret_cast<const uint2*>(gamma + (size_t)q * HQ + 4 * i);
-      const float2 g0 = __half22float2(*reinterpret_cast<const __half2*>(&gw.x));
-      const float2 g1 = __half22float2(*reinterpret_cast<const __half2*>(&gw.y));
+      const float2 g0 = unpack16x2(gw.x, bf);
+      const float2 g1 = unpack16x2(gw.y, bf);
       uint2 o;
-      o.x = pack_half2(__fmul_rn(__fmul_rn(v[it].x, rs), g0.x), __fmul_rn(__fmul_rn(v[it].y, rs), g0.y));
-      o.y = pack_half2(__fmul_rn(__fmul_rn(v[it].z, rs), g1.x), __fmul_rn(__fmul_rn(v[it].w, rs), g1.y));
+      o.x = pack16x2(__fmul_rn(__fmul_rn(v[it].x, rs), g0.x), __fmul_rn(__fmul_rn(v[it].y, rs), g0.y), bf);
+      o.y = pack16x2(__fmul_rn(__fmul_rn(v[it].z, rs), g1.x), __fmul_rn(__fmul_rn(v[it].w, rs), g1.y), bf);
       *reinterpret_cast<uint2*>(xn + (size_t)r * H + (size_t)q * HQ + 4 * i) = o;
     }
   }

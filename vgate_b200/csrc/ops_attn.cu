@@ -41,6 +41,7 @@ struct PrefillAttnParams {
   const QTile* tiles;
   int n_heads, n_kv;
   __half* out;                   // [T, nh * 128]
+  int bf16;
 };
 
 template <int GQ>
@@ -58,6 +59,7 @@ prefill_attn_kernel(const PrefillAttnParams p) {
   using L = PrefillSmem<GQ>;
   const unsigned tl = kernel_prologue(kKidAttn);
   const int j = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool bf = p.bf16 != 0;
   const QTile qt = p.tiles[blockIdx.y];
   const int n_heads = p.n_heads, n_kv = p.n_kv;
   const int head = j * GQ + warp;
@@ -136,8 +138,8 @@ prefill_attn_kernel(const PrefillAttnParams p) {
         for (int k2 = 0; k2 < 4; ++k2) {
           uint32_t b0, b1, b2, b3;
           ldmatrix_x4(rowaddr + ((((4 * k2 + mj) ^ (tok & 7))) << 4), b0, b1, b2, b3);
-          mma_16816(d, qa[2 * k2], b0, b1);
-          mma_16816(d, qa[2 * k2 + 1], b2, b3);
+          mma_16816(d, qa[2 * k2], b0, b1, bf);
+          mma_16816(d, qa[2 * k2 + 1], b2, b3, bf);
         }
       }
       const int t0 = c * kChunkTokens + nt * 8 + 2 * tq;       // absolute key position
@@ -163,7 +165,7 @@ prefill_attn_kernel(const PrefillAttnParams p) {
       for (int nt = 0; nt < 8; ++nt) {
         const float p0 = expf(sc[nt][2 * hr] - m_use), p1 = expf(sc[nt][2 * hr + 1] - m_use);
         sum += p0 + p1;
-        pa[nt >> 1][(nt & 1) * 2 + hr] = pack_half2(p0, p1);
+        pa[nt >> 1][(nt & 1) * 2 + hr] = pack16x2(p0, p1, bf);
       }
       sum += __shfl_xor_sync(0xffffffffu, sum, 1);
       sum += __shfl_xor_sync(0xffffffffu, sum, 2);
@@ -181,8 +183,8 @@ prefill_attn_kernel(const PrefillAttnParams p) {
         for (int d2 = 0; d2 < 8; ++d2) {
           uint32_t b0, b1, b2, b3;
           ldmatrix_x4_trans(rowaddr + (((2 * d2 + (mj >> 1)) ^ (r & 7)) << 4), b0, b1, b2, b3);
-          mma_16816(o[2 * d2], pa[kt], b0, b1);
-          mma_16816(o[2 * d2 + 1], pa[kt], b2, b3);
+          mma_16816(o[2 * d2], pa[kt], b0, b1, bf);
+          mma_16816(o[2 * d2 + 1], pa[kt], b2, b3, bf);
         }
       }
     }
@@ -199,7 +201,7 @@ prefill_attn_kernel(const PrefillAttnParams p) {
       __half* orow = p.out + ((size_t)(qt.row0 + r) * n_heads + head) * kHeadDim;
 #pragma unroll
       for (int dn = 0; dn < 16; ++dn)
-        *reinterpret_cast<uint32_t*>(orow + dn * 8 + 2 * tq) = pack_half2(o[dn][2 * hr] * inv, o[dn][2 * hr + 1] * inv);
+        *reinterpret_cast<uint32_t*>(orow + dn * 8 + 2 * tq) = pack16x2(o[dn][2 * hr] * inv, o[dn][2 * hr + 1] * inv, bf);
     }
   }
   kernel_epilogue(tl);
@@ -218,13 +220,13 @@ static int launch_prefill_gq(const PrefillAttnParams& p, int n_tiles, cudaStream
 
 int launch_prefill_attn(const __half* q, const __half* k_cache, const __half* v_cache, const int32_t* block_tables,
                         int bt_stride, const int32_t* tiles, int n_tiles, int n_heads, int n_kv, __half* out,
-                        cudaStream_t s) {
+                        cudaStream_t s, bool bf16) {
   B200_REQUIRE(n_kv > 0 && n_heads % n_kv == 0, "prefill_attn: n_heads % n_kv");
   B200_REQUIRE(n_tiles <= 65535, "prefill_attn: at most 65535 query tiles per launch");
   if (n_tiles == 0) return B200_OK;
   PrefillAttnParams p{};
   p.q = q; p.k_cache = k_cache; p.v_cache = v_cache; p.block_tables = block_tables; p.bt_stride = bt_stride;
-  p.tiles = reinterpret_cast<const QTile*>(tiles); p.n_heads = n_heads; p.n_kv = n_kv; p.out = out;
+  p.tiles = reinterpret_cast<const QTile*>(tiles); p.n_heads = n_heads; p.n_kv = n_kv; p.out = out; p.bf16 = bf16 ? 1 : 0;
 #define CASE(G) case G: return launch_prefill_gq<G>(p, n_tiles, s)
   switch (n_heads / n_kv) {
     CASE(1); CASE(2); CASE(3); CASE(4); CASE(5); CASE(6); CASE(7); CASE(8);
@@ -278,8 +280,9 @@ static int dispatch(const AttnParams& p, int T, bool fused, cudaStream_t s) {
 
 int launch_paged_attn(const __half* q, const __half* k_cache, const __half* v_cache, const int32_t* block_tables,
                       int bt_stride, const int32_t* bt_row, const int32_t* ctx_len, int T, int n_heads, int n_kv,
-                      int n_splits, float* scratch, int32_t* counters, __half* out, cudaStream_t s) {
+                      int n_splits, float* scratch, int32_t* counters, __half* out, cudaStream_t s, bool bf16) {
   AttnParams p{};
+  p.bf16 = bf16 ? 1 : 0;
   p.trace = g_attn_trace;
   p.q = q; p.k_cache = const_cast<__half*>(k_cache); p.v_cache = const_cast<__half*>(v_cache);
   p.block_tables = block_tables; p.bt_stride = bt_stride; p.bt_row = bt_row; p.ctx_len = ctx_len;
@@ -291,9 +294,10 @@ int launch_attn_decode_fused(const float* qkv, int n_parts, int64_t part_stride,
                              const int32_t* slot, const float* cos_t, const float* sin_t, __half* k_cache,
                              __half* v_cache, const int32_t* block_tables, int bt_stride, const int32_t* bt_row,
                              const int32_t* ctx_len, int T, int n_heads, int n_kv, int n_splits, float* scratch,
-                             int32_t* counters, __half* out, cudaStream_t s) {
+                             int32_t* counters, __half* out, cudaStream_t s, bool bf16) {
   B200_REQUIRE(n_parts >= 1, "attn_decode_fused: n_parts >= 1");
   AttnParams p{};
+  p.bf16 = bf16 ? 1 : 0;
   p.trace = g_attn_trace;
   p.qkv = qkv; p.n_parts = n_parts; p.part_stride = part_stride; p.bias = bias; p.pos = pos; p.slot = slot;
   p.cos_t = cos_t; p.sin_t = sin_t; p.k_cache = k_cache; p.v_cache = v_cache;

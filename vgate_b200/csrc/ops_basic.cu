@@ -83,29 +83,28 @@ int launch_awq_dequant(const uint32_t* wq, const __half* sc, const __half* zp, i
 // ---------------------------------------------------------------------------------------------
 // Embedding gather into the fp32 residual stream.
 __global__ void embed_kernel(const __half* __restrict__ table, const int32_t* __restrict__ ids, int H,
-                             float* __restrict__ h) {
+                             float* __restrict__ h, int bf) {
   const unsigned tl = kernel_prologue(kKidEmbed);
   const int t = blockIdx.x;
   const __half* row = table + (size_t)ids[t] * H;
   for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
     const uint4 v = ldg_cached(row + i);
-    const __half2* p = reinterpret_cast<const __half2*>(&v);
     float4 a, b;
     float2 f;
-    f = __half22float2(p[0]); a.x = f.x; a.y = f.y;
-    f = __half22float2(p[1]); a.z = f.x; a.w = f.y;
-    f = __half22float2(p[2]); b.x = f.x; b.y = f.y;
-    f = __half22float2(p[3]); b.z = f.x; b.w = f.y;
+    f = unpack16x2(v.x, bf); a.x = f.x; a.y = f.y;
+    f = unpack16x2(v.y, bf); a.z = f.x; a.w = f.y;
+    f = unpack16x2(v.z, bf); b.x = f.x; b.y = f.y;
+    f = unpack16x2(v.w, bf); b.z = f.x; b.w = f.y;
     *reinterpret_cast<float4*>(h + (size_t)t * H + i) = a;
     *reinterpret_cast<float4*>(h + (size_t)t * H + i + 4) = b;
   }
   kernel_epilogue(tl);
 }
 
-int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s) {
+int launch_embed(const __half* table, const int32_t* ids, int T, int H, float* h, cudaStream_t s, bool bf16) {
   B200_REQUIRE(H % 8 == 0, "embed: H % 8");
   if (T == 0) return B200_OK;
-  launch_k(embed_kernel, dim3(T), dim3(192), 0, s, table, ids, H, h);
+  launch_k(embed_kernel, dim3(T), dim3(192), 0, s, table, ids, H, h, bf16 ? 1 : 0);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -123,7 +122,7 @@ template <bool kOneRow>       // kOneRow: exactly one row per cluster (decode, s
 __global__ void __cluster_dims__(kNormCluster, 1, 1) __launch_bounds__(kNormThreads)
 rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_parts, int64_t part_stride,
                const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows, int n_rows, int H,
-               __half* __restrict__ xn) {
+               __half* __restrict__ xn, int bf) {
   // red is double-buffered by row parity: a CTA may push the partials of its next row while a slower
   // CTA of the cluster still reads the previous row's (one cluster barrier per row is then enough:
   // nobody can be two rows ahead of a CTA that has not passed the barrier in between)
@@ -144,7 +143,7 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
     }
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
     const float rs = rms_scale(red[it & 1], H, eps);
-    rms_quarter_store(v, rs, gamma, xn, r, q, H, threadIdx.x);
+    rms_quarter_store(v, rs, gamma, xn, r, q, H, threadIdx.x, bf != 0);
   }
   kernel_epilogue(tl);
 }
@@ -157,7 +156,7 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
 constexpr int kNormWarpRowMaxH = 2048;
 __global__ void __launch_bounds__(256)
 rmsnorm_rows_kernel(const float* __restrict__ h, const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows,
-                    int n_rows, int H, __half* __restrict__ xn) {
+                    int n_rows, int H, __half* __restrict__ xn, int bf) {
   const unsigned tl = kernel_prologue(kKidRmsnorm);
   const int lane = threadIdx.x & 31;
   const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -189,11 +188,11 @@ rmsnorm_rows_kernel(const float* __restrict__ h, const __half* __restrict__ gamm
       if (w < wpq && i < nvec) {
         const int e = (q * nvec + i) * 4;
         const uint2 gw = *reinterpret_cast<const uint2*>(gamma + e);
-        const float2 g0 = __half22float2(*reinterpret_cast<const __half2*>(&gw.x));
-        const float2 g1 = __half22float2(*reinterpret_cast<const __half2*>(&gw.y));
+        const float2 g0 = unpack16x2(gw.x, bf);
+        const float2 g1 = unpack16x2(gw.y, bf);
         uint2 o;
-        o.x = pack_half2(__fmul_rn(__fmul_rn(v[k].x, rs), g0.x), __fmul_rn(__fmul_rn(v[k].y, rs), g0.y));
-        o.y = pack_half2(__fmul_rn(__fmul_rn(v[k].z, rs), g1.x), __fmul_rn(__fmul_rn(v[k].w, rs), g1.y));
+        o.x = pack16x2(__fmul_rn(__fmul_rn(v[k].x, rs), g0.x), __fmul_rn(__fmul_rn(v[k].y, rs), g0.y), bf);
+        o.y = pack16x2(__fmul_rn(__fmul_rn(v[k].z, rs), g1.x), __fmul_rn(__fmul_rn(v[k].w, rs), g1.y), bf);
         *reinterpret_cast<uint2*>(dst + e) = o;
       }
     }
@@ -202,12 +201,13 @@ rmsnorm_rows_kernel(const float* __restrict__ h, const __half* __restrict__ gamm
 }
 
 int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_stride, const __half* gamma, float eps,
-                   const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s) {
+                   const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s, bool bf16) {
+  const int bf = bf16 ? 1 : 0;
   B200_REQUIRE(H % (4 * kNormCluster) == 0 && H <= kNormCluster * kNormThreads * 4 * kNormMaxPerThread,
                "rmsnorm: H % 16 == 0 && H <= 8192");
   if (n_rows == 0) return B200_OK;
   if (n_parts == 0 && n_rows >= 1024 && H <= kNormWarpRowMaxH) {     // large prefill pass: warp per row, same bits
-    launch_k(rmsnorm_rows_kernel, dim3((n_rows + 7) / 8), dim3(256), 0, s, (const float*)h, gamma, eps, rows, n_rows, H, xn);
+    launch_k(rmsnorm_rows_kernel, dim3((n_rows + 7) / 8), dim3(256), 0, s, (const float*)h, gamma, eps, rows, n_rows, H, xn, bf);
     g_launch_count += 1;
     B200_CUDA(cudaGetLastError());
     return B200_OK;
@@ -215,10 +215,10 @@ int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_strid
   const int n_clusters = n_rows < 2048 ? n_rows : 2048;      // beyond that a cluster walks several rows
   if (n_clusters == n_rows)
     launch_k(rmsnorm_kernel<true>, dim3(n_clusters * kNormCluster), dim3(kNormThreads), 0, s, h, parts, n_parts, part_stride, gamma,
-             eps, rows, n_rows, H, xn);
+             eps, rows, n_rows, H, xn, bf);
   else
     launch_k(rmsnorm_kernel<false>, dim3(n_clusters * kNormCluster), dim3(kNormThreads), 0, s, h, parts, n_parts, part_stride, gamma,
-             eps, rows, n_rows, H, xn);
+             eps, rows, n_rows, H, xn, bf);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -232,7 +232,7 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_parts, int64
                                const __half* __restrict__ bias, const int32_t* __restrict__ pos,
                                const int32_t* __restrict__ slot, const float* __restrict__ cos_t,
                                const float* __restrict__ sin_t, int n_heads, int n_kv, __half* __restrict__ q_out,
-                               __half* __restrict__ k_cache, __half* __restrict__ v_cache) {
+                               __half* __restrict__ k_cache, __half* __restrict__ v_cache, int bf) {
   const unsigned tl = kernel_prologue(kKidRope);
   const int t = blockIdx.x;
   const int p = pos[t];
@@ -254,31 +254,32 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_parts, int64
       for (int k = 0; k < 4; ++k) { x1 += a[k]; x2 += b[k]; }
     }
     if (bias) {
-      x1 += __half2float(bias[head * kHeadDim + i]);
-      x2 += __half2float(bias[head * kHeadDim + i + 64]);
+      const uint16_t* b16 = reinterpret_cast<const uint16_t*>(bias);
+      x1 += from16(b16[head * kHeadDim + i], bf);
+      x2 += from16(b16[head * kHeadDim + i + 64], bf);
     }
     if (head < n_heads) {
       const float c = cos_t[(size_t)p * 64 + i], sn = sin_t[(size_t)p * 64 + i];
-      __half* o = q_out + ((size_t)t * n_heads + head) * kHeadDim;
+      uint16_t* o = reinterpret_cast<uint16_t*>(q_out) + ((size_t)t * n_heads + head) * kHeadDim;
       float r1, r2;
       rope_rotate(x1, x2, c, sn, r1, r2);
-      o[i] = __float2half_rn(r1);
-      o[i + 64] = __float2half_rn(r2);
+      o[i] = to16(r1, bf);
+      o[i + 64] = to16(r2, bf);
     } else if (sl >= 0) {
       const int blk = sl / kBlockTokens, off = sl % kBlockTokens;
       if (head < n_heads + n_kv) {
         const int j = head - n_heads;
         const float c = cos_t[(size_t)p * 64 + i], sn = sin_t[(size_t)p * 64 + i];
-        __half* o = k_cache + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
+        uint16_t* o = reinterpret_cast<uint16_t*>(k_cache) + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
         float r1, r2;
         rope_rotate(x1, x2, c, sn, r1, r2);
-        o[kv_swz(off, i)] = __float2half_rn(r1);                     // swizzled row layout, see common.cuh
-        o[kv_swz(off, i + 64)] = __float2half_rn(r2);
+        o[kv_swz(off, i)] = to16(r1, bf);                            // swizzled row layout, see common.cuh
+        o[kv_swz(off, i + 64)] = to16(r2, bf);
       } else {
         const int j = head - n_heads - n_kv;
-        __half* o = v_cache + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
-        o[kv_swz(off, i)] = __float2half_rn(x1);
-        o[kv_swz(off, i + 64)] = __float2half_rn(x2);
+        uint16_t* o = reinterpret_cast<uint16_t*>(v_cache) + (((size_t)blk * n_kv + j) * kBlockTokens + off) * kHeadDim;
+        o[kv_swz(off, i)] = to16(x1, bf);
+        o[kv_swz(off, i + 64)] = to16(x2, bf);
       }
     }
   }
@@ -287,11 +288,11 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_parts, int64
 
 int launch_rope_kv(const float* qkv, int n_parts, int64_t part_stride, const __half* bias, const int32_t* pos,
                    const int32_t* slot, const float* cos_t, const float* sin_t, int T, int n_heads, int n_kv,
-                   __half* q_out, __half* k_cache, __half* v_cache, cudaStream_t s) {
+                   __half* q_out, __half* k_cache, __half* v_cache, cudaStream_t s, bool bf16) {
   B200_REQUIRE(n_parts >= 1, "rope_kv: n_parts >= 1");
   if (T == 0) return B200_OK;
   launch_k(rope_kv_kernel, dim3(T), dim3(256), 0, s, qkv, n_parts, part_stride, bias, pos, slot, cos_t, sin_t, n_heads,
-           n_kv, q_out, k_cache, v_cache);
+           n_kv, q_out, k_cache, v_cache, bf16 ? 1 : 0);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;

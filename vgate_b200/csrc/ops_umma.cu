@@ -114,9 +114,9 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     for (int t = 0; t < MT; ++t) {
       if (t > 0) asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");   // the staging buffer is reused
       umma_epilogue<NT>(p.mode, p.y, p.ldy, p.mode == kPartialF32 ? (size_t)split * p.part_stride : 0, p.bias, p.T, tok0,
-                        nt * MT + t, reinterpret_cast<float*>(smem), tmem + (uint32_t)(t * (Cfg::kAccCols / MT)), tr);
+                        nt * MT + t, reinterpret_cast<float*>(smem), tmem + (uint32_t)(t * (Cfg::kAccCols / MT)), tr, p.bf16 != 0);
     }
-    if constexpr (kW4 && MT == 1) {
+    if constexpr (MT == 1) {
       if (p.norm.counter) {
         // ---- norm tail: split-K reduction + residual add + RMSNorm, without a kernel boundary ----
         // Same arithmetic, same order, same bits as rmsnorm_kernel (norm.cuh): warpgroup q owns quarter q of a row.
@@ -135,7 +135,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
           if ((tid & 31) == 0) red[it & 1][q][tid >> 5] = ss;
           asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");
           const float rs = rms_scale(red[it & 1], p.N, p.norm.eps);
-          rms_quarter_store(v, rs, p.norm.gamma, p.norm.xn, r, q, p.N, tid);
+          rms_quarter_store(v, rs, p.norm.gamma, p.norm.xn, r, q, p.N, tid, p.bf16 != 0);
         }
       }
     }
@@ -193,7 +193,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
   } else {
     // ===================== MMA issuer =====================
     if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc(kUmmaM, NT);
+      // bf16 operands (dense path): a_format [7,10) = b_format [10,13) = 1
+      const uint32_t idesc = make_idesc(kUmmaM, NT) | ((!kW4 && p.bf16) ? ((1u << 7) | (1u << 10)) : 0u);
       for (int gi = 0; gi < nst; ++gi) {
         const int s = gi % kStages;
         const int nt_here = min(tps, nkt - gi * tps);
@@ -409,15 +410,42 @@ int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T,
   return dispatch_nt<true>(nt_sel, map_x, map_x, p, n_splits, s);
 }
 
+int umma_dense_effective_splits(int K, int n_splits) {
+  const int KT = K / kUmmaBK;
+  const int per = (KT + n_splits - 1) / n_splits;
+  return (KT + per - 1) / per;
+}
+
+bool umma_dense_norm_tail_ok(int T, int K, int N, int n_splits, int device) {
+  if (T <= 0 || T > 256 || N % 128 != 0 || K % kUmmaBK != 0 || N % (4 * kNormCluster) != 0 ||
+      N > kNormCluster * kNormThreads * 4 * kNormMaxPerThread)
+    return false;
+  return (N / kUmmaM) * umma_dense_effective_splits(K, n_splits) <= sm_count(device);
+}
+
+// Dense 16-bit weights W[N, K] (fp16 or bf16) by TMA.  n_splits > 1 requires mode == kPartialF32.
 int launch_umma_f16(const CUtensorMap& map_w, int K, int N, const CUtensorMap& map_x, int nt_sel, int T, float* y,
-                    int ldy, int mode, cudaStream_t s) {
+                    int ldy, int mode, cudaStream_t s, int n_splits, int64_t part_stride, const __half* bias, bool bf16,
+                    const UmmaNormTail* norm) {
   B200_REQUIRE(N % 128 == 0 && K % 64 == 0, "umma_f16: N % 128, K % 64");
+  B200_REQUIRE(n_splits >= 1 && (n_splits == 1 || mode == kPartialF32), "umma_f16: split-K needs partial mode");
   if (T == 0) return B200_OK;
   UmmaParams p{};
   p.trace = g_umma_trace;
-  p.y = y; p.ldy = ldy; p.T = T; p.K = K; p.N = N; p.G = 128; p.mode = mode;
-  p.kt_per_split = K / kUmmaBK;
-  return dispatch_nt<false>(nt_sel, map_x, map_w, p, 1, s);
+  p.y = y; p.ldy = ldy; p.T = T; p.K = K; p.N = N; p.G = 128; p.mode = mode; p.bias = bias; p.bf16 = bf16 ? 1 : 0;
+  p.part_stride = part_stride;
+  const int KT = K / kUmmaBK;
+  p.kt_per_split = (KT + n_splits - 1) / n_splits;
+  n_splits = (KT + p.kt_per_split - 1) / p.kt_per_split;
+  if (norm && norm->counter) {
+    int dev = 0;
+    B200_CUDA(cudaGetDevice(&dev));
+    B200_REQUIRE(mode == kPartialF32 && ldy == N && norm->h && norm->gamma && norm->xn && part_stride == (int64_t)T * N &&
+                     (T + nt_sel - 1) / nt_sel == 1 && umma_dense_norm_tail_ok(T, K, N, n_splits, dev),
+                 "umma_f16: the norm tail needs split-K partial mode, dense [T, N] partials, one token tile and a grid that fits the GPU at once");
+    p.norm = *norm;
+  }
+  return dispatch_nt<false>(nt_sel, map_x, map_w, p, n_splits, s);
 }
 
 }  // namespace b200

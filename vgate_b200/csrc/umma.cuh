@@ -178,6 +178,7 @@ struct UmmaParams {
   int ldy, T, K, N, G;
   int kt_per_split;       // k tiles handled by one CTA along grid.z (W4: a multiple of G/64)
   int mode;
+  int bf16;               // dense path: weights and activations are bf16 (0: fp16).  The W4 path is fp16 only.
   const unsigned char* l2_prefetch;   // weights of the NEXT kernel to pull into L2 (or null), shared out over the CTAs
   int64_t l2_prefetch_bytes;
   // Norm tail (kPartialF32 with norm.counter != null): once every CTA of the grid has published its split-K
@@ -259,7 +260,8 @@ __device__ __forceinline__ void w4_chunk_to_tmem(const uint32_t ch, uint64_t* pk
 template <int NT>
 __device__ __forceinline__ void umma_epilogue(const int mode, float* y, const int ldy, const size_t part_off,
                                               const __half* bias, const int T, const int tok0, const int nt,
-                                              float* stage, const uint32_t tmem, unsigned long long* tr) {
+                                              float* stage, const uint32_t tmem, unsigned long long* tr,
+                                              const bool bf = false) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // Stage the whole [NT tokens x 128 features] fp32 accumulator tile in shared memory (the
     // activation stages are idle once the accumulator is complete), then write global memory with
@@ -293,10 +295,10 @@ __device__ __forceinline__ void umma_epilogue(const int mode, float* y, const in
           const float4 u1 = *reinterpret_cast<const float4*>(stage + bcol * 128 + 64 + f8 + 4);
           auto f = [](float g, float u) { return g / (1.f + expf(-g)) * u; };
           uint4 o;
-          o.x = pack_half2(f(g0.x, u0.x), f(g0.y, u0.y));
-          o.y = pack_half2(f(g0.z, u0.z), f(g0.w, u0.w));
-          o.z = pack_half2(f(g1.x, u1.x), f(g1.y, u1.y));
-          o.w = pack_half2(f(g1.z, u1.z), f(g1.w, u1.w));
+          o.x = pack16x2(f(g0.x, u0.x), f(g0.y, u0.y), bf);
+          o.y = pack16x2(f(g0.z, u0.z), f(g0.w, u0.w), bf);
+          o.z = pack16x2(f(g1.x, u1.x), f(g1.y, u1.y), bf);
+          o.w = pack16x2(f(g1.z, u1.z), f(g1.w, u1.w), bf);
           *reinterpret_cast<uint4*>(act + (size_t)b * ldy + nt * 64 + f8) = o;
         }
       }
@@ -334,8 +336,8 @@ __device__ __forceinline__ void umma_epilogue(const int mode, float* y, const in
             a.x += o.x; a.y += o.y; a.z += o.z; a.w += o.w;
           } else if (mode == kStoreF32 && bias) {
             const uint2 bw = *reinterpret_cast<const uint2*>(bias + nt * kUmmaM + f4);
-            const float2 b0 = __half22float2(*reinterpret_cast<const __half2*>(&bw.x));
-            const float2 b1 = __half22float2(*reinterpret_cast<const __half2*>(&bw.y));
+            const float2 b0 = unpack16x2(bw.x, bf);
+            const float2 b1 = unpack16x2(bw.y, bf);
             a.x += b0.x; a.y += b0.y; a.z += b1.x; a.w += b1.y;
           }
           *yp = a;
