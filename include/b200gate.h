@@ -175,19 +175,6 @@ int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, flo
                              const void* bias, int32_t T, int32_t K, int32_t N, int32_t G, int32_t epilogue,
                              int32_t n_splits, int64_t part_stride, void* stream);
 int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits);
-/* A split-K projection that feeds a residual add + RMSNorm (o_proj, down_proj; vLLM qwen2.py:287-312), with both
- * finished inside the GEMM kernel: every CTA writes its split's partial tensor to `parts` ([n_splits, T, N] fp32,
- * left there), and once all CTAs of the grid have done so they share out the token rows:
- *     h[t] += sum_s parts[s][t]   (fixed order s = 0, 1, ...);   xn[t] = fp16(rmsnorm(h[t]) * gamma)
- * -- the same arithmetic, in the same order, as b200_op_w4_gemm_umma followed by b200_op_rmsnorm (bit-identical),
- * minus one kernel boundary.  N is the row width of h.  The CTAs wait for one another, so the whole grid
- * ((N / 128) * n_splits CTAs, one per SM) must be resident at once: T <= 128 and (N / 128) * n_splits <= the
- * GPU's SM count, else B200_ERR_INVALID.  `counter`: one device uint64, zero before its first use and then
- * left alone (it only grows; no reset between launches or CUDA-graph replays); launches that share a counter
- * must not overlap on the GPU and must have the same grid. */
-int32_t b200_op_w4_gemm_umma_norm(const void* chunks, const void* x, int32_t ldx, float* parts, int32_t T, int32_t K,
-                                  int32_t N, int32_t G, int32_t n_splits, float* h, const void* gamma, float eps, void* xn,
-                                  uint64_t* counter, void* stream);
 /* tcgen05/TMEM GEMM with dense fp16 weights W[N, K] fed by TMA (lm_head); N % 128 == 0, K % 64 == 0. */
 int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T,
                               int32_t K, int32_t N, int32_t accumulate, void* stream);

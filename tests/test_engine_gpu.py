@@ -322,33 +322,6 @@ def test_more_requests_than_sequences_and_kv_blocks():
     assert st["requests_finished"] == 24 and st["kv_blocks_free"] == st["kv_blocks_total"]
 
 
-def test_norm_tail_changes_no_bit(monkeypatch):
-    """The decode path with the residual add + RMSNorm folded into the o_proj / down_proj kernels (default) against
-    the separate-kernel path (VGATE_B200_NORM_TAIL=0): identical logits and tokens, bit for bit, at a batch that
-    shares rows among the CTAs unevenly (13), at 64 and above one 64-row tile (100)."""
-    from vgate_b200.engine import Engine
-    dims = PRESETS["qwen2.5-1.5b-awq-l4"]
-    ckpt = synthetic_checkpoint(dims, seed=5)
-    out = {}
-    for flag in ("1", "0"):
-        monkeypatch.setenv("VGATE_B200_NORM_TAIL", flag)
-        eng = Engine(dims, max_seqs=128, max_model_len=96, max_batch_tokens=4096).load_checkpoint(ckpt)
-        try:
-            res = []
-            for n in (13, 64, 100):
-                prompts = np.random.default_rng(n).integers(0, dims.vocab, size=(n, 20), dtype=np.int32)
-                toks, logits, _ = eng.generate_batch(prompts, 6, n_logit_steps=3)
-                res.append((toks, logits))
-            st = eng.stats()
-        finally:
-            eng.close()
-        out[flag] = (res, st["kernel_launches"])
-    for (ta, la), (tb, lb) in zip(out["1"][0], out["0"][0]):
-        assert np.array_equal(ta, tb)
-        assert np.array_equal(la, lb)
-    assert out["1"][1] < out["0"][1]              # two norm kernels less per layer and decode step
-
-
 def test_chunked_prefill_interleaves_with_decode_and_changes_nothing(monkeypatch):
     """Prompts that arrive while other sequences decode are prefilled in chunks that alternate with decode steps
     (VGATE_B200_PREFILL_CHUNK, here 48 tokens so that a 300-token prompt takes 7 passes): every sequence still

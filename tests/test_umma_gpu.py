@@ -198,53 +198,3 @@ def test_w4_umma_two_row_tiles_per_cta_bitwise():
     check(lib().b200_op_w4_gemm_umma(ptr(chp), ptr(xd), K, ptr(as_), N // 2, None, 128, K, N, 128, 2, 1, 0, stream()))
     assert torch.equal(ab[:128].view(torch.int16), as_.view(torch.int16))
     assert ab[1000:].float().abs().sum().item() > 0
-
-
-@pytest.mark.parametrize("K,N,splits", [(1536, 1536, 4), (8960, 1536, 12)])
-@pytest.mark.parametrize("T", [1, 17, 64, 100, 128])
-def test_w4_umma_norm_tail_equals_gemm_then_rmsnorm(K, N, splits, T):
-    """o_proj / down_proj with the residual add + RMSNorm finished inside the GEMM kernel (every CTA of the grid
-    waits for the others, then the token rows are shared out) == the split-K GEMM followed by b200_op_rmsnorm,
-    bit for bit; twice in a row on one counter (it only grows), and against fp64."""
-    rng = np.random.default_rng(K + T)
-    qw, qz, sc = random_awq(rng, K, N)
-    wq, s, z = repack(qw, qz, sc)
-    ch = tile(wq, s, z, K, N)
-    splits = lib().b200_op_w4_effective_splits(K, 128, splits)
-    x = rng.standard_normal((T, K)).astype(np.float16)
-    h0 = rng.standard_normal((T, N)).astype(np.float32)
-    gamma = (1.0 + 0.1 * rng.standard_normal(N)).astype(np.float16)
-    xd, gd = dev(x), dev(gamma)
-    # reference path: partials, then the norm kernel
-    parts_a = torch.zeros((splits, T, N), dtype=torch.float32, device="cuda")
-    h_a = dev(h0)
-    xn_a = torch.zeros((T, N), dtype=torch.float16, device="cuda")
-    check(lib().b200_op_w4_gemm_umma(ptr(ch), ptr(xd), K, ptr(parts_a), N, None, T, K, N, 128, 0, splits, T * N, stream()))
-    check(lib().b200_op_rmsnorm(ptr(h_a), ptr(parts_a), splits, T * N, ptr(gd), 1e-6, None, T, N, ptr(xn_a), stream()))
-    counter = torch.zeros(1, dtype=torch.int64, device="cuda")
-    for rep in range(2):
-        parts_b = torch.zeros((splits, T, N), dtype=torch.float32, device="cuda")
-        h_b = dev(h0)
-        xn_b = torch.zeros((T, N), dtype=torch.float16, device="cuda")
-        check(lib().b200_op_w4_gemm_umma_norm(ptr(ch), ptr(xd), K, ptr(parts_b), T, K, N, 128, splits, ptr(h_b), ptr(gd),
-                                              1e-6, ptr(xn_b), ptr(counter), stream()))
-        assert torch.equal(parts_a, parts_b)
-        assert torch.equal(h_a, h_b), rep
-        assert torch.equal(xn_a, xn_b), rep
-        assert int(counter.item()) == (rep + 1) * (N // 128) * splits
-    ref_h = h0.astype(np.float64) + x.astype(np.float64) @ dequantize_awq(qw, qz, sc, 128).astype(np.float64)
-    assert np.abs(h_b.cpu().numpy() - ref_h).max() < TOL
-    ref_xn = ref_h / np.sqrt((ref_h ** 2).mean(-1, keepdims=True) + 1e-6) * gamma.astype(np.float64)
-    assert np.abs(xn_b.cpu().numpy().astype(np.float64) - ref_xn).max() < 4e-3
-
-
-def test_w4_umma_norm_tail_refuses_grids_that_cannot_be_resident():
-    K, N, T = 1536, 1536, 200                      # two token tiles
-    ch = torch.zeros(lib().b200_op_w4_tile_bytes(K, N, 128), dtype=torch.uint8, device="cuda")
-    z = torch.zeros(8 * 200 * 1536, dtype=torch.float32, device="cuda")
-    from vgate_b200 import _lib
-    code = lib().b200_op_w4_gemm_umma_norm(ptr(ch), ptr(z), K, ptr(z), T, K, N, 128, 4, ptr(z), ptr(z), 1e-6, ptr(z), ptr(z), stream())
-    assert code == _lib.ERR_INVALID
-    code = lib().b200_op_w4_gemm_umma_norm(ptr(ch), ptr(z), K, ptr(z), 64, K, 8 * N, 128, 4, ptr(z), ptr(z), 1e-6, ptr(z), ptr(z), stream())
-    assert code == _lib.ERR_INVALID                # 96 tiles x 4 splits = 384 CTAs cannot wait for one another on 148 SMs
-    torch.cuda.synchronize()

@@ -68,7 +68,6 @@ SIGNATURES = {
     "b200_op_w4_tile_bytes": (_i64, [_i32, _i32, _i32]),
     "b200_op_w4_gemm_umma": (_i32, [_vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i64, _vp]),
     "b200_op_w4_effective_splits": (_i32, [_i32, _i32, _i32]),
-    "b200_op_w4_gemm_umma_norm": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _f32, _vp, _vp, _vp]),
     "b200_debug_umma_trace": (None, [_vp]),
     "b200_debug_umma_trace_grid": (None, [_vp, _i32, _i32]),
     "b200_debug_attn_trace": (None, [_vp]),

@@ -227,23 +227,6 @@ struct b200_engine {
   int debug_skip = getenv("VGATE_B200_DEBUG_SKIP") ? atoi(getenv("VGATE_B200_DEBUG_SKIP")) : 0;
   bool skip(int bit) const { return (debug_skip >> bit) & 1; }
   DevMem parts;                                  // fp32 split-K partials [splits][T][N]
-  // Norm tail: o_proj and down_proj of a decode pass finish the residual add + RMSNorm themselves (one kernel
-  // boundary less per sub-layer; same bits as the separate rmsnorm kernel).  VGATE_B200_NORM_TAIL=0 switches it off.
-  bool norm_tail_enabled = !(getenv("VGATE_B200_NORM_TAIL") && atoi(getenv("VGATE_B200_NORM_TAIL")) == 0);
-  DevMem norm_counters;                          // 2 x uint64 arrival counters (o_proj, down_proj), only ever grow
-  bool norm_tail_ok(int T) const {
-    if (!norm_tail_enabled || !use_umma(T) || debug_skip != 0 || debug_gemv_mask != 0) return false;
-    for (int i : {1, 3}) {
-      const W4Linear& a = layers[0].lin[i];
-      if (dense) {
-        if (umma_dense_effective_splits(a.K, splits[i]) < 2 || umma_pick_nt(T, false) < T ||
-            !umma_dense_norm_tail_ok(T, a.K, a.N, splits[i], cfg.device)) return false;
-      } else if (umma_w4_effective_splits(a.K, a.G, splits[i]) < 2 || !umma_norm_tail_ok(T, a.K, a.N, a.G, splits[i], cfg.device)) {
-        return false;
-      }
-    }
-    return true;
-  }
   DevMem attn_scratch, attn_counters;            // flash-decoding partials + per-(row, kv head) arrival counters
   // KV splits of the decode attention across CTAs.  1: the four warps of a CTA already take different
   // 64-token chunks, and a split count that followed the batch size would make bits batch-dependent.
@@ -255,10 +238,8 @@ struct b200_engine {
   // token tiles enough and write the result once (at 12 800 tokens the partials of the down projection
   // alone were 0.9 GB written and read back per layer).  Which of the two a token goes through is decided
   // by its request's state (prompt token or generated token), never by what else is in the batch.
-  // tail (split-K projections of a decode pass only): the GEMM also performs the residual add and the RMSNorm that
-  // follow it (UmmaNormTail); *n_parts_out is then 0 -- nothing is left pending.
   int linear(const LayerWeights& lw, int i, const __half* x, int64_t x_rows, float* y, int ldy, int T, bool accumulate,
-             int* n_parts_out, cudaStream_t st, float* pbuf, bool split_k, const UmmaNormTail* tail = nullptr) {
+             int* n_parts_out, cudaStream_t st, float* pbuf, bool split_k) {
     const W4Linear& w = lw.lin[i];
     *n_parts_out = 0;
     if (dense) {
@@ -268,10 +249,9 @@ struct b200_engine {
       if ((rc = get_map(x, x_rows, w.K, nt, &mx)) || (rc = get_map(lw.dense[i].p, w.N, w.K, 128, &mw))) return rc;
       const int ns = split_k ? umma_dense_effective_splits(w.K, splits[i]) : 1;
       if (ns > 1) {
-        *n_parts_out = tail ? 0 : ns;
-        return launch_umma_f16(*mw, w.K, w.N, *mx, nt, T, pbuf, w.N, kUmmaPartialF32, st, ns, (int64_t)T * w.N, nullptr, bf16, tail);
+        *n_parts_out = ns;
+        return launch_umma_f16(*mw, w.K, w.N, *mx, nt, T, pbuf, w.N, kUmmaPartialF32, st, ns, (int64_t)T * w.N, nullptr, bf16);
       }
-      if (tail) { set_last_error("norm tail requested for a projection that is not split"); return B200_ERR_STATE; }
       if (i == 2) return launch_umma_f16(*mw, w.K, w.N, *mx, nt, T, y, ldy, kUmmaSwigluF16, st, 1, 0, nullptr, bf16);
       return launch_umma_f16(*mw, w.K, w.N, *mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, st, 1, 0,
                              accumulate ? nullptr : w.bias, bf16);
@@ -283,10 +263,9 @@ struct b200_engine {
     if (rc) return rc;
     const int ns = split_k ? umma_w4_effective_splits(w.K, w.G, splits[i]) : 1;
     if (ns > 1) {
-      *n_parts_out = tail ? 0 : ns;
-      return launch_umma_w4(lw.ulin[i], *mx, nt, T, pbuf, w.N, kUmmaPartialF32, ns, (int64_t)T * w.N, st, tail);
+      *n_parts_out = ns;
+      return launch_umma_w4(lw.ulin[i], *mx, nt, T, pbuf, w.N, kUmmaPartialF32, ns, (int64_t)T * w.N, st);
     }
-    if (tail) { set_last_error("norm tail requested for a projection that is not split"); return B200_ERR_STATE; }
     if (i == 2)    // gate_up: fused SwiGLU epilogue writes fp16 act [T, I] (y is the act buffer)
       return launch_umma_w4(lw.ulin[i], *mx, nt, T, y, ldy, kUmmaSwigluF16, 1, 0, st);
     return launch_umma_w4(lw.ulin[i], *mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, 1, 0, st);
@@ -326,17 +305,14 @@ struct b200_engine {
     if ((rc = launch_embed(embed.as<__half>(), d_ids.as<int32_t>() + r0, T, H, hh, st, bf16))) return rc;
     int pend = 0;                 // split-K partials of the previous projection still to be added into h
     const int64_t pend_stride = (int64_t)T * H;
-    const bool tail = decode_rows && r0 == 0 && norm_tail_ok(T);
-    bool normed = false;          // xx already holds this layer's normed input (written by the previous down's tail)
     for (int l = 0; l < L; ++l) {
       LayerWeights& w = layers[l];
       __half* kc = k_cache.as<__half>() + layer_kv_offset(l);
       __half* vc = v_cache.as<__half>() + layer_kv_offset(l);
       int np = 0;
-      if (!normed && !skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln1.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st, bf16)))
+      if (!skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln1.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st, bf16)))
         return rc;
       pend = 0;
-      normed = false;
       if (!skip(1) && (rc = linear(w, 0, xx, xrows, qq, QKV, T, false, &np, st, pbuf, decode_rows))) return rc;
       const float* qsrc = np ? pbuf : qq;
       const __half* qbias = np ? w.bias_qkv.as<__half>() : nullptr;
@@ -355,12 +331,8 @@ struct b200_engine {
         } else if (!skip(3) && (rc = launch_paged_attn(qhh, kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq, btrow, ctx, T, NH,
                                                        NKV, 1, nullptr, nullptr, aa, st, bf16))) return rc;
       }
-      UmmaNormTail nt{};
-      if (tail) {
-        nt.counter = norm_counters.as<unsigned long long>(); nt.h = hh; nt.gamma = w.ln2.as<__half>(); nt.xn = xx; nt.eps = cfg.rms_eps;
-      }
-      if (!skip(4) && (rc = linear(w, 1, aa, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows, tail ? &nt : nullptr))) return rc;
-      if (!tail && !skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st, bf16)))
+      if (!skip(4) && (rc = linear(w, 1, aa, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows))) return rc;
+      if (!skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st, bf16)))
         return rc;
       pend = 0;
       if (use_umma(T) && !(debug_gemv_mask >> 2 & 1)) {
@@ -370,16 +342,9 @@ struct b200_engine {
         if ((rc = launch_swiglu(gu.as<float>() + (size_t)r0 * 2 * I, T, I, cc, st))) return rc;
       }
       if (np) { set_last_error("gate_up projection must not be split"); return B200_ERR_STATE; }
-      if (tail) {               // down's tail normalises for the next layer, or for the LM head after the last one
-        const bool last = l + 1 == L;
-        nt.counter = norm_counters.as<unsigned long long>() + 1;
-        nt.gamma = last ? final_norm.as<__half>() : layers[l + 1].ln1.as<__half>();
-        nt.xn = last ? xn_last.as<__half>() + (size_t)r0 * H : xx;
-        normed = true;
-      }
-      if (!skip(6) && (rc = linear(w, 3, cc, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows, tail ? &nt : nullptr))) return rc;
+      if (!skip(6) && (rc = linear(w, 3, cc, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows))) return rc;
     }
-    *pend_out = (tail && L > 0) ? -1 : pend;      // -1: the final norm is done as well (xn_last is written)
+    *pend_out = pend;
     return B200_OK;
   }
 
@@ -392,9 +357,8 @@ struct b200_engine {
     {
       int pend = 0;
       if ((rc = layers_pass(0, T, decode_rows, stream, parts.as<float>(), &pend))) return rc;
-      // decode rows: n_rows == T and row r is token r, which is what the last down projection's norm tail wrote
-      if (pend >= 0 && (rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, (int64_t)T * H, final_norm.as<__half>(), cfg.rms_eps,
-                                            rows, n_rows, H, xn_last.as<__half>(), stream, bf16))) return rc;
+      if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, (int64_t)T * H, final_norm.as<__half>(), cfg.rms_eps,
+                               rows, n_rows, H, xn_last.as<__half>(), stream, bf16))) return rc;
     }
     const __half* head = cfg.tie_embeddings ? embed.as<__half>() : lm_head_w.as<__half>();
     bool fused = false;
@@ -1126,8 +1090,7 @@ int32_t b200_engine_finalize(b200_engine* e) {
       if (eff > 1) part_elems = std::max(part_elems, (size_t)eff * S * a.N);   // split-K only runs on decode passes (<= max_seqs rows)
     }
   }
-  if ((rc = e->parts.alloc(part_elems * 4)) || (rc = e->norm_counters.alloc(2 * sizeof(unsigned long long)))) return rc;
-  B200_CUDA(cudaMemset(e->norm_counters.p, 0, e->norm_counters.bytes));
+  if ((rc = e->parts.alloc(part_elems * 4))) return rc;
   if ((rc = e->attn_scratch.alloc(attn_scratch_floats(c.max_seqs, e->NH, e->NKV, b200_engine::kDecodeSplits) * 4)) ||
       (rc = e->attn_counters.alloc((size_t)c.max_seqs * e->NKV * 4)))
     return rc;
@@ -1162,7 +1125,7 @@ void b200_engine_destroy(b200_engine* e) {
   DevMem* all[] = {&e->embed, &e->lm_head_w, &e->final_norm, &e->cos_t, &e->sin_t, &e->k_cache, &e->v_cache, &e->h,
                    &e->xn, &e->qkv, &e->qh, &e->attn, &e->gu, &e->act, &e->xn_last, &e->logits, &e->amax, &e->d_ids, &e->d_pos,
                    &e->d_slot, &e->d_btrow, &e->d_ctx, &e->d_lastrows, &e->d_bt, &e->d_temp, &e->d_topp, &e->d_seed,
-                   &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens, &e->parts, &e->norm_counters, &e->attn_scratch, &e->attn_counters, &e->d_tiles};
+                   &e->d_step, &e->d_next, &e->d_ngen, &e->d_out_tokens, &e->parts, &e->attn_scratch, &e->attn_counters, &e->d_tiles};
   for (DevMem* m : all) m->release();
   for (int i = 0; i < 2; ++i) {
     if (e->ev_a[i]) cudaEventDestroy(e->ev_a[i]);
@@ -1463,23 +1426,6 @@ int32_t b200_op_w4_gemm_umma(const void* chunks, const void* x, int32_t ldx, flo
   if (rc) return rc;
   const int mode = n_splits > 1 ? kUmmaPartialF32 : epilogue == 2 ? kUmmaSwigluF16 : accumulate ? kUmmaAccumF32 : kUmmaStoreF32;
   return launch_umma_w4(w, mx, nt, T, y, ldy, mode, n_splits, part_stride, (cudaStream_t)stream);
-}
-int32_t b200_op_w4_gemm_umma_norm(const void* chunks, const void* x, int32_t ldx, float* parts, int32_t T, int32_t K,
-                                  int32_t N, int32_t G, int32_t n_splits, float* h, const void* gamma, float eps, void* xn,
-                                  uint64_t* counter, void* stream) {
-  B200_REQUIRE(chunks && x && parts && h && gamma && xn && counter, "w4_gemm_umma_norm: null argument");
-  B200_REQUIRE(T > 0 && n_splits >= 2 && n_splits == umma_w4_effective_splits(K, G, n_splits),
-               "w4_gemm_umma_norm: T > 0, n_splits >= 2 and equal to b200_op_w4_effective_splits(K, G, n_splits)");
-  UmmaW4 w;
-  w.chunks = (const unsigned char*)chunks; w.K = K; w.N = N; w.G = G;
-  const int nt = umma_pick_nt(T, true);
-  CUtensorMap mx;
-  int rc = make_tensor_map_f16(&mx, x, T, K, ldx, nt);
-  if (rc) return rc;
-  UmmaNormTail tail;
-  tail.counter = reinterpret_cast<unsigned long long*>(counter); tail.h = h; tail.gamma = (const __half*)gamma;
-  tail.xn = (__half*)xn; tail.eps = eps;
-  return launch_umma_w4(w, mx, nt, T, parts, N, kUmmaPartialF32, n_splits, (int64_t)T * N, (cudaStream_t)stream, &tail);
 }
 void b200_debug_umma_trace(void* dev_buf) { umma_set_trace((unsigned long long*)dev_buf, 0, 0); }
 void b200_debug_umma_trace_grid(void* dev_buf, int32_t grid_x, int32_t grid_z) { umma_set_trace((unsigned long long*)dev_buf, grid_x, grid_z); }

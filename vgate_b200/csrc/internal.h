@@ -66,14 +66,6 @@ struct UmmaW4 {
   const unsigned char* next_chunks = nullptr;
   int64_t next_bytes = 0;
 };
-// Fused tail of a split-K projection that feeds a residual add + RMSNorm (o_proj, down_proj): see UmmaParams.
-struct UmmaNormTail {
-  unsigned long long* counter = nullptr;   // device, zero-initialised once, only ever grows (null: no tail)
-  float* h = nullptr;                      // [T, N] fp32 residual stream, updated in place
-  const __half* gamma = nullptr;           // [N] norm weight of the NEXT sub-layer
-  __half* xn = nullptr;                    // [T, N] fp16 normalised activations out
-  float eps = 0.f;
-};
 enum { kUmmaStoreF32 = 0, kUmmaAccumF32 = 1, kUmmaPartialF32 = 2, kUmmaSwigluF16 = 3, kUmmaArgmaxF32 = 4 };
 
 size_t umma_w4_chunk_bytes(int K, int N, int G);
@@ -84,14 +76,11 @@ int make_tensor_map_f16(CUtensorMap* map, const void* base, int64_t rows, int64_
 int umma_pick_nt(int T, bool w4);
 void umma_set_trace(unsigned long long* dev_buf, int grid_x, int grid_z);
 int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T, float* y, int ldy, int mode,
-                   int n_splits, int64_t part_stride, cudaStream_t s, const UmmaNormTail* norm = nullptr);
-// May this projection run with the norm tail?  Every CTA of the grid must be resident at once.
-bool umma_norm_tail_ok(int T, int K, int N, int G, int n_splits, int device);
+                   int n_splits, int64_t part_stride, cudaStream_t s);
 int launch_umma_f16(const CUtensorMap& map_w, int K, int N, const CUtensorMap& map_x, int nt_sel, int T, float* y,
                     int ldy, int mode, cudaStream_t s, int n_splits = 1, int64_t part_stride = 0, const __half* bias = nullptr,
-                    bool bf16 = false, const UmmaNormTail* norm = nullptr);
+                    bool bf16 = false);
 int umma_dense_effective_splits(int K, int n_splits);
-bool umma_dense_norm_tail_ok(int T, int K, int N, int n_splits, int device);
 
 int launch_awq_repack(const int32_t* qweight, const int32_t* qzeros, const __half* scales, int K, int N, int G,
                       uint32_t* wq, __half* sc, __half* zp, int row_offset, cudaStream_t s);

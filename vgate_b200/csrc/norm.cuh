@@ -1,5 +1,5 @@
 // Residual-sum + RMSNorm arithmetic shared by rmsnorm_kernel (ops_basic.cu: one 4-CTA cluster per row) and
-// the norm tail of the split-K GEMM (ops_umma.cu: the four producer warpgroups of one CTA per row).  A row is cut in
+// experiments that ran the same arithmetic inside other kernels (history: 8d75821 persistent kernel, f28aa97 norm tail of the split-K GEMM).  A row is cut in
 // four quarters; 128 threads own a quarter; every quarter's warps contribute one partial sum of squares
 // each, and the 16 partials are added in one fixed order, so both callers produce the same bits.
 #pragma once

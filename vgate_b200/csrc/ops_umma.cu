@@ -116,29 +116,6 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       umma_epilogue<NT>(p.mode, p.y, p.ldy, p.mode == kPartialF32 ? (size_t)split * p.part_stride : 0, p.bias, p.T, tok0,
                         nt * MT + t, reinterpret_cast<float*>(smem), tmem + (uint32_t)(t * (Cfg::kAccCols / MT)), tr, p.bf16 != 0);
     }
-    if constexpr (MT == 1) {
-      if (p.norm.counter) {
-        // ---- norm tail: split-K reduction + residual add + RMSNorm, without a kernel boundary ----
-        // Same arithmetic, same order, same bits as rmsnorm_kernel (norm.cuh): warpgroup q owns quarter q of a row.
-        __threadfence();                                         // this thread's partial stores, GPU-wide
-        asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");
-        const unsigned long long n_ctas = (unsigned long long)gridDim.x * gridDim.z;
-        if (threadIdx.x == 0) grid_rendezvous(p.norm.counter, n_ctas);
-        asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");
-        grid_dep_wait();                                         // h / gamma are older than the upstream kernel: returns at once
-        float (*red)[kNormCluster][kNormWarps] = reinterpret_cast<float (*)[kNormCluster][kNormWarps]>(smem);   // the staging tile is free
-        const int q = threadIdx.x >> 7, tid = threadIdx.x & (kNormThreads - 1);
-        int it = 0;
-        for (int r = blockIdx.x + gridDim.x * blockIdx.z; r < p.T; r += (int)n_ctas, ++it) {
-          float4 v[kNormMaxPerThread];
-          const float ss = rms_quarter_load<12>(p.norm.h, p.y, (int)gridDim.z, p.part_stride, r, q, p.N, tid, v);
-          if ((tid & 31) == 0) red[it & 1][q][tid >> 5] = ss;
-          asm volatile("bar.sync 1, %0;" ::"n"(kProducerWarps * 32) : "memory");
-          const float rs = rms_scale(red[it & 1], p.N, p.norm.eps);
-          rms_quarter_store(v, rs, p.norm.gamma, p.norm.xn, r, q, p.N, tid, p.bf16 != 0);
-        }
-      }
-    }
   } else if (warp == kWarpTmaW) {
     // ===================== TMA: packed weight chunks (do not depend on upstream kernels) =====================
     if (kW4 && elect_one()) {
@@ -365,27 +342,8 @@ int umma_w4_effective_splits(int K, int G, int n_splits) {
 int umma_pick_nt(int T, bool w4) { return T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : (T <= 128 || w4) ? 128 : 256; }
 
 // W4: y = x . W^T.  n_splits > 1 requires mode == kPartialF32 (y then holds n_splits partial tensors).
-static int sm_count(int device) {
-  static std::mutex mu;
-  static int cached[64] = {0};
-  std::lock_guard<std::mutex> lk(mu);
-  if (device < 0 || device >= 64) return 0;
-  if (!cached[device]) cudaDeviceGetAttribute(&cached[device], cudaDevAttrMultiProcessorCount, device);
-  return cached[device];
-}
-
-// The norm tail makes CTAs wait for one another: every CTA of the grid must hold an SM at the same time (the
-// kernel runs one CTA per SM), the token rows must fit one tile (grid.y == 1) and the row must be what the norm
-// code supports.
-bool umma_norm_tail_ok(int T, int K, int N, int G, int n_splits, int device) {
-  if (T <= 0 || T > 128 || N % 128 != 0 || K % G != 0 || N % (4 * kNormCluster) != 0 || N > kNormCluster * kNormThreads * 4 * kNormMaxPerThread)
-    return false;
-  const int grid = (N / kUmmaM) * umma_w4_effective_splits(K, G, n_splits);
-  return grid <= sm_count(device);
-}
-
 int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T, float* y, int ldy, int mode,
-                   int n_splits, int64_t part_stride, cudaStream_t s, const UmmaNormTail* norm) {
+                   int n_splits, int64_t part_stride, cudaStream_t s) {
   B200_REQUIRE(w.N % 128 == 0 && w.K % w.G == 0 && (w.G == 64 || w.G == 128), "umma_w4: N % 128, K % G, G in {64, 128}");
   B200_REQUIRE(n_splits >= 1 && (n_splits == 1 || mode == kPartialF32), "umma_w4: split-K needs partial mode");
   B200_REQUIRE(mode != kSwigluF16 || nt_sel <= 128, "umma_w4: SwiGLU epilogue needs a token tile <= 128");
@@ -395,14 +353,6 @@ int launch_umma_w4(const UmmaW4& w, const CUtensorMap& map_x, int nt_sel, int T,
   p.chunks = w.chunks; p.bias = w.bias; p.y = y; p.part_stride = part_stride;
   p.l2_prefetch = w.next_chunks; p.l2_prefetch_bytes = w.next_bytes;
   p.ldy = ldy; p.T = T; p.K = w.K; p.N = w.N; p.G = w.G; p.mode = mode;
-  if (norm && norm->counter) {
-    int dev = 0;
-    B200_CUDA(cudaGetDevice(&dev));
-    B200_REQUIRE(mode == kPartialF32 && ldy == w.N && norm->h && norm->gamma && norm->xn && part_stride == (int64_t)T * w.N &&
-                     umma_norm_tail_ok(T, w.K, w.N, w.G, n_splits, dev),
-                 "umma_w4: the norm tail needs split-K partial mode, dense [T, N] partials, T <= 128 and a grid that fits the GPU at once");
-    p.norm = *norm;
-  }
   const int KG = w.K / w.G, tpg = w.G / kUmmaBK;
   const int groups_per_split = (KG + n_splits - 1) / n_splits;     // split boundaries fall on quantisation groups
   p.kt_per_split = groups_per_split * tpg;
@@ -416,17 +366,9 @@ int umma_dense_effective_splits(int K, int n_splits) {
   return (KT + per - 1) / per;
 }
 
-bool umma_dense_norm_tail_ok(int T, int K, int N, int n_splits, int device) {
-  if (T <= 0 || T > 256 || N % 128 != 0 || K % kUmmaBK != 0 || N % (4 * kNormCluster) != 0 ||
-      N > kNormCluster * kNormThreads * 4 * kNormMaxPerThread)
-    return false;
-  return (N / kUmmaM) * umma_dense_effective_splits(K, n_splits) <= sm_count(device);
-}
-
 // Dense 16-bit weights W[N, K] (fp16 or bf16) by TMA.  n_splits > 1 requires mode == kPartialF32.
 int launch_umma_f16(const CUtensorMap& map_w, int K, int N, const CUtensorMap& map_x, int nt_sel, int T, float* y,
-                    int ldy, int mode, cudaStream_t s, int n_splits, int64_t part_stride, const __half* bias, bool bf16,
-                    const UmmaNormTail* norm) {
+                    int ldy, int mode, cudaStream_t s, int n_splits, int64_t part_stride, const __half* bias, bool bf16) {
   B200_REQUIRE(N % 128 == 0 && K % 64 == 0, "umma_f16: N % 128, K % 64");
   B200_REQUIRE(n_splits >= 1 && (n_splits == 1 || mode == kPartialF32), "umma_f16: split-K needs partial mode");
   if (T == 0) return B200_OK;
@@ -437,14 +379,6 @@ int launch_umma_f16(const CUtensorMap& map_w, int K, int N, const CUtensorMap& m
   const int KT = K / kUmmaBK;
   p.kt_per_split = (KT + n_splits - 1) / n_splits;
   n_splits = (KT + p.kt_per_split - 1) / p.kt_per_split;
-  if (norm && norm->counter) {
-    int dev = 0;
-    B200_CUDA(cudaGetDevice(&dev));
-    B200_REQUIRE(mode == kPartialF32 && ldy == N && norm->h && norm->gamma && norm->xn && part_stride == (int64_t)T * N &&
-                     (T + nt_sel - 1) / nt_sel == 1 && umma_dense_norm_tail_ok(T, K, N, n_splits, dev),
-                 "umma_f16: the norm tail needs split-K partial mode, dense [T, N] partials, one token tile and a grid that fits the GPU at once");
-    p.norm = *norm;
-  }
   return dispatch_nt<false>(nt_sel, map_x, map_w, p, n_splits, s);
 }
 

@@ -6,7 +6,6 @@
 
 #include "common.cuh"
 #include "internal.h"
-#include "norm.cuh"
 
 namespace b200 {
 
@@ -22,7 +21,7 @@ constexpr int kMaxStages = 8, kMaxRing = 12;
 constexpr int kTileABytes = kUmmaM * kUmmaBK * 2;          // 16 KB
 
 enum UmmaMode : int { kStoreF32 = 0, kAccumF32 = 1, kPartialF32 = 2, kSwigluF16 = 3, kArgmaxF32 = 4 };
-static_assert(kNormCluster * kNormThreads == kProducerWarps * 32, "the norm tail maps one producer warpgroup to one row quarter");
+
 
 // ---- PTX wrappers -------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* map, int x, int y, uint64_t* bar) {
@@ -181,28 +180,7 @@ struct UmmaParams {
   int bf16;               // dense path: weights and activations are bf16 (0: fp16).  The W4 path is fp16 only.
   const unsigned char* l2_prefetch;   // weights of the NEXT kernel to pull into L2 (or null), shared out over the CTAs
   int64_t l2_prefetch_bytes;
-  // Norm tail (kPartialF32 with norm.counter != null): once every CTA of the grid has published its split-K
-  // partial, the CTAs share out the token rows and finish what the separate rmsnorm kernel used to do:
-  //   h[t] += sum_s parts[s][t];  xn[t] = fp16(rmsnorm(h[t]) * gamma)      (N == the row width H)
-  UmmaNormTail norm;
 };
-
-// Grid-wide rendezvous of the producer threads' first lane (all CTAs of the grid are co-resident: the launcher
-// checks grid <= SM count and the kernel needs an SM to itself).  `ctr` only ever grows: a launch adds exactly
-// n_ctas, so the arrival that brings it to the next multiple of n_ctas completes the launch's round -- no reset,
-// nothing to clear between CUDA-graph replays.  Bounded like mbar_wait: a scheduling surprise must trap, not hang.
-static __device__ __noinline__ void grid_rendezvous(unsigned long long* ctr, unsigned long long n_ctas) {
-  __threadfence();                                                   // the CTA's partial stores (ordered by the bar.sync before)
-  const unsigned long long old = atomicAdd(ctr, 1ull);
-  const unsigned long long target = (old / n_ctas + 1ull) * n_ctas;
-  unsigned long long seen = old + 1ull;
-#pragma unroll 1
-  for (uint32_t spin = 0; seen < target; ++spin) {
-    if (spin >= (1u << 26)) __trap();
-    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(seen) : "l"(ctr) : "memory");
-  }
-  __threadfence();
-}
 
 __device__ __forceinline__ uint4 lds128(uint32_t saddr) {
   uint4 r;
