@@ -178,6 +178,17 @@ int32_t b200_op_w4_effective_splits(int32_t K, int32_t G, int32_t n_splits);
 /* tcgen05/TMEM GEMM with dense fp16 weights W[N, K] fed by TMA (lm_head); N % 128 == 0, K % 64 == 0. */
 int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, int32_t T,
                               int32_t K, int32_t N, int32_t accumulate, void* stream);
+/* The same kernel with every epilogue of the W4 GEMM, for dense 16-bit checkpoints (Qwen2.5-7B / 14B bf16: vLLM runs
+ * their linears as plain GEMMs, model_executor/layers/linear.py UnquantizedLinearMethod.apply): W[N, K], x[T, K] and bias
+ * in `dtype` (B200_DTYPE_F16 or B200_DTYPE_BF16), fp32 accumulation in tensor memory.  epilogue 0 store (+bias),
+ * 1 accumulate into y, 2 fused SwiGLU -- W then holds gate and up rows interleaved in blocks of 64 (rows 128 t .. 128 t + 63
+ * gate features 64 t .., rows 128 t + 64 .. the matching up features) and y is a 16-bit matrix act[T, N / 2] with row
+ * stride ldy.  n_splits > 1: split-K over 64-wide k tiles into n_splits partial tensors (epilogue 0, no bias), n_splits ==
+ * b200_op_dense_effective_splits(K, n_splits). */
+int32_t b200_op_dense_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, const void* bias, int32_t T,
+                                int32_t K, int32_t N, int32_t dtype, int32_t epilogue, int32_t n_splits, int64_t part_stride,
+                                void* stream);
+int32_t b200_op_dense_effective_splits(int32_t K, int32_t n_splits);
 /* Greedy lm_head (vLLM sampler.py:223-236 greedy branch over LogitsProcessor output): out[t] =
  * argmax_n x[t] . W[n]  (highest logit, lowest index on ties) without writing the [T, N] logits: the
  * GEMM epilogue reduces every 128-row tile to {max, argmax}, a second kernel finishes per token.

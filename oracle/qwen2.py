@@ -16,6 +16,7 @@ Arithmetic modes:
             activations rounded to fp16 where the CUDA path stores fp16 (normed activations, q/k/v after
             RoPE, attention output, SwiGLU output).  Useful to tell rounding-point effects from
             summation-order effects when a logit differs.
+  ``bf16r`` diagnostic, like ``fp16`` with bfloat16 rounding points (the dense bf16 engine path).
   ``bf16``  timing only (``bench.py`` CPU legs): weights and matmul operands in bfloat16, the eager
             CPU arithmetic a PyTorch user of this model would run on the host.
 """
@@ -42,7 +43,11 @@ class Qwen2Dims:
 
 
 def _t(a):
-    return torch.from_numpy(np.ascontiguousarray(a))
+    """numpy -> torch; uint16 arrays are bfloat16 bit patterns (dense bf16 checkpoints)."""
+    a = np.ascontiguousarray(a)
+    if a.dtype == np.uint16:
+        return torch.from_numpy(a.view(np.int16)).view(torch.bfloat16)
+    return torch.from_numpy(a)
 
 
 def rope_table(dims: Qwen2Dims, max_pos: int):
@@ -58,7 +63,7 @@ class OracleQwen2:
     """Batched (equal-length) forward with a dense per-sequence KV cache."""
 
     def __init__(self, dims: Qwen2Dims, ckpt: dict, mode: str = "fp32", max_pos: int = 4096):
-        assert mode in ("fp32", "fp16", "bf16")
+        assert mode in ("fp32", "fp16", "bf16", "bf16r")
         self.d, self.mode = dims, mode
         wdt = torch.bfloat16 if mode == "bf16" else torch.float32
         self.cos, self.sin = rope_table(dims, max_pos)
@@ -99,6 +104,8 @@ class OracleQwen2:
         self.n_cached = 0
 
     def _rnd(self, x):
+        if self.mode == "bf16r":
+            return x.bfloat16().float()
         return x.half().float() if self.mode == "fp16" else x
 
     def _mm(self, x, w):

@@ -73,6 +73,8 @@ SIGNATURES = {
     "b200_debug_attn_trace": (None, [_vp]),
     "b200_debug_timeline": (None, [_vp, _vp, C.c_uint32]),
     "b200_op_f16_gemm_umma": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b200_op_dense_gemm_umma": (_i32, [_vp, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _i64, _vp]),
+    "b200_op_dense_effective_splits": (_i32, [_i32, _i32]),
     "b200_op_lm_head_argmax": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp]),
     "b200_op_f16_gemv": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200_op_rmsnorm": (_i32, [_vp, _vp, _i32, _i64, _vp, _f32, _vp, _i32, _i32, _vp, _vp]),

@@ -1449,6 +1449,29 @@ int32_t b200_op_f16_gemm_umma(const void* w, const void* x, int32_t ldx, float* 
   if ((rc = make_tensor_map_f16(&mw, w, N, K, K, 128))) return rc;
   return launch_umma_f16(mw, K, N, mx, nt, T, y, ldy, accumulate ? kUmmaAccumF32 : kUmmaStoreF32, (cudaStream_t)stream);
 }
+int32_t b200_op_dense_gemm_umma(const void* w, const void* x, int32_t ldx, float* y, int32_t ldy, const void* bias, int32_t T,
+                                int32_t K, int32_t N, int32_t dtype, int32_t epilogue, int32_t n_splits, int64_t part_stride,
+                                void* stream) {
+  B200_REQUIRE(dtype == B200_DTYPE_F16 || dtype == B200_DTYPE_BF16, "dense_gemm_umma: dtype is B200_DTYPE_F16 or B200_DTYPE_BF16");
+  B200_REQUIRE(T >= 0 && n_splits >= 1 && epilogue >= 0 && epilogue <= 2, "dense_gemm_umma: T >= 0, n_splits >= 1, epilogue in 0..2");
+  B200_REQUIRE(n_splits == 1 || (epilogue == 0 && !bias), "dense_gemm_umma: split-K output is raw partials");
+  B200_REQUIRE(epilogue != 2 || !bias, "dense_gemm_umma: SwiGLU epilogue takes no bias");
+  B200_REQUIRE(K > 0 && K % 64 == 0 && n_splits == umma_dense_effective_splits(K, n_splits),
+               "dense_gemm_umma: K % 64 == 0 and n_splits must equal b200_op_dense_effective_splits(K, n_splits)");
+  if (T == 0) return B200_OK;
+  const int nt = umma_pick_nt(T, false);
+  CUtensorMap mx, mw;
+  int rc = make_tensor_map_f16(&mx, x, T, K, ldx, nt);
+  if (rc) return rc;
+  if ((rc = make_tensor_map_f16(&mw, w, N, K, K, 128))) return rc;
+  const int mode = n_splits > 1 ? kUmmaPartialF32 : epilogue == 2 ? kUmmaSwigluF16 : epilogue == 1 ? kUmmaAccumF32 : kUmmaStoreF32;
+  return launch_umma_f16(mw, K, N, mx, nt, T, y, ldy, mode, (cudaStream_t)stream, n_splits, part_stride, (const __half*)bias,
+                         dtype == B200_DTYPE_BF16);
+}
+int32_t b200_op_dense_effective_splits(int32_t K, int32_t n_splits) {
+  if (K <= 0 || K % 64 != 0 || n_splits < 1) return B200_ERR_INVALID;
+  return umma_dense_effective_splits(K, n_splits);
+}
 int32_t b200_op_lm_head_argmax(const void* w, const void* x, int32_t ldx, int32_t T, int32_t K, int32_t N, float* scratch,
                                int32_t* out, void* stream) {
   if (T == 0) return B200_OK;

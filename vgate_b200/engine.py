@@ -9,7 +9,7 @@ from ._lib import B200Error  # noqa: F401  (re-export)
 from .weights import ModelDims
 
 _NP_DTYPE = {np.dtype(np.float16): _lib.DTYPE_F16, np.dtype(np.int32): _lib.DTYPE_I32,
-             np.dtype(np.float32): _lib.DTYPE_F32}
+             np.dtype(np.float32): _lib.DTYPE_F32, np.dtype(np.uint16): _lib.DTYPE_BF16}   # uint16 = bf16 bit patterns
 
 
 def rope_table(dims: ModelDims, n_pos: int):
@@ -36,6 +36,8 @@ class Engine:
         cfg.max_seqs, cfg.max_model_len, cfg.max_batch_tokens = max_seqs, max_model_len, max_batch_tokens
         cfg.kv_bytes, cfg.eos_token_id = kv_bytes, eos_token_id
         cfg.use_cuda_graphs, cfg.gemm_path = int(use_cuda_graphs), gemm_path
+        cfg.act_dtype = _lib.DTYPE_BF16 if getattr(dims, "dtype", "fp16") == "bf16" else _lib.DTYPE_F16
+        cfg.dense_weights = int(getattr(dims, "quant", "awq") == "none")
         self.cfg = cfg
         h = C.c_void_p()
         _lib.check(self._lib.b200_engine_create(C.byref(cfg), C.byref(h)))

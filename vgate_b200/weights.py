@@ -25,9 +25,14 @@ class ModelDims:
     rope_theta: float = 1e6
     group_size: int = 128
     tie_embeddings: bool = True
+    quant: str = "awq"         # "awq": int4 linears (qweight / qzeros / scales) | "none": dense 16-bit linears (.weight)
+    dtype: str = "fp16"        # 16-bit storage of activations and non-quantised tensors: "fp16" | "bf16" (dense only)
 
     def to_dict(self):
-        return asdict(self)
+        """The architecture fields (what the oracle's Qwen2Dims takes)."""
+        d = asdict(self)
+        d.pop("quant"); d.pop("dtype")
+        return d
 
 
 PEAKED_EMBED_STD = 1.5       # embedding scale of the ``peaked`` synthetic profile (see synthetic_checkpoint)
@@ -46,7 +51,28 @@ PRESETS = {
     "qwen2.5-1.5b-awq-l4-untied": ModelDims(n_layers=4, tie_embeddings=False),
     "tiny-awq": ModelDims(hidden=256, intermediate=512, n_layers=2, n_heads=2, n_kv_heads=1,
                           head_dim=128, vocab=1024),
+    # Config #4 / #5 (public HF config.json values): dense bf16 checkpoints
+    "qwen2.5-7b-bf16": ModelDims(hidden=3584, intermediate=18944, n_layers=28, n_heads=28, n_kv_heads=4, vocab=152064,
+                                 tie_embeddings=False, quant="none", dtype="bf16"),
+    "qwen2.5-7b-bf16-l2": ModelDims(hidden=3584, intermediate=18944, n_layers=2, n_heads=28, n_kv_heads=4, vocab=152064,
+                                    tie_embeddings=False, quant="none", dtype="bf16"),
+    "qwen2.5-14b-bf16": ModelDims(hidden=5120, intermediate=13824, n_layers=48, n_heads=40, n_kv_heads=8, vocab=152064,
+                                  tie_embeddings=False, quant="none", dtype="bf16"),
+    "tiny-bf16": ModelDims(hidden=256, intermediate=512, n_layers=2, n_heads=4, n_kv_heads=2, head_dim=128, vocab=1024,
+                           tie_embeddings=False, quant="none", dtype="bf16"),
+    "tiny-f16-dense": ModelDims(hidden=256, intermediate=512, n_layers=2, n_heads=2, n_kv_heads=1, head_dim=128, vocab=1024,
+                                quant="none", dtype="fp16"),
 }
+
+
+def to_bf16_bits(a) -> np.ndarray:
+    """fp32 array -> uint16 array of bfloat16 bit patterns (round to nearest even; numpy has no bfloat16)."""
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+    return ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+
+
+def from_bf16_bits(a) -> np.ndarray:
+    return (np.asarray(a, dtype=np.uint16).astype(np.uint32) << 16).view(np.float32)
 
 
 def linear_shapes(d: ModelDims):
@@ -97,8 +123,8 @@ def synthetic_checkpoint(d: ModelDims, seed: int = 0, w_std: float = 0.02, profi
     G = d.group_size
     ck = {}
 
-    def f16(a):
-        return np.asarray(a, dtype=np.float16)
+    def f16(a):                          # the checkpoint's 16-bit type: fp16 arrays, or uint16 arrays of bf16 bits
+        return to_bf16_bits(a) if d.dtype == "bf16" else np.asarray(a, dtype=np.float16)
 
     peaked = profile == "peaked"
     e_std = PEAKED_EMBED_STD if peaked else w_std
@@ -117,6 +143,11 @@ def synthetic_checkpoint(d: ModelDims, seed: int = 0, w_std: float = 0.02, profi
         ck[p + "input_layernorm.weight"] = f16(1.0 + 0.1 * rng.standard_normal(d.hidden, dtype=np.float32))
         ck[p + "post_attention_layernorm.weight"] = f16(1.0 + 0.1 * rng.standard_normal(d.hidden, dtype=np.float32))
         for name, K, N, has_bias in linear_shapes(d):
+            if d.quant == "none":            # dense: HF layout weight[out, in]
+                ck[p + name + ".weight"] = f16(rng.standard_normal((N, K), dtype=np.float32) * w_std)
+                if has_bias:
+                    ck[p + name + ".bias"] = f16(rng.standard_normal(N, dtype=np.float32) * w_std)
+                continue
             assert K % G == 0 and N % 8 == 0, (name, K, N)
             ck[p + name + ".qweight"] = rng.integers(0, 2**32, size=(K, N // 8), dtype=np.uint32).view(np.int32)
             ck[p + name + ".qzeros"] = rng.integers(0, 2**32, size=(K // G, N // 8), dtype=np.uint32).view(np.int32)
@@ -128,14 +159,19 @@ def synthetic_checkpoint(d: ModelDims, seed: int = 0, w_std: float = 0.02, profi
 
 
 def load_hf_checkpoint(model_dir: str):
-    """(dims, checkpoint dict) from a mounted HF AWQ model directory."""
-    from safetensors.numpy import load_file
+    """(dims, checkpoint dict) from a mounted HF model directory: AWQ int4 (quantization_config present) or a
+    dense fp16 / bf16 checkpoint (``torch_dtype``).  bf16 tensors come back as uint16 bit patterns."""
     with open(os.path.join(model_dir, "config.json")) as f:
         c = json.load(f)
-    q = c.get("quantization_config", {})
-    if q.get("quant_method", "awq") != "awq" or q.get("bits", 4) != 4:
+    q = c.get("quantization_config")
+    if q is not None and (q.get("quant_method", "awq") != "awq" or q.get("bits", 4) != 4):
         raise ValueError(f"unsupported quantization_config {q}")
-    d = ModelDims(
+    dtype = "fp16" if q is not None else {"bfloat16": "bf16", "float16": "fp16"}.get(str(c.get("torch_dtype", "bfloat16")))
+    if dtype is None:
+        raise ValueError(f"unsupported torch_dtype {c.get('torch_dtype')}")
+    q = q or {}
+    d = ModelDims(quant="awq" if c.get("quantization_config") is not None else "none", dtype=dtype,
+                  
         hidden=c["hidden_size"], intermediate=c["intermediate_size"], n_layers=c["num_hidden_layers"],
         n_heads=c["num_attention_heads"], n_kv_heads=c["num_key_value_heads"],
         head_dim=c.get("head_dim") or c["hidden_size"] // c["num_attention_heads"],
@@ -144,5 +180,43 @@ def load_hf_checkpoint(model_dir: str):
     ck = {}
     for fn in sorted(os.listdir(model_dir)):
         if fn.endswith(".safetensors"):
-            ck.update(load_file(os.path.join(model_dir, fn)))
+            ck.update(_load_safetensors(os.path.join(model_dir, fn)))
     return d, ck
+
+
+def _load_safetensors(path: str) -> dict:
+    """safetensors -> numpy; BF16 tensors (which numpy cannot represent) as uint16 bit patterns."""
+    import struct
+    with open(path, "rb") as f:
+        n = struct.unpack("<Q", f.read(8))[0]
+        header = json.loads(f.read(n))
+        base = 8 + n
+        out = {}
+        np_dt = {"F16": np.float16, "BF16": np.uint16, "F32": np.float32, "I32": np.int32, "I64": np.int64, "U8": np.uint8}
+        for name, meta in header.items():
+            if name == "__metadata__":
+                continue
+            a, b = meta["data_offsets"]
+            f.seek(base + a)
+            out[name] = np.frombuffer(f.read(b - a), dtype=np_dt[meta["dtype"]]).reshape(meta["shape"])
+    return out
+
+
+def save_safetensors(ckpt: dict, path: str, bf16: bool = False) -> None:
+    """numpy checkpoint -> one safetensors file (uint16 arrays are written as BF16 when ``bf16``)."""
+    names = {np.dtype(np.float16): "F16", np.dtype(np.float32): "F32", np.dtype(np.int32): "I32", np.dtype(np.int64): "I64",
+             np.dtype(np.uint8): "U8", np.dtype(np.uint16): "BF16" if bf16 else "U16"}
+    header, blobs, off = {}, [], 0
+    for name, arr in ckpt.items():
+        arr = np.ascontiguousarray(arr)
+        header[name] = {"dtype": names[arr.dtype], "shape": list(arr.shape), "data_offsets": [off, off + arr.nbytes]}
+        blobs.append(arr.tobytes())
+        off += arr.nbytes
+    h = json.dumps(header).encode()
+    h += b" " * (-len(h) % 8)
+    import struct
+    with open(path, "wb") as f:
+        f.write(struct.pack("<Q", len(h)))
+        f.write(h)
+        for b in blobs:
+            f.write(b)
