@@ -5,7 +5,7 @@ token ids, greedy, 256 new tokens, EOS ignored.  Prints one JSON line.  Also che
 greedy tokens against vLLM's on the first prompts (different kernels: near-tie flips are expected).
 
 Not part of the test suite or bench contract: vLLM is third-party, takes minutes to start, and may
-not run offline on every box.  usage: python tools/vllm_b200_baseline.py [batch] [new_tokens]"""
+not run offline on every box.  usage: python tools/vllm_b200_baseline.py [batch] [new_tokens] [preset] [profile]"""
 import json
 import os
 import sys
@@ -46,12 +46,13 @@ def write_model_dir(dims, ckpt, path):
 def main():
     batch = int(sys.argv[1]) if len(sys.argv) > 1 else 64
     new_tokens = int(sys.argv[2]) if len(sys.argv) > 2 else 256
-    preset = "qwen2.5-1.5b-awq"
+    preset = sys.argv[3] if len(sys.argv) > 3 else "qwen2.5-1.5b-awq"
+    profile = sys.argv[4] if len(sys.argv) > 4 else "flat"
     dims = PRESETS[preset]
-    ckpt = synthetic_checkpoint(dims, seed=0)
+    ckpt = synthetic_checkpoint(dims, seed=0, profile=profile)
     rng = np.random.default_rng(1)
     prompts = rng.integers(0, dims.vocab, size=(batch, 128), dtype=np.int32)
-    out = {"impl": "vllm", "preset": preset, "batch": batch, "prompt_len": 128, "new_tokens": new_tokens}
+    out = {"impl": "vllm", "preset": preset, "profile": profile, "batch": batch, "prompt_len": 128, "new_tokens": new_tokens}
     with tempfile.TemporaryDirectory() as d:
         write_model_dir(dims, ckpt, d)
         import vllm
@@ -79,7 +80,7 @@ def main():
         gc.collect()
         torch.cuda.empty_cache()
         from vgate_b200.engine import Engine
-        n = min(batch, 16)
+        n = min(batch, 64)
         eng = Engine(dims, max_seqs=64, max_model_len=512, max_batch_tokens=4096).load_checkpoint(ckpt)
         ours, _, _ = eng.generate_batch(prompts[:n], min(new_tokens, 32))
         eng.close()
