@@ -50,7 +50,7 @@ extern "C" {
 #define B200_DTYPE_F32 2
 #define B200_DTYPE_BF16 3
 
-#define B200_ABI_VERSION 1
+#define B200_ABI_VERSION 2
 
 typedef struct b200_engine b200_engine;
 
@@ -93,6 +93,8 @@ typedef struct b200_stats {
   int64_t requests_finished, requests_aborted;
   int32_t running, waiting;
   int32_t kv_blocks_total, kv_blocks_free;
+  int64_t prefix_hit_tokens;       /* prompt tokens served from the prefix cache (their K/V blocks were shared) */
+  int64_t prefix_query_tokens;     /* prompt tokens of all admitted requests */
 } b200_stats;
 
 int32_t b200_abi_version(void);

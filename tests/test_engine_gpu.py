@@ -357,3 +357,48 @@ def test_chunked_prefill_interleaves_with_decode_and_changes_nothing(monkeypatch
     # 579 prompt tokens in chunks of <= 48 while four sequences decode: at least 12 prefill passes
     assert st1["steps_prefill"] - st0["steps_prefill"] >= 12
     assert st1["kv_blocks_free"] == st1["kv_blocks_total"]
+
+
+def test_prefix_cache_shares_prompt_blocks_and_changes_nothing(monkeypatch):
+    """Requests whose prompts start with the same tokens share the K/V blocks of that prefix (block granularity, 16
+    tokens) and prefill only the rest: same tokens as with the cache switched off, fewer prompt tokens computed,
+    every block reclaimable afterwards, and eviction under a small KV pool keeps results intact."""
+    from vgate_b200.engine import Engine
+    dims = PRESETS["qwen2.5-1.5b-awq-l2-v8k"]
+    ckpt = synthetic_checkpoint(dims, seed=8)
+    rng = np.random.default_rng(51)
+    common = rng.integers(0, dims.vocab, size=70, dtype=np.int32)                 # 4 full blocks + 6 tokens
+    prompts = [np.concatenate([common, rng.integers(0, dims.vocab, size=int(n), dtype=np.int32)]) for n in (1, 9, 30, 58, 3)]
+    prompts.append(common[:64].copy())                                            # exactly 4 blocks: the last one is recomputed
+    other = [rng.integers(0, dims.vocab, size=90, dtype=np.int32) for _ in range(3)]
+    kv_tok_bytes = 2 * dims.n_layers * dims.n_kv_heads * dims.head_dim * 2
+
+    def run(flag, kv_blocks):
+        monkeypatch.setenv("VGATE_B200_PREFIX_CACHE", flag)
+        eng = Engine(dims, max_seqs=8, max_model_len=256, max_batch_tokens=512, kv_bytes=kv_tok_bytes * 16 * kv_blocks).load_checkpoint(ckpt)
+        try:
+            first = eng.wait(eng.submit(prompts[0], 0.0, 1.0, 6), 6)[0]           # registers the common prefix
+            rids = [eng.submit(p, 0.0, 1.0, 6) for p in prompts[1:] + other]
+            outs = [first] + [eng.wait(r, 6)[0] for r in rids]
+            again = eng.wait(eng.submit(prompts[2], 0.0, 1.0, 6), 6)[0]           # after other traffic (possibly evicted)
+            st = eng.stats()
+        finally:
+            eng.close()
+        return outs, again, st
+
+    base, base_again, st0 = run("0", 200)
+    outs, again, st1 = run("1", 200)
+    for a, b in zip(outs, base):
+        assert np.array_equal(a, b)
+    assert np.array_equal(again, base_again) and np.array_equal(again, outs[2])
+    assert st0["prefix_hit_tokens"] == 0
+    # prompts[1..4] and the repeat share 4 blocks each, the 64-token prompt 3 (one token must be computed)
+    assert st1["prefix_hit_tokens"] == 5 * 64 + 48
+    assert st1["tokens_prefill"] == st0["tokens_prefill"] - st1["prefix_hit_tokens"]
+    assert st1["kv_blocks_free"] == st1["kv_blocks_total"]
+    # a pool of 40 blocks (a 90-token request reserves 6-7): registered blocks are evicted to make room, results hold
+    outs_small, again_small, st2 = run("1", 40)
+    for a, b in zip(outs_small, base):
+        assert np.array_equal(a, b)
+    assert np.array_equal(again_small, base_again)
+    assert st2["kv_blocks_free"] == st2["kv_blocks_total"] == 40

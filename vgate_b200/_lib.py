@@ -5,7 +5,7 @@ import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("VGATE_B200_LIB", os.path.join(HERE, "libb200gate.so"))
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_CAPACITY, ERR_STATE, ERR_NOT_FOUND, ERR_ABORTED = -1, -2, -3, -4, -5, -6
@@ -37,6 +37,7 @@ class Stats(C.Structure):
         ("decode_batch_sum", C.c_int64), ("hbm_bytes_decode", C.c_double), ("kernel_launches", C.c_int64),
         ("requests_finished", C.c_int64), ("requests_aborted", C.c_int64), ("running", C.c_int32),
         ("waiting", C.c_int32), ("kv_blocks_total", C.c_int32), ("kv_blocks_free", C.c_int32),
+        ("prefix_hit_tokens", C.c_int64), ("prefix_query_tokens", C.c_int64),
     ]
 
     def to_dict(self):

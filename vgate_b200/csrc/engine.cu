@@ -115,7 +115,9 @@ struct Request {
   int seq_slot = -1;
   std::vector<int32_t> blocks;
   std::vector<int32_t> out;
-  int n_prefilled = 0;                         // prompt tokens whose K/V are in the cache (chunked prefill)
+  int n_prefilled = 0;                         // prompt tokens whose K/V are in the cache (chunked prefill, shared prefix)
+  int n_registered = 0;                        // full prompt blocks offered to the prefix cache so far
+  uint64_t h1 = 0xCBF29CE484222325ull, h2 = 0x1234567;   // running chained hash of the registered blocks
   bool bt_uploaded = false;                    // its block-table row is on the device (blocks never change after admission)
   size_t n_polled = 0;
   double t_submit = 0, t_first = 0, t_last = 0;
@@ -147,6 +149,33 @@ struct b200_engine {
   size_t kv_layer_elems = 0;
   int n_blocks = 0, max_blocks_per_seq = 0;
   std::vector<int32_t> free_blocks;            // LIFO free list
+  // ---- prefix cache (vLLM's automatic prefix caching, at KV-block granularity) ----
+  // A FULL block of prompt tokens whose K/V are in the cache is registered under the chained hash of all prompt
+  // tokens up to its end.  A new request whose prompt starts with the same tokens shares those blocks (reference
+  // counted) and prefills only the rest; K/V rows depend on the tokens before them and their positions only, and a
+  // row's arithmetic never depends on what else is in its pass, so the shared rows hold the very bits the request
+  // would have written itself.  Blocks nobody references stay registered and reclaimable (least recently used first).
+  bool prefix_cache_enabled = !(getenv("VGATE_B200_PREFIX_CACHE") && atoi(getenv("VGATE_B200_PREFIX_CACHE")) == 0);
+  struct BlockMeta { int32_t ref = 0; uint64_t h1 = 0, h2 = 0; int64_t stamp = 0; };   // h1 == 0: not registered
+  std::vector<BlockMeta> block_meta;
+  std::unordered_map<uint64_t, int32_t> prefix_map;      // h1 -> block id
+  std::map<int64_t, int32_t> evictable;                   // stamp -> registered block with ref == 0
+  int64_t lru_clock = 0;
+  static void hash_block(const int32_t* tok, uint64_t& h1, uint64_t& h2) {   // chained: (h1, h2) enter as the parent
+    for (int i = 0; i < kBlockTokens; ++i) {
+      const uint64_t v = (uint64_t)(uint32_t)tok[i] + 0x9E3779B97F4A7C15ull;
+      h1 = (h1 ^ v) * 0x100000001B3ull;                                      // FNV-1a style
+      h2 = (h2 + v) * 0xD6E8FEB86659FD93ull; h2 ^= h2 >> 32;
+    }
+    if (h1 == 0) h1 = 1;
+  }
+  int reclaimable_blocks() const { return (int)free_blocks.size() + (int)evictable.size(); }
+  void drop_prefix_cache() {                   // generate_batch addresses blocks directly: nothing cached survives it
+    for (auto& kv : evictable) { block_meta[kv.second] = BlockMeta{}; free_blocks.push_back(kv.second); }
+    evictable.clear();
+    prefix_map.clear();
+    for (auto& m : block_meta) { m.h1 = m.h2 = 0; }
+  }
   std::vector<int32_t> free_slots;
 
   // ---- activations / metadata ----
@@ -386,12 +415,61 @@ struct b200_engine {
 
   // ---- block allocator ---------------------------------------------------------------------
   bool alloc_blocks(int n, std::vector<int32_t>& out) {
-    if ((int)free_blocks.size() < n) return false;
-    for (int i = 0; i < n; ++i) { out.push_back(free_blocks.back()); free_blocks.pop_back(); }
+    if (reclaimable_blocks() < n) return false;
+    for (int i = 0; i < n; ++i) {
+      int32_t b;
+      if (!free_blocks.empty()) { b = free_blocks.back(); free_blocks.pop_back(); }
+      else {                                   // evict the least recently used registered block
+        auto it = evictable.begin();
+        b = it->second;
+        evictable.erase(it);
+        prefix_map.erase(block_meta[b].h1);
+      }
+      block_meta[b] = BlockMeta{};
+      block_meta[b].ref = 1;
+      out.push_back(b);
+    }
     return true;
   }
+  // Longest run of registered blocks that matches the start of `prompt`; they are pinned (ref + 1) and appended to
+  // `out`.  At least one prompt token is always left to compute (its logits sample the first generated token).
+  int share_prefix(const std::vector<int32_t>& prompt, std::vector<int32_t>& out) {
+    if (!prefix_cache_enabled) return 0;
+    const int nb_full = (int)prompt.size() / kBlockTokens;
+    uint64_t h1 = 0xCBF29CE484222325ull, h2 = 0x1234567;
+    int hits = 0;
+    for (int i = 0; i < nb_full && (i + 1) * kBlockTokens < (int)prompt.size(); ++i) {
+      hash_block(prompt.data() + (size_t)i * kBlockTokens, h1, h2);
+      auto it = prefix_map.find(h1);
+      if (it == prefix_map.end() || block_meta[it->second].h2 != h2) break;
+      BlockMeta& m = block_meta[it->second];
+      if (m.ref == 0) evictable.erase(m.stamp);
+      m.ref++;
+      out.push_back(it->second);
+      ++hits;
+    }
+    return hits;
+  }
+  // Register the full prompt blocks of `r` whose K/V are complete (positions < r.n_prefilled) and not yet registered.
+  void register_prefix(Request& r) {
+    if (!prefix_cache_enabled) return;
+    const int nb_done = std::min((int)r.prompt.size(), r.n_prefilled) / kBlockTokens;
+    for (; r.n_registered < nb_done; ++r.n_registered) {
+      hash_block(r.prompt.data() + (size_t)r.n_registered * kBlockTokens, r.h1, r.h2);
+      const int32_t b = r.blocks[r.n_registered];
+      if (block_meta[b].h1 != 0) continue;                      // a shared block: registered by its first owner
+      if (prefix_map.count(r.h1)) continue;                     // the same prefix was registered meanwhile: ours stays private
+      block_meta[b].h1 = r.h1; block_meta[b].h2 = r.h2;
+      prefix_map[r.h1] = b;
+    }
+  }
   void release_request_resources(Request& r) {
-    for (int32_t b : r.blocks) free_blocks.push_back(b);
+    for (int32_t b : r.blocks) {
+      BlockMeta& m = block_meta[b];
+      if (--m.ref > 0) continue;
+      if (m.h1 != 0) { m.stamp = ++lru_clock; evictable[m.stamp] = b; }
+      else free_blocks.push_back(b);
+    }
     r.blocks.clear();
     if (r.seq_slot >= 0) free_slots.push_back(r.seq_slot);
     r.seq_slot = -1;
@@ -701,8 +779,17 @@ struct b200_engine {
         auto& r = waiting.front();
         const int need_tokens = (int)r->prompt.size() + r->max_tokens;
         const int need_blocks = (need_tokens + kBlockTokens - 1) / kBlockTokens;
-        if ((int)free_blocks.size() < need_blocks) break;
-        alloc_blocks(need_blocks, r->blocks);
+        const int shared = share_prefix(r->prompt, r->blocks);        // pins the blocks it finds
+        if (reclaimable_blocks() < need_blocks - shared) {            // does not fit yet: give the pins back, keep waiting
+          release_request_resources(*r);
+          break;
+        }
+        alloc_blocks(need_blocks - shared, r->blocks);
+        r->n_prefilled = shared * kBlockTokens;
+        r->n_registered = shared;
+        for (int i = 0; i < shared; ++i) hash_block(r->prompt.data() + (size_t)i * kBlockTokens, r->h1, r->h2);
+        stats.prefix_hit_tokens += r->n_prefilled;
+        stats.prefix_query_tokens += (int64_t)r->prompt.size();
         r->seq_slot = free_slots.back(); free_slots.pop_back();
         r->state = ReqState::RUNNING;
         prefilling.push_back(r);
@@ -733,6 +820,7 @@ struct b200_engine {
       last_step_was_prefill = do_prefill;
       if (rc != B200_OK) { inflight = Inflight{}; fail_all(g_last_error); continue; }
       if (do_prefill) {                              // sequences whose prompt is in the cache start decoding
+        for (auto& c : chunks) register_prefix(*c.req);
         for (auto it = prefilling.begin(); it != prefilling.end();) {
           if ((*it)->n_prefilled == (int)(*it)->prompt.size()) { running.push_back(*it); it = prefilling.erase(it); }
           else ++it;
@@ -1043,6 +1131,7 @@ int32_t b200_engine_finalize(b200_engine* e) {
   B200_CUDA(cudaMemset(e->k_cache.p, 0, e->k_cache.bytes));
   B200_CUDA(cudaMemset(e->v_cache.p, 0, e->v_cache.bytes));
   for (int b = e->n_blocks - 1; b >= 0; --b) e->free_blocks.push_back(b);
+  e->block_meta.assign((size_t)e->n_blocks, b200_engine::BlockMeta{});
   for (int s = c.max_seqs - 1; s >= 0; --s) e->free_slots.push_back(s);
   // activations
   e->Tmax = std::max(std::max(c.max_batch_tokens, c.max_model_len), c.max_seqs);
@@ -1250,7 +1339,7 @@ int32_t b200_stats_get(b200_engine* e, b200_stats* out) {
   out->running = (int)(e->running.size() + e->prefilling.size());
   out->waiting = (int)e->waiting.size();
   out->kv_blocks_total = e->n_blocks;
-  out->kv_blocks_free = (int)e->free_blocks.size();
+  out->kv_blocks_free = e->reclaimable_blocks();           // registered prefix blocks nobody references are reclaimable
   return B200_OK;
 }
 
@@ -1285,6 +1374,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
   B200_CUDA(cudaSetDevice(e->cfg.device));
   cudaStream_t s = e->stream;
   { const int rc0 = e->collect_decode(); if (rc0) return rc0; }   // a look-ahead step of sequences aborted since
+  { std::lock_guard<std::mutex> lk(e->mu); e->drop_prefix_cache(); }
   e->last_decode_ids.clear();
   const int bps = (n_prompt + max_tokens + 1 + kBlockTokens - 1) / kBlockTokens;   // blocks per sequence
   B200_REQUIRE(bps <= e->max_blocks_per_seq, "sequence needs more blocks than max_blocks_per_seq");
