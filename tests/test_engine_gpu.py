@@ -393,8 +393,9 @@ def test_prefix_cache_shares_prompt_blocks_and_changes_nothing(monkeypatch):
         assert np.array_equal(a, b)
     assert np.array_equal(again, base_again) and np.array_equal(again, outs[2])
     assert st0["prefix_hit_tokens"] == 0
-    # prompts[1..4] and the repeat share 4 blocks each, the 64-token prompt 3 (one token must be computed)
-    assert st1["prefix_hit_tokens"] == 5 * 64 + 48
+    # prompts[1..4] share the 4 blocks of the common prefix, the 64-token prompt 3 of them (one token must be computed),
+    # and the repeat of prompts[2] (100 tokens) all 6 full blocks its first run registered
+    assert st1["prefix_hit_tokens"] == 4 * 64 + 48 + 96
     assert st1["tokens_prefill"] == st0["tokens_prefill"] - st1["prefix_hit_tokens"]
     assert st1["kv_blocks_free"] == st1["kv_blocks_total"]
     # a pool of 40 blocks (a 90-token request reserves 6-7): registered blocks are evicted to make room, results hold

@@ -93,6 +93,6 @@ def test_request_batcher_fans_out_to_the_real_engine(vgate_b200_engine):
         assert ByteTokenizer.parse(r["text"]) == w                 # token ids survive as text only (batcher.py:433-438)
         assert r["total_tokens"] == 10 and r["ttft"] > 0 and r["tpot"] >= 0
     assert again["text"] == res[3]["text"]
-    assert metrics["total_requests"] >= 25
+    assert metrics["total_requests"] >= 24                         # the repeat was answered by the result cache
     st = eng.backend.engine.stats()
     assert st["kv_blocks_free"] == st["kv_blocks_total"]
