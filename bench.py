@@ -381,8 +381,10 @@ def run_b200(a):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    ctl = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        ctl = dist.new_group(backend="gloo")      # host-side rendezvous: an NCCL barrier spins ON the GPU while it waits
     hbm_peak, peak_src = load_peaks()
     dims = PRESETS[a.preset]
     ckpt = synthetic_checkpoint(dims, seed=0, profile=a.profile)
@@ -496,13 +498,16 @@ def run_b200(a):
     if not a.no_gateway:
         eng.close()
         eng = None
-        barrier()
+        torch.cuda.synchronize()
+        if ctl is not None:                             # the other ranks wait on the host: their GPUs belong to the workers now
+            dist.barrier(group=ctl)
         if rank == 0:
             try:
                 levels = gateway_levels(a, world)
             except Exception as exc:                    # reported, never fatal for the engine-level line
                 levels = {"error": repr(exc)[:300]}
-        barrier()
+        if ctl is not None:
+            dist.barrier(group=ctl)
 
     if rank == 0:
         d_steps = st1["steps_decode"] - st0["steps_decode"]

@@ -8,6 +8,8 @@
 #include <condition_variable>
 #include <cstring>
 #include <deque>
+#include <dlfcn.h>
+#include <functional>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -43,6 +45,41 @@ void tl_set_gemv(unsigned long long*, unsigned int*, unsigned int);
 void tl_set_attn(unsigned long long*, unsigned int*, unsigned int);
 void tl_set_sample(unsigned long long*, unsigned int*, unsigned int);
 void tl_set_umma(unsigned long long*, unsigned int*, unsigned int);
+
+// ---- NCCL, loaded on demand (tensor-parallel engines only: a single-GPU worker has no NCCL dependency) ----------
+struct NcclApi {
+  int (*get_unique_id)(void* id128) = nullptr;
+  int (*all_reduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*comm_destroy)(void*) = nullptr;
+  const char* (*error_string)(int) = nullptr;
+  void* raw_init = nullptr;
+  bool ok = false;
+};
+struct NcclId { char b[128]; };
+static NcclApi& nccl_api() {
+  static NcclApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* h = nullptr;
+    for (const char* name : {"libnccl.so.2", "libnccl.so"}) if ((h = dlopen(name, RTLD_NOW | RTLD_GLOBAL))) break;
+    if (!h) {                                  // the copy PyTorch ships (this image: site-packages/nvidia/nccl/lib)
+      if (const char* env = getenv("VGATE_B200_NCCL_LIB")) h = dlopen(env, RTLD_NOW | RTLD_GLOBAL);
+    }
+    if (!h) return;
+    api.get_unique_id = reinterpret_cast<int (*)(void*)>(dlsym(h, "ncclGetUniqueId"));
+    api.raw_init = dlsym(h, "ncclCommInitRank");
+    api.all_reduce = reinterpret_cast<int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t)>(dlsym(h, "ncclAllReduce"));
+    api.comm_destroy = reinterpret_cast<int (*)(void*)>(dlsym(h, "ncclCommDestroy"));
+    api.error_string = reinterpret_cast<const char* (*)(int)>(dlsym(h, "ncclGetErrorString"));
+    api.ok = api.get_unique_id && api.raw_init && api.all_reduce && api.comm_destroy && api.error_string;
+  });
+  return api;
+}
+static int nccl_fail(int code, const char* what) {
+  NcclApi& a = nccl_api();
+  set_last_error(std::string("NCCL error in ") + what + ": " + (a.error_string ? a.error_string(code) : "?"));
+  return B200_ERR_CUDA;
+}
 
 static double now_s() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -203,6 +240,66 @@ struct b200_engine {
   int poll_waiters = 0;                        // threads blocked in b200_poll (guarded by mu)
   std::vector<int64_t> last_decode_ids;        // scheduler: request ids of the previous decode step, in row order
 
+  // ---- tensor parallelism (config #5: one engine object per rank, heads and intermediate columns divided) ----
+  // Every rank runs the same kernels on its shard; o_proj and down_proj are row-parallel, so their outputs are
+  // partial sums that an NCCL all-reduce completes before the residual add (2 per layer).  The
+  // residual stream, the norms and the LM head are replicated, so all ranks sample the same token from the same
+  // bits and the device-resident decode state stays consistent without any host exchange.  Rank 0 (the leader) owns
+  // the scheduler; the other ranks execute the device half of every step on a thread of their own (NCCL expects
+  // one thread per device, or group calls).
+  int tp_size = 1, tp_rank = 0;
+  void* nccl_comm = nullptr;
+  std::vector<b200_engine*> tp_followers;      // leader only
+  std::thread tp_thread;                       // followers only
+  std::mutex tp_mu;
+  std::condition_variable tp_cv;
+  std::function<int()> tp_cmd;
+  bool tp_has_cmd = false, tp_done = true, tp_stop = false;
+  int tp_rc = 0;
+  std::string tp_err;
+  void tp_loop() {
+    cudaSetDevice(cfg.device);
+    std::unique_lock<std::mutex> lk(tp_mu);
+    while (true) {
+      tp_cv.wait(lk, [&] { return tp_stop || tp_has_cmd; });
+      if (tp_stop) break;
+      std::function<int()> cmd = std::move(tp_cmd);
+      tp_has_cmd = false;
+      lk.unlock();
+      const int rc = cmd();
+      lk.lock();
+      tp_rc = rc;
+      tp_err = rc ? g_last_error : std::string();
+      tp_done = true;
+      tp_cv.notify_all();
+    }
+  }
+  void tp_post(std::function<int()> f) {
+    std::lock_guard<std::mutex> lk(tp_mu);
+    tp_cmd = std::move(f); tp_has_cmd = true; tp_done = false;
+    tp_cv.notify_all();
+  }
+  int tp_wait() {
+    std::unique_lock<std::mutex> lk(tp_mu);
+    tp_cv.wait(lk, [&] { return tp_done; });
+    if (tp_rc) set_last_error("tensor-parallel rank " + std::to_string(tp_rank) + ": " + tp_err);
+    return tp_rc;
+  }
+  // f(rank engine) on every rank: followers on their own threads, the leader inline; returns when all have ENQUEUED.
+  template <class F> int tp_each(F&& f) {
+    for (b200_engine* r : tp_followers) r->tp_post([r, &f] { return f(r); });
+    int rc = f(this);
+    for (b200_engine* r : tp_followers) { const int rr = r->tp_wait(); if (!rc) rc = rr; }
+    return rc;
+  }
+  int tp_allreduce(float* buf, size_t count, cudaStream_t st) {
+    if (tp_size <= 1) return B200_OK;
+    const int rc = nccl_api().all_reduce(buf, buf, count, /*ncclFloat32*/ 7, /*ncclSum*/ 0, nccl_comm, st);
+    if (rc != 0) return nccl_fail(rc, "ncclAllReduce");
+    g_launch_count += 1;
+    return B200_OK;
+  }
+
   // ---- scheduler ----
   std::mutex mu;
   std::condition_variable cv_work, cv_done;
@@ -277,7 +374,7 @@ struct b200_engine {
       int rc;
       if ((rc = get_map(x, x_rows, w.K, nt, &mx)) || (rc = get_map(lw.dense[i].p, w.N, w.K, 128, &mw))) return rc;
       const int ns = split_k ? umma_dense_effective_splits(w.K, splits[i]) : 1;
-      if (ns > 1) {
+      if (ns > 1 || (tp_size > 1 && (i == 1 || i == 3))) {     // a row-parallel shard's output is a partial sum by nature
         *n_parts_out = ns;
         return launch_umma_f16(*mw, w.K, w.N, *mx, nt, T, pbuf, w.N, kUmmaPartialF32, st, ns, (int64_t)T * w.N, nullptr, bf16);
       }
@@ -291,7 +388,7 @@ struct b200_engine {
     int rc = get_map(x, x_rows, w.K, nt, &mx);
     if (rc) return rc;
     const int ns = split_k ? umma_w4_effective_splits(w.K, w.G, splits[i]) : 1;
-    if (ns > 1) {
+    if (ns > 1 || (tp_size > 1 && (i == 1 || i == 3))) {
       *n_parts_out = ns;
       return launch_umma_w4(lw.ulin[i], *mx, nt, T, pbuf, w.N, kUmmaPartialF32, ns, (int64_t)T * w.N, st);
     }
@@ -361,6 +458,7 @@ struct b200_engine {
                                                        NKV, 1, nullptr, nullptr, aa, st, bf16))) return rc;
       }
       if (!skip(4) && (rc = linear(w, 1, aa, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows))) return rc;
+      if ((rc = tp_allreduce(pbuf, (size_t)pend * T * H, st))) return rc;
       if (!skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st, bf16)))
         return rc;
       pend = 0;
@@ -372,6 +470,7 @@ struct b200_engine {
       }
       if (np) { set_last_error("gate_up projection must not be split"); return B200_ERR_STATE; }
       if (!skip(6) && (rc = linear(w, 3, cc, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows))) return rc;
+      if ((rc = tp_allreduce(pbuf, (size_t)pend * T * H, st))) return rc;
     }
     *pend_out = pend;
     return B200_OK;
@@ -568,6 +667,30 @@ struct b200_engine {
   cudaEvent_t ev_a[2] = {nullptr, nullptr}, ev_b[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
   bool lookahead_enabled = !(getenv("VGATE_B200_LOOKAHEAD") && atoi(getenv("VGATE_B200_LOOKAHEAD")) == 0);
 
+  // The device half of one decode step, executed by every tensor-parallel rank: optional state upload, the step
+  // (CUDA-graph replay), and the copy of the sampled tokens into pinned slot `slot`.
+  int decode_device(int n, const int32_t* state, bool greedy, int slot) {
+    int rc;
+    greedy_only = greedy;
+    if (state) {
+      const int k = (up_slot ^= 1);
+      B200_CUDA(cudaEventSynchronize(ev_up[k]));       // the copies that last used this buffer (long done)
+      const size_t S = (size_t)cfg.max_seqs;
+      int32_t* base = hp_up[k];
+      std::memcpy(base, state, 7 * S * 4);
+      auto up = [&](DevMem& dst, const void* src) { return cudaMemcpyAsync(dst.p, src, (size_t)n * 4, cudaMemcpyHostToDevice, stream); };
+      B200_CUDA(up(d_next, base)); B200_CUDA(up(d_pos, base + S)); B200_CUDA(up(d_btrow, base + 2 * S)); B200_CUDA(up(d_step, base + 3 * S));
+      B200_CUDA(up(d_seed, base + 4 * S)); B200_CUDA(up(d_temp, base + 5 * S)); B200_CUDA(up(d_topp, base + 6 * S));
+      B200_CUDA(cudaEventRecord(ev_up[k], stream));
+    }
+    B200_CUDA(cudaEventRecord(ev_a[slot], stream));
+    if ((rc = decode_step(n, nullptr, 0))) return rc;
+    B200_CUDA(cudaEventRecord(ev_b[slot], stream));
+    B200_CUDA(cudaMemcpyAsync(hp_next[slot], d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+    B200_CUDA(cudaEventRecord(ev_copied[slot], stream));
+    return B200_OK;
+  }
+
   // Launch one decode step for `batch` (state upload if the batch changed) and queue the copy of its tokens.
   int launch_decode(const std::vector<std::shared_ptr<Request>>& batch, const std::vector<int64_t>& idsig, int64_t extra_ctx) {
     const int n = (int)batch.size();
@@ -578,14 +701,14 @@ struct b200_engine {
       ctx_sum += (int64_t)batch[r]->prompt.size() + (int64_t)batch[r]->out.size();
       greedy_only = greedy_only && batch[r]->temperature < 1e-5f;
     }
+    std::vector<int32_t> state;                      // non-empty: the batch changed, the device state is re-uploaded
     if (idsig != last_decode_ids) {
       // state BEFORE the advance kernel: last token in d_next, position one behind.  Seven small per-row arrays
       // go through a pinned double buffer (no stream synchronisation: the decode pipeline keeps running while
       // the host moves on); block-table rows were uploaded when their sequences were admitted.
-      const int k = (up_slot ^= 1);
-      B200_CUDA(cudaEventSynchronize(ev_up[k]));       // the copies that last used this buffer (long done)
-      int32_t* base = hp_up[k];
       const size_t S = (size_t)cfg.max_seqs;
+      state.assign(7 * S, 0);
+      int32_t* base = state.data();
       int32_t *next = base, *pos = base + S, *btrow = base + 2 * S, *step = base + 3 * S, *seed = base + 4 * S;
       float *temp = reinterpret_cast<float*>(base + 5 * S), *topp = reinterpret_cast<float*>(base + 6 * S);
       for (int r = 0; r < n; ++r) {
@@ -599,19 +722,12 @@ struct b200_engine {
         temp[r] = q.temperature;
         topp[r] = q.top_p;
       }
-      auto up = [&](DevMem& dst, const void* src) { return cudaMemcpyAsync(dst.p, src, (size_t)n * 4, cudaMemcpyHostToDevice, stream); };
-      B200_CUDA(up(d_next, next)); B200_CUDA(up(d_pos, pos)); B200_CUDA(up(d_btrow, btrow)); B200_CUDA(up(d_step, step));
-      B200_CUDA(up(d_seed, seed)); B200_CUDA(up(d_temp, temp)); B200_CUDA(up(d_topp, topp));
-      B200_CUDA(cudaEventRecord(ev_up[k], stream));
       last_decode_ids = idsig;
     }
     const int slot = inflight.slot ^ 1;
     const int64_t launches0 = g_launch_count;
-    B200_CUDA(cudaEventRecord(ev_a[slot], stream));
-    if ((rc = decode_step(n, nullptr, 0))) return rc;
-    B200_CUDA(cudaEventRecord(ev_b[slot], stream));
-    B200_CUDA(cudaMemcpyAsync(hp_next[slot], d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
-    B200_CUDA(cudaEventRecord(ev_copied[slot], stream));
+    const bool greedy = greedy_only;
+    if ((rc = tp_each([&](b200_engine* e) { return e->decode_device(n, state.empty() ? nullptr : state.data(), greedy, slot); }))) return rc;
     inflight.active = true; inflight.batch = batch; inflight.ids = idsig; inflight.slot = slot;
     inflight.ctx_sum = ctx_sum; inflight.launches = g_launch_count - launches0;
     return B200_OK;
@@ -683,11 +799,11 @@ struct b200_engine {
     std::vector<Request*> done;                      // requests whose prompt completes in this pass
     int rc;
     greedy_only = true;
+    std::vector<Request*> new_rows;                  // sequences whose block-table row is not on the device(s) yet
     for (const Chunk& c : chunks) {
       Request& q = *c.req;
       if (!q.bt_uploaded) {                          // once per sequence: its blocks are reserved for its whole life
-        B200_CUDA(cudaMemcpyAsync(d_bt.as<int32_t>() + (size_t)q.seq_slot * max_blocks_per_seq, q.blocks.data(),
-                                  q.blocks.size() * 4, cudaMemcpyHostToDevice, stream));   // q.blocks outlives the pass
+        new_rows.push_back(&q);
         q.bt_uploaded = true;
       }
       for (int p = c.start; p < c.start + c.count; ++p) {
@@ -708,18 +824,30 @@ struct b200_engine {
       }
     }
     const int T = (int)ids.size(), n = (int)done.size();
-    if ((rc = upload_i32(d_ids, ids)) || (rc = upload_i32(d_pos, pos)) || (rc = upload_i32(d_slot, slot)) ||
-        (rc = upload_i32(d_btrow, btrow)) || (rc = upload_i32(d_ctx, ctx)) || (rc = upload_i32(d_lastrows, lastrows)) ||
-        (rc = upload_q_tiles(btrow, ctx)) || (rc = upload_f32(d_temp, temp)) || (rc = upload_f32(d_topp, topp)) ||
-        (rc = upload_i32(d_seed, seed)) || (rc = upload_i32(d_step, step)))
-      return rc;
     const int64_t launches0 = g_launch_count;
-    B200_CUDA(cudaEventRecord(ev0, stream));
-    if ((rc = forward(T, n, d_lastrows.as<int32_t>(), false, n > 0))) return rc;
-    B200_CUDA(cudaEventRecord(ev1, stream));
+    const bool greedy = greedy_only;
     std::vector<int32_t> next(n);
-    if (n > 0) B200_CUDA(cudaMemcpyAsync(next.data(), d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
-    B200_CUDA(cudaStreamSynchronize(stream));        // the host vectors above stay alive until here
+    // the device half, on every tensor-parallel rank (each ends with a stream synchronisation: the host vectors
+    // above stay alive until then); the leader also reads the sampled tokens back
+    rc = tp_each([&](b200_engine* e) -> int {
+      int r;
+      e->greedy_only = greedy;
+      for (Request* q : new_rows)
+        B200_CUDA(cudaMemcpyAsync(e->d_bt.as<int32_t>() + (size_t)q->seq_slot * e->max_blocks_per_seq, q->blocks.data(),
+                                  q->blocks.size() * 4, cudaMemcpyHostToDevice, e->stream));
+      if ((r = e->upload_i32(e->d_ids, ids)) || (r = e->upload_i32(e->d_pos, pos)) || (r = e->upload_i32(e->d_slot, slot)) ||
+          (r = e->upload_i32(e->d_btrow, btrow)) || (r = e->upload_i32(e->d_ctx, ctx)) || (r = e->upload_i32(e->d_lastrows, lastrows)) ||
+          (r = e->upload_q_tiles(btrow, ctx)) || (r = e->upload_f32(e->d_temp, temp)) || (r = e->upload_f32(e->d_topp, topp)) ||
+          (r = e->upload_i32(e->d_seed, seed)) || (r = e->upload_i32(e->d_step, step)))
+        return r;
+      B200_CUDA(cudaEventRecord(e->ev0, e->stream));
+      if ((r = e->forward(T, n, e->d_lastrows.as<int32_t>(), false, n > 0))) return r;
+      B200_CUDA(cudaEventRecord(e->ev1, e->stream));
+      if (e == this && n > 0) B200_CUDA(cudaMemcpyAsync(next.data(), e->d_next.p, (size_t)n * 4, cudaMemcpyDeviceToHost, e->stream));
+      B200_CUDA(cudaStreamSynchronize(e->stream));
+      return B200_OK;
+    });
+    if (rc) return rc;
     float ms = 0.f;
     B200_CUDA(cudaEventElapsedTime(&ms, ev0, ev1));
     const double t = now_s();
