@@ -80,7 +80,10 @@ typedef struct b200_config {
                               or B200_DTYPE_BF16 */
   int32_t dense_weights;   /* 0: AWQ int4 linears (qweight / qzeros / scales, fp16 activations only);
                               1: dense 16-bit linears ("...proj.weight" [out, in] in act_dtype) -- Qwen2.5-7B/14B bf16 */
-  int32_t reserved[6];
+  int32_t tp_size;         /* tensor-parallel group size (0 or 1: none).  One engine per rank, each created with the
+                              dimensions of ITS shard: n_heads / tp, n_kv_heads / tp, intermediate / tp; hidden and vocab whole */
+  int32_t tp_rank;         /* 0 = the leader (owns the scheduler, takes the requests) */
+  int32_t reserved[4];
 } b200_config;
 
 typedef struct b200_stats {
@@ -128,6 +131,18 @@ int32_t b200_poll(b200_engine* e, int64_t rid, int32_t* out_ids, int32_t cap, in
  * already blocked in b200_wait / b200_poll on it gets B200_ERR_ABORTED). */
 int32_t b200_abort(b200_engine* e, int64_t rid);
 int32_t b200_stats_get(b200_engine* e, b200_stats* out);
+/* Tensor parallelism (north_star: "used only for the larger-model config"; the reference has no counterpart --
+ * vgate/backends/sglang_backend.py:40 hard-codes tp_size = 1 -- so SURVEY.md section 8e is the specification):
+ * q / k / v and gate / up are column-parallel (each rank holds its heads / intermediate columns), o_proj and
+ * down_proj row-parallel, and their partial outputs meet in an NCCL all-reduce (sum) inside the step; residual
+ * stream, norms, embeddings and LM head are replicated.  Bring-up, per rank r (threads may run concurrently):
+ *   b200_engine_create(cfg with tp_size, tp_rank = r, shard dimensions) -> load that rank's tensors ->
+ *   b200_engine_tp_init(e_r, id)   [id from ONE b200_tp_unique_id call; blocks until all ranks arrive: one thread per rank] ->
+ *   b200_engine_finalize(e_r);   then b200_engine_tp_attach(e_0, e_r) for r > 0.  Requests go to e_0 only.
+ * NCCL is loaded on first use (libnccl.so.2, or the path in VGATE_B200_NCCL_LIB). */
+int32_t b200_tp_unique_id(void* id128);                       /* 128 bytes out */
+int32_t b200_engine_tp_init(b200_engine* e, const void* id128);
+int32_t b200_engine_tp_attach(b200_engine* leader, b200_engine* follower);
 /* Liveness for health probes: B200_OK while the engine serves; B200_ERR_CUDA (b200_last_error() = the first
  * failure) once a CUDA error has poisoned it and every request was failed.  What /health should report and the
  * reference's unconditional route cannot (main.py:288-295; probed by vgate/health_checker.py:307-312). */

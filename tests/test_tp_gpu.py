@@ -1,0 +1,46 @@
+"""Config #5's mechanism at test size: a dense bf16 model run tensor-parallel over two B200s -- one rank engine per
+device, column-parallel q/k/v and gate/up, row-parallel o_proj / down_proj completed by an NCCL all-reduce inside the
+step (CUDA-graph replays included) -- against the pinned fp32 oracle of the WHOLE model and against the same model
+on one GPU.  Needs two GPUs (skipped on a single-GPU box)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle.qwen2 import OracleQwen2, Qwen2Dims
+from vgate_b200.weights import ModelDims, synthetic_checkpoint
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(torch.cuda.device_count() < 2, reason="tensor parallelism needs two GPUs")]
+
+
+def test_tp2_matches_oracle_and_single_gpu():
+    from vgate_b200.engine import Engine, TPEngine
+    dims = ModelDims(hidden=512, intermediate=1024, n_layers=3, n_heads=8, n_kv_heads=2, head_dim=128, vocab=2048,
+                     tie_embeddings=False, quant="none", dtype="bf16")
+    ckpt = synthetic_checkpoint(dims, seed=4, profile="peaked")
+    rng = np.random.default_rng(13)
+    prompts = [rng.integers(0, dims.vocab, size=int(n), dtype=np.int32) for n in (33, 33, 33, 33, 7, 90)]
+    n_new = 12
+    kw = dict(max_seqs=16, max_model_len=160, max_batch_tokens=256)
+    one = Engine(dims, **kw).load_checkpoint(ckpt)
+    try:
+        solo = [one.wait(one.submit(p, 0.0, 1.0, n_new), n_new)[0] for p in prompts]
+    finally:
+        one.close()
+    tp = TPEngine(dims, ckpt, devices=(0, 1), **kw)
+    try:
+        rids = [tp.submit(p, 0.0, 1.0, n_new) for p in prompts]          # batched, ragged, through the scheduler
+        outs = [tp.wait(r, n_new)[0] for r in rids]
+        again = tp.wait(tp.submit(prompts[0], 0.0, 1.0, n_new), n_new)[0]    # alone: decode graph of another batch size
+        sampled = [tp.wait(tp.submit(prompts[1], 0.8, 0.9, 6, seed=5), 6)[0] for _ in range(2)]
+        st = tp.stats()
+    finally:
+        tp.close()
+    ref = OracleQwen2(Qwen2Dims(**dims.to_dict()), ckpt, mode="fp32")
+    ref_toks = ref.generate_greedy(np.stack(prompts[:4]), n_new)
+    for i in range(4):
+        assert np.array_equal(outs[i], ref_toks[i]), i
+    for a, b in zip(outs, solo):                      # and the single-GPU engine on the whole model
+        assert np.array_equal(a, b)
+    assert np.array_equal(again, outs[0])
+    assert np.array_equal(sampled[0], sampled[1])     # ranks draw the same samples (same logits, same counter hash)
+    assert st["kv_blocks_free"] == st["kv_blocks_total"]

@@ -26,7 +26,7 @@ class Config(C.Structure):
         ("rope_theta", C.c_float), ("max_seqs", C.c_int32), ("max_model_len", C.c_int32),
         ("max_batch_tokens", C.c_int32), ("kv_bytes", C.c_int64), ("eos_token_id", C.c_int32),
         ("use_cuda_graphs", C.c_int32), ("gemm_path", C.c_int32), ("act_dtype", C.c_int32), ("dense_weights", C.c_int32),
-        ("reserved", C.c_int32 * 6),
+        ("tp_size", C.c_int32), ("tp_rank", C.c_int32), ("reserved", C.c_int32 * 4),
     ]
 
 
@@ -61,6 +61,9 @@ SIGNATURES = {
     "b200_abort": (_i32, [_vp, _i64]),
     "b200_stats_get": (_i32, [_vp, C.POINTER(Stats)]),
     "b200_engine_status": (_i32, [_vp]),
+    "b200_tp_unique_id": (_i32, [_vp]),
+    "b200_engine_tp_init": (_i32, [_vp, _vp]),
+    "b200_engine_tp_attach": (_i32, [_vp, _vp]),
     "b200_generate_batch": (_i32, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _i32, _pf64]),
     "b200_op_awq_repack": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "b200_op_awq_dequant": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),

@@ -985,6 +985,7 @@ int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
   B200_REQUIRE(cfg->struct_size == (int32_t)sizeof(b200_config), "b200_config.struct_size mismatch");
   B200_REQUIRE(cfg->head_dim == kHeadDim, "head_dim must be 128");
   B200_REQUIRE(cfg->hidden > 0 && cfg->hidden % 128 == 0 && cfg->intermediate % 128 == 0, "hidden/intermediate % 128");
+  B200_REQUIRE(cfg->tp_size >= 0 && cfg->tp_size <= 8 && cfg->tp_rank >= 0 && cfg->tp_rank < std::max(1, cfg->tp_size), "0 <= tp_rank < tp_size <= 8");
   B200_REQUIRE(cfg->dense_weights == 0 || cfg->dense_weights == 1, "dense_weights in {0, 1}");
   B200_REQUIRE(cfg->act_dtype == B200_DTYPE_F16 || cfg->act_dtype == B200_DTYPE_BF16, "act_dtype is B200_DTYPE_F16 or B200_DTYPE_BF16");
   B200_REQUIRE(cfg->dense_weights == 1 || cfg->act_dtype == B200_DTYPE_F16, "AWQ int4 linears run with fp16 activations");
@@ -1007,6 +1008,7 @@ int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
   e->H = cfg->hidden; e->I = cfg->intermediate; e->L = cfg->n_layers; e->NH = cfg->n_heads; e->NKV = cfg->n_kv_heads;
   e->V = cfg->vocab; e->G = cfg->dense_weights ? 128 : cfg->group_size; e->QKV = (cfg->n_heads + 2 * cfg->n_kv_heads) * kHeadDim;
   e->bf16 = cfg->act_dtype == B200_DTYPE_BF16; e->dense = cfg->dense_weights == 1;
+  e->tp_size = std::max(1, cfg->tp_size); e->tp_rank = cfg->tp_rank;
   int rc = B200_OK;
   auto fail = [&](int code) { b200_engine_destroy(e); return code; };
   if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -1307,6 +1309,10 @@ int32_t b200_engine_finalize(b200_engine* e) {
       if (eff > 1) part_elems = std::max(part_elems, (size_t)eff * S * a.N);   // split-K only runs on decode passes (<= max_seqs rows)
     }
   }
+  if (e->tp_size > 1) {
+    if (!e->nccl_comm) { set_last_error("finalize: tensor-parallel engine without a communicator (call b200_engine_tp_init first)"); return B200_ERR_STATE; }
+    part_elems = std::max(part_elems, T * (size_t)e->H);          // o_proj / down_proj outputs of a prefill pass are all-reduced too
+  }
   if ((rc = e->parts.alloc(part_elems * 4))) return rc;
   if ((rc = e->attn_scratch.alloc(attn_scratch_floats(c.max_seqs, e->NH, e->NKV, b200_engine::kDecodeSplits) * 4)) ||
       (rc = e->attn_counters.alloc((size_t)c.max_seqs * e->NKV * 4)))
@@ -1314,7 +1320,8 @@ int32_t b200_engine_finalize(b200_engine* e) {
   B200_CUDA(cudaMemset(e->attn_counters.p, 0, e->attn_counters.bytes));
   B200_CUDA(cudaDeviceSynchronize());
   e->finalized = true;
-  e->worker = std::thread([e] { e->scheduler_loop(); });
+  if (e->tp_rank == 0) e->worker = std::thread([e] { e->scheduler_loop(); });
+  else e->tp_thread = std::thread([e] { e->tp_loop(); });          // a follower rank: executes what the leader posts
   return B200_OK;
 }
 
@@ -1331,6 +1338,12 @@ void b200_engine_destroy(b200_engine* e) {
     e->cv_done.notify_all();
   }
   if (e->worker.joinable()) e->worker.join();
+  {
+    std::lock_guard<std::mutex> lk(e->tp_mu);
+    e->tp_stop = true;
+    e->tp_cv.notify_all();
+  }
+  if (e->tp_thread.joinable()) e->tp_thread.join();
   cudaSetDevice(e->cfg.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (auto& g : e->decode_graphs) cudaGraphExecDestroy(g.second.exec);
@@ -1352,6 +1365,7 @@ void b200_engine_destroy(b200_engine* e) {
     if (e->hp_up[i]) cudaFreeHost(e->hp_up[i]);
     if (e->ev_up[i]) cudaEventDestroy(e->ev_up[i]);
   }
+  if (e->nccl_comm) nccl_api().comm_destroy(e->nccl_comm);
   if (e->ev0) cudaEventDestroy(e->ev0);
   if (e->ev1) cudaEventDestroy(e->ev1);
   if (e->stream) cudaStreamDestroy(e->stream);
@@ -1364,6 +1378,8 @@ int64_t b200_submit(b200_engine* e, const int32_t* prompt_ids, int32_t n_prompt,
   B200_REQUIRE(n_prompt > 0 && max_tokens > 0, "n_prompt > 0 && max_tokens > 0");
   B200_REQUIRE(top_p > 0.f && top_p <= 1.f && temperature >= 0.f, "0 < top_p <= 1, temperature >= 0");
   if (!e->finalized) { set_last_error("submit before finalize"); return B200_ERR_STATE; }
+  if (e->tp_rank != 0) { set_last_error("submit on a tensor-parallel follower rank: requests go to rank 0"); return B200_ERR_STATE; }
+  if (e->tp_size > 1 && (int)e->tp_followers.size() != e->tp_size - 1) { set_last_error("tensor-parallel leader without its followers (b200_engine_tp_attach)"); return B200_ERR_STATE; }
   // vLLM accepts any prompt shorter than max_model_len and stops the generation when the sequence reaches
   // max_model_len (finish reason "length"); only a prompt that leaves no room for a single token is refused.
   if (n_prompt >= e->cfg.max_model_len) {
@@ -1471,6 +1487,38 @@ int32_t b200_stats_get(b200_engine* e, b200_stats* out) {
   return B200_OK;
 }
 
+int32_t b200_tp_unique_id(void* id128) {
+  B200_REQUIRE(id128, "null argument");
+  NcclApi& a = nccl_api();
+  if (!a.ok) { set_last_error("libnccl.so.2 not found (set VGATE_B200_NCCL_LIB)"); return B200_ERR_STATE; }
+  const int rc = a.get_unique_id(id128);
+  return rc ? nccl_fail(rc, "ncclGetUniqueId") : B200_OK;
+}
+int32_t b200_engine_tp_init(b200_engine* e, const void* id128) {
+  B200_REQUIRE(e && id128, "null argument");
+  if (e->finalized || e->nccl_comm) { set_last_error("tp_init: call once, before finalize"); return B200_ERR_STATE; }
+  B200_REQUIRE(e->tp_size > 1, "tp_init on an engine created with tp_size <= 1");
+  NcclApi& a = nccl_api();
+  if (!a.ok) { set_last_error("libnccl.so.2 not found (set VGATE_B200_NCCL_LIB)"); return B200_ERR_STATE; }
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  NcclId id;
+  std::memcpy(&id, id128, sizeof(id));
+  typedef int (*InitFn)(void**, int, NcclId, int);
+  const int rc = reinterpret_cast<InitFn>(a.raw_init)(&e->nccl_comm, e->tp_size, id, e->tp_rank);   // blocks until every rank has called
+  return rc ? nccl_fail(rc, "ncclCommInitRank") : B200_OK;
+}
+int32_t b200_engine_tp_attach(b200_engine* leader, b200_engine* follower) {
+  B200_REQUIRE(leader && follower && leader != follower, "null / identical engines");
+  B200_REQUIRE(leader->tp_rank == 0 && follower->tp_rank > 0 && leader->tp_size == follower->tp_size, "attach(rank 0, rank r > 0) of one group");
+  if (!leader->finalized || !follower->finalized) { set_last_error("tp_attach before finalize"); return B200_ERR_STATE; }
+  B200_REQUIRE(leader->n_blocks == follower->n_blocks && leader->cfg.max_seqs == follower->cfg.max_seqs &&
+                   leader->Tmax == follower->Tmax && leader->H == follower->H && leader->V == follower->V,
+               "tensor-parallel ranks must share max_seqs, token budgets, KV block count, hidden size and vocabulary");
+  std::lock_guard<std::mutex> lk(leader->mu);
+  leader->tp_followers.push_back(follower);
+  return B200_OK;
+}
+
 int32_t b200_engine_status(b200_engine* e) {
   B200_REQUIRE(e, "null engine");
   std::lock_guard<std::mutex> lk(e->mu);
@@ -1487,6 +1535,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
   B200_REQUIRE(n_prompt > 0 && max_tokens > 0 && n_prompt + max_tokens <= e->cfg.max_model_len, "prompt + max_tokens <= max_model_len");
   B200_REQUIRE(n_logit_steps >= 0 && n_logit_steps <= max_tokens, "n_logit_steps <= max_tokens");
   if (!e->finalized) { set_last_error("generate_batch before finalize"); return B200_ERR_STATE; }
+  if (e->tp_size > 1) { set_last_error("generate_batch runs on single-GPU engines; tensor-parallel engines take submit / wait"); return B200_ERR_STATE; }
   for (int64_t i = 0; i < (int64_t)n_seqs * n_prompt; ++i)
     if (prompt_ids[i] < 0 || prompt_ids[i] >= e->V) { set_last_error("prompt token id out of range"); return B200_ERR_INVALID; }
   {

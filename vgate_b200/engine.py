@@ -23,7 +23,7 @@ def rope_table(dims: ModelDims, n_pos: int):
 
 class Engine:
     def __init__(self, dims: ModelDims, *, device=0, max_seqs=256, max_model_len=2048, max_batch_tokens=8192,
-                 kv_bytes=0, eos_token_id=-1, use_cuda_graphs=True, gemm_path=0):
+                 kv_bytes=0, eos_token_id=-1, use_cuda_graphs=True, gemm_path=0, tp_size=1, tp_rank=0):
         self._lib = _lib.load()
         self.dims = dims
         cfg = _lib.Config()
@@ -38,6 +38,7 @@ class Engine:
         cfg.use_cuda_graphs, cfg.gemm_path = int(use_cuda_graphs), gemm_path
         cfg.act_dtype = _lib.DTYPE_BF16 if getattr(dims, "dtype", "fp16") == "bf16" else _lib.DTYPE_F16
         cfg.dense_weights = int(getattr(dims, "quant", "awq") == "none")
+        cfg.tp_size, cfg.tp_rank = tp_size, tp_rank
         self.cfg = cfg
         h = C.c_void_p()
         _lib.check(self._lib.b200_engine_create(C.byref(cfg), C.byref(h)))
@@ -51,7 +52,7 @@ class Engine:
         _lib.check(self._lib.b200_engine_load_tensor(self._h, name.encode(), arr.ctypes.data_as(C.c_void_p),
                                                      _NP_DTYPE[arr.dtype], arr.ndim, shape))
 
-    def load_checkpoint(self, ckpt: dict):
+    def load_checkpoint(self, ckpt: dict, finalize=True):
         cos, sin = rope_table(self.dims, self.max_model_len + 1)
         self.load_tensor("b200.rope_cos", cos)
         self.load_tensor("b200.rope_sin", sin)
@@ -59,7 +60,8 @@ class Engine:
             if name == "lm_head.weight" and self.dims.tie_embeddings:
                 continue
             self.load_tensor(name, arr)
-        _lib.check(self._lib.b200_engine_finalize(self._h))
+        if finalize:
+            _lib.check(self._lib.b200_engine_finalize(self._h))
         return self
 
     # -- requests --------------------------------------------------------------------------
@@ -122,3 +124,57 @@ class Engine:
             self.close()
         except Exception:
             pass
+
+
+class TPEngine:
+    """A tensor-parallel engine: one rank engine per device (include/b200gate.h, "Tensor parallelism"), the same
+    request surface as :class:`Engine` (requests go to rank 0).  `dims` and `ckpt` are the WHOLE model's."""
+
+    def __init__(self, dims: ModelDims, ckpt: dict, *, devices=(0, 1), **kw):
+        import os
+        import threading
+        from .weights import shard_checkpoint, shard_dims
+        lib = _lib.load()
+        tp = len(devices)
+        here = os.path.dirname(os.path.abspath(__file__))
+        if "VGATE_B200_NCCL_LIB" not in os.environ:          # the NCCL that ships with PyTorch in this image
+            import importlib.util
+            spec = importlib.util.find_spec("nvidia.nccl")
+            if spec and spec.submodule_search_locations:
+                cand = os.path.join(list(spec.submodule_search_locations)[0], "lib", "libnccl.so.2")
+                if os.path.exists(cand):
+                    os.environ["VGATE_B200_NCCL_LIB"] = cand
+        uid = C.create_string_buffer(128)
+        _lib.check(lib.b200_tp_unique_id(uid))
+        rdims = shard_dims(dims, tp)
+        self.dims, self.ranks = dims, []
+        for r, dev in enumerate(devices):
+            e = Engine(rdims, device=dev, tp_size=tp, tp_rank=r, **kw)
+            e.load_checkpoint(shard_checkpoint(dims, ckpt, tp, r), finalize=False)
+            self.ranks.append(e)
+        errs = [None] * tp
+
+        def init(r):                                         # ncclCommInitRank blocks until every rank has called
+            try:
+                _lib.check(lib.b200_engine_tp_init(self.ranks[r]._h, uid))
+                _lib.check(lib.b200_engine_finalize(self.ranks[r]._h))
+            except Exception as exc:  # noqa: BLE001
+                errs[r] = exc
+        ts = [threading.Thread(target=init, args=(r,)) for r in range(tp)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        for exc in errs:
+            if exc is not None:
+                raise exc
+        for r in range(1, tp):
+            _lib.check(lib.b200_engine_tp_attach(self.ranks[0]._h, self.ranks[r]._h))
+        lead = self.ranks[0]
+        self.submit, self.wait, self.poll, self.abort, self.stats, self.status = (lead.submit, lead.wait, lead.poll, lead.abort,
+                                                                                  lead.stats, lead.status)
+
+    def close(self):
+        for e in self.ranks:           # the leader first: it stops posting work to the followers
+            e.close()
+        self.ranks = []

@@ -220,3 +220,39 @@ def save_safetensors(ckpt: dict, path: str, bf16: bool = False) -> None:
         f.write(h)
         for b in blobs:
             f.write(b)
+
+
+def shard_dims(d: ModelDims, tp: int) -> ModelDims:
+    """The dimensions ONE tensor-parallel rank is created with: its share of the heads and of the MLP's
+    intermediate columns; hidden size, vocabulary and depth are whole."""
+    assert d.n_heads % tp == 0 and d.n_kv_heads % tp == 0 and d.intermediate % (64 * tp) == 0, (d, tp)
+    from dataclasses import replace
+    return replace(d, n_heads=d.n_heads // tp, n_kv_heads=d.n_kv_heads // tp, intermediate=d.intermediate // tp)
+
+
+def shard_checkpoint(d: ModelDims, ckpt: dict, tp: int, rank: int) -> dict:
+    """Megatron-style partition of a dense checkpoint for rank `rank` of `tp`: q / k / v and
+    gate / up column-parallel (rows of the HF [out, in] weights, and their biases), o_proj / down_proj row-parallel
+    (columns); embeddings, norms and LM head replicated."""
+    assert d.quant == "none", "tensor parallelism is built for dense checkpoints"
+    hd = d.head_dim
+    out = {}
+    for name, a in ckpt.items():
+        if ".self_attn.q_proj." in name:
+            n = d.n_heads // tp * hd
+            out[name] = a[rank * n:(rank + 1) * n]
+        elif ".self_attn.k_proj." in name or ".self_attn.v_proj." in name:
+            n = d.n_kv_heads // tp * hd
+            out[name] = a[rank * n:(rank + 1) * n]
+        elif ".mlp.gate_proj." in name or ".mlp.up_proj." in name:
+            n = d.intermediate // tp
+            out[name] = a[rank * n:(rank + 1) * n]
+        elif name.endswith(".self_attn.o_proj.weight"):
+            n = d.n_heads // tp * hd
+            out[name] = np.ascontiguousarray(a[:, rank * n:(rank + 1) * n])
+        elif name.endswith(".mlp.down_proj.weight"):
+            n = d.intermediate // tp
+            out[name] = np.ascontiguousarray(a[:, rank * n:(rank + 1) * n])
+        else:
+            out[name] = a
+    return out
