@@ -270,7 +270,7 @@ async def run_config1(ref_dir, log_dir, latency_ms=None):
             "cores": os.cpu_count(), "gateway": s, "raw": res}
 
 
-async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, levels, devices=None):
+async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, levels, devices=None, remote=None):
     threads = n_gpus * batch + 64
     devices = devices or [str(i) for i in range(n_gpus)]
 
@@ -281,9 +281,11 @@ async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, 
 
     genv = {"VGATE_BATCH__MAX_BATCH_SIZE": str(n_gpus * batch),        # admission above N x batch (scaling.md:77-85)
             "VGATE_WORKER__TIMEOUT_SECONDS": "600", "B200_EXECUTOR_THREADS": str(threads)}
+    if remote:                                     # "coalesce": vgate_b200.remote.CoalescingRemoteBackend as the worker hop
+        genv["VGATE_B200_REMOTE"] = remote
     out = {"config": f"#3 {preset}: {n_gpus} b200 worker(s), one per GPU, behind one gateway; {batch} concurrent "
                      f"128-token prompts per GPU, greedy-by-wire max_tokens {max_tokens}",
-           "n_gpus": n_gpus, "batch_per_gpu": batch, "cores": os.cpu_count()}
+           "n_gpus": n_gpus, "batch_per_gpu": batch, "cores": os.cpu_count(), "worker_hop": remote or "RemoteBackend (reference)"}
     async with Topology(ref_dir, n_gpus, wenv, genv, log_dir) as topo:
         if "worker_http" in levels:
             out["worker_http_multi"] = await worker_http_level(topo.endpoints(), batch, max_tokens, rounds, True)
@@ -312,6 +314,7 @@ def main():
     ap.add_argument("--levels", default="worker_http,gateway")
     ap.add_argument("--log-dir", default=os.path.join(ROOT, "gpurun_out", "gateway_logs"))
     ap.add_argument("--latency-ms", type=int, default=None, help="config 1: dry-run synthetic latency")
+    ap.add_argument("--remote", default=None, choices=[None, "coalesce"], help="gateway-side worker hop (default: the reference's RemoteBackend)")
     ap.add_argument("--stage", action="store_true")
     a = ap.parse_args()
     if a.stage:
@@ -324,7 +327,7 @@ def main():
     if a.config == 1:
         out = asyncio.run(run_config1(ref, a.log_dir, a.latency_ms))
     else:
-        out = asyncio.run(run_b200(ref, a.log_dir, a.gpus, a.batch, a.max_tokens, a.rounds, a.preset, a.levels.split(",")))
+        out = asyncio.run(run_b200(ref, a.log_dir, a.gpus, a.batch, a.max_tokens, a.rounds, a.preset, a.levels.split(","), remote=a.remote))
     out["reference_dir"] = ref
     print(json.dumps(out))
 
