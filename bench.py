@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--tp", type=int, default=1, help="tensor-parallel ranks per replica (config #5: 2); a replica then spans "
+                    "--tp consecutive GPUs and is driven by the torchrun rank of its first GPU")
     ap.add_argument("--no-gateway", action="store_true", help="skip the worker-HTTP / gateway levels (tools/bench_gateway.py)")
     ap.add_argument("--profile", default="peaked", choices=["peaked", "flat"],
                     help="synthetic checkpoint profile (vgate_b200/weights.py); timing does not depend on it, the "
@@ -57,7 +59,9 @@ def workload_name(a):
 
 def config_of(a, world):
     """The workload both arms are measured on (the reference arm prints the identical dict)."""
-    return {"workload": workload_name(a), "replicas": world, "parallelism": f"dp{world} (one replica per GPU)",
+    tp = getattr(a, "tp", 1)
+    return {"workload": workload_name(a), "replicas": world // tp,
+            "parallelism": f"dp{world} (one replica per GPU)" if tp == 1 else f"dp{world // tp} x tp{tp} (NCCL all-reduce inside a replica)",
             "l2": "per-step working set (weights 1.15 GB + KV) exceeds the 126 MB L2",
             "checkpoint_profile": a.profile}
 
@@ -387,13 +391,31 @@ def run_b200(a):
         ctl = dist.new_group(backend="gloo")      # host-side rendezvous: an NCCL barrier spins ON the GPU while it waits
     hbm_peak, peak_src = load_peaks()
     dims = PRESETS[a.preset]
-    ckpt = synthetic_checkpoint(dims, seed=0, profile=a.profile)
     max_len = a.prompt_len + a.new_tokens + 16
-    eng = Engine(dims, device=local, max_seqs=max(a.batch, 8), max_model_len=max_len,
-                 max_batch_tokens=max(8192, a.prompt_len), use_cuda_graphs=not a.no_graphs,
-                 gemm_path=a.gemm_path).load_checkpoint(ckpt)
-    del ckpt
+    kw = dict(max_seqs=max(a.batch, 8), max_model_len=max_len, max_batch_tokens=max(8192, a.prompt_len),
+              use_cuda_graphs=not a.no_graphs, gemm_path=a.gemm_path)
+    drives = local % a.tp == 0                        # with --tp K only every K-th rank drives a replica (K GPUs each)
+    eng = None
+    if drives:
+        ckpt = synthetic_checkpoint(dims, seed=0, profile=a.profile)
+        if a.tp > 1:
+            from vgate_b200.engine import TPEngine
+            eng = TPEngine(dims, ckpt, devices=tuple(range(local, local + a.tp)), **kw)
+        else:
+            eng = Engine(dims, device=local, **kw).load_checkpoint(ckpt)
+        del ckpt
     rng = np.random.default_rng(1000 + rank)          # unique prompts per rank and per step
+
+    def one_pass(prompts):
+        """tokens [batch, new_tokens], (prefill_s, decode_s) device-timed on the engine's stream"""
+        if a.tp == 1:
+            toks, _, secs = eng.generate_batch(prompts, a.new_tokens)
+            return toks, secs
+        s0 = eng.stats()                              # tensor-parallel engines take requests only: the scheduler path
+        rids = [eng.submit(p, 0.0, 1.0, a.new_tokens) for p in prompts]
+        toks = np.stack([eng.wait(r, a.new_tokens)[0] for r in rids])
+        s1 = eng.stats()
+        return toks, (s1["gpu_seconds_prefill"] - s0["gpu_seconds_prefill"], s1["gpu_seconds_decode"] - s0["gpu_seconds_decode"])
 
     def barrier():
         torch.cuda.synchronize()
@@ -401,9 +423,9 @@ def run_b200(a):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(a.warmup):
-        eng.generate_batch(make_prompts(rng, a, dims.vocab), a.new_tokens)
-    st0 = eng.stats()
+    for _ in range(a.warmup if drives else 0):
+        one_pass(make_prompts(rng, a, dims.vocab))
+    st0 = eng.stats() if drives else None
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
@@ -411,9 +433,9 @@ def run_b200(a):
     t0 = time.perf_counter()
     gpu_prefill = gpu_decode = 0.0
     checked = None                                   # prompts and tokens of the first timed step, for the self-check
-    for i in range(a.steps):
+    for i in range(a.steps if drives else 0):
         pr = make_prompts(rng, a, dims.vocab)
-        toks, _, (tp, td) = eng.generate_batch(pr, a.new_tokens)
+        toks, (tp, td) = one_pass(pr)
         if i == 0:
             checked = (pr[:4].copy(), toks[:4, :8].copy())
         gpu_prefill += tp
@@ -421,11 +443,11 @@ def run_b200(a):
     barrier()
     wall = time.perf_counter() - t0
     clk = clocks.stop() if rank == 0 else None
-    st1 = eng.stats()
+    st1 = eng.stats() if drives else None
 
     # device-timed whole-step time (CUDA events on the engine's stream), max over ranks
     dev_time = gpu_prefill + gpu_decode
-    tokens_per_rank = a.batch * a.new_tokens * a.steps
+    tokens_per_rank = a.batch * a.new_tokens * a.steps if drives else 0
     value, _ = aggregate_throughput(tokens_per_rank, dev_time, device="cuda")
     dev_time, wall, gpu_decode_max, gpu_prefill_max = reduce_over_ranks([dev_time, wall, gpu_decode, gpu_prefill], "max", "cuda")
 
@@ -434,7 +456,10 @@ def run_b200(a):
     # (vgate/worker_api.py:112, vgate/batcher.py:422): host strings in, host dicts out; tokenisation,
     # H2D of prompt ids, continuous batching, D2H of every step's sampled ids are all inside the timing.
     e2e = None
-    if not a.no_e2e:
+    if not a.no_e2e and not drives:                   # a rank whose GPU belongs to another rank's replica: collectives only
+        barrier(); barrier()
+        aggregate_throughput(0, 0.0, device="cuda")
+    if not a.no_e2e and drives:
         from concurrent.futures import ThreadPoolExecutor
         from vgate_b200.backend import B200Backend
         from vgate_b200.tokenizer import ByteTokenizer
@@ -495,6 +520,8 @@ def run_b200(a):
     # spawned by rank 0 once every rank has released its GPU; skipped when no reference checkout travelled here
     # (baseline/_ref, git-ignored) or with --no-gateway.
     levels = None
+    if a.tp > 1:
+        a.no_gateway = True                           # the gateway levels are measured on the replica-per-GPU topology
     if not a.no_gateway:
         eng.close()
         eng = None
@@ -520,11 +547,12 @@ def run_b200(a):
             "dtype": ("f16 (int4 weights, fp16 activations, fp32 accumulate)" if dims.quant == "awq" else
                       f"{dims.dtype} (dense {dims.dtype} weights and activations, fp32 accumulate)"), "data": "synthetic",
             "config": config_of(a, world), "cuda_graphs": not a.no_graphs, "gemm_path": a.gemm_path,
+            "replicas_x_tp": f"{world // a.tp} x {a.tp}",
             "wall_ms_per_step": wall / a.steps * 1e3,
             "decode": {"tpot_ms_mean": gpu_decode_max / d_steps * 1e3 if d_steps else None,
-                       "steps": d_steps, "tok_per_s": world * a.batch * d_steps / gpu_decode_max if gpu_decode_max else None,
+                       "steps": d_steps, "tok_per_s": (world // a.tp) * a.batch * d_steps / gpu_decode_max if gpu_decode_max else None,
                        "hbm_gbs": step_ach, "hbm_roofline_frac": step_ach / hbm_peak},
-            "prefill": {"tok_per_s": world * a.batch * a.prompt_len * a.steps / gpu_prefill_max if gpu_prefill_max else None},
+            "prefill": {"tok_per_s": (world // a.tp) * a.batch * a.prompt_len * a.steps / gpu_prefill_max if gpu_prefill_max else None},
             "roofline": roof,
             "gpu_launches": int(st1["kernel_launches"] - st0["kernel_launches"]),
             "clocks": clk,

@@ -71,6 +71,16 @@ class B200Backend:
             dims = PRESETS[preset]
             ckpt = synthetic_checkpoint(dims, seed=seed)
         self.tokenizer = load_tokenizer(model_id)
+        tp = _env_int("VGATE_B200_TP", 1)
+        if tp > 1:                       # the larger-model config: one replica over `tp` consecutive GPUs (NCCL all-reduce inside)
+            from .engine import TPEngine
+            dev = _env_int("VGATE_B200_DEVICE", 0)
+            self.engine = TPEngine(
+                dims, ckpt, devices=tuple(range(dev, dev + tp)), max_seqs=max_seqs, max_model_len=max_model_len,
+                max_batch_tokens=_env_int("VGATE_B200_MAX_BATCH_TOKENS", 8192), kv_bytes=_env_int("VGATE_B200_KV_BYTES", 0),
+                eos_token_id=getattr(self.tokenizer, "eos_token_id", -1),
+                use_cuda_graphs=bool(_env_int("VGATE_B200_CUDA_GRAPHS", 1)))
+            return
         self.engine = Engine(
             dims, device=_env_int("VGATE_B200_DEVICE", 0), max_seqs=max_seqs, max_model_len=max_model_len,
             max_batch_tokens=_env_int("VGATE_B200_MAX_BATCH_TOKENS", 8192),
