@@ -27,10 +27,10 @@ def _bits(a, dtype):
 
 
 @pytest.mark.parametrize("dtype", ["fp16", "bf16"])
-@pytest.mark.parametrize("T", [1, 33, 128, 300])
-def test_dense_gemm_epilogues_match_fp64(dtype, T):
+@pytest.mark.parametrize("T,K,N", [(1, 1024, 512), (33, 1024, 512), (128, 1024, 512), (300, 1024, 512),
+                                   (600, 512, 9728)])       # the last: 256 weight rows per CTA (76 tiles x 3 token tiles > 148)
+def test_dense_gemm_epilogues_match_fp64(dtype, T, K, N):
     rng = np.random.default_rng(T)
-    K, N = 1024, 512
     code = _lib.DTYPE_BF16 if dtype == "bf16" else _lib.DTYPE_F16
     w = _round16(rng.standard_normal((N, K)).astype(np.float32) * 0.05, dtype)
     x = _round16(rng.standard_normal((T, K)).astype(np.float32), dtype)

@@ -41,7 +41,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
   using Cfg = UmmaCfg<NT, kW4, true, MT>;
   constexpr int kStages = Cfg::kStages, kRing = Cfg::kRing;
   constexpr int kTileBBytes = Cfg::kTileBBytes, kStageBytes = Cfg::kStageBytes;
-  constexpr int kXInStage = kW4 ? 0 : kTileABytes;           // byte offset of the first X tile inside a stage
+  constexpr int kXInStage = kW4 ? 0 : MT * kTileABytes;      // byte offset of the first X tile inside a stage
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   // SWIZZLE_128B needs 1024-byte alignment; the dynamic smem base is only guaranteed 16
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -150,7 +150,9 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       const int pre = kW4 ? 0 : min(nst, kStages);
       for (int gi = 0; gi < pre; ++gi) {
         mbar_arrive_expect_tx(&sb->full[gi], (uint32_t)(kXInStage + kTileBBytes));
-        tma_load_2d(smem + gi * kStageBytes, &map_w, (kt0 + gi) * kUmmaBK, nt * kUmmaM, &sb->full[gi]);
+#pragma unroll
+        for (int m = 0; m < MT; ++m)
+          tma_load_2d(smem + gi * kStageBytes + m * kTileABytes, &map_w, (kt0 + gi) * kUmmaBK, (nt * MT + m) * kUmmaM, &sb->full[gi]);
       }
       grid_dep_wait();                         // activations come from the upstream kernel
       if (tr) tr[7] = clock64();
@@ -161,7 +163,11 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         if (gi >= pre) {
           mbar_wait(&sb->empty[s], ((uint32_t)(gi / kStages) & 1u) ^ 1u);
           mbar_arrive_expect_tx(&sb->full[s], (uint32_t)(kXInStage + nt_here * kTileBBytes));
-          if (!kW4) tma_load_2d(stage, &map_w, (kt0 + gi) * kUmmaBK, nt * kUmmaM, &sb->full[s]);
+          if constexpr (!kW4) {
+#pragma unroll
+            for (int m = 0; m < MT; ++m)
+              tma_load_2d(stage + m * kTileABytes, &map_w, (kt0 + gi) * kUmmaBK, (nt * MT + m) * kUmmaM, &sb->full[s]);
+          }
         }
         for (int t = 0; t < nt_here; ++t)
           tma_load_2d(stage + kXInStage + t * kTileBBytes, &map_x, (kt0 + gi * tps + t) * kUmmaBK, tok0, &sb->full[s]);
@@ -191,10 +197,14 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                             (gi | t | k) != 0 ? 1u : 0u);
             }
           } else {
-            const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
 #pragma unroll
-            for (int k = 0; k < kUmmaBK / 16; ++k)     // advance 16 elements (32 bytes) inside the 128-byte swizzle row
-              umma_f16(tmem, make_smem_desc(a_addr + k * 32), make_smem_desc(b_addr + k * 32), idesc, (gi | t | k) != 0 ? 1u : 0u);
+            for (int m = 0; m < MT; ++m) {               // row tile m: its own accumulator, the same activation tile
+              const uint32_t a_addr = smem_u32(smem + s * kStageBytes + m * kTileABytes);
+#pragma unroll
+              for (int k = 0; k < kUmmaBK / 16; ++k)     // advance 16 elements (32 bytes) inside the 128-byte swizzle row
+                umma_f16(tmem + (uint32_t)(m * (Cfg::kAccCols / MT)), make_smem_desc(a_addr + k * 32), make_smem_desc(b_addr + k * 32), idesc,
+                         (gi | t | k) != 0 ? 1u : 0u);
+            }
           }
         }
         umma_commit(&sb->empty[s]);            // the stage is free again when the MMAs above retire
@@ -325,7 +335,12 @@ static int dispatch_nt(int nt_sel, const CUtensorMap& mx, const CUtensorMap& mw,
       return launch_nt<128, kW4>(mx, mw, p, n_splits, s);
     default:
       if constexpr (kW4) { set_last_error("umma_w4: token tile must be <= 128"); return B200_ERR_INVALID; }
-      else return launch_nt<256, kW4>(mx, mw, p, n_splits, s);
+      else {
+        // 256 weight rows per CTA once 128-row tiles would need more than one wave: half the operand traffic through L2
+        if (p.N % (2 * kUmmaM) == 0 && n_splits == 1 && (int64_t)(p.N / kUmmaM) * ((p.T + 255) / 256) > 148)
+          return launch_nt<256, kW4, 2>(mx, mw, p, n_splits, s);
+        return launch_nt<256, kW4>(mx, mw, p, n_splits, s);
+      }
   }
 }
 

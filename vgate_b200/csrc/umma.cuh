@@ -140,6 +140,10 @@ struct UmmaSmem {                      // barriers live after the tile rings
 // Warpgroup w still takes groups w, w + 4, ...; stage = group % 7 is then shared between warpgroups, which
 // is safe for the parity waits because a warpgroup's previous group g - 4 already waited for group
 // g - 4 - 7 to be consumed, so the barrier of stage g % 7 is never more than one phase behind.
+// Dense MT = 2 (token tile 256): a CTA multiplies 256 weight rows by 256 tokens -- 128 flop per byte through L2 instead
+// of 85 for a 128 x 256 tile; a large dense GEMM on 148 SMs is bound by L2->SM bandwidth before it is bound by the
+// tensor pipe (26 GB of operand traffic for the 7B gate_up GEMM at 8192 tokens with 128-row tiles).  Three stages of
+// {A0, A1, B} = 64 KB; two 256-column accumulators fill the tensor memory.
 // MT (W4 prefill, token tile 128): weight-row tiles per CTA.  With MT = 2 a CTA multiplies 256 weight rows by
 // the activation tile it stages, which halves the activation traffic through L2 -- the bound of the prefill
 // GEMM (6.97 GB of L2->SM reads for one gate_up at 12 800 tokens, profiles/r01_kernels_ncu_full.txt).  Tensor
@@ -147,21 +151,22 @@ struct UmmaSmem {                      // barriers live after the tile rings
 template <int NT, bool kW4, bool kDeep = true, int MT = 1>
 struct UmmaCfg {
   static constexpr int kMaxTilesPerStage = kW4 ? 2 : 1;
-  static constexpr int kStages = MT == 2 ? 2 : (kW4 && kDeep && NT <= 64) ? 7 : 4;
+  static constexpr int kStages = MT == 2 ? (kW4 ? 2 : 3) : (kW4 && kDeep && NT <= 64) ? 7 : 4;
   // private ring slots per producer warpgroup.  3 (all 12 chunks of a gate_up CTA requested at once) was
   // measured: no change -- the kernel's stall samples sit in the wait for the first chunk (HBM latency) and
   // in the wait for the accumulator (12 groups x 256 tensor cycles), not in ring refills.
   static constexpr int kSlotsPerWg = 2;
   static constexpr int kRing = kW4 ? 4 * kSlotsPerWg : 0;
   static constexpr int kTileBBytes = NT * kUmmaBK * 2;
-  static constexpr int kStageBytes = (kW4 ? 0 : kTileABytes) + kMaxTilesPerStage * kTileBBytes;
+  static constexpr int kStageBytes = (kW4 ? 0 : MT * kTileABytes) + kMaxTilesPerStage * kTileBBytes;
   static constexpr int kAccCols = MT * (NT < 32 ? 32 : NT);  // TMEM: accumulator(s), then (W4) the A slots, 64 columns each
   static constexpr int kTmemNeed = kAccCols + (kW4 ? kStages * MT * 64 : 0);
   static constexpr int kTmemCols = kTmemNeed <= 32 ? 32 : kTmemNeed <= 64 ? 64 : kTmemNeed <= 128 ? 128 : kTmemNeed <= 256 ? 256 : 512;
   static constexpr int kRingOff = kStages * kStageBytes;
   static constexpr int kBarOff = kRingOff + kRing * kChunkStride;
   static constexpr int kSmemBytes = kBarOff + (int)sizeof(UmmaSmem) + 1024;
-  static_assert(MT == 1 || (MT == 2 && kW4 && NT == 128), "two row tiles per CTA: W4, token tile 128");
+  static_assert(MT == 1 || (MT == 2 && kW4 && NT == 128) || (MT == 2 && !kW4 && NT == 256),
+                "two row tiles per CTA: W4 with token tile 128, dense with token tile 256");
   static_assert(kStages * MT >= 4 && kStages <= kMaxStages && kRing <= kMaxRing, "ring sizes");
   static_assert(kTmemNeed <= 512, "tensor memory budget");
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
