@@ -83,6 +83,32 @@ def test_concurrent_single_prompt_calls_share_bodies(vgate_env):
         be.shutdown()
 
 
+def test_prefix_affinity_routing_keeps_a_prefix_on_one_worker(vgate_env):
+    import httpx
+    seen = {}
+
+    def handler(request):
+        body = json.loads(request.content)
+        for p in body["prompts"]:
+            seen.setdefault(p[:40], set()).add(request.url.host)
+        return httpx.Response(200, json={"results": [{"text": "", "token_ids": [], "num_tokens": 0, "metrics": {}} for _ in body["prompts"]]})
+
+    be = _backend(handler, endpoints=("http://w0", "http://w1", "http://w2"), VGATE_B200_ROUTE="prefix", VGATE_B200_ROUTE_CHARS=40)
+    try:
+        sp = be.create_sampling_params(0.0, 1.0, 4)
+        systems = [f"System prompt number {i:02d}, forty characters.."[:40] for i in range(12)]
+        prompts = [s + f" question {j}" for s in systems for j in range(5)]
+        ts = [threading.Thread(target=lambda p=p: be.generate([p], sp)) for p in prompts]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        assert all(len(hosts) == 1 for hosts in seen.values())            # a prefix class never changes worker
+        assert len({next(iter(h)) for h in seen.values()}) >= 2           # and the classes spread over the pool
+    finally:
+        be.shutdown()
+
+
 def test_retry_and_failure_policy_follow_the_reference(vgate_env):
     import httpx
     from vgate.backends.remote_backend import RemoteInferenceError

@@ -16,6 +16,12 @@ gaps SURVEY.md section 8(f) ranks first:
    dicts the in-process backends yield; closing the generator closes the connection, the worker sees the
    disconnect and aborts the engine request -- cancellation crosses both connections.
 
+3. **Prefix-affinity routing** (optional, ``VGATE_B200_ROUTE=prefix``; ROADMAP.md:664-675).  Round-robin sends
+   prompts with a common start (a system prompt, a conversation so far) to different workers, so each worker's
+   engine prefix cache sees a fraction of them.  With this switch a body goes to the healthy worker chosen by the
+   hash of the first ``VGATE_B200_ROUTE_CHARS`` (256) characters of its first prompt -- and prompts are grouped into
+   bodies by that same key -- falling back to round-robin when that worker is out of rotation.
+
 Selected from outside the reference tree: ``vgate_b200.register`` returns this class instead of
 ``RemoteBackend`` when ``VGATE_B200_REMOTE=coalesce`` is set for a gateway with worker endpoints.
 """
@@ -50,6 +56,8 @@ class CoalescingRemoteBackend:
         self._client = httpx.Client(timeout=self._timeout, headers=self._headers,
                                     limits=httpx.Limits(max_connections=None, max_keepalive_connections=64))
         self.max_body = int(os.environ.get("VGATE_B200_COALESCE_MAX", "64"))       # prompts per body
+        self.route_prefix = os.environ.get("VGATE_B200_ROUTE") == "prefix"
+        self.route_chars = int(os.environ.get("VGATE_B200_ROUTE_CHARS", "256"))
         n_senders = int(os.environ.get("VGATE_B200_COALESCE_SENDERS", "16"))
         self._queues: Dict[str, Any] = {}       # sampling-parameter class -> (params, [(prompt, future, t_enqueued)])
         self._cv = threading.Condition()
@@ -73,9 +81,28 @@ class CoalescingRemoteBackend:
         futs = []
         for p in prompts:
             f: Future = Future()
-            self._enqueue(key, sampling_params, p, f)
+            k = key if not self.route_prefix else f"{key}|{self._affinity(p)}"    # one body = one worker = one prefix class
+            self._enqueue(k, sampling_params, p, f)
             futs.append(f)
         return [f.result() for f in futs]       # raises what the sender set (RemoteInferenceError, NoHealthyWorkersError)
+
+    def _affinity(self, prompt: str) -> int:
+        import zlib
+        n = max(1, len(self.registry.endpoints()))
+        return zlib.crc32(prompt[:self.route_chars].encode("utf-8", "replace")) % n
+
+    def _pick(self, prompts, tried):
+        """Round-robin (vgate/worker_registry.py:178-201), or the prefix class's own worker while it is healthy."""
+        if self.route_prefix and not tried:
+            eps = self.registry.endpoints()
+            if eps:
+                want = eps[self._affinity(prompts[0]) % len(eps)]
+                others = set(eps) - {want}
+                try:
+                    return self.registry.pick(exclude=others)
+                except NoHealthyWorkersError:
+                    pass
+        return self.registry.pick(exclude=tried)
 
     # -- coalescing senders ----------------------------------------------------------------------------
     def _enqueue(self, key, sp, prompt, fut):
@@ -119,7 +146,7 @@ class CoalescingRemoteBackend:
         last_connect_error = None
         for attempt in range(max(1, len(self.registry.endpoints()))):
             try:
-                endpoint = self.registry.pick(exclude=tried)
+                endpoint = self._pick(prompts, tried)
             except NoHealthyWorkersError:
                 break
             if attempt > 0:
