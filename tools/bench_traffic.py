@@ -17,7 +17,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 
 
-def run(eng_kw, preset, rate, n_req, seed, max_inflight):
+def run(eng_kw, preset, rate, n_req, seed, max_inflight, long_frac=0.0, long_len=1536):
     from vgate_b200.backend import B200Backend
     from vgate_b200.engine import Engine
     from vgate_b200.tokenizer import ByteTokenizer
@@ -27,7 +27,8 @@ def run(eng_kw, preset, rate, n_req, seed, max_inflight):
     be = B200Backend()
     be.engine, be.tokenizer = eng, ByteTokenizer()
     rng = np.random.default_rng(seed)
-    prompts = [bytes(rng.integers(32, 127, size=128, dtype=np.uint8)).decode("ascii") for _ in range(n_req)]
+    lens = np.where(rng.random(n_req) < long_frac, long_len, 128)       # a share of long prompts: their prefill is what chunking cuts up
+    prompts = [bytes(rng.integers(32, 127, size=int(n), dtype=np.uint8)).decode("ascii") for n in lens]
     news = rng.integers(64, 257, size=n_req)
     gaps = rng.exponential(1.0 / rate, size=n_req)
     # warm-up: every decode batch size gets its kernels loaded / graph captured lazily; touch a few
@@ -73,13 +74,16 @@ def main():
     ap.add_argument("--requests", type=int, default=600)
     ap.add_argument("--max-seqs", type=int, default=64)
     ap.add_argument("--chunks", default="2048,512,8192", help="VGATE_B200_PREFILL_CHUNK values to compare")
+    ap.add_argument("--long-frac", type=float, default=0.0, help="share of requests with a --long-len-token prompt")
+    ap.add_argument("--long-len", type=int, default=1536)
     a = ap.parse_args()
     out = {"workload": f"{a.preset}: Poisson arrivals at {a.rate:g} req/s, {a.requests} requests, 128-token prompts, greedy, "
-                       f"max_tokens uniform in 64..256, at most {a.max_seqs} sequences in the engine", "runs": {}}
+                       f"max_tokens uniform in 64..256, at most {a.max_seqs} sequences in the engine"
+                       + (f"; {a.long_frac:.0%} of the prompts have {a.long_len} tokens" if a.long_frac > 0 else ""), "runs": {}}
     for chunk in a.chunks.split(","):
         os.environ["VGATE_B200_PREFILL_CHUNK"] = chunk
-        kw = dict(max_seqs=a.max_seqs, max_model_len=128 + 256 + 16, max_batch_tokens=8192)
-        out["runs"][f"prefill_chunk_{chunk}"] = run(kw, a.preset, a.rate, a.requests, 7, a.max_seqs * 2)
+        kw = dict(max_seqs=a.max_seqs, max_model_len=max(128, a.long_len if a.long_frac > 0 else 0) + 256 + 16, max_batch_tokens=8192)
+        out["runs"][f"prefill_chunk_{chunk}"] = run(kw, a.preset, a.rate, a.requests, 7, a.max_seqs * 2, a.long_frac, a.long_len)
     print(json.dumps(out))
 
 
