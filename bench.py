@@ -448,8 +448,9 @@ def run_b200(a):
     # device-timed whole-step time (CUDA events on the engine's stream), max over ranks
     dev_time = gpu_prefill + gpu_decode
     tokens_per_rank = a.batch * a.new_tokens * a.steps if drives else 0
-    value, _ = aggregate_throughput(tokens_per_rank, dev_time, device="cuda")
-    dev_time, wall, gpu_decode_max, gpu_prefill_max = reduce_over_ranks([dev_time, wall, gpu_decode, gpu_prefill], "max", "cuda")
+    cuda_dev = f"cuda:{local}"
+    value, _ = aggregate_throughput(tokens_per_rank, dev_time, device=cuda_dev)
+    dev_time, wall, gpu_decode_max, gpu_prefill_max = reduce_over_ranks([dev_time, wall, gpu_decode, gpu_prefill], "max", cuda_dev)
 
     # ---- e2e: the public API, called the way V-Gate calls it ----
     # B200Backend.generate([one prompt], sampling_params) from one thread per in-flight request
@@ -458,7 +459,7 @@ def run_b200(a):
     e2e = None
     if not a.no_e2e and not drives:                   # a rank whose GPU belongs to another rank's replica: collectives only
         barrier(); barrier()
-        aggregate_throughput(0, 0.0, device="cuda")
+        aggregate_throughput(0, 0.0, device=f"cuda:{local}")
     if not a.no_e2e and drives:
         from concurrent.futures import ThreadPoolExecutor
         from vgate_b200.backend import B200Backend
@@ -485,7 +486,7 @@ def run_b200(a):
             tpots += [r["metrics"]["gen_time"] / r["num_tokens"] for r in results]   # vgate/batcher.py:431
         barrier()
         pool.shutdown()
-        e2e_value, _ = aggregate_throughput(tot_n, tot_t, device="cuda")
+        e2e_value, _ = aggregate_throughput(tot_n, tot_t, device=f"cuda:{local}")
         e2e = {"value": e2e_value, "unit": UNIT,
                "h2d_bytes_per_step": int(a.batch * a.prompt_len * 4),       # prompt token ids
                "d2h_bytes_per_step": int(a.batch * a.new_tokens * 4),       # sampled ids, read back every decode step

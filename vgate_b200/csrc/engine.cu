@@ -81,6 +81,16 @@ static int nccl_fail(int code, const char* what) {
   return B200_ERR_CUDA;
 }
 
+// The library selects the engine's device for the duration of a call and gives the caller's current device back
+// (a host that drives several devices -- a tensor-parallel group, PyTorch next to it -- must not find it changed).
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; cudaSetDevice(dev); }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+  DeviceGuard(const DeviceGuard&) = delete;
+  DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+
 static double now_s() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -995,7 +1005,7 @@ int32_t b200_engine_create(const b200_config* cfg, b200_engine** out) {
   int ndev = 0;
   B200_CUDA(cudaGetDeviceCount(&ndev));
   B200_REQUIRE(cfg->device >= 0 && cfg->device < ndev, "device ordinal out of range");
-  B200_CUDA(cudaSetDevice(cfg->device));
+  DeviceGuard guard(cfg->device);
   cudaDeviceProp prop;
   B200_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
   if (prop.major != 10) {
@@ -1071,7 +1081,7 @@ int32_t b200_engine_load_tensor(b200_engine* e, const char* name_c, const void* 
                                 const int64_t* shape) {
   B200_REQUIRE(e && name_c && data && shape && ndim >= 1 && ndim <= 2, "load_tensor: null / ndim");
   if (e->finalized) { set_last_error("load_tensor after finalize"); return B200_ERR_STATE; }
-  B200_CUDA(cudaSetDevice(e->cfg.device));
+  DeviceGuard guard(e->cfg.device);
   const std::string name(name_c);
   size_t count = 1;
   for (int i = 0; i < ndim; ++i) count *= (size_t)shape[i];
@@ -1199,7 +1209,7 @@ int32_t b200_engine_finalize(b200_engine* e) {
                    " checkpoint tensors loaded");
     return B200_ERR_STATE;
   }
-  B200_CUDA(cudaSetDevice(e->cfg.device));
+  DeviceGuard guard(e->cfg.device);
   const b200_config& c = e->cfg;
   int rc;
   // RoPE table: inv_freq = theta^(-2i/d), angle = pos * inv_freq, all fp32 like the HF/vLLM cache
@@ -1344,7 +1354,7 @@ void b200_engine_destroy(b200_engine* e) {
     e->tp_cv.notify_all();
   }
   if (e->tp_thread.joinable()) e->tp_thread.join();
-  cudaSetDevice(e->cfg.device);
+  DeviceGuard guard(e->cfg.device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (auto& g : e->decode_graphs) cudaGraphExecDestroy(g.second.exec);
   for (auto& w : e->layers) {
@@ -1500,7 +1510,7 @@ int32_t b200_engine_tp_init(b200_engine* e, const void* id128) {
   B200_REQUIRE(e->tp_size > 1, "tp_init on an engine created with tp_size <= 1");
   NcclApi& a = nccl_api();
   if (!a.ok) { set_last_error("libnccl.so.2 not found (set VGATE_B200_NCCL_LIB)"); return B200_ERR_STATE; }
-  B200_CUDA(cudaSetDevice(e->cfg.device));
+  DeviceGuard guard(e->cfg.device);
   NcclId id;
   std::memcpy(&id, id128, sizeof(id));
   typedef int (*InitFn)(void**, int, NcclId, int);
@@ -1548,7 +1558,7 @@ int32_t b200_generate_batch(b200_engine* e, const int32_t* prompt_ids, int32_t n
     e->exclusive = true;
   }
   struct Release { b200_engine* e; ~Release() { std::lock_guard<std::mutex> lk(e->mu); e->exclusive = false; e->cv_work.notify_all(); } } release{e};
-  B200_CUDA(cudaSetDevice(e->cfg.device));
+  DeviceGuard guard(e->cfg.device);
   cudaStream_t s = e->stream;
   { const int rc0 = e->collect_decode(); if (rc0) return rc0; }   // a look-ahead step of sequences aborted since
   { std::lock_guard<std::mutex> lk(e->mu); e->drop_prefix_cache(); }
