@@ -336,6 +336,7 @@ def test_chunked_prefill_interleaves_with_decode_and_changes_nothing(monkeypatch
     late = [rng.integers(0, dims.vocab, size=n, dtype=np.int32) for n in lens]
     early = [rng.integers(0, dims.vocab, size=20, dtype=np.int32) for _ in range(4)]
     monkeypatch.setenv("VGATE_B200_PREFILL_CHUNK", "48")
+    monkeypatch.setenv("VGATE_B200_MAX_STALL_MS", "0")        # strict alternation: a decode step after every chunk
     monkeypatch.setenv("VGATE_B200_PREFIX_CACHE", "0")      # the solo runs below would otherwise leave the prompts cached
     eng = Engine(dims, max_seqs=16, max_model_len=512, max_batch_tokens=256).load_checkpoint(ckpt)
     try:

@@ -246,7 +246,7 @@ struct b200_engine {
   };
   struct GraphVal { cudaGraphExec_t exec; int64_t launches; };
   std::map<GraphKey, GraphVal> decode_graphs;  // one captured decode step (advance + forward) per configuration
-  std::map<int, bool> decode_warm;             // batch sizes whose kernels have run eagerly once
+  std::map<int, int> decode_warm;              // per batch size and sampling kind: eager steps run so far
   int poll_waiters = 0;                        // threads blocked in b200_poll (guarded by mu)
   std::vector<int64_t> last_decode_ids;        // scheduler: request ids of the previous decode step, in row order
 
@@ -327,6 +327,10 @@ struct b200_engine {
   // stall is one chunk, and decode steps alternate with the chunks (the policy vLLM's scheduler follows for
   // vllm_backend.py:105-132 callers).  With nothing decoding the full budget is used.
   int prefill_chunk = getenv("VGATE_B200_PREFILL_CHUNK") ? std::max(16, atoi(getenv("VGATE_B200_PREFILL_CHUNK"))) : 2048;
+  // ... and prefill passes run back to back until they have held the decoding sequences up for this long (GPU time of
+  // the passes since the last decode step); then one decode step.  0 alternates strictly.
+  double max_stall_ms = getenv("VGATE_B200_MAX_STALL_MS") ? atof(getenv("VGATE_B200_MAX_STALL_MS")) : 25.0;
+  double stall_ms = 0.0;                       // scheduler thread only
   bool last_step_was_prefill = false;
   std::unordered_map<int64_t, std::shared_ptr<Request>> table;
   b200_stats stats{};
@@ -624,8 +628,11 @@ struct b200_engine {
       g_launch_count += 1;
       return forward(n, n, nullptr, true);
     };
-    if (!cfg.use_cuda_graphs || !decode_warm[2 * n + (greedy_only ? 1 : 0)]) {
-      decode_warm[2 * n + (greedy_only ? 1 : 0)] = true;
+    // A configuration's first two steps run eagerly, the third is captured: while a batch ramps up or drains, every
+    // step has another size, and capturing + instantiating a graph (milliseconds for hundreds of nodes) for a size
+    // that is used once costs more than it saves.
+    if (!cfg.use_cuda_graphs || decode_warm[2 * n + (greedy_only ? 1 : 0)] < 2) {
+      decode_warm[2 * n + (greedy_only ? 1 : 0)]++;
       return eager();
     }
     const GraphKey key{n, out_tokens, out_stride, greedy_only};
@@ -865,6 +872,7 @@ struct b200_engine {
     stats.kernel_launches += g_launch_count - launches0;
     stats.steps_prefill++; stats.tokens_prefill += T; stats.gpu_seconds_prefill += ms * 1e-3;
     stats.tokens_generated += n;
+    stall_ms += ms;
     for (const Chunk& c : chunks) c.req->n_prefilled = c.start + c.count;
     for (int r = 0; r < n; ++r) {
       Request& q = *done[r];
@@ -934,7 +942,7 @@ struct b200_engine {
         waiting.pop_front();
       }
       // choose the step: prompt chunks and decode steps alternate while both kinds of work exist
-      const bool do_prefill = !prefilling.empty() && (running.empty() || !last_step_was_prefill);
+      const bool do_prefill = !prefilling.empty() && (running.empty() || !last_step_was_prefill || stall_ms < max_stall_ms);
       std::vector<Chunk> chunks;
       std::vector<std::shared_ptr<Request>> batch;
       if (do_prefill) {
@@ -956,6 +964,7 @@ struct b200_engine {
       lk.lock();
       stepping = false;
       last_step_was_prefill = do_prefill;
+      if (!do_prefill) stall_ms = 0.0;
       if (rc != B200_OK) { inflight = Inflight{}; fail_all(g_last_error); continue; }
       if (do_prefill) {                              // sequences whose prompt is in the cache start decoding
         for (auto& c : chunks) register_prefix(*c.req);
