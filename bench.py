@@ -370,8 +370,11 @@ def gateway_levels(a, world):
         return {"unavailable": "no V-Gate checkout on this box (tools/bench_gateway.py --stage copies it to baseline/_ref)"}
     vis = os.environ.get("CUDA_VISIBLE_DEVICES")
     devs = vis.split(",") if vis else [str(i) for i in range(world)]
+    # at N >= 2 also with as many gateway server processes as workers (tools/vgate_launch.py): one process is one
+    # event loop, which is what binds behind the unmodified single-process gateway
     out = asyncio.run(bg.run_b200(ref, os.path.join(ROOT, "gpurun_out", "gateway_logs"), world, a.batch, a.new_tokens, 2,
-                                  a.preset, ["worker_http", "gateway"], devices=devs[:world]))
+                                  a.preset, ["worker_http", "gateway"], devices=devs[:world],
+                                  extra_gateway_procs=world if world > 1 else 0))
     return out
 
 
@@ -567,8 +570,12 @@ def run_b200(a):
                 line["worker_http"] = levels["worker_http_multi"]
                 line["worker_http_single_prompt_bodies"] = levels["worker_http_single"]
                 line["gateway"] = levels["gateway"]
+                if "gateway_multi_process" in levels:
+                    line["gateway_multi_process"] = levels["gateway_multi_process"]
                 lv = {"engine_c_abi": value, "backend_threads": e2e["value"] if e2e else None,
                       "worker_http": levels["worker_http_multi"]["tok_per_s"], "gateway": levels["gateway"]["tok_per_s"]}
+                if "gateway_multi_process" in levels:
+                    lv[f"gateway_{levels['gateway_multi_process']['processes']}_processes"] = levels["gateway_multi_process"]["tok_per_s"]
                 line["levels_tok_per_s"] = lv
                 line["binding_level"] = ("gateway (CPU control plane: one event loop, one thread per in-flight request)"
                                          if lv["gateway"] < 0.9 * lv["worker_http"] else

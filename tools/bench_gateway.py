@@ -152,6 +152,20 @@ class Topology:
             raise
         return self
 
+    async def restart_gateway(self, gateway_env):
+        """The same workers behind a gateway started with other settings."""
+        _terminate(self.gateway)
+        for _ in range(100):
+            if _port_free(GATEWAY_PORT):
+                break
+            await asyncio.sleep(0.1)
+        env = {"VGATE_ROLE": "gateway", "VGATE_SERVER__PORT": str(GATEWAY_PORT),
+               "VGATE_WORKER__ENDPOINTS": json.dumps(self.endpoints())}
+        env.update(gateway_env)
+        self.gateway = _spawn(self.ref, env, os.path.join(self.logs, "gateway-restarted.log"), self.plain)
+        await _wait_healthy(self.base_url, self.gateway, 60)
+        await asyncio.sleep(1.0)
+
     async def __aexit__(self, *exc):
         _terminate(self.gateway)
         for w in self.workers:
@@ -270,7 +284,8 @@ async def run_config1(ref_dir, log_dir, latency_ms=None):
             "cores": os.cpu_count(), "gateway": s, "raw": res}
 
 
-async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, levels, devices=None, remote=None):
+async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, levels, devices=None, remote=None, gateway_procs=1,
+                   extra_gateway_procs=0):
     threads = n_gpus * batch + 64
     devices = devices or [str(i) for i in range(n_gpus)]
 
@@ -283,23 +298,40 @@ async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, 
             "VGATE_WORKER__TIMEOUT_SECONDS": "600", "B200_EXECUTOR_THREADS": str(threads)}
     if remote:                                     # "coalesce": vgate_b200.remote.CoalescingRemoteBackend as the worker hop
         genv["VGATE_B200_REMOTE"] = remote
+    if gateway_procs > 1:                          # K server processes of the unmodified gateway app on the one port
+        genv["B200_GATEWAY_PROCESSES"] = str(gateway_procs)
+        genv["VGATE_BATCH__MAX_BATCH_SIZE"] = str(max(8, (n_gpus * batch + gateway_procs - 1) // gateway_procs * 2))
     out = {"config": f"#3 {preset}: {n_gpus} b200 worker(s), one per GPU, behind one gateway; {batch} concurrent "
                      f"128-token prompts per GPU, greedy-by-wire max_tokens {max_tokens}",
-           "n_gpus": n_gpus, "batch_per_gpu": batch, "cores": os.cpu_count(), "worker_hop": remote or "RemoteBackend (reference)"}
+           "n_gpus": n_gpus, "batch_per_gpu": batch, "cores": os.cpu_count(), "worker_hop": remote or "RemoteBackend (reference)", "gateway_processes": gateway_procs}
     async with Topology(ref_dir, n_gpus, wenv, genv, log_dir) as topo:
         if "worker_http" in levels:
             out["worker_http_multi"] = await worker_http_level(topo.endpoints(), batch, max_tokens, rounds, True)
             out["worker_http_single"] = await worker_http_level(topo.endpoints(), batch, max_tokens, rounds, False)
         if "gateway" in levels:
             conc = n_gpus * batch
-            warm = unique_prompts(conc, "gw-warm")
-            await gateway_level(ref_dir, topo.base_url, conc, conc, max_tokens, warm)
-            prompts = unique_prompts(conc * rounds, "gw")
-            res, stats = await gateway_level(ref_dir, topo.base_url, conc, conc * rounds, max_tokens, prompts)
-            out["gateway"] = summarise_gateway(res, stats)
-            # the wire carries temperature 0.7 / top_p 0.9 by default (main.py request defaults): bench_load cannot
-            # ask for greedy, so the gateway level samples; token counts are what is measured
-            out["gateway"]["note"] = "bench_load.py sends the API's default sampling (temperature 0.7, top_p 0.9)"
+
+            async def measure(tag):
+                warm = unique_prompts(conc, tag + "-warm")
+                await gateway_level(ref_dir, topo.base_url, conc, conc, max_tokens, warm)
+                prompts = unique_prompts(conc * rounds, tag)
+                res, stats = await gateway_level(ref_dir, topo.base_url, conc, conc * rounds, max_tokens, prompts)
+                g = summarise_gateway(res, stats)
+                # the wire carries temperature 0.7 / top_p 0.9 by default (main.py request defaults): bench_load cannot
+                # ask for greedy, so the gateway level samples; token counts are what is measured
+                g["note"] = "bench_load.py sends the API's default sampling (temperature 0.7, top_p 0.9)"
+                return g
+            out["gateway"] = await measure("gw")
+            if extra_gateway_procs and extra_gateway_procs > 1:
+                # the same workers behind the same gateway app served by K processes on the one port
+                g2 = dict(genv)
+                g2["B200_GATEWAY_PROCESSES"] = str(extra_gateway_procs)
+                g2["VGATE_BATCH__MAX_BATCH_SIZE"] = str(max(8, (conc + extra_gateway_procs - 1) // extra_gateway_procs * 2))
+                await topo.restart_gateway(g2)
+                out["gateway_multi_process"] = await measure("gwmp")
+                out["gateway_multi_process"]["processes"] = extra_gateway_procs
+                out["gateway_multi_process"]["note"] += ("; /stats counters (dedup, cache hits, TPOT) are per process and are read "
+                                                          "from whichever process answers")
     return out
 
 
@@ -315,6 +347,8 @@ def main():
     ap.add_argument("--log-dir", default=os.path.join(ROOT, "gpurun_out", "gateway_logs"))
     ap.add_argument("--latency-ms", type=int, default=None, help="config 1: dry-run synthetic latency")
     ap.add_argument("--remote", default=None, choices=[None, "coalesce"], help="gateway-side worker hop (default: the reference's RemoteBackend)")
+    ap.add_argument("--gateway-procs", type=int, default=1, help="server processes of the gateway app on its one port (uvicorn workers)")
+    ap.add_argument("--extra-gateway-procs", type=int, default=0, help="after the main gateway run, restart the gateway with K processes and measure again")
     ap.add_argument("--stage", action="store_true")
     a = ap.parse_args()
     if a.stage:
@@ -327,7 +361,8 @@ def main():
     if a.config == 1:
         out = asyncio.run(run_config1(ref, a.log_dir, a.latency_ms))
     else:
-        out = asyncio.run(run_b200(ref, a.log_dir, a.gpus, a.batch, a.max_tokens, a.rounds, a.preset, a.levels.split(","), remote=a.remote))
+        out = asyncio.run(run_b200(ref, a.log_dir, a.gpus, a.batch, a.max_tokens, a.rounds, a.preset, a.levels.split(","), remote=a.remote, gateway_procs=a.gateway_procs,
+                                   extra_gateway_procs=a.extra_gateway_procs))
     out["reference_dir"] = ref
     print(json.dumps(out))
 
