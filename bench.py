@@ -349,10 +349,13 @@ def dominant_kernel_roofline(a, dims, hbm_peak, peak_src):
     ach = alg / t / 1e9
     return {"bound": "hbm", "kernel": ("umma_gemm_kernel<64, W4> gate_up + SwiGLU" if use_umma else "w4_gemv_kernel gate_up")
             + f" [{T}x{K}]x[{N}x{K}]", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-            # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at T=64 from one `ncu --set full`
-            # capture (profiles/r01_gateup_ncu_full.txt): 14.86 MB read + 0 written (output stays in L2)
-            "traffic": (14863104 if use_umma and T == 64 else None),
-            "traffic_source": "profiles/r01_gateup_ncu_full.txt", "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
+            # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at T=64 from one `ncu --set full` capture
+            # (profiles/r02_kernels_ncu_full.txt, grid 140): 22.18 MB read + 0 written (the output stays in L2).  Of the
+            # read, 8.5 MB are the down projection's weights, which this kernel's TMA warp pulls into L2 for its
+            # successor (profiles/r01_gateup_ncu_full.txt, captured before that prefetch existed: 14.86 MB)
+            "traffic": (22180000 if use_umma and T == 64 else None),
+            "traffic_note": "includes 8.5 MB of L2 prefetch for the next kernel (down projection weights); own operands 14.9 MB",
+            "traffic_source": "profiles/r02_kernels_ncu_full.txt", "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
             "avg_launch_us": t * 1e6,
             "l2": f"{n_copies} weight copies ({n_copies * N * K // 2 >> 20} MiB) walked round-robin: weights always come from HBM",
             "timing": f"CUDA events around a graph of {reps} back-to-back launches, mean of 5 replays after 3 warm-up replays"}
