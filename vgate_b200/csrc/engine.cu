@@ -1306,7 +1306,7 @@ int32_t b200_engine_finalize(b200_engine* e) {
     for (int i = 0; i < 4; ++i) {
       const W4Linear& a = e->layers[0].lin[i];
       const int tiles = a.N / 128, KT = a.K / 64;
-      int sp = std::max(1, std::min((148 + tiles / 2) / tiles, KT / 4));
+      int sp = std::max(1, std::min(148 / tiles, KT / 4));    // tiles x splits within one wave of the 148 SMs
       if (i == 2) sp = 1;                               // gate_up feeds SwiGLU directly
       e->splits[i] = sp;
       const int eff = umma_dense_effective_splits(a.K, sp);
