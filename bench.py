@@ -424,9 +424,12 @@ def run_b200(a):
         return toks, (s1["gpu_seconds_prefill"] - s0["gpu_seconds_prefill"], s1["gpu_seconds_decode"] - s0["gpu_seconds_decode"])
 
     def barrier():
+        # host-side (gloo) rendezvous: an NCCL barrier is a kernel that SPINS on the waiting rank's GPU, and with --tp K the
+        # ranks that drive no replica wait here for the whole timed region while their GPU serves another rank's engine
+        # (measured: the 14B TP=2 step ran 2.3x slower under that spinning kernel)
         torch.cuda.synchronize()
         if world > 1:
-            dist.barrier()
+            dist.barrier(group=ctl)
         torch.cuda.synchronize()
 
     for _ in range(a.warmup if drives else 0):

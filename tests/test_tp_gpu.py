@@ -1,7 +1,10 @@
 """Config #5's mechanism at test size: a dense bf16 model run tensor-parallel over two B200s -- one rank engine per
-device, column-parallel q/k/v and gate/up, row-parallel o_proj / down_proj completed by an NCCL all-reduce inside the
-step (CUDA-graph replays included) -- against the pinned fp32 oracle of the WHOLE model and against the same model
-on one GPU.  Needs two GPUs (skipped on a single-GPU box)."""
+device, column-parallel q/k/v and gate/up, row-parallel o_proj / down_proj completed inside the step (CUDA-graph
+replays included): by an NCCL all-reduce in prefill passes, by the consuming RMSNorm's own peer loads over NVLink in
+decode passes -- against the pinned fp32 oracle of the WHOLE model, against the same model on one GPU, and the
+peer-load decode path against NCCL everywhere.  Needs two GPUs (skipped on a single-GPU box)."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -26,15 +29,29 @@ def test_tp2_matches_oracle_and_single_gpu():
         solo = [one.wait(one.submit(p, 0.0, 1.0, n_new), n_new)[0] for p in prompts]
     finally:
         one.close()
-    tp = TPEngine(dims, ckpt, devices=(0, 1), **kw)
+    def run_tp():
+        tp = TPEngine(dims, ckpt, devices=(0, 1), **kw)
+        try:
+            rids = [tp.submit(p, 0.0, 1.0, n_new) for p in prompts]          # batched, ragged, through the scheduler
+            outs = [tp.wait(r, n_new)[0] for r in rids]
+            again = tp.wait(tp.submit(prompts[0], 0.0, 1.0, n_new), n_new)[0]    # alone: decode graph of another batch size
+            sampled = [tp.wait(tp.submit(prompts[1], 0.8, 0.9, 6, seed=5), 6)[0] for _ in range(2)]
+            for _ in range(3):                                               # enough replays of one batch size for a captured graph
+                again2 = tp.wait(tp.submit(prompts[0], 0.0, 1.0, n_new), n_new)[0]
+            return outs, again, sampled, again2, tp.stats()
+        finally:
+            tp.close()
+
+    outs, again, sampled, again2, st = run_tp()      # decode passes: peer loads inside the norm (the default)
+    os.environ["VGATE_B200_TP_ALLREDUCE"] = "nccl"
     try:
-        rids = [tp.submit(p, 0.0, 1.0, n_new) for p in prompts]          # batched, ragged, through the scheduler
-        outs = [tp.wait(r, n_new)[0] for r in rids]
-        again = tp.wait(tp.submit(prompts[0], 0.0, 1.0, n_new), n_new)[0]    # alone: decode graph of another batch size
-        sampled = [tp.wait(tp.submit(prompts[1], 0.8, 0.9, 6, seed=5), 6)[0] for _ in range(2)]
-        st = tp.stats()
+        outs_n, again_n, sampled_n, again2_n, st_n = run_tp()
     finally:
-        tp.close()
+        del os.environ["VGATE_B200_TP_ALLREDUCE"]
+    for a, b in zip(outs + [again, again2] + sampled, outs_n + [again_n, again2_n] + sampled_n):
+        assert np.array_equal(a, b)                   # a + b over two ranks: the same bits whoever adds
+    assert st["steps_decode"] == st_n["steps_decode"] and st["kernel_launches"] < st_n["kernel_launches"]   # 1 tick instead of 2L all-reduces
+    assert np.array_equal(again2, outs[0])
     ref = OracleQwen2(Qwen2Dims(**dims.to_dict()), ckpt, mode="fp32")
     ref_toks = ref.generate_greedy(np.stack(prompts[:4]), n_new)
     for i in range(4):

@@ -203,7 +203,7 @@ __device__ __forceinline__ unsigned long long gtime() {
   return t;
 }
 enum KernelId { kKidEmbed = 1, kKidRmsnorm, kKidRope, kKidAttn, kKidSwiglu, kKidW4Gemv, kKidF16Gemv, kKidUmmaW4,
-                kKidUmmaF16, kKidSample, kKidAdvance };
+                kKidUmmaF16, kKidSample, kKidAdvance, kKidTpTick };
 // PDL prologue + timeline entry; returns the timeline slot (or ~0u).
 // kWait = false: the kernel places griddepcontrol.wait itself (after work that does not depend on upstream).
 template <bool kWait = true>

@@ -259,6 +259,29 @@ struct b200_engine {
   // one thread per device, or group calls).
   int tp_size = 1, tp_rank = 0;
   void* nccl_comm = nullptr;
+  // Decode passes (<= kTpNormMaxRows token rows) do not call NCCL: the RMSNorm that consumes a row-parallel
+  // projection reads every rank's split-K partials itself -- its own from local HBM, the others' with peer loads
+  // over NVLink -- after a flag rendezvous with the other ranks' norm kernels (norm.cuh; bit-identical to
+  // ncclAllReduce + norm at two ranks).  An NCCL all-reduce of 64 x 5120 x 3 fp32 partials took 45 us of a 240 us
+  // 14B layer, twice per layer.  Prefill passes (MBs per all-reduce, bandwidth-bound) stay on NCCL.
+  // `parts` is then cut in three regions: sites alternate between two (a rank may still be reading the peer's
+  // site-s partials while the peer's next projection writes site s+1), qkv's local partials get the third.
+  bool tp_peer_ok = false;                     // peer access enabled between all ranks' devices, pointers exchanged
+  bool tp_use_peer = !(getenv("VGATE_B200_TP_ALLREDUCE") && !strcmp(getenv("VGATE_B200_TP_ALLREDUCE"), "nccl"));
+  DevMem tp_flags, tp_epoch;                   // arrival words [2L + 2 sites][kMaxTp writers]; this rank's pass counter
+  float* tp_parts_of[kMaxTp] = {};             // every rank's `parts`
+  uint32_t* tp_flags_of[kMaxTp] = {};
+  size_t tp_region_elems = 0;                  // R: regions at 0 and R (sites), 2R (qkv partials)
+  int tp_last_site = -1;                       // site of the pending partials layers_pass left for the final norm (-1: NCCL path)
+  TpPeers tp_site(int site) const {
+    TpPeers t{};
+    t.n_ranks = tp_size; t.rank = tp_rank;
+    for (int r = 0; r < tp_size; ++r) {
+      t.parts[r] = tp_parts_of[r] + (size_t)(site & 1) * tp_region_elems;
+      t.flags[r] = tp_flags_of[r] + (size_t)site * kMaxTp;
+    }
+    return t;
+  }
   std::vector<b200_engine*> tp_followers;      // leader only
   std::thread tp_thread;                       // followers only
   std::mutex tp_mu;
@@ -442,19 +465,40 @@ struct b200_engine {
     const int32_t *pos = d_pos.as<int32_t>() + r0, *slot = d_slot.as<int32_t>() + r0, *btrow = d_btrow.as<int32_t>() + r0,
                   *ctx = d_ctx.as<int32_t>() + r0;
     const int64_t xrows = Tmax - r0;
+    // tensor-parallel decode pass: no NCCL, the norms read all ranks' partials (see tp_peer_ok)
+    const bool peer = tp_size > 1 && tp_peer_ok && tp_use_peer && decode_rows && r0 == 0 && T <= kTpNormMaxRows && T <= cfg.max_seqs;
+    int site = 0, pend_site = -1;
+    if (peer) {
+      if ((rc = launch_tp_tick(tp_epoch.as<uint32_t>(), st))) return rc;
+      pbuf = parts.as<float>();
+    }
+    float* const qkv_pbuf = peer ? pbuf + 2 * tp_region_elems : pbuf;
     if ((rc = launch_embed(embed.as<__half>(), d_ids.as<int32_t>() + r0, T, H, hh, st, bf16))) return rc;
     int pend = 0;                 // split-K partials of the previous projection still to be added into h
     const int64_t pend_stride = (int64_t)T * H;
+    // residual-sum + norm of the pending partials: from pbuf (after the NCCL all-reduce, or single GPU) or from every rank's site buffer
+    auto norm = [&](const __half* gamma) -> int {
+      if (skip(0)) return B200_OK;
+      if (peer && pend > 0)
+        return launch_rmsnorm_tp(hh, tp_site(pend_site), tp_epoch.as<uint32_t>(), pend, pend_stride, gamma, cfg.rms_eps, nullptr, T, H, xx, st, bf16);
+      return launch_rmsnorm(hh, pbuf, pend, pend_stride, gamma, cfg.rms_eps, nullptr, T, H, xx, st, bf16);
+    };
+    // a row-parallel projection (o, down): partials into this site's buffer; all-reduced by NCCL unless the norm will do it
+    auto row_parallel = [&](LayerWeights& w, int i, const __half* x) -> int {
+      float* dst = peer ? pbuf + (size_t)(site & 1) * tp_region_elems : pbuf;
+      if ((rc = linear(w, i, x, xrows, hh, H, T, true, &pend, st, dst, decode_rows))) return rc;
+      if (peer) { pend_site = site++; return B200_OK; }
+      return tp_allreduce(pbuf, (size_t)pend * T * H, st);
+    };
     for (int l = 0; l < L; ++l) {
       LayerWeights& w = layers[l];
       __half* kc = k_cache.as<__half>() + layer_kv_offset(l);
       __half* vc = v_cache.as<__half>() + layer_kv_offset(l);
       int np = 0;
-      if (!skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln1.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st, bf16)))
-        return rc;
+      if ((rc = norm(w.ln1.as<__half>()))) return rc;
       pend = 0;
-      if (!skip(1) && (rc = linear(w, 0, xx, xrows, qq, QKV, T, false, &np, st, pbuf, decode_rows))) return rc;
-      const float* qsrc = np ? pbuf : qq;
+      if (!skip(1) && (rc = linear(w, 0, xx, xrows, qq, QKV, T, false, &np, st, qkv_pbuf, decode_rows))) return rc;
+      const float* qsrc = np ? qkv_pbuf : qq;
       const __half* qbias = np ? w.bias_qkv.as<__half>() : nullptr;
       if (decode_rows && T <= cfg.max_seqs) {
         if (!skip(3) && (rc = launch_attn_decode_fused(qsrc, np ? np : 1, (int64_t)T * QKV, qbias, pos, slot, cos_t.as<float>(),
@@ -471,10 +515,8 @@ struct b200_engine {
         } else if (!skip(3) && (rc = launch_paged_attn(qhh, kc, vc, d_bt.as<int32_t>(), max_blocks_per_seq, btrow, ctx, T, NH,
                                                        NKV, 1, nullptr, nullptr, aa, st, bf16))) return rc;
       }
-      if (!skip(4) && (rc = linear(w, 1, aa, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows))) return rc;
-      if ((rc = tp_allreduce(pbuf, (size_t)pend * T * H, st))) return rc;
-      if (!skip(0) && (rc = launch_rmsnorm(hh, pbuf, pend, pend_stride, w.ln2.as<__half>(), cfg.rms_eps, nullptr, T, H, xx, st, bf16)))
-        return rc;
+      if (!skip(4) && (rc = row_parallel(w, 1, aa))) return rc;
+      if ((rc = norm(w.ln2.as<__half>()))) return rc;
       pend = 0;
       if (use_umma(T) && !(debug_gemv_mask >> 2 & 1)) {
         if (!skip(5) && (rc = linear(w, 2, xx, xrows, reinterpret_cast<float*>(cc), I, T, false, &np, st, pbuf, decode_rows))) return rc;
@@ -483,10 +525,10 @@ struct b200_engine {
         if ((rc = launch_swiglu(gu.as<float>() + (size_t)r0 * 2 * I, T, I, cc, st))) return rc;
       }
       if (np) { set_last_error("gate_up projection must not be split"); return B200_ERR_STATE; }
-      if (!skip(6) && (rc = linear(w, 3, cc, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows))) return rc;
-      if ((rc = tp_allreduce(pbuf, (size_t)pend * T * H, st))) return rc;
+      if (!skip(6) && (rc = row_parallel(w, 3, cc))) return rc;
     }
     *pend_out = pend;
+    tp_last_site = peer ? pend_site : -1;
     return B200_OK;
   }
 
@@ -499,8 +541,11 @@ struct b200_engine {
     {
       int pend = 0;
       if ((rc = layers_pass(0, T, decode_rows, stream, parts.as<float>(), &pend))) return rc;
-      if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, (int64_t)T * H, final_norm.as<__half>(), cfg.rms_eps,
-                               rows, n_rows, H, xn_last.as<__half>(), stream, bf16))) return rc;
+      if (tp_last_site >= 0 && pend > 0) {          // tensor-parallel decode pass: the final norm completes the last down_proj's sum
+        if ((rc = launch_rmsnorm_tp(h.as<float>(), tp_site(tp_last_site), tp_epoch.as<uint32_t>(), pend, (int64_t)T * H,
+                                    final_norm.as<__half>(), cfg.rms_eps, rows, n_rows, H, xn_last.as<__half>(), stream, bf16))) return rc;
+      } else if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, (int64_t)T * H, final_norm.as<__half>(), cfg.rms_eps,
+                                      rows, n_rows, H, xn_last.as<__half>(), stream, bf16))) return rc;
     }
     const __half* head = cfg.tie_embeddings ? embed.as<__half>() : lm_head_w.as<__half>();
     bool fused = false;
@@ -1331,6 +1376,19 @@ int32_t b200_engine_finalize(b200_engine* e) {
   if (e->tp_size > 1) {
     if (!e->nccl_comm) { set_last_error("finalize: tensor-parallel engine without a communicator (call b200_engine_tp_init first)"); return B200_ERR_STATE; }
     part_elems = std::max(part_elems, T * (size_t)e->H);          // o_proj / down_proj outputs of a prefill pass are all-reduced too
+    // decode passes: two alternating site regions + qkv's own (see tp_peer_ok); same offsets on every rank
+    size_t site_elems = 0, qkv_elems = 16;
+    for (int i = 0; i < 4; ++i) {
+      const W4Linear& a = e->layers[0].lin[i];
+      const int eff = e->dense ? umma_dense_effective_splits(a.K, e->splits[i]) : umma_w4_effective_splits(a.K, a.G, e->splits[i]);
+      if (i == 1 || i == 3) site_elems = std::max(site_elems, (size_t)std::max(1, eff) * S * a.N);
+      if (i == 0 && eff > 1) qkv_elems = (size_t)eff * S * a.N;
+    }
+    e->tp_region_elems = (site_elems + 63) / 64 * 64;
+    part_elems = std::max(part_elems, 2 * e->tp_region_elems + qkv_elems);
+    if ((rc = e->tp_flags.alloc(((size_t)2 * e->L + 2) * kMaxTp * 4)) || (rc = e->tp_epoch.alloc(4))) return rc;
+    B200_CUDA(cudaMemset(e->tp_flags.p, 0, e->tp_flags.bytes));
+    B200_CUDA(cudaMemset(e->tp_epoch.p, 0, 4));
   }
   if ((rc = e->parts.alloc(part_elems * 4))) return rc;
   if ((rc = e->attn_scratch.alloc(attn_scratch_floats(c.max_seqs, e->NH, e->NKV, b200_engine::kDecodeSplits) * 4)) ||
@@ -1535,6 +1593,35 @@ int32_t b200_engine_tp_attach(b200_engine* leader, b200_engine* follower) {
                "tensor-parallel ranks must share max_seqs, token budgets, KV block count, hidden size and vocabulary");
   std::lock_guard<std::mutex> lk(leader->mu);
   leader->tp_followers.push_back(follower);
+  if ((int)leader->tp_followers.size() != leader->tp_size - 1) return B200_OK;
+  // the group is complete: peer access between every pair of devices, and everybody learns where the others'
+  // partial buffers and arrival words live.  Without peer access the decode passes keep using NCCL.
+  std::vector<b200_engine*> ranks((size_t)leader->tp_size, nullptr);
+  ranks[0] = leader;
+  for (b200_engine* f : leader->tp_followers) {
+    B200_REQUIRE(!ranks[(size_t)f->tp_rank], "two tensor-parallel followers with the same rank");
+    ranks[(size_t)f->tp_rank] = f;
+  }
+  bool ok = true;
+  for (b200_engine* a : ranks)
+    for (b200_engine* b : ranks) {
+      if (a == b) continue;
+      if (a->cfg.device == b->cfg.device) { ok = false; continue; }   // two ranks' kernels waiting for each other on ONE GPU can starve each other of SMs
+      int can = 0;
+      B200_CUDA(cudaDeviceCanAccessPeer(&can, a->cfg.device, b->cfg.device));
+      if (!can) { ok = false; continue; }
+      DeviceGuard guard(a->cfg.device);
+      const cudaError_t err = cudaDeviceEnablePeerAccess(b->cfg.device, 0);
+      if (err == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
+      else if (err != cudaSuccess) return cuda_fail(err, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
+    }
+  for (b200_engine* a : ranks) {
+    for (b200_engine* b : ranks) {
+      a->tp_parts_of[b->tp_rank] = b->parts.as<float>();
+      a->tp_flags_of[b->tp_rank] = b->tp_flags.as<uint32_t>();
+    }
+    a->tp_peer_ok = ok;
+  }
   return B200_OK;
 }
 

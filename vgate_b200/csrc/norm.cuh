@@ -4,6 +4,7 @@
 // each, and the 16 partials are added in one fixed order, so both callers produce the same bits.
 #pragma once
 #include "common.cuh"
+#include "internal.h"
 
 namespace b200 {
 
@@ -43,6 +44,73 @@ __device__ __forceinline__ float rms_quarter_load(float* __restrict__ h, const f
       if (n_parts > 0) *reinterpret_cast<float4*>(h + in_off + 4 * i) = a;
       v[it] = a;
       // explicit FMAs: the two callers must not be contracted differently by the compiler
+      ss = __fmaf_rn(a.x, a.x, ss); ss = __fmaf_rn(a.y, a.y, ss); ss = __fmaf_rn(a.z, a.z, ss); ss = __fmaf_rn(a.w, a.w, ss);
+    }
+  }
+  return warp_sum(ss);
+}
+
+// ---- tensor-parallel variant: the all-reduce is part of the load ---------------------------------
+// Every rank's o_proj / down_proj leaves its split-K partials of the row-parallel product in its own HBM; instead
+// of an all-reduce kernel followed by the norm, the norm of every rank reads all ranks' partials (its own from
+// local memory, the others' through NVLink peer loads) and adds them in rank order, so every rank computes the same
+// bits -- with two ranks the same bits as ncclAllReduce(sum) followed by rms_quarter_load.
+// peer data: relaxed system-scope loads (peer lines may sit in this SM's L1 from an earlier step otherwise)
+__device__ __forceinline__ float4 ld_sys_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+// Cross-GPU rendezvous at one site of the step.  Called by every CTA after its dependency wait (this rank's
+// partials are complete and visible): block 0 tells every peer "my partials of epoch `epoch` are ready", every CTA
+// waits until all peers have said so.  Arrival words only grow, one per (site, writer): nothing is ever reset.
+__device__ __forceinline__ void tp_rendezvous(const TpPeers& tp, const uint32_t epoch) {
+  if (blockIdx.x == 0 && threadIdx.x < tp.n_ranks && (int)threadIdx.x != tp.rank)
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(tp.flags[threadIdx.x] + tp.rank), "r"(epoch) : "memory");
+  if (threadIdx.x < tp.n_ranks && (int)threadIdx.x != tp.rank) {
+    const uint32_t* f = tp.flags[tp.rank] + threadIdx.x;
+    const unsigned long long t0 = gtime();
+    for (;;) {
+      uint32_t v;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+      if ((int32_t)(v - epoch) >= 0) break;
+      if (gtime() - t0 > 20000000000ull) __trap();     // 20 s: the peer rank is gone; fail the context rather than hang
+    }
+  }
+  __syncthreads();
+}
+template <int kRanks>
+__device__ __forceinline__ float rms_quarter_load_ranks(float* __restrict__ h, const TpPeers& tp, const int n_parts,
+                                                        const int64_t part_stride, const int row, const int q, const int H,
+                                                        const int tid, float4 (&v)[kNormMaxPerThread]) {
+  constexpr int kBatch = 8 / kRanks;                 // partials per rank in flight per pass
+  const int HQ = H / kNormCluster;
+  const size_t in_off = (size_t)row * H + (size_t)q * HQ;
+  const int nvec = HQ / 4;
+  float ss = 0.f;
+#pragma unroll
+  for (int it = 0; it < kNormMaxPerThread; ++it) {
+    const int i = tid + it * kNormThreads;
+    if (i < nvec) {
+      float4 a = *reinterpret_cast<const float4*>(h + in_off + 4 * i);
+      for (int p0 = 0; p0 < n_parts; p0 += kBatch) {
+        float4 b[kBatch][kRanks];
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k)
+#pragma unroll
+          for (int r = 0; r < kRanks; ++r)
+            b[k][r] = p0 + k < n_parts ? ld_sys_f4(tp.parts[r] + (size_t)(p0 + k) * part_stride + in_off + 4 * i)
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k) {
+          float4 s = b[k][0];                           // sum over ranks first (what the all-reduce computed) ...
+#pragma unroll
+          for (int r = 1; r < kRanks; ++r) { s.x += b[k][r].x; s.y += b[k][r].y; s.z += b[k][r].z; s.w += b[k][r].w; }
+          a.x += s.x; a.y += s.y; a.z += s.z; a.w += s.w;   // ... then the partials in their fixed order
+        }
+      }
+      *reinterpret_cast<float4*>(h + in_off + 4 * i) = a;
+      v[it] = a;
       ss = __fmaf_rn(a.x, a.x, ss); ss = __fmaf_rn(a.y, a.y, ss); ss = __fmaf_rn(a.z, a.z, ss); ss = __fmaf_rn(a.w, a.w, ss);
     }
   }

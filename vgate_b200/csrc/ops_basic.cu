@@ -148,6 +148,67 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
   kernel_epilogue(tl);
 }
 
+// Tensor-parallel decode passes: residual-sum + RMSNorm with the all-reduce of the row-parallel projection's
+// partials folded into the load (norm.cuh: tp_rendezvous, rms_quarter_load_ranks).  One row per cluster.
+template <int kRanks>
+__global__ void __cluster_dims__(kNormCluster, 1, 1) __launch_bounds__(kNormThreads)
+rmsnorm_tp_kernel(float* __restrict__ h, const TpPeers tp, const uint32_t* __restrict__ epoch, int n_parts, int64_t part_stride,
+                  const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows, int n_rows, int H,
+                  __half* __restrict__ xn, int bf) {
+  __shared__ float red[kNormCluster][kNormWarps];
+  const unsigned tl = kernel_prologue(kKidRmsnorm);
+  tp_rendezvous(tp, *epoch);
+  const int q = blockIdx.x % kNormCluster;
+  const int r = blockIdx.x / kNormCluster;
+  const int row = rows ? rows[r] : r;
+  float4 v[kNormMaxPerThread];
+  const float ss = rms_quarter_load_ranks<kRanks>(h, tp, n_parts, part_stride, row, q, H, threadIdx.x, v);
+  if ((threadIdx.x & 31) < kNormCluster) {
+    const uint32_t local = smem_u32(&red[q][threadIdx.x >> 5]);
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(threadIdx.x & 31));
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(ss) : "memory");
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  const float rs = rms_scale(red, H, eps);
+  rms_quarter_store(v, rs, gamma, xn, r, q, H, threadIdx.x, bf != 0);
+  kernel_epilogue(tl);
+}
+
+// The step counter the rendezvous words are compared with: one tick at the start of every pass that uses them.
+__global__ void tp_tick_kernel(uint32_t* epoch) {
+  const unsigned tl = kernel_prologue(kKidTpTick);
+  if (threadIdx.x == 0) *epoch += 1;
+  kernel_epilogue(tl);
+}
+
+int launch_tp_tick(uint32_t* epoch, cudaStream_t s) {
+  launch_k(tp_tick_kernel, dim3(1), dim3(32), 0, s, epoch);
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+int launch_rmsnorm_tp(float* h, const TpPeers& tp, const uint32_t* epoch, int n_parts, int64_t part_stride, const __half* gamma,
+                      float eps, const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s, bool bf16) {
+  const int bf = bf16 ? 1 : 0;
+  B200_REQUIRE(H % (4 * kNormCluster) == 0 && H <= kNormCluster * kNormThreads * 4 * kNormMaxPerThread,
+               "rmsnorm_tp: H % 16 == 0 && H <= 8192");
+  // every CTA of the grid spins in the rendezvous: the whole grid has to be resident at once
+  B200_REQUIRE(n_rows >= 1 && n_rows <= kTpNormMaxRows, "rmsnorm_tp: 1 <= rows <= 256");
+  B200_REQUIRE(n_parts >= 1 && (tp.n_ranks == 2 || tp.n_ranks == 4 || tp.n_ranks == 8), "rmsnorm_tp: 2, 4 or 8 ranks, >= 1 partial");
+  const dim3 grid(n_rows * kNormCluster), block(kNormThreads);
+  if (tp.n_ranks == 2)
+    launch_k(rmsnorm_tp_kernel<2>, grid, block, 0, s, h, tp, epoch, n_parts, part_stride, gamma, eps, rows, n_rows, H, xn, bf);
+  else if (tp.n_ranks == 4)
+    launch_k(rmsnorm_tp_kernel<4>, grid, block, 0, s, h, tp, epoch, n_parts, part_stride, gamma, eps, rows, n_rows, H, xn, bf);
+  else
+    launch_k(rmsnorm_tp_kernel<8>, grid, block, 0, s, h, tp, epoch, n_parts, part_stride, gamma, eps, rows, n_rows, H, xn, bf);
+  g_launch_count += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 // Prefill variant (no partials, thousands of rows): one WARP per row, every load of the row in flight at
 // once (the cluster kernel keeps only ~185 rows in flight on the whole GPU and is latency-bound there:
 // 88 us for 8192 rows).  Bit-identical to the cluster kernel: lane l plays thread (w * 32 + l) of quarter q
