@@ -13,7 +13,7 @@ from vgate_b200.engine import Engine, TPEngine
 from vgate_b200.weights import ModelDims, synthetic_checkpoint
 
 NAMES = {1: "embed", 2: "rmsnorm", 3: "rope", 4: "attn", 5: "swiglu", 6: "w4_gemv", 7: "f16_gemv", 8: "umma_w4",
-         9: "umma_dense", 10: "sample", 11: "advance", 12: "tp_tick"}
+         9: "umma_dense", 10: "sample", 11: "advance", 12: "tp_tick", 13: " tp phases"}
 
 
 def main():
@@ -62,7 +62,7 @@ def main():
         t0 = step[0, 1]
         print(f"# decode step: {b - a} kernels of rank 0, {(rec[b, 1] - t0) / 1e3:.1f} us from advance to advance")
         prev_exit = t0
-        for r, k in list(zip(step, kid[a:b]))[:22]:
+        for r, k in list(zip(step, kid[a:b]))[:30]:
             gx, gy, gz = (r[0] >> 8) & 0xFFFFF, (r[0] >> 28) & 0xFFFFF, (r[0] >> 48) & 0xFFFF
             print(f"  {NAMES.get(int(k), str(k)):10s} grid {gx}x{gy}x{gz:<3d} entry {(r[1] - t0) / 1e3:9.2f} ready {(r[2] - t0) / 1e3:9.2f} exit {(r[3] - t0) / 1e3:9.2f}   gap before ready {(r[2] - prev_exit) / 1e3:8.2f}")
             prev_exit = max(prev_exit, r[3])

@@ -260,25 +260,23 @@ struct b200_engine {
   int tp_size = 1, tp_rank = 0;
   void* nccl_comm = nullptr;
   // Decode passes (<= kTpNormMaxRows token rows) do not call NCCL: the RMSNorm that consumes a row-parallel
-  // projection reads every rank's split-K partials itself -- its own from local HBM, the others' with peer loads
-  // over NVLink -- after a flag rendezvous with the other ranks' norm kernels (norm.cuh; bit-identical to
-  // ncclAllReduce + norm at two ranks).  An NCCL all-reduce of 64 x 5120 x 3 fp32 partials took 45 us of a 240 us
-  // 14B layer, twice per layer.  Prefill passes (MBs per all-reduce, bandwidth-bound) stay on NCCL.
-  // `parts` is then cut in three regions: sites alternate between two (a rank may still be reading the peer's
-  // site-s partials while the peer's next projection writes site s+1), qkv's local partials get the third.
+  // projection adds this rank's split-K partials, exports the sum, and reads the other ranks' sums with peer loads
+  // over NVLink after a per-row flag rendezvous with their norm kernels (norm.cuh).  An NCCL all-reduce of
+  // 64 x 5120 x 3 fp32 partials took 45 us of a 240 us 14B layer, twice per layer.  Prefill passes (MBs per
+  // all-reduce, bandwidth-bound) stay on NCCL.  The 2L sites of a pass alternate between two export buffers: a rank
+  // may still be reading the peer's site-s export when the peer's norm of site s+1 writes its next one.
   bool tp_peer_ok = false;                     // peer access enabled between all ranks' devices, pointers exchanged
   bool tp_use_peer = !(getenv("VGATE_B200_TP_ALLREDUCE") && !strcmp(getenv("VGATE_B200_TP_ALLREDUCE"), "nccl"));
-  DevMem tp_flags, tp_epoch;                   // arrival words [2L + 2 sites][kMaxTp writers]; this rank's pass counter
-  float* tp_parts_of[kMaxTp] = {};             // every rank's `parts`
+  DevMem tp_flags, tp_epoch, tp_export;        // arrival words [2L + 2 sites][256 rows][kMaxTp writers]; this rank's pass counter; [2][max_seqs][H] fp32
+  float* tp_export_of[kMaxTp] = {};            // every rank's export buffers
   uint32_t* tp_flags_of[kMaxTp] = {};
-  size_t tp_region_elems = 0;                  // R: regions at 0 and R (sites), 2R (qkv partials)
   int tp_last_site = -1;                       // site of the pending partials layers_pass left for the final norm (-1: NCCL path)
   TpPeers tp_site(int site) const {
     TpPeers t{};
     t.n_ranks = tp_size; t.rank = tp_rank;
     for (int r = 0; r < tp_size; ++r) {
-      t.parts[r] = tp_parts_of[r] + (size_t)(site & 1) * tp_region_elems;
-      t.flags[r] = tp_flags_of[r] + (size_t)site * kMaxTp;
+      t.exports[r] = tp_export_of[r] + (size_t)(site & 1) * cfg.max_seqs * H;
+      t.flags[r] = tp_flags_of[r] + (size_t)site * kTpNormMaxRows * kMaxTp;
     }
     return t;
   }
@@ -468,11 +466,7 @@ struct b200_engine {
     // tensor-parallel decode pass: no NCCL, the norms read all ranks' partials (see tp_peer_ok)
     const bool peer = tp_size > 1 && tp_peer_ok && tp_use_peer && decode_rows && r0 == 0 && T <= kTpNormMaxRows && T <= cfg.max_seqs;
     int site = 0, pend_site = -1;
-    if (peer) {
-      if ((rc = launch_tp_tick(tp_epoch.as<uint32_t>(), st))) return rc;
-      pbuf = parts.as<float>();
-    }
-    float* const qkv_pbuf = peer ? pbuf + 2 * tp_region_elems : pbuf;
+    if (peer && (rc = launch_tp_tick(tp_epoch.as<uint32_t>(), st))) return rc;
     if ((rc = launch_embed(embed.as<__half>(), d_ids.as<int32_t>() + r0, T, H, hh, st, bf16))) return rc;
     int pend = 0;                 // split-K partials of the previous projection still to be added into h
     const int64_t pend_stride = (int64_t)T * H;
@@ -480,13 +474,12 @@ struct b200_engine {
     auto norm = [&](const __half* gamma) -> int {
       if (skip(0)) return B200_OK;
       if (peer && pend > 0)
-        return launch_rmsnorm_tp(hh, tp_site(pend_site), tp_epoch.as<uint32_t>(), pend, pend_stride, gamma, cfg.rms_eps, nullptr, T, H, xx, st, bf16);
+        return launch_rmsnorm_tp(hh, pbuf, pend, pend_stride, tp_site(pend_site), tp_epoch.as<uint32_t>(), gamma, cfg.rms_eps, nullptr, T, H, xx, st, bf16);
       return launch_rmsnorm(hh, pbuf, pend, pend_stride, gamma, cfg.rms_eps, nullptr, T, H, xx, st, bf16);
     };
     // a row-parallel projection (o, down): partials into this site's buffer; all-reduced by NCCL unless the norm will do it
     auto row_parallel = [&](LayerWeights& w, int i, const __half* x) -> int {
-      float* dst = peer ? pbuf + (size_t)(site & 1) * tp_region_elems : pbuf;
-      if ((rc = linear(w, i, x, xrows, hh, H, T, true, &pend, st, dst, decode_rows))) return rc;
+      if ((rc = linear(w, i, x, xrows, hh, H, T, true, &pend, st, pbuf, decode_rows))) return rc;
       if (peer) { pend_site = site++; return B200_OK; }
       return tp_allreduce(pbuf, (size_t)pend * T * H, st);
     };
@@ -497,8 +490,8 @@ struct b200_engine {
       int np = 0;
       if ((rc = norm(w.ln1.as<__half>()))) return rc;
       pend = 0;
-      if (!skip(1) && (rc = linear(w, 0, xx, xrows, qq, QKV, T, false, &np, st, qkv_pbuf, decode_rows))) return rc;
-      const float* qsrc = np ? qkv_pbuf : qq;
+      if (!skip(1) && (rc = linear(w, 0, xx, xrows, qq, QKV, T, false, &np, st, pbuf, decode_rows))) return rc;
+      const float* qsrc = np ? pbuf : qq;
       const __half* qbias = np ? w.bias_qkv.as<__half>() : nullptr;
       if (decode_rows && T <= cfg.max_seqs) {
         if (!skip(3) && (rc = launch_attn_decode_fused(qsrc, np ? np : 1, (int64_t)T * QKV, qbias, pos, slot, cos_t.as<float>(),
@@ -542,7 +535,7 @@ struct b200_engine {
       int pend = 0;
       if ((rc = layers_pass(0, T, decode_rows, stream, parts.as<float>(), &pend))) return rc;
       if (tp_last_site >= 0 && pend > 0) {          // tensor-parallel decode pass: the final norm completes the last down_proj's sum
-        if ((rc = launch_rmsnorm_tp(h.as<float>(), tp_site(tp_last_site), tp_epoch.as<uint32_t>(), pend, (int64_t)T * H,
+        if ((rc = launch_rmsnorm_tp(h.as<float>(), parts.as<float>(), pend, (int64_t)T * H, tp_site(tp_last_site), tp_epoch.as<uint32_t>(),
                                     final_norm.as<__half>(), cfg.rms_eps, rows, n_rows, H, xn_last.as<__half>(), stream, bf16))) return rc;
       } else if ((rc = launch_rmsnorm(h.as<float>(), parts.as<float>(), pend, (int64_t)T * H, final_norm.as<__half>(), cfg.rms_eps,
                                       rows, n_rows, H, xn_last.as<__half>(), stream, bf16))) return rc;
@@ -1376,17 +1369,9 @@ int32_t b200_engine_finalize(b200_engine* e) {
   if (e->tp_size > 1) {
     if (!e->nccl_comm) { set_last_error("finalize: tensor-parallel engine without a communicator (call b200_engine_tp_init first)"); return B200_ERR_STATE; }
     part_elems = std::max(part_elems, T * (size_t)e->H);          // o_proj / down_proj outputs of a prefill pass are all-reduced too
-    // decode passes: two alternating site regions + qkv's own (see tp_peer_ok); same offsets on every rank
-    size_t site_elems = 0, qkv_elems = 16;
-    for (int i = 0; i < 4; ++i) {
-      const W4Linear& a = e->layers[0].lin[i];
-      const int eff = e->dense ? umma_dense_effective_splits(a.K, e->splits[i]) : umma_w4_effective_splits(a.K, a.G, e->splits[i]);
-      if (i == 1 || i == 3) site_elems = std::max(site_elems, (size_t)std::max(1, eff) * S * a.N);
-      if (i == 0 && eff > 1) qkv_elems = (size_t)eff * S * a.N;
-    }
-    e->tp_region_elems = (site_elems + 63) / 64 * 64;
-    part_elems = std::max(part_elems, 2 * e->tp_region_elems + qkv_elems);
-    if ((rc = e->tp_flags.alloc(((size_t)2 * e->L + 2) * kMaxTp * 4)) || (rc = e->tp_epoch.alloc(4))) return rc;
+    if ((rc = e->tp_flags.alloc(((size_t)2 * e->L + 2) * kTpNormMaxRows * kMaxTp * 4)) || (rc = e->tp_epoch.alloc(4)) ||
+        (rc = e->tp_export.alloc((size_t)2 * S * e->H * 4)))
+      return rc;
     B200_CUDA(cudaMemset(e->tp_flags.p, 0, e->tp_flags.bytes));
     B200_CUDA(cudaMemset(e->tp_epoch.p, 0, 4));
   }
@@ -1617,7 +1602,7 @@ int32_t b200_engine_tp_attach(b200_engine* leader, b200_engine* follower) {
     }
   for (b200_engine* a : ranks) {
     for (b200_engine* b : ranks) {
-      a->tp_parts_of[b->tp_rank] = b->parts.as<float>();
+      a->tp_export_of[b->tp_rank] = b->tp_export.as<float>();
       a->tp_flags_of[b->tp_rank] = b->tp_flags.as<uint32_t>();
     }
     a->tp_peer_ok = ok;

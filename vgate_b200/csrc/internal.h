@@ -97,12 +97,12 @@ int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_strid
 constexpr int kMaxTp = 8;
 constexpr int kTpNormMaxRows = 256;   // the rendezvous needs the whole grid resident: 4 CTAs of 128 threads per row
 struct TpPeers {
-  const float* parts[kMaxTp];       // this site's partial buffer on every rank, in rank order (own included)
-  uint32_t* flags[kMaxTp];          // every rank's arrival words for this site: flags[r][j] is written by rank j
+  const float* exports[kMaxTp];     // this site's exported per-rank sums [rows][H] on every rank, in rank order (own included)
+  uint32_t* flags[kMaxTp];          // every rank's arrival words for this site: flags[r][row * kMaxTp + j] is written by rank j
   int n_ranks, rank;
 };
-int launch_rmsnorm_tp(float* h, const TpPeers& tp, const uint32_t* epoch, int n_parts, int64_t part_stride, const __half* gamma,
-                      float eps, const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s, bool bf16);
+int launch_rmsnorm_tp(float* h, const float* parts, int n_parts, int64_t part_stride, const TpPeers& tp, const uint32_t* epoch,
+                      const __half* gamma, float eps, const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s, bool bf16);
 int launch_tp_tick(uint32_t* epoch, cudaStream_t s);
 int launch_rope_kv(const float* qkv, int n_parts, int64_t part_stride, const __half* bias, const int32_t* pos, const int32_t* slot, const float* cos_t,
                    const float* sin_t, int T, int n_heads, int n_kv, __half* q_out, __half* k_cache,

@@ -149,20 +149,28 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
 }
 
 // Tensor-parallel decode passes: residual-sum + RMSNorm with the all-reduce of the row-parallel projection's
-// partials folded into the load (norm.cuh: tp_rendezvous, rms_quarter_load_ranks).  One row per cluster.
+// partials folded in (norm.cuh: tp_own_sum, tp_row_rendezvous, tp_rank_sum).  One row per cluster.
 template <int kRanks>
 __global__ void __cluster_dims__(kNormCluster, 1, 1) __launch_bounds__(kNormThreads)
-rmsnorm_tp_kernel(float* __restrict__ h, const TpPeers tp, const uint32_t* __restrict__ epoch, int n_parts, int64_t part_stride,
-                  const __half* __restrict__ gamma, float eps, const int32_t* __restrict__ rows, int n_rows, int H,
-                  __half* __restrict__ xn, int bf) {
+rmsnorm_tp_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_parts, int64_t part_stride, const TpPeers tp,
+                  const uint32_t* __restrict__ epoch, const __half* __restrict__ gamma, float eps,
+                  const int32_t* __restrict__ rows, int n_rows, int H, __half* __restrict__ xn, int bf) {
   __shared__ float red[kNormCluster][kNormWarps];
   const unsigned tl = kernel_prologue(kKidRmsnorm);
-  tp_rendezvous(tp, *epoch);
+  const uint32_t ep = *epoch;
   const int q = blockIdx.x % kNormCluster;
   const int r = blockIdx.x / kNormCluster;
   const int row = rows ? rows[r] : r;
-  float4 v[kNormMaxPerThread];
-  const float ss = rms_quarter_load_ranks<kRanks>(h, tp, n_parts, part_stride, row, q, H, threadIdx.x, v);
+  float4 own[kNormMaxPerThread], hv[kNormMaxPerThread], v[kNormMaxPerThread];
+  tp_own_sum(h, parts, n_parts, part_stride, const_cast<float*>(tp.exports[tp.rank]), row, q, H, threadIdx.x, own, hv);
+  const unsigned long long t_own = tl != ~0u ? gtime() : 0;
+  tp_row_rendezvous(tp, row, q, ep);
+  const unsigned long long t_met = tl != ~0u ? gtime() : 0;
+  const float ss = tp_rank_sum<kRanks>(h, tp, row, q, H, threadIdx.x, own, hv, v);
+  if (tl != ~0u) {                     // timeline: a second record {13, own partials summed, peers met, peer sums added}
+    const unsigned slot = atomicAdd(d_tl.ctr, 1u);
+    if (slot < d_tl.cap) { d_tl.buf[4 * slot] = 13; d_tl.buf[4 * slot + 1] = t_own; d_tl.buf[4 * slot + 2] = t_met; d_tl.buf[4 * slot + 3] = gtime(); }
+  }
   if ((threadIdx.x & 31) < kNormCluster) {
     const uint32_t local = smem_u32(&red[q][threadIdx.x >> 5]);
     uint32_t remote;
@@ -189,21 +197,21 @@ int launch_tp_tick(uint32_t* epoch, cudaStream_t s) {
   return B200_OK;
 }
 
-int launch_rmsnorm_tp(float* h, const TpPeers& tp, const uint32_t* epoch, int n_parts, int64_t part_stride, const __half* gamma,
-                      float eps, const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s, bool bf16) {
+int launch_rmsnorm_tp(float* h, const float* parts, int n_parts, int64_t part_stride, const TpPeers& tp, const uint32_t* epoch,
+                      const __half* gamma, float eps, const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s, bool bf16) {
   const int bf = bf16 ? 1 : 0;
   B200_REQUIRE(H % (4 * kNormCluster) == 0 && H <= kNormCluster * kNormThreads * 4 * kNormMaxPerThread,
                "rmsnorm_tp: H % 16 == 0 && H <= 8192");
-  // every CTA of the grid spins in the rendezvous: the whole grid has to be resident at once
+  // every cluster of the grid spins in its rendezvous: the whole grid has to be resident at once
   B200_REQUIRE(n_rows >= 1 && n_rows <= kTpNormMaxRows, "rmsnorm_tp: 1 <= rows <= 256");
   B200_REQUIRE(n_parts >= 1 && (tp.n_ranks == 2 || tp.n_ranks == 4 || tp.n_ranks == 8), "rmsnorm_tp: 2, 4 or 8 ranks, >= 1 partial");
   const dim3 grid(n_rows * kNormCluster), block(kNormThreads);
   if (tp.n_ranks == 2)
-    launch_k(rmsnorm_tp_kernel<2>, grid, block, 0, s, h, tp, epoch, n_parts, part_stride, gamma, eps, rows, n_rows, H, xn, bf);
+    launch_k(rmsnorm_tp_kernel<2>, grid, block, 0, s, h, parts, n_parts, part_stride, tp, epoch, gamma, eps, rows, n_rows, H, xn, bf);
   else if (tp.n_ranks == 4)
-    launch_k(rmsnorm_tp_kernel<4>, grid, block, 0, s, h, tp, epoch, n_parts, part_stride, gamma, eps, rows, n_rows, H, xn, bf);
+    launch_k(rmsnorm_tp_kernel<4>, grid, block, 0, s, h, parts, n_parts, part_stride, tp, epoch, gamma, eps, rows, n_rows, H, xn, bf);
   else
-    launch_k(rmsnorm_tp_kernel<8>, grid, block, 0, s, h, tp, epoch, n_parts, part_stride, gamma, eps, rows, n_rows, H, xn, bf);
+    launch_k(rmsnorm_tp_kernel<8>, grid, block, 0, s, h, parts, n_parts, part_stride, tp, epoch, gamma, eps, rows, n_rows, H, xn, bf);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;

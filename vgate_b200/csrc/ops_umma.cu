@@ -34,11 +34,11 @@ void umma_set_trace(unsigned long long* dev_buf, int grid_x, int grid_z) {
   g_umma_trace = dev_buf; g_umma_trace_gridx = grid_x; g_umma_trace_gridz = grid_z;
 }
 
-template <int NT, bool kW4, int MT = 1>
+template <int NT, bool kW4, int MT = 1, bool kDeep = true>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
 umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                  const UmmaParams p) {
-  using Cfg = UmmaCfg<NT, kW4, true, MT>;
+  using Cfg = UmmaCfg<NT, kW4, kDeep, MT>;
   constexpr int kStages = Cfg::kStages, kRing = Cfg::kRing;
   constexpr int kTileBBytes = Cfg::kTileBBytes, kStageBytes = Cfg::kStageBytes;
   constexpr int kXInStage = kW4 ? 0 : MT * kTileABytes;      // byte offset of the first X tile inside a stage
@@ -302,10 +302,10 @@ int make_tensor_map_f16(CUtensorMap* map, const void* base, int64_t rows, int64_
 }
 
 // ---- launch -------------------------------------------------------------------------------------------
-template <int NT, bool kW4, int MT = 1>
-static int launch_nt(const CUtensorMap& mx, const CUtensorMap& mw, const UmmaParams& p, int n_splits, cudaStream_t s) {
-  constexpr int smem_bytes = UmmaCfg<NT, kW4, true, MT>::kSmemBytes;
-  auto kern = umma_gemm_kernel<NT, kW4, MT>;
+template <int NT, bool kW4, int MT = 1, bool kDeep = true>
+static int launch_nt_cfg(const CUtensorMap& mx, const CUtensorMap& mw, const UmmaParams& p, int n_splits, cudaStream_t s) {
+  constexpr int smem_bytes = UmmaCfg<NT, kW4, kDeep, MT>::kSmemBytes;
+  auto kern = umma_gemm_kernel<NT, kW4, MT, kDeep>;
   // per device and cheap: set on every launch (a process-wide "configured" flag would leave a second device unset)
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   dim3 grid(p.N / (kUmmaM * MT), (p.T + NT - 1) / NT, n_splits);
@@ -315,6 +315,14 @@ static int launch_nt(const CUtensorMap& mx, const CUtensorMap& mw, const UmmaPar
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
+}
+
+template <int NT, bool kW4, int MT = 1>
+static int launch_nt(const CUtensorMap& mx, const CUtensorMap& mw, const UmmaParams& p, int n_splits, cudaStream_t s) {
+  if constexpr (!kW4 && MT == 1 && NT <= 64) {       // dense: the deep ring only while every CTA has an SM to itself
+    if ((int64_t)(p.N / kUmmaM) * ((p.T + NT - 1) / NT) * n_splits > 148) return launch_nt_cfg<NT, kW4, MT, false>(mx, mw, p, n_splits, s);
+  }
+  return launch_nt_cfg<NT, kW4, MT, true>(mx, mw, p, n_splits, s);
 }
 
 template <bool kW4>

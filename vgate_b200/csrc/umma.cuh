@@ -151,7 +151,11 @@ struct UmmaSmem {                      // barriers live after the tile rings
 template <int NT, bool kW4, bool kDeep = true, int MT = 1>
 struct UmmaCfg {
   static constexpr int kMaxTilesPerStage = kW4 ? 2 : 1;
-  static constexpr int kStages = MT == 2 ? (kW4 ? 2 : 3) : (kW4 && kDeep && NT <= 64) ? 7 : 4;
+  // dense, kDeep (token tile <= 64, a grid of at most one CTA per SM -- decode passes of 16-bit models): eight stages of
+  // {weight tile, activation tile} = 192 KB in flight per SM.  A weight-streaming CTA is latency-bound: with four
+  // stages (96 KB) the 14B shapes pulled 20 GB/s per SM, half of an SM's share of HBM.  Grids of several waves keep
+  // four stages: two CTAs per SM then overlap one's epilogue with the other's stream (lm_head: 84 % of HBM).
+  static constexpr int kStages = MT == 2 ? (kW4 ? 2 : 3) : (kW4 && kDeep && NT <= 64) ? 7 : (!kW4 && kDeep && NT <= 64) ? 8 : 4;
   // private ring slots per producer warpgroup.  3 (all 12 chunks of a gate_up CTA requested at once) was
   // measured: no change -- the kernel's stall samples sit in the wait for the first chunk (HBM latency) and
   // in the wait for the accumulator (12 groups x 256 tensor cycles), not in ring refills.
