@@ -41,10 +41,11 @@ def main():
         return {k: s1[k] - s0[k] for k in ("gpu_seconds_prefill", "gpu_seconds_decode", "steps_decode", "steps_prefill")}, time.perf_counter() - t0
 
     print("warm", run(8))
-    torch.cuda.set_device(0)
+    tl_dev = int(os.environ.get("TL_DEV", "0"))              # which rank's kernels to record
+    torch.cuda.set_device(tl_dev)
     cap = 40000
-    buf = torch.zeros((cap, 4), dtype=torch.int64, device="cuda:0")
-    ctr = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+    buf = torch.zeros((cap, 4), dtype=torch.int64, device=f"cuda:{tl_dev}")
+    ctr = torch.zeros(1, dtype=torch.int32, device=f"cuda:{tl_dev}")
     lib.b200_debug_timeline(C.c_void_p(buf.data_ptr()), C.c_void_p(ctr.data_ptr()), cap)
     st, wall = run(24)
     torch.cuda.synchronize()
@@ -60,7 +61,7 @@ def main():
         a, b = adv[-3], adv[-2]
         step = rec[a:b]
         t0 = step[0, 1]
-        print(f"# decode step: {b - a} kernels of rank 0, {(rec[b, 1] - t0) / 1e3:.1f} us from advance to advance")
+        print(f"# decode step: {b - a} kernels of rank {tl_dev}, {(rec[b, 1] - t0) / 1e3:.1f} us from advance to advance")
         prev_exit = t0
         for r, k in list(zip(step, kid[a:b]))[:30]:
             gx, gy, gz = (r[0] >> 8) & 0xFFFFF, (r[0] >> 28) & 0xFFFFF, (r[0] >> 48) & 0xFFFF

@@ -260,24 +260,20 @@ struct b200_engine {
   int tp_size = 1, tp_rank = 0;
   void* nccl_comm = nullptr;
   // Decode passes (<= kTpNormMaxRows token rows) do not call NCCL: the RMSNorm that consumes a row-parallel
-  // projection adds this rank's split-K partials, exports the sum, and reads the other ranks' sums with peer loads
-  // over NVLink after a per-row flag rendezvous with their norm kernels (norm.cuh).  An NCCL all-reduce of
-  // 64 x 5120 x 3 fp32 partials took 45 us of a 240 us 14B layer, twice per layer.  Prefill passes (MBs per
-  // all-reduce, bandwidth-bound) stay on NCCL.  The 2L sites of a pass alternate between two export buffers: a rank
-  // may still be reading the peer's site-s export when the peer's norm of site s+1 writes its next one.
+  // projection adds this rank's split-K partials, pushes the sum into the other ranks' receive buffers over NVLink
+  // as self-validating {value, sequence} words, and collects theirs from its own buffer (norm.cuh).  An NCCL
+  // all-reduce of 64 x 5120 x 3 fp32 partials took 45 us of a 240 us 14B layer, twice per layer.  Prefill passes
+  // (MBs per all-reduce, bandwidth-bound) stay on NCCL.  The 2L sites of a pass alternate between two receive slots.
   bool tp_peer_ok = false;                     // peer access enabled between all ranks' devices, pointers exchanged
   bool tp_use_peer = !(getenv("VGATE_B200_TP_ALLREDUCE") && !strcmp(getenv("VGATE_B200_TP_ALLREDUCE"), "nccl"));
-  DevMem tp_flags, tp_epoch, tp_export;        // arrival words [2L + 2 sites][256 rows][kMaxTp writers]; this rank's pass counter; [2][max_seqs][H] fp32
-  float* tp_export_of[kMaxTp] = {};            // every rank's export buffers
-  uint32_t* tp_flags_of[kMaxTp] = {};
+  DevMem tp_epoch, tp_recv;                    // this rank's pass counter; receive words [2 slots][tp_size writers][max_seqs][H] x 8 bytes
+  uint2* tp_recv_of[kMaxTp] = {};              // every rank's receive buffer
   int tp_last_site = -1;                       // site of the pending partials layers_pass left for the final norm (-1: NCCL path)
   TpPeers tp_site(int site) const {
     TpPeers t{};
-    t.n_ranks = tp_size; t.rank = tp_rank;
-    for (int r = 0; r < tp_size; ++r) {
-      t.exports[r] = tp_export_of[r] + (size_t)(site & 1) * cfg.max_seqs * H;
-      t.flags[r] = tp_flags_of[r] + (size_t)site * kTpNormMaxRows * kMaxTp;
-    }
+    t.n_ranks = tp_size; t.rank = tp_rank; t.rows_cap = cfg.max_seqs;
+    t.site = (uint32_t)site; t.n_sites = (uint32_t)(2 * L + 2);
+    for (int r = 0; r < tp_size; ++r) t.recv[r] = tp_recv_of[r] + (size_t)(site & 1) * tp_size * cfg.max_seqs * H;
     return t;
   }
   std::vector<b200_engine*> tp_followers;      // leader only
@@ -1369,10 +1365,8 @@ int32_t b200_engine_finalize(b200_engine* e) {
   if (e->tp_size > 1) {
     if (!e->nccl_comm) { set_last_error("finalize: tensor-parallel engine without a communicator (call b200_engine_tp_init first)"); return B200_ERR_STATE; }
     part_elems = std::max(part_elems, T * (size_t)e->H);          // o_proj / down_proj outputs of a prefill pass are all-reduced too
-    if ((rc = e->tp_flags.alloc(((size_t)2 * e->L + 2) * kTpNormMaxRows * kMaxTp * 4)) || (rc = e->tp_epoch.alloc(4)) ||
-        (rc = e->tp_export.alloc((size_t)2 * S * e->H * 4)))
-      return rc;
-    B200_CUDA(cudaMemset(e->tp_flags.p, 0, e->tp_flags.bytes));
+    if ((rc = e->tp_epoch.alloc(4)) || (rc = e->tp_recv.alloc((size_t)2 * e->tp_size * S * e->H * 8))) return rc;
+    B200_CUDA(cudaMemset(e->tp_recv.p, 0, e->tp_recv.bytes));      // sequence numbers start at 1
     B200_CUDA(cudaMemset(e->tp_epoch.p, 0, 4));
   }
   if ((rc = e->parts.alloc(part_elems * 4))) return rc;
@@ -1602,8 +1596,7 @@ int32_t b200_engine_tp_attach(b200_engine* leader, b200_engine* follower) {
     }
   for (b200_engine* a : ranks) {
     for (b200_engine* b : ranks) {
-      a->tp_export_of[b->tp_rank] = b->tp_export.as<float>();
-      a->tp_flags_of[b->tp_rank] = b->tp_flags.as<uint32_t>();
+      a->tp_recv_of[b->tp_rank] = b->tp_recv.as<uint2>();
     }
     a->tp_peer_ok = ok;
   }

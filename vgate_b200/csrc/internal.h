@@ -97,9 +97,9 @@ int launch_rmsnorm(float* h, const float* parts, int n_parts, int64_t part_strid
 constexpr int kMaxTp = 8;
 constexpr int kTpNormMaxRows = 256;   // the rendezvous needs the whole grid resident: 4 CTAs of 128 threads per row
 struct TpPeers {
-  const float* exports[kMaxTp];     // this site's exported per-rank sums [rows][H] on every rank, in rank order (own included)
-  uint32_t* flags[kMaxTp];          // every rank's arrival words for this site: flags[r][row * kMaxTp + j] is written by rank j
-  int n_ranks, rank;
+  uint2* recv[kMaxTp];              // every rank's receive buffer of this site's slot: [writer rank][rows_cap][H] {value, seq} words
+  int n_ranks, rank, rows_cap;
+  uint32_t site, n_sites;           // sequence number of a word = pass counter * n_sites + site + 1
 };
 int launch_rmsnorm_tp(float* h, const float* parts, int n_parts, int64_t part_stride, const TpPeers& tp, const uint32_t* epoch,
                       const __half* gamma, float eps, const int32_t* rows, int n_rows, int H, __half* xn, cudaStream_t s, bool bf16);

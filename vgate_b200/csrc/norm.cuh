@@ -53,29 +53,38 @@ __device__ __forceinline__ float rms_quarter_load(float* __restrict__ h, const f
 // ---- tensor-parallel variant: the all-reduce is part of the norm -----------------------------------
 // Every rank's o_proj / down_proj leaves its split-K partials of the row-parallel product in its own HBM.  Instead
 // of an all-reduce kernel followed by the norm, the norm cluster of row r on every rank
-//   1. adds this rank's partials of the row in their fixed order and EXPORTS the sum (local fp32 buffer),
-//   2. tells the other ranks' clusters of the same row "exported" (one arrival word per row, site and writer, written
-//      into the peers' HBM; the words only grow, nothing is ever reset) and waits for theirs,
-//   3. reads the other ranks' exported sums with NVLink peer loads, adds the sums in rank order into the residual
-//      stream -- every rank computes the same bits -- and normalises as rmsnorm_kernel does.
-// One third of the partial bytes cross NVLink (three split-K partials per rank at the 14B shapes), and a row
-// waits for its own row only.
-// peer data: relaxed system-scope loads (peer lines may sit in this SM's L1 from an earlier step otherwise)
-__device__ __forceinline__ float4 ld_sys_f4(const float* p) {
-  float4 v;
-  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+//   1. adds this rank's partials of the row in their fixed order and PUSHES the sum into every other rank's receive
+//      buffer over NVLink as 8-byte {value, sequence number} words,
+//   2. polls its own receive buffer until every word of the row carries this site's sequence number -- the data is
+//      its own arrival flag, so there is no fence and no separate flag round trip (a release store at system scope,
+//      which a flag protocol needs, took ~10 us under load here; an 8-byte aligned store is single-copy atomic),
+//   3. adds the per-rank sums in rank order into the residual stream -- every rank computes the same bits -- and
+//      normalises as rmsnorm_kernel does.
+// One third of the partial bytes cross NVLink (three split-K partials per rank at the 14B shapes) at half wire
+// efficiency, and a row waits for its own row only.  Sequence numbers are unique per (pass, site) and compared for
+// equality, so the words never need resetting; the two receive slots alternate by site (a peer two sites ahead is
+// impossible: it needs this rank's words of the site in between).
+// Word layout of one row quarter in a receive buffer: plane k (component k of every float4) is contiguous, so the 32
+// lanes of a warp store / load 256 contiguous bytes per instruction.
+__device__ __forceinline__ void st_sys_u2(uint2* p, uint32_t x, uint32_t y) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ uint2 ld_sys_u2(const uint2* p) {
+  uint2 v;
+  asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
   return v;
 }
-// step 1: own[it] = sum_p parts[p][row] (fixed p order) for this thread's float4s of quarter q, stored to `exp_out`
-// as well; hv[it] = h[row] (loaded here so that its latency overlaps)
-__device__ __forceinline__ void tp_own_sum(const float* __restrict__ h, const float* __restrict__ parts, const int n_parts,
-                                           const int64_t part_stride, float* __restrict__ exp_out, const int row, const int q,
-                                           const int H, const int tid, float4 (&own)[kNormMaxPerThread],
-                                           float4 (&hv)[kNormMaxPerThread]) {
+// step 1: own[it] = sum_p parts[p][row] (fixed p order) for this thread's float4s of quarter q, pushed to the peers;
+// hv[it] = h[row] (loaded here so that its latency overlaps)
+__device__ __forceinline__ void tp_own_sum_push(const float* __restrict__ h, const float* __restrict__ parts, const int n_parts,
+                                                const int64_t part_stride, const TpPeers& tp, const uint32_t seq, const int row,
+                                                const int q, const int H, const int tid, float4 (&own)[kNormMaxPerThread],
+                                                float4 (&hv)[kNormMaxPerThread]) {
   constexpr int kBatch = 4;
   const int HQ = H / kNormCluster;
   const size_t in_off = (size_t)row * H + (size_t)q * HQ;
   const int nvec = HQ / 4;
+  const size_t w_off = ((size_t)tp.rank * tp.rows_cap + row) * H + (size_t)q * HQ;     // my words in a peer's buffer
 #pragma unroll
   for (int it = 0; it < kNormMaxPerThread; ++it) {
     const int i = tid + it * kNormThreads;
@@ -93,58 +102,62 @@ __device__ __forceinline__ void tp_own_sum(const float* __restrict__ h, const fl
         for (int k = 0; k < kBatch; ++k) { a.x += b[k].x; a.y += b[k].y; a.z += b[k].z; a.w += b[k].w; }
       }
       own[it] = a;
-      *reinterpret_cast<float4*>(exp_out + in_off + 4 * i) = a;
+      for (int r = 0; r < tp.n_ranks; ++r) {
+        if (r == tp.rank) continue;
+        uint2* dst = tp.recv[r] + w_off + i;
+        st_sys_u2(dst, __float_as_uint(a.x), seq);
+        st_sys_u2(dst + nvec, __float_as_uint(a.y), seq);
+        st_sys_u2(dst + 2 * nvec, __float_as_uint(a.z), seq);
+        st_sys_u2(dst + 3 * nvec, __float_as_uint(a.w), seq);
+      }
     }
   }
 }
-// step 2 for one row: called by all threads of the four CTAs of the row's cluster, after their export stores.
-__device__ __forceinline__ void tp_row_rendezvous(const TpPeers& tp, const int row, const int q, const uint32_t epoch) {
-  // the cluster barrier (release / acquire) orders the 512 threads' export stores before the signalling thread's
-  // system-scope release store; release is cumulative, so the peer that acquires the word sees the exports.  (A
-  // __threadfence_system() per thread instead cost several microseconds per site.)
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-  const int t = threadIdx.x;
-  if (t < tp.n_ranks && t != tp.rank) {
-    if (q == 0)
-      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(tp.flags[t] + (size_t)row * kMaxTp + tp.rank), "r"(epoch) : "memory");
-    const uint32_t* f = tp.flags[tp.rank] + (size_t)row * kMaxTp + t;
-    const unsigned long long t0 = gtime();
-    for (;;) {
-      uint32_t v;
-      asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-      if ((int32_t)(v - epoch) >= 0) break;
-      if (gtime() - t0 > 20000000000ull) __trap();         // 20 s: the peer rank is gone; fail the context rather than hang
-    }
-    asm volatile("fence.acq_rel.sys;" ::: "memory");       // acquire: the peer's exports, stored before its release, are visible now
-  }
-  __syncthreads();
-}
-// step 3: v = h + (sum over ranks, in rank order, of the exported sums); h updated; returns the warp's sum of squares
-template <int kRanks>
-__device__ __forceinline__ float tp_rank_sum(float* __restrict__ h, const TpPeers& tp, const int row, const int q, const int H,
-                                             const int tid, const float4 (&own)[kNormMaxPerThread],
-                                             const float4 (&hv)[kNormMaxPerThread], float4 (&v)[kNormMaxPerThread]) {
+// steps 2 and 3: v = h + (sum over ranks, in rank order, of the per-rank sums); h updated; returns the warp's sum of squares
+__device__ __forceinline__ float tp_collect(float* __restrict__ h, const TpPeers& tp, const uint32_t seq, const int row, const int q,
+                                            const int H, const int tid, const float4 (&own)[kNormMaxPerThread],
+                                            const float4 (&hv)[kNormMaxPerThread], float4 (&v)[kNormMaxPerThread]) {
   const int HQ = H / kNormCluster;
   const size_t in_off = (size_t)row * H + (size_t)q * HQ;
   const int nvec = HQ / 4;
-  float4 b[kNormMaxPerThread][kRanks];
+  float4 s[kNormMaxPerThread];
+  for (int r = 0; r < tp.n_ranks; ++r) {
+    float4 x[kNormMaxPerThread];
+    if (r == tp.rank) {
 #pragma unroll
-  for (int it = 0; it < kNormMaxPerThread; ++it) {          // every peer load of the thread in flight at once
-    const int i = tid + it * kNormThreads;
+      for (int it = 0; it < kNormMaxPerThread; ++it) x[it] = own[it];
+    } else {
+      const uint2* src = tp.recv[tp.rank] + ((size_t)r * tp.rows_cap + row) * H + (size_t)q * HQ;
+      const unsigned long long t0 = gtime();
+      for (;;) {                                            // every word of the thread in flight at once, until all carry seq
+        bool ok = true;
 #pragma unroll
-    for (int r = 0; r < kRanks; ++r)
-      b[it][r] = (i < nvec && r != tp.rank) ? ld_sys_f4(tp.exports[r] + in_off + 4 * i) : own[it];
+        for (int it = 0; it < kNormMaxPerThread; ++it) {
+          const int i = tid + it * kNormThreads;
+          if (i < nvec) {
+            const uint2 w0 = ld_sys_u2(src + i), w1 = ld_sys_u2(src + nvec + i), w2 = ld_sys_u2(src + 2 * nvec + i),
+                        w3 = ld_sys_u2(src + 3 * nvec + i);
+            ok = ok && w0.y == seq && w1.y == seq && w2.y == seq && w3.y == seq;
+            x[it] = make_float4(__uint_as_float(w0.x), __uint_as_float(w1.x), __uint_as_float(w2.x), __uint_as_float(w3.x));
+          }
+        }
+        if (ok) break;
+        if (gtime() - t0 > 20000000000ull) __trap();        // 20 s: the peer rank is gone; fail the context rather than hang
+      }
+    }
+#pragma unroll
+    for (int it = 0; it < kNormMaxPerThread; ++it) {
+      if (r == 0) s[it] = x[it];
+      else { s[it].x += x[it].x; s[it].y += x[it].y; s[it].z += x[it].z; s[it].w += x[it].w; }
+    }
   }
   float ss = 0.f;
 #pragma unroll
   for (int it = 0; it < kNormMaxPerThread; ++it) {
     const int i = tid + it * kNormThreads;
     if (i < nvec) {
-      float4 s = b[it][0];
-#pragma unroll
-      for (int r = 1; r < kRanks; ++r) { s.x += b[it][r].x; s.y += b[it][r].y; s.z += b[it][r].z; s.w += b[it][r].w; }
       float4 a = hv[it];
-      a.x += s.x; a.y += s.y; a.z += s.z; a.w += s.w;
+      a.x += s[it].x; a.y += s[it].y; a.z += s[it].z; a.w += s[it].w;
       *reinterpret_cast<float4*>(h + in_off + 4 * i) = a;
       v[it] = a;
       ss = __fmaf_rn(a.x, a.x, ss); ss = __fmaf_rn(a.y, a.y, ss); ss = __fmaf_rn(a.z, a.z, ss); ss = __fmaf_rn(a.w, a.w, ss);

@@ -149,27 +149,24 @@ rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_par
 }
 
 // Tensor-parallel decode passes: residual-sum + RMSNorm with the all-reduce of the row-parallel projection's
-// partials folded in (norm.cuh: tp_own_sum, tp_row_rendezvous, tp_rank_sum).  One row per cluster.
-template <int kRanks>
+// partials folded in (norm.cuh: tp_own_sum_push, tp_collect).  One row per cluster.
 __global__ void __cluster_dims__(kNormCluster, 1, 1) __launch_bounds__(kNormThreads)
 rmsnorm_tp_kernel(float* __restrict__ h, const float* __restrict__ parts, int n_parts, int64_t part_stride, const TpPeers tp,
                   const uint32_t* __restrict__ epoch, const __half* __restrict__ gamma, float eps,
                   const int32_t* __restrict__ rows, int n_rows, int H, __half* __restrict__ xn, int bf) {
   __shared__ float red[kNormCluster][kNormWarps];
   const unsigned tl = kernel_prologue(kKidRmsnorm);
-  const uint32_t ep = *epoch;
+  const uint32_t seq = *epoch * tp.n_sites + tp.site + 1u;
   const int q = blockIdx.x % kNormCluster;
   const int r = blockIdx.x / kNormCluster;
   const int row = rows ? rows[r] : r;
   float4 own[kNormMaxPerThread], hv[kNormMaxPerThread], v[kNormMaxPerThread];
-  tp_own_sum(h, parts, n_parts, part_stride, const_cast<float*>(tp.exports[tp.rank]), row, q, H, threadIdx.x, own, hv);
+  tp_own_sum_push(h, parts, n_parts, part_stride, tp, seq, row, q, H, threadIdx.x, own, hv);
   const unsigned long long t_own = tl != ~0u ? gtime() : 0;
-  tp_row_rendezvous(tp, row, q, ep);
-  const unsigned long long t_met = tl != ~0u ? gtime() : 0;
-  const float ss = tp_rank_sum<kRanks>(h, tp, row, q, H, threadIdx.x, own, hv, v);
-  if (tl != ~0u) {                     // timeline: a second record {13, own partials summed, peers met, peer sums added}
+  const float ss = tp_collect(h, tp, seq, row, q, H, threadIdx.x, own, hv, v);
+  if (tl != ~0u) {                     // timeline: a second record {13, own partials summed and pushed, -, peer sums added}
     const unsigned slot = atomicAdd(d_tl.ctr, 1u);
-    if (slot < d_tl.cap) { d_tl.buf[4 * slot] = 13; d_tl.buf[4 * slot + 1] = t_own; d_tl.buf[4 * slot + 2] = t_met; d_tl.buf[4 * slot + 3] = gtime(); }
+    if (slot < d_tl.cap) { d_tl.buf[4 * slot] = 13; d_tl.buf[4 * slot + 1] = t_own; d_tl.buf[4 * slot + 2] = t_own; d_tl.buf[4 * slot + 3] = gtime(); }
   }
   if ((threadIdx.x & 31) < kNormCluster) {
     const uint32_t local = smem_u32(&red[q][threadIdx.x >> 5]);
@@ -202,16 +199,11 @@ int launch_rmsnorm_tp(float* h, const float* parts, int n_parts, int64_t part_st
   const int bf = bf16 ? 1 : 0;
   B200_REQUIRE(H % (4 * kNormCluster) == 0 && H <= kNormCluster * kNormThreads * 4 * kNormMaxPerThread,
                "rmsnorm_tp: H % 16 == 0 && H <= 8192");
-  // every cluster of the grid spins in its rendezvous: the whole grid has to be resident at once
+  // every cluster of the grid spins until its peers' words arrive: the whole grid has to be resident at once
   B200_REQUIRE(n_rows >= 1 && n_rows <= kTpNormMaxRows, "rmsnorm_tp: 1 <= rows <= 256");
-  B200_REQUIRE(n_parts >= 1 && (tp.n_ranks == 2 || tp.n_ranks == 4 || tp.n_ranks == 8), "rmsnorm_tp: 2, 4 or 8 ranks, >= 1 partial");
-  const dim3 grid(n_rows * kNormCluster), block(kNormThreads);
-  if (tp.n_ranks == 2)
-    launch_k(rmsnorm_tp_kernel<2>, grid, block, 0, s, h, parts, n_parts, part_stride, tp, epoch, gamma, eps, rows, n_rows, H, xn, bf);
-  else if (tp.n_ranks == 4)
-    launch_k(rmsnorm_tp_kernel<4>, grid, block, 0, s, h, parts, n_parts, part_stride, tp, epoch, gamma, eps, rows, n_rows, H, xn, bf);
-  else
-    launch_k(rmsnorm_tp_kernel<8>, grid, block, 0, s, h, parts, n_parts, part_stride, tp, epoch, gamma, eps, rows, n_rows, H, xn, bf);
+  B200_REQUIRE(n_parts >= 1 && tp.n_ranks >= 2 && tp.n_ranks <= kMaxTp && n_rows <= tp.rows_cap, "rmsnorm_tp: 2..8 ranks, >= 1 partial, rows within the receive buffers");
+  launch_k(rmsnorm_tp_kernel, dim3(n_rows * kNormCluster), dim3(kNormThreads), 0, s, h, parts, n_parts, part_stride, tp, epoch, gamma, eps,
+           rows, n_rows, H, xn, bf);
   g_launch_count += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
