@@ -250,7 +250,7 @@ def dense_kernel_roofline(a, dims):
     import torch
     from vgate_b200 import _lib
     lib = _lib.load()
-    K, I = dims.hidden, dims.intermediate
+    K, I = dims.hidden, dims.intermediate // max(1, getattr(a, "tp", 1))   # a tensor-parallel rank holds I / tp of the columns
     N, T = 2 * I, min(8192, a.batch * a.prompt_len)
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     peak, src = (float(peaks["bf16_tflops"]), "measured burst (MEASURED_PEAKS.json bf16_tflops)") if peaks else (1590.0, "fallback (B200_PROFILING.md)")
