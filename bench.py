@@ -351,10 +351,10 @@ def dominant_kernel_roofline(a, dims, hbm_peak, peak_src):
             + f" [{T}x{K}]x[{N}x{K}]", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
             # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at T=64 from one `ncu --set full` capture
             # (profiles/r02_kernels_ncu_full.txt, grid 140): 22.18 MB read + 0 written (the output stays in L2).  Of the
-            # read, 8.5 MB are the down projection's weights, which this kernel's TMA warp pulls into L2 for its
+            # read, 7.3 MB are the down projection's weights, which this kernel's TMA warp pulls into L2 for its
             # successor (profiles/r01_gateup_ncu_full.txt, captured before that prefetch existed: 14.86 MB)
             "traffic": (22180000 if use_umma and T == 64 else None),
-            "traffic_note": "includes 8.5 MB of L2 prefetch for the next kernel (down projection weights); own operands 14.9 MB",
+            "traffic_note": "includes 7.3 MB of L2 prefetch for the next kernel (down projection weights); own operands 14.9 MB",
             "traffic_source": "profiles/r02_kernels_ncu_full.txt", "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
             "avg_launch_us": t * 1e6,
             "l2": f"{n_copies} weight copies ({n_copies * N * K // 2 >> 20} MiB) walked round-robin: weights always come from HBM",
@@ -375,7 +375,7 @@ def gateway_levels(a, world):
     devs = vis.split(",") if vis else [str(i) for i in range(world)]
     # at N >= 2 also with as many gateway server processes as workers (tools/vgate_launch.py): one process is one
     # event loop, which is what binds behind the unmodified single-process gateway
-    out = asyncio.run(bg.run_b200(ref, os.path.join(ROOT, "gpurun_out", "gateway_logs"), world, a.batch, a.new_tokens, 2,
+    out = asyncio.run(bg.run_b200(ref, os.path.join(ROOT, "gpurun_out", "gateway_logs"), world, a.batch, a.new_tokens, 4,
                                   a.preset, ["worker_http", "gateway"], devices=devs[:world],
                                   extra_gateway_procs=world if world > 1 else 0))
     return out

@@ -242,10 +242,29 @@ async def worker_http_level(endpoints, per_worker, max_tokens, rounds, multi_pro
 
 async def gateway_level(ref_dir, base_url, concurrency, total_requests, max_tokens, prompts):
     sys.path.insert(0, ref_dir)
-    from benchmarks.bench_load import run_load_test       # the reference's load generator, as is
+    import benchmarks.bench_load as bl                    # the reference's load generator, as is ...
     import aiohttp
-    res = await run_load_test(base_url=base_url, concurrency=concurrency, total_requests=total_requests, prompts=prompts,
-                              max_tokens=max_tokens)
+
+    class _Aiohttp:
+        """... except for its connection pool: run_load_test opens aiohttp.ClientSession() with aiohttp's default of 100
+        connections, so a concurrency above 100 queues inside the CLIENT (measured: N = 2 and N = 4 workers both
+        stopped at ~100 requests in flight, 190-225 req/s, whatever the gateway did).  Same generator, pool sized
+        to the requested concurrency."""
+        def __getattr__(self, name):
+            return getattr(aiohttp, name)
+
+        @staticmethod
+        def ClientSession(*a, **kw):
+            kw.setdefault("connector", aiohttp.TCPConnector(limit=0))
+            return aiohttp.ClientSession(*a, **kw)
+
+    saved = bl.aiohttp
+    bl.aiohttp = _Aiohttp() if concurrency > 100 else saved
+    try:
+        res = await bl.run_load_test(base_url=base_url, concurrency=concurrency, total_requests=total_requests, prompts=prompts,
+                                     max_tokens=max_tokens)
+    finally:
+        bl.aiohttp = saved
     async with aiohttp.ClientSession() as session:
         async with session.get(f"{base_url}/stats") as r:
             stats = await r.json()
@@ -320,6 +339,7 @@ async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, 
                 # the wire carries temperature 0.7 / top_p 0.9 by default (main.py request defaults): bench_load cannot
                 # ask for greedy, so the gateway level samples; token counts are what is measured
                 g["note"] = "bench_load.py sends the API's default sampling (temperature 0.7, top_p 0.9)"
+                g["client_connections"] = "sized to the concurrency" if conc > 100 else "aiohttp default pool (100)"
                 return g
             out["gateway"] = await measure("gw")
             if extra_gateway_procs and extra_gateway_procs > 1:
