@@ -579,12 +579,14 @@ def run_b200(a):
                 if "gateway_multi_process" in levels:
                     line["gateway_multi_process"] = levels["gateway_multi_process"]
                 lv = {"engine_c_abi": value, "backend_threads": e2e["value"] if e2e else None,
-                      "worker_http": levels["worker_http_multi"]["tok_per_s"], "gateway": levels["gateway"]["tok_per_s"]}
+                      "worker_http": levels["worker_http_multi"]["tok_per_s"], "gateway": levels["gateway"].get("tok_per_s")}
                 if "gateway_multi_process" in levels:
-                    lv[f"gateway_{levels['gateway_multi_process']['processes']}_processes"] = levels["gateway_multi_process"]["tok_per_s"]
+                    lv[f"gateway_{levels['gateway_multi_process']['processes']}_processes"] = levels["gateway_multi_process"].get("tok_per_s")
                 line["levels_tok_per_s"] = lv
-                line["binding_level"] = ("gateway (CPU control plane: one event loop, one thread per in-flight request)"
-                                         if lv["gateway"] < 0.9 * lv["worker_http"] else
+                gw_best = max([v for k, v in lv.items() if k.startswith("gateway") and v] or [0.0])
+                line["binding_level"] = ("gateway (CPU control plane: one event loop per process, one thread and one of 100 hop "
+                                         "connections per in-flight request)"
+                                         if gw_best < 0.9 * lv["worker_http"] else
                                          "worker HTTP" if lv["worker_http"] < 0.9 * lv["engine_c_abi"] else "engine")
         line.update(checks)
         # informational: the reference's own GPU path (vLLM) measured once on this pool, same checkpoint and

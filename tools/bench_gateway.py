@@ -240,26 +240,28 @@ async def worker_http_level(endpoints, per_worker, max_tokens, rounds, multi_pro
             "bodies": "one multi-prompt body per worker" if multi_prompt else "one prompt per body"}
 
 
-async def gateway_level(ref_dir, base_url, concurrency, total_requests, max_tokens, prompts):
+async def gateway_level(ref_dir, base_url, concurrency, total_requests, max_tokens, prompts, client_pool=100):
     sys.path.insert(0, ref_dir)
     import benchmarks.bench_load as bl                    # the reference's load generator, as is ...
     import aiohttp
 
     class _Aiohttp:
-        """... except for its connection pool: run_load_test opens aiohttp.ClientSession() with aiohttp's default of 100
-        connections, so a concurrency above 100 queues inside the CLIENT (measured: N = 2 and N = 4 workers both
-        stopped at ~100 requests in flight, 190-225 req/s, whatever the gateway did).  Same generator, pool sized
-        to the requested concurrency."""
+        """... except, on request, for its connection pool: run_load_test opens aiohttp.ClientSession() with aiohttp's
+        default of 100 connections, so a concurrency above 100 queues inside the CLIENT (measured: N = 2 and N = 4
+        workers both stopped at ~100 requests in flight, 190-225 req/s, whatever the gateway did).  client_pool = 0:
+        same generator, pool sized to the requested concurrency.  The default stays 100 -- which is also the
+        connection limit of the reference gateway's worker hop (httpx defaults, remote_backend.py:87); a single gateway
+        process driven beyond it lost requests."""
         def __getattr__(self, name):
             return getattr(aiohttp, name)
 
         @staticmethod
         def ClientSession(*a, **kw):
-            kw.setdefault("connector", aiohttp.TCPConnector(limit=0))
+            kw.setdefault("connector", aiohttp.TCPConnector(limit=client_pool))
             return aiohttp.ClientSession(*a, **kw)
 
     saved = bl.aiohttp
-    bl.aiohttp = _Aiohttp() if concurrency > 100 else saved
+    bl.aiohttp = _Aiohttp() if client_pool != 100 else saved
     try:
         res = await bl.run_load_test(base_url=base_url, concurrency=concurrency, total_requests=total_requests, prompts=prompts,
                                      max_tokens=max_tokens)
@@ -309,6 +311,9 @@ async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, 
     devices = devices or [str(i) for i in range(n_gpus)]
 
     def wenv(i):
+        if os.environ.get("B200_GATEWAY_DRYRUN_WORKERS"):      # harness check on a box without GPUs: the reference's synthetic backend
+            return {"VGATE_DRY_RUN": "true", "VGATE_DRYRUN_SIMULATED_LATENCY_MS": os.environ["B200_GATEWAY_DRYRUN_WORKERS"],
+                    "B200_EXECUTOR_THREADS": str(batch + 16)}
         return {"CUDA_VISIBLE_DEVICES": devices[i], "VGATE_MODEL__ENGINE_TYPE": "b200", "VGATE_DRY_RUN": "false",
                 "VGATE_B200_SYNTHETIC": preset, "VGATE_B200_MAX_SEQS": str(max(batch, 64)),
                 "VGATE_MODEL__MAX_MODEL_LEN": str(128 + max_tokens + 16)}
@@ -330,28 +335,38 @@ async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, 
         if "gateway" in levels:
             conc = n_gpus * batch
 
-            async def measure(tag):
+            async def measure(tag, client_pool=100):
+                # bounded: a gateway that loses requests would otherwise hold the bench for the generator's 300 s timeout
                 warm = unique_prompts(conc, tag + "-warm")
-                await gateway_level(ref_dir, topo.base_url, conc, conc, max_tokens, warm)
+                await asyncio.wait_for(gateway_level(ref_dir, topo.base_url, conc, conc, max_tokens, warm, client_pool), 60)
                 prompts = unique_prompts(conc * rounds, tag)
-                res, stats = await gateway_level(ref_dir, topo.base_url, conc, conc * rounds, max_tokens, prompts)
+                res, stats = await asyncio.wait_for(gateway_level(ref_dir, topo.base_url, conc, conc * rounds, max_tokens, prompts, client_pool), 90)
                 g = summarise_gateway(res, stats)
                 # the wire carries temperature 0.7 / top_p 0.9 by default (main.py request defaults): bench_load cannot
                 # ask for greedy, so the gateway level samples; token counts are what is measured
                 g["note"] = "bench_load.py sends the API's default sampling (temperature 0.7, top_p 0.9)"
-                g["client_connections"] = "sized to the concurrency" if conc > 100 else "aiohttp default pool (100)"
+                g["client_connections"] = ("sized to the concurrency" if client_pool == 0 else
+                                           f"bench_load.py default pool ({client_pool}): at most {min(conc, client_pool)} requests in flight")
                 return g
-            out["gateway"] = await measure("gw")
+
+            async def guarded(tag, client_pool=100):
+                try:
+                    return await measure(tag, client_pool)
+                except asyncio.TimeoutError:
+                    return {"error": "timed out: the gateway stopped answering part of the requests", "concurrency": conc,
+                            "client_connections": client_pool or "sized to the concurrency"}
+            out["gateway"] = await guarded("gw")
             if extra_gateway_procs and extra_gateway_procs > 1:
                 # the same workers behind the same gateway app served by K processes on the one port
                 g2 = dict(genv)
                 g2["B200_GATEWAY_PROCESSES"] = str(extra_gateway_procs)
                 g2["VGATE_BATCH__MAX_BATCH_SIZE"] = str(max(8, (conc + extra_gateway_procs - 1) // extra_gateway_procs * 2))
                 await topo.restart_gateway(g2)
-                out["gateway_multi_process"] = await measure("gwmp")
+                out["gateway_multi_process"] = await guarded("gwmp", client_pool=0)
                 out["gateway_multi_process"]["processes"] = extra_gateway_procs
-                out["gateway_multi_process"]["note"] += ("; /stats counters (dedup, cache hits, TPOT) are per process and are read "
-                                                          "from whichever process answers")
+                if "note" in out["gateway_multi_process"]:
+                    out["gateway_multi_process"]["note"] += ("; /stats counters (dedup, cache hits, TPOT) are per process and are read "
+                                                              "from whichever process answers")
     return out
 
 

@@ -54,13 +54,20 @@ def create_app():
     return app
 
 
+KEEP_ALIVE_S = int(os.environ.get("B200_KEEP_ALIVE_S", "65"))
+
+
 async def _serve():
     n = int(os.environ.get("B200_EXECUTOR_THREADS", "0"))
     if n > 0:
         asyncio.get_running_loop().set_default_executor(ThreadPoolExecutor(n, thread_name_prefix="vgate-call"))
     main = _load_main()
     import uvicorn
-    cfg = uvicorn.Config(main.app, host=main.config.server.host, port=main.config.server.port, log_level="warning")
+    # keep-alive longer than the gateway hop's: RemoteBackend's httpx pool expires idle connections after 5 s, uvicorn's
+    # default closes them after 5 s too, and a request sent into that race dies with "failed mid-request: ReadError"
+    # (seen at 1 of 320 requests with dry-run workers).  With 65 s the client always gives a connection up first.
+    cfg = uvicorn.Config(main.app, host=main.config.server.host, port=main.config.server.port, log_level="warning",
+                         timeout_keep_alive=KEEP_ALIVE_S)
     await uvicorn.Server(cfg).serve()
 
 
@@ -71,6 +78,6 @@ if __name__ == "__main__":
         from vgate.config import get_config
         c = get_config()
         uvicorn.run("vgate_launch:create_app", factory=True, host=c.server.host, port=c.server.port, workers=procs,
-                    log_level="warning")
+                    log_level="warning", timeout_keep_alive=KEEP_ALIVE_S)
     else:
         asyncio.run(_serve())
