@@ -29,6 +29,7 @@ def vgate_env(monkeypatch):
 
 def _backend(handler, endpoints=("http://w0", "http://w1"), **env):
     import httpx
+    env.setdefault("VGATE_B200_COALESCE_MODE", "body")       # the reference's wire form unless a test asks for "nd"
     from vgate.config import WorkerConfig
     from vgate_b200.remote import CoalescingRemoteBackend
     for k, v in env.items():
@@ -81,6 +82,78 @@ def test_concurrent_single_prompt_calls_share_bodies(vgate_env):
         assert [r["text"] for r in res] == ["echo a", "echo b", "echo c"]
     finally:
         be.shutdown()
+
+
+def test_nd_mode_releases_every_caller_with_its_own_line(vgate_env):
+    """/internal/generate_nd: results arrive in completion order and each caller returns with its own line -- a slow
+    prompt does not hold the fast ones of its body; mixed sampling parameters share a body; an unmodified worker (404)
+    is served through the reference's route."""
+    import httpx
+    bodies, lock = [], threading.Lock()
+    release_slow = threading.Event()
+
+    class Lines(httpx.SyncByteStream):
+        def __init__(self, items):
+            self.items = items
+
+        def __iter__(self):
+            slow = [i for i, it in enumerate(self.items) if it["prompt"].startswith("slow")]
+            for i, it in enumerate(self.items):
+                if i not in slow:
+                    yield (json.dumps({"i": i, "result": {"text": "echo " + it["prompt"], "token_ids": [], "num_tokens": it["sampling_params"]["max_tokens"],
+                                                              "metrics": {}}}) + "\n").encode()
+            release_slow.wait(5)
+            for i in slow:
+                yield (json.dumps({"i": i, "error": "RuntimeError"} if self.items[i]["prompt"] == "slow bad" else
+                                  {"i": i, "result": {"text": "echo slow", "token_ids": [], "num_tokens": 1, "metrics": {}}}) + "\n").encode()
+
+    def handler(request):
+        body = json.loads(request.content)
+        with lock:
+            bodies.append((request.url.path, body))
+        if request.url.host == "w1":                       # an unmodified worker
+            if request.url.path == "/internal/generate_nd":
+                return httpx.Response(404, json={"detail": "Not Found"})
+            return httpx.Response(200, json={"results": [{"text": "ref " + p, "token_ids": [], "num_tokens": 0, "metrics": {}} for p in body["prompts"]]})
+        return httpx.Response(200, stream=Lines(body["items"]))
+
+    from vgate.backends.remote_backend import RemoteInferenceError
+    be = _backend(handler, endpoints=("http://w0",), VGATE_B200_COALESCE_MODE="nd", VGATE_B200_COALESCE_SENDERS=1)
+    try:
+        done, errs = {}, {}
+        def call(p, mt):
+            try:
+                done[p] = be.generate([p], be.create_sampling_params(0.0, 1.0, mt))[0]
+            except Exception as exc:  # noqa: BLE001
+                errs[p] = exc
+        first = threading.Thread(target=call, args=("warm", 4))
+        first.start(); first.join()
+        ts = [threading.Thread(target=call, args=(p, mt)) for p, mt in (("slow one", 8), ("slow bad", 8), ("fast a", 8), ("fast b", 16), ("fast c", 32))]
+        for t in ts:
+            t.start()
+            time.sleep(0.01)
+        deadline = time.time() + 5
+        while time.time() < deadline and not all(k in done for k in ("fast a", "fast b", "fast c")):
+            time.sleep(0.01)
+        assert all(k in done for k in ("fast a", "fast b", "fast c")) and "slow one" not in done    # released before the slow ones finish
+        assert done["fast b"]["num_tokens"] == 16 and done["fast c"]["num_tokens"] == 32              # per-item sampling parameters
+        release_slow.set()
+        for t in ts:
+            t.join()
+        assert done["slow one"]["text"] == "echo slow"
+        assert isinstance(errs["slow bad"], RemoteInferenceError)                                   # one item's failure is its caller's only
+        assert all(path == "/internal/generate_nd" for path, _ in bodies)
+        assert be.prompts_sent == 6 and be.bodies_sent < 6
+    finally:
+        be.shutdown()
+    bodies.clear()
+    be2 = _backend(handler, endpoints=("http://w1",), VGATE_B200_COALESCE_MODE="nd")
+    try:
+        assert be2.generate(["x"], be2.create_sampling_params(0.0, 1.0, 4))[0]["text"] == "ref x"     # fell back to /internal/generate
+        assert be2.generate(["y"], be2.create_sampling_params(0.0, 1.0, 4))[0]["text"] == "ref y"
+        assert [p for p, _ in bodies] == ["/internal/generate_nd", "/internal/generate", "/internal/generate"]   # asked once
+    finally:
+        be2.shutdown()
 
 
 def test_prefix_affinity_routing_keeps_a_prefix_on_one_worker(vgate_env):

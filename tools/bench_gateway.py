@@ -306,7 +306,7 @@ async def run_config1(ref_dir, log_dir, latency_ms=None):
 
 
 async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, levels, devices=None, remote=None, gateway_procs=1,
-                   extra_gateway_procs=0):
+                   extra_gateway_procs=0, client_pool=100):
     threads = n_gpus * batch + 64
     devices = devices or [str(i) for i in range(n_gpus)]
 
@@ -355,7 +355,7 @@ async def run_b200(ref_dir, log_dir, n_gpus, batch, max_tokens, rounds, preset, 
                 except asyncio.TimeoutError:
                     return {"error": "timed out: the gateway stopped answering part of the requests", "concurrency": conc,
                             "client_connections": client_pool or "sized to the concurrency"}
-            out["gateway"] = await guarded("gw")
+            out["gateway"] = await guarded("gw", client_pool)
             if extra_gateway_procs and extra_gateway_procs > 1:
                 # the same workers behind the same gateway app served by K processes on the one port
                 g2 = dict(genv)
@@ -384,6 +384,8 @@ def main():
     ap.add_argument("--remote", default=None, choices=[None, "coalesce"], help="gateway-side worker hop (default: the reference's RemoteBackend)")
     ap.add_argument("--gateway-procs", type=int, default=1, help="server processes of the gateway app on its one port (uvicorn workers)")
     ap.add_argument("--extra-gateway-procs", type=int, default=0, help="after the main gateway run, restart the gateway with K processes and measure again")
+    ap.add_argument("--client-pool", type=int, default=100, help="connections of the load generator for the main gateway run "
+                    "(100: bench_load.py's own default; 0: sized to the concurrency)")
     ap.add_argument("--stage", action="store_true")
     a = ap.parse_args()
     if a.stage:
@@ -397,7 +399,7 @@ def main():
         out = asyncio.run(run_config1(ref, a.log_dir, a.latency_ms))
     else:
         out = asyncio.run(run_b200(ref, a.log_dir, a.gpus, a.batch, a.max_tokens, a.rounds, a.preset, a.levels.split(","), remote=a.remote, gateway_procs=a.gateway_procs,
-                                   extra_gateway_procs=a.extra_gateway_procs))
+                                   extra_gateway_procs=a.extra_gateway_procs, client_pool=a.client_pool))
     out["reference_dir"] = ref
     print(json.dumps(out))
 

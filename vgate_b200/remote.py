@@ -8,7 +8,13 @@ gaps SURVEY.md section 8(f) ranks first:
    multi-prompt ``/internal/generate`` body per worker: callers enqueue and block on a future, a few sender
    threads per gateway drain whatever is queued when they become free (no added delay), pick a worker
    round-robin and demultiplex the response.  One body, one JSON document and one connection instead of 64.
-   A body completes when its slowest prompt does, so only prompts with equal ``max_tokens`` share a body.
+   Two wire forms (``VGATE_B200_COALESCE_MODE``):
+   ``nd`` (default) posts to ``/internal/generate_nd`` (``vgate_b200.worker_stream``): the worker answers with one
+   newline-delimited result per prompt in COMPLETION order and every caller is released the moment its own line
+   arrives -- prompts of any sampling parameters share a body, nobody waits for the slowest.
+   ``body`` uses the reference's own ``/internal/generate``: a body completes when its slowest prompt does (so only
+   prompts with equal parameters share one, and finished sequences wait for their body: measured slower than the
+   reference hop on two B200s).  ``nd`` falls back to ``body`` for a worker that answers 404 (an unmodified worker).
 
 2. **Streaming through the hop** (``remote_backend.py:209-224`` raises; the gateway answers 501,
    ``main.py:429-436``).  ``stream_generate`` opens ``POST /internal/stream`` on a worker (a route
@@ -58,6 +64,8 @@ class CoalescingRemoteBackend:
         self.max_body = int(os.environ.get("VGATE_B200_COALESCE_MAX", "64"))       # prompts per body
         self.route_prefix = os.environ.get("VGATE_B200_ROUTE") == "prefix"
         self.route_chars = int(os.environ.get("VGATE_B200_ROUTE_CHARS", "256"))
+        self.mode = os.environ.get("VGATE_B200_COALESCE_MODE", "nd")
+        self._no_nd: set = set()                # workers that answered 404 to /internal/generate_nd
         n_senders = int(os.environ.get("VGATE_B200_COALESCE_SENDERS", "16"))
         self._queues: Dict[str, Any] = {}       # sampling-parameter class -> (params, [(prompt, future, t_enqueued)])
         self._cv = threading.Condition()
@@ -77,7 +85,7 @@ class CoalescingRemoteBackend:
 
     def generate(self, prompts: List[str], sampling_params: Any) -> List[Dict[str, Any]]:
         """Blocking; called from executor threads (vgate/batcher.py:374).  Results in prompt order."""
-        key = json.dumps(sampling_params, sort_keys=True)
+        key = json.dumps(sampling_params, sort_keys=True) if self.mode != "nd" else "*"   # nd: any mix shares a body
         futs = []
         for p in prompts:
             f: Future = Future()
@@ -107,7 +115,7 @@ class CoalescingRemoteBackend:
     # -- coalescing senders ----------------------------------------------------------------------------
     def _enqueue(self, key, sp, prompt, fut):
         with self._cv:
-            self._queues.setdefault(key, (sp, []))[1].append((prompt, fut, time.monotonic()))
+            self._queues.setdefault(key, (sp, []))[1].append((prompt, fut, time.monotonic(), sp))
             self._cv.notify()
 
     def _take_batch(self):
@@ -132,13 +140,84 @@ class CoalescingRemoteBackend:
             if not batch:
                 continue
             try:
-                results = self._post_with_retry([it[0] for it in batch], sp)
-                for it, res in zip(batch, results):
-                    it[1].set_result(res)
+                if self.mode == "nd":
+                    self._post_nd(batch)
+                else:
+                    results = self._post_with_retry([it[0] for it in batch], sp)
+                    for it, res in zip(batch, results):
+                        it[1].set_result(res)
             except BaseException as exc:        # noqa: BLE001 -- every waiting caller must be released
                 for it in batch:
                     if not it[1].done():
                         it[1].set_exception(exc)
+
+    def _post_nd(self, batch):
+        """One /internal/generate_nd exchange for `batch` = [(prompt, future, t, sampling_params)]: futures are resolved
+        line by line.  Same policy as below: another worker only after a connection failure (nothing was sent)."""
+        prompts = [it[0] for it in batch]
+        tried: set = set()
+        last_connect_error = None
+        for attempt in range(max(1, len(self.registry.endpoints()))):
+            try:
+                endpoint = self._pick(prompts, tried)
+            except NoHealthyWorkersError:
+                break
+            if endpoint in self._no_nd:          # an unmodified worker: the reference's wire form, per parameter class
+                by_sp: Dict[str, list] = {}
+                for it in batch:
+                    by_sp.setdefault(json.dumps(it[3], sort_keys=True), []).append(it)
+                for group in by_sp.values():
+                    for it, res in zip(group, self._post_with_retry([g[0] for g in group], group[0][3])):
+                        it[1].set_result(res)
+                return
+            if attempt > 0:
+                WORKER_RETRIES.labels(worker=endpoint).inc()
+            started = time.perf_counter()
+            try:
+                with self._client.stream("POST", f"{endpoint}/internal/generate_nd",
+                                         json={"items": [{"prompt": it[0], "sampling_params": it[3]} for it in batch]}) as resp:
+                    if resp.status_code in (404, 405, 501):      # no such route / a backend that is called under a lock
+                        self._no_nd.add(endpoint)
+                        return self._post_nd(batch)
+                    if resp.status_code != 200:
+                        body = resp.read()[:200]
+                        self.registry.record_failure(endpoint)
+                        WORKER_REQUESTS.labels(worker=endpoint, outcome="http_error").inc()
+                        raise RemoteInferenceError(f"worker at {endpoint} returned {resp.status_code}: {body!r}")
+                    seen = 0
+                    for line in resp.iter_lines():
+                        if not line:
+                            continue
+                        msg = json.loads(line)
+                        fut = batch[int(msg["i"])][1]
+                        if "error" in msg:
+                            fut.set_exception(RemoteInferenceError(f"worker at {endpoint} returned 500: Inference failed: {msg['error']}"))
+                        else:
+                            fut.set_result(msg["result"])
+                        seen += 1
+                    if seen != len(batch):
+                        self.registry.record_failure(endpoint)
+                        WORKER_REQUESTS.labels(worker=endpoint, outcome="bad_response").inc()
+                        raise RemoteInferenceError(f"worker at {endpoint} returned {seen} results for {len(batch)} prompts")
+            except httpx.ConnectError as exc:
+                self.registry.record_failure(endpoint)
+                WORKER_REQUESTS.labels(worker=endpoint, outcome="connect_error").inc()
+                tried.add(endpoint)
+                last_connect_error = exc
+                continue
+            except httpx.RequestError as exc:
+                self.registry.record_failure(endpoint)
+                WORKER_REQUESTS.labels(worker=endpoint, outcome="request_error").inc()
+                raise RemoteInferenceError(f"worker at {endpoint} failed mid-request: {type(exc).__name__}") from exc
+            finally:
+                WORKER_LATENCY.labels(worker=endpoint).observe(time.perf_counter() - started)
+            self.registry.record_success(endpoint)
+            WORKER_REQUESTS.labels(worker=endpoint, outcome="success").inc()
+            self.bodies_sent += 1
+            self.prompts_sent += len(batch)
+            return
+        detail = f"last error: {type(last_connect_error).__name__}" if last_connect_error else "none reachable"
+        raise NoHealthyWorkersError(f"no healthy worker served the request after {len(tried)} attempt(s); {detail}")
 
     def _post_with_retry(self, prompts, sampling_params):
         """remote_backend.py:114-207: retry on connection failures only; a timeout or an error status is final."""
