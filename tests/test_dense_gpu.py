@@ -28,7 +28,8 @@ def _bits(a, dtype):
 
 @pytest.mark.parametrize("dtype", ["fp16", "bf16"])
 @pytest.mark.parametrize("T,K,N", [(1, 1024, 512), (33, 1024, 512), (128, 1024, 512), (300, 1024, 512),
-                                   (600, 512, 9728)])       # the last: 256 weight rows per CTA (76 tiles x 3 token tiles > 148)
+                                   (600, 512, 9728),        # 256 weight rows per CTA (76 tiles x 3 token tiles > 148)
+                                   (1100, 256, 19456)])     # ... and token-tile-fastest rasterisation (76 x 5 CTAs > two waves, weights > activations)
 def test_dense_gemm_epilogues_match_fp64(dtype, T, K, N):
     rng = np.random.default_rng(T)
     code = _lib.DTYPE_BF16 if dtype == "bf16" else _lib.DTYPE_F16

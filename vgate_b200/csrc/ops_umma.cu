@@ -57,8 +57,14 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
   if (tl_rec) tl_t0 = gtime();
   grid_dep_launch();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nt = blockIdx.x;                 // weight-row tile
-  const int tok0 = blockIdx.y * NT;          // token tile
+  int nt = blockIdx.x;                       // weight-row tile
+  int tt = blockIdx.y;                       // token tile
+  if (p.raster) {                            // token tiles fastest (see UmmaParams::raster)
+    const int lin = blockIdx.x + gridDim.x * blockIdx.y;
+    tt = lin % gridDim.y;
+    nt = lin / gridDim.y;
+  }
+  const int tok0 = tt * NT;
   const int split = blockIdx.z;
   const int KT = p.K / kUmmaBK;
   const int kt0 = split * p.kt_per_split;
@@ -310,6 +316,12 @@ static int launch_nt_cfg(const CUtensorMap& mx, const CUtensorMap& mw, const Umm
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   dim3 grid(p.N / (kUmmaM * MT), (p.T + NT - 1) / NT, n_splits);
   UmmaParams pp = p;
+  if constexpr (!kW4) {
+    // token tiles fastest when the activations fit comfortably in the 126 MB L2, the weights are the larger operand
+    // and the grid is several waves; split-K grids keep the default (their z index already separates the waves)
+    const int64_t x_bytes = (int64_t)p.T * p.K * 2, w_bytes = (int64_t)p.N * p.K * 2;
+    pp.raster = (n_splits == 1 && grid.y > 1 && (int64_t)grid.x * grid.y > 2 * 148 && x_bytes <= (64ll << 20) && w_bytes > x_bytes) ? 1 : 0;
+  }
   if (g_umma_trace_gridx && ((int)grid.x != g_umma_trace_gridx || (int)grid.z != g_umma_trace_gridz)) pp.trace = nullptr;
   launch_k(kern, grid, dim3(kUmmaThreads), (size_t)smem_bytes, s, mx, mw, pp);
   g_launch_count += 1;
