@@ -278,3 +278,20 @@ def test_reference_worker_http_route_serves_b200_backend(monkeypatch):
     finally:
         worker_api.set_engine(None)
         eng.backend.shutdown()
+
+
+def test_qwen_chat_template_rewrites_the_reference_prompt_format():
+    """main.py:269-271 flattens a chat into "Role: content" lines + "Assistant:"; VGATE_B200_CHAT_TEMPLATE=qwen turns
+    that back into Qwen2.5-Instruct's ChatML prompt (off by default: the reference hands the flat string to vLLM)."""
+    from vgate_b200.tokenizer import qwen_chat_prompt
+    flat = "System: Be brief.\nUser: first line\nsecond line: with a colon\nAssistant: earlier answer\nUser: again?\nAssistant:"
+    want = ("<|im_start|>system\nBe brief.<|im_end|>\n"
+            "<|im_start|>user\nfirst line\nsecond line: with a colon<|im_end|>\n"
+            "<|im_start|>assistant\nearlier answer<|im_end|>\n"
+            "<|im_start|>user\nagain?<|im_end|>\n"
+            "<|im_start|>assistant\n")
+    assert qwen_chat_prompt(flat) == want
+    one = qwen_chat_prompt("User: hello\nAssistant:")
+    assert one.startswith("<|im_start|>system\nYou are Qwen") and one.endswith("<|im_start|>user\nhello<|im_end|>\n<|im_start|>assistant\n")
+    assert qwen_chat_prompt("a raw completion prompt") == "a raw completion prompt"          # not the chat format: untouched
+    assert qwen_chat_prompt("no role here\nAssistant:") == "no role here\nAssistant:"

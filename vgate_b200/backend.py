@@ -17,7 +17,7 @@ import secrets
 from concurrent.futures import ThreadPoolExecutor
 from typing import Any, AsyncIterator, Dict, List
 
-from .tokenizer import load_tokenizer, IncrementalDetokenizer
+from .tokenizer import load_tokenizer, IncrementalDetokenizer, qwen_chat_prompt
 from .weights import PRESETS, synthetic_checkpoint, load_hf_checkpoint
 
 
@@ -41,6 +41,9 @@ class B200Backend:
     def __init__(self):
         self.engine = None
         self.tokenizer = None
+        # "" (default): the flat "User: ...\nAssistant:" prompt goes to the model as the reference sends it to vLLM;
+        # "qwen": rewritten into Qwen2.5-Instruct's ChatML template first (tokenizer.qwen_chat_prompt)
+        self._chat_template = os.environ.get("VGATE_B200_CHAT_TEMPLATE", "")
         self._loop = None
 
     # ------------------------------------------------------------------------------------
@@ -98,6 +101,8 @@ class B200Backend:
     def _submit(self, prompt: str, sampling_params: Any):
         if self.engine is None:
             raise RuntimeError("B200Backend.load_model() has not been called")
+        if self._chat_template == "qwen":
+            prompt = qwen_chat_prompt(prompt)
         ids = self.tokenizer.encode(prompt)
         max_tokens = int(_sp_get(sampling_params, "max_tokens", 256))
         seed = _sp_get(sampling_params, "seed", None)

@@ -65,6 +65,36 @@ class IncrementalDetokenizer:
         return delta
 
 
+_ROLES = ("System", "User", "Assistant", "Tool")
+
+
+def qwen_chat_prompt(flat: str) -> str:
+    """V-Gate flattens a chat into ``"Role: content\n...\nAssistant:"`` (main.py:269-271) and the reference passes
+    that string to vLLM as a raw prompt (vllm_backend.py:113), which is what this backend does by default.  With a real
+    Qwen2.5-Instruct checkpoint the model expects its chat template; ``VGATE_B200_CHAT_TEMPLATE=qwen`` rewrites the
+    flat prompt into it (the ChatML form of Qwen2.5's ``tokenizer_config.json``):
+    ``<|im_start|>role\ncontent<|im_end|>\n`` per message, then ``<|im_start|>assistant\n``.  A line starts a new
+    message only when it begins with a capitalised role name followed by ": ", so message bodies keep their newlines;
+    a prompt that does not end in the reference's ``"\nAssistant:"`` marker is returned unchanged."""
+    tail = "\nAssistant:"
+    if not flat.endswith(tail):
+        return flat
+    msgs = []
+    for line in flat[:-len(tail)].split("\n"):
+        head, sep, rest = line.partition(": ")
+        if sep and head in _ROLES:
+            msgs.append([head.lower(), rest])
+        elif msgs:
+            msgs[-1][1] += "\n" + line
+        else:
+            return flat                    # no role on the first line: not the reference's format
+    if not msgs:
+        return flat
+    if msgs[0][0] != "system":             # Qwen2.5's template inserts its default system message
+        msgs.insert(0, ["system", "You are Qwen, created by Alibaba Cloud. You are a helpful assistant."])
+    return "".join(f"<|im_start|>{r}\n{c}<|im_end|>\n" for r, c in msgs) + "<|im_start|>assistant\n"
+
+
 def load_tokenizer(model_id: str):
     if model_id and os.path.isdir(model_id) and os.path.exists(os.path.join(model_id, "tokenizer.json")):
         return HFTokenizer(model_id)
