@@ -79,5 +79,22 @@ if __name__ == "__main__":
         c = get_config()
         uvicorn.run("vgate_launch:create_app", factory=True, host=c.server.host, port=c.server.port, workers=procs,
                     log_level="warning", timeout_keep_alive=KEEP_ALIVE_S)
+    elif os.environ.get("B200_PROFILE"):          # where does a gateway / worker process spend its CPU (event-loop thread only)
+        import cProfile
+        import pstats
+        prof = cProfile.Profile()
+
+        def dump():
+            prof.disable()
+            with open(os.environ["B200_PROFILE"], "w") as f:
+                pstats.Stats(prof, stream=f).sort_stats("tottime").print_stats(45)
+            prof.enable()
+            asyncio.get_running_loop().call_later(5.0, dump)
+
+        async def profiled():
+            asyncio.get_running_loop().call_later(5.0, dump)      # rewritten every 5 s: the process is ended by a signal
+            await _serve()
+        prof.enable()
+        asyncio.run(profiled())
     else:
         asyncio.run(_serve())
