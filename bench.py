@@ -373,11 +373,11 @@ def gateway_levels(a, world):
         return {"unavailable": "no V-Gate checkout on this box (tools/bench_gateway.py --stage copies it to baseline/_ref)"}
     vis = os.environ.get("CUDA_VISIBLE_DEVICES")
     devs = vis.split(",") if vis else [str(i) for i in range(world)]
-    # at N >= 2 also with as many gateway server processes as workers (tools/vgate_launch.py): one process is one
-    # event loop, which is what binds behind the unmodified single-process gateway
+    # also with max(2, N) gateway server processes (tools/vgate_launch.py): one process is one event loop, which is
+    # what binds behind the unmodified single-process gateway -- already at one GPU (140 of the worker's 178 req/s)
     out = asyncio.run(bg.run_b200(ref, os.path.join(ROOT, "gpurun_out", "gateway_logs"), world, a.batch, a.new_tokens, 4,
                                   a.preset, ["worker_http", "gateway"], devices=devs[:world],
-                                  extra_gateway_procs=world if world > 1 else 0))
+                                  extra_gateway_procs=max(2, world)))
     return out
 
 
